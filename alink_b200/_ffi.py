@@ -1,0 +1,320 @@
+"""ctypes binding of libalink_b200.so (C ABI: include/alink_b200.h).
+
+This is the only bridge between the Python host code and the CUDA kernels. There is no CPU
+fallback: if the shared library is missing or no CUDA device is visible, every entry point
+raises — loudly — instead of computing on the host.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+SO_PATH = os.path.join(_HERE, "csrc", "libalink_b200.so")
+
+HOST, DEVICE = 0, 1
+F32, BF16 = 0, 1
+FEAT_ABSDIFF, FEAT_ABSDIFF_HADAMARD = 0, 1
+FP32_EXACT, BF16_TC = 0, 1
+ACT_ID = {"softmax": 0, "sigmoid": 1}
+MEASURE_ID = {"uncertainty": 0, "neg_margin": 1, "entropy": 2, "vote_entropy": 3,
+              "consensus_entropy": 4, "kl_max": 5}
+COMPUTE_ID = {"fp32": FP32_EXACT, "fp32_exact": FP32_EXACT, "bf16": BF16_TC, "bf16_tc": BF16_TC}
+MAX_SLOTS = 8
+
+# every symbol include/alink_b200.h declares (tests/test_abi.py checks the .so exports them all)
+SYMBOLS = (
+    "alink_abi_version", "alink_create", "alink_destroy", "alink_last_error", "alink_sync",
+    "alink_set_stream", "alink_launch_count", "alink_host_alloc", "alink_host_free", "alink_set_heads", "alink_set_table",
+    "alink_score_indexed", "alink_score_dense", "alink_utility", "alink_utility_from_proba",
+    "alink_select_topk", "alink_topk_values", "alink_topk_keys", "alink_query", "alink_disparity_select",
+)
+
+
+class AlinkError(RuntimeError):
+    pass
+
+
+class Timing(C.Structure):
+    _fields_ = [("ms_h2d", C.c_float), ("ms_score", C.c_float), ("ms_utility", C.c_float),
+                ("ms_select", C.c_float), ("ms_d2h", C.c_float), ("ms_total", C.c_float),
+                ("launches", C.c_int64)]
+
+    def as_dict(self):
+        return {k: getattr(self, k) for k, _ in self._fields_}
+
+
+_lib = None
+
+
+def load():
+    """Load the product library; raise if it has not been built (see __graft_entry__.build())."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(SO_PATH):
+        raise AlinkError(
+            f"{SO_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+            "(or `make -C alink_b200/csrc`). There is no CPU fallback.")
+    L = C.CDLL(SO_PATH)
+    vp, i32, i64, u64, dbl = C.c_void_p, C.c_int, C.c_int64, C.c_uint64, C.c_double
+    pp = C.POINTER(C.c_void_p)
+    L.alink_abi_version.restype = i32
+    L.alink_create.restype = i32
+    L.alink_create.argtypes = [C.POINTER(vp), i32, C.c_uint]
+    L.alink_destroy.restype = i32
+    L.alink_destroy.argtypes = [vp]
+    L.alink_last_error.restype = C.c_char_p
+    L.alink_last_error.argtypes = [vp]
+    L.alink_sync.restype = i32
+    L.alink_sync.argtypes = [vp]
+    L.alink_set_stream.restype = i32
+    L.alink_set_stream.argtypes = [vp, vp]
+    L.alink_launch_count.restype = i64
+    L.alink_launch_count.argtypes = [vp]
+    L.alink_host_alloc.restype = i32
+    L.alink_host_alloc.argtypes = [C.POINTER(vp), u64]
+    L.alink_host_free.restype = i32
+    L.alink_host_free.argtypes = [vp]
+    L.alink_set_heads.restype = i32
+    L.alink_set_heads.argtypes = [vp, i32, i32, i32, i32, i32, i32, i32, i32, pp, pp, pp, pp, pp, pp, i32]
+    L.alink_set_table.restype = i32
+    L.alink_set_table.argtypes = [vp, i32, vp, i64, i32, i32, i32]
+    L.alink_score_indexed.restype = i32
+    L.alink_score_indexed.argtypes = [vp, i32, i32, i32, vp, vp, i64, i32, vp, vp, i32]
+    L.alink_score_dense.restype = i32
+    L.alink_score_dense.argtypes = [vp, i32, vp, vp, i64, i32, i32, vp, vp, i32]
+    L.alink_utility.restype = i32
+    L.alink_utility.argtypes = [vp, i32, vp, i32]
+    L.alink_utility_from_proba.restype = i32
+    L.alink_utility_from_proba.argtypes = [vp, vp, i64, i32, i32, i32, i32, vp, vp, i32]
+    L.alink_select_topk.restype = i32
+    L.alink_select_topk.argtypes = [vp, i64, i64, vp, vp, vp, i32]
+    L.alink_topk_values.restype = i32
+    L.alink_topk_values.argtypes = [vp, vp, i64, i64, i64, i32, vp, vp, vp, i32]
+    L.alink_topk_keys.restype = i32
+    L.alink_topk_keys.argtypes = [vp, vp, i64, i64, i32, vp, i32]
+    L.alink_query.restype = i32
+    L.alink_query.argtypes = [vp, i32, i32, i32, vp, vp, i64, i32, i32, i64, i64, vp, vp, vp, i32,
+                              C.POINTER(Timing)]
+    L.alink_disparity_select.restype = i32
+    L.alink_disparity_select.argtypes = [vp, vp, vp, i64, i32, dbl, dbl, i32, vp, i32, vp, i32,
+                                         C.POINTER(i64), C.POINTER(i64)]
+    _lib = L
+    return L
+
+
+def _is_torch(a):
+    return type(a).__module__.startswith("torch")
+
+
+def _ptr_space(a):
+    """(void* address, space) of a numpy array (host) or torch tensor (host or cuda). None -> (None, HOST)."""
+    if a is None:
+        return None, HOST
+    if _is_torch(a):
+        assert a.is_contiguous(), "tensor must be contiguous"
+        return C.c_void_p(a.data_ptr()), (DEVICE if a.is_cuda else HOST)
+    assert a.flags["C_CONTIGUOUS"], "array must be C-contiguous"
+    return a.ctypes.data_as(C.c_void_p), HOST
+
+
+def _space_of(*arrs):
+    spaces = {_ptr_space(a)[1] for a in arrs if a is not None}
+    if len(spaces) > 1:
+        raise AlinkError("all buffers of one call must live in the same memory space")
+    return spaces.pop() if spaces else HOST
+
+
+def _pp(arrs):
+    holder = (C.c_void_p * len(arrs))(*[a.ctypes.data for a in arrs])
+    return C.cast(holder, C.POINTER(C.c_void_p)), holder
+
+
+def _f32(a):
+    return np.ascontiguousarray(a, dtype=np.float32)
+
+
+class Context:
+    """One GPU, one stream, all scratch. Mirrors `alink_ctx`."""
+
+    def __init__(self, device: int = 0):
+        self._L = load()
+        h = C.c_void_p()
+        rc = self._L.alink_create(C.byref(h), int(device), 0)
+        if rc != 0:
+            raise AlinkError(f"alink_create(device={device}) failed with {rc}: no usable CUDA device "
+                             "(this library has no CPU fallback)")
+        self._h = h
+        self.device = device
+        self._keep = {}
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._L.alink_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check(self, rc):
+        if rc != 0:
+            raise AlinkError(f"[{rc}] {self._L.alink_last_error(self._h).decode()}")
+
+    # ---- state
+    def set_heads(self, group, heads, feat_mode=FEAT_ABSDIFF, compute=FP32_EXACT):
+        """heads: object with K, D_in, H1, H2, C, act, W1..b3 lists (alink_b200.synth.Heads)."""
+        keep, ptrs = [], []
+        for lst in (heads.W1, heads.b1, heads.W2, heads.b2, heads.W3, heads.b3):
+            arrs = [_f32(a) for a in lst]
+            p, holder = _pp(arrs)
+            keep.append((arrs, holder))
+            ptrs.append(p)
+        self._check(self._L.alink_set_heads(self._h, group, heads.K, heads.D_in, heads.H1, heads.H2, heads.C,
+                                            ACT_ID[heads.act], feat_mode, *ptrs, compute))
+
+    def set_table(self, slot, emb):
+        p, space = _ptr_space(emb)
+        if _is_torch(emb):
+            import torch
+            dtype = {torch.float32: F32, torch.bfloat16: BF16}[emb.dtype]
+        else:
+            if emb.dtype != np.float32:
+                raise AlinkError("host tables must be float32")
+            dtype = F32
+        M, D = emb.shape
+        self._check(self._L.alink_set_table(self._h, slot, p, M, D, dtype, space))
+        if space == DEVICE:
+            self._keep[("table", slot)] = emb  # borrowed: keep alive
+
+    # ---- scoring
+    def _outs(self, N, K, Cc, want_per, want_cons, out_device):
+        if out_device:
+            import torch
+            dev = torch.device("cuda", self.device)
+            per = torch.empty((N, K, Cc), dtype=torch.float32, device=dev) if want_per else None
+            cons = torch.empty((N, Cc), dtype=torch.float32, device=dev) if want_cons else None
+        else:
+            per = np.empty((N, K, Cc), np.float32) if want_per else None
+            cons = np.empty((N, Cc), np.float32) if want_cons else None
+        return per, cons
+
+    def score_indexed(self, group, slot_a, slot_b, ia, ib, N, K, Cc, want_per=True, want_cons=True,
+                      out_device=False):
+        per, cons = self._outs(N, K, Cc, want_per, want_cons, out_device)
+        pia, sp = _ptr_space(ia)
+        pib, _ = _ptr_space(ib)
+        _space_of(ia, ib)
+        self._check(self._L.alink_score_indexed(self._h, group, slot_a, slot_b, pia, pib, N, sp,
+                                                _ptr_space(per)[0], _ptr_space(cons)[0],
+                                                DEVICE if out_device else HOST))
+        return per, cons
+
+    def score_dense(self, group, XL, XR, K, Cc, want_per=True, want_cons=True, out_device=False):
+        N, D = XL.shape
+        per, cons = self._outs(N, K, Cc, want_per, want_cons, out_device)
+        pl, sp = _ptr_space(XL)
+        pr, _ = _ptr_space(XR)
+        _space_of(XL, XR)
+        self._check(self._L.alink_score_dense(self._h, group, pl, pr, N, D, sp, _ptr_space(per)[0],
+                                              _ptr_space(cons)[0], DEVICE if out_device else HOST))
+        return per, cons
+
+    def utility(self, measure, N, want=True):
+        util = np.empty((N,), np.float32) if want else None
+        self._check(self._L.alink_utility(self._h, MEASURE_ID[measure], _ptr_space(util)[0], HOST))
+        return util
+
+    def utility_from_proba(self, per_learner, measure, want_consensus=False):
+        per_learner = np.ascontiguousarray(per_learner, dtype=np.float32) if not _is_torch(per_learner) else per_learner
+        N, K, Cc = per_learner.shape
+        p, sp = _ptr_space(per_learner)
+        util = np.empty((N,), np.float32)
+        cons = np.empty((N, Cc), np.float32) if want_consensus else None
+        self._check(self._L.alink_utility_from_proba(self._h, p, N, K, Cc, MEASURE_ID[measure], sp,
+                                                     _ptr_space(util)[0], _ptr_space(cons)[0], HOST))
+        return (util, cons) if want_consensus else util
+
+    # ---- selection
+    def select_topk(self, B, base=0):
+        idx = np.empty((B,), np.int64)
+        util = np.empty((B,), np.float32)
+        keys = np.empty((B,), np.uint64)
+        self._check(self._L.alink_select_topk(self._h, B, base, _ptr_space(idx)[0], _ptr_space(util)[0],
+                                              _ptr_space(keys)[0], HOST))
+        return idx, util, keys
+
+    def topk_values(self, values, B, base=0):
+        if not _is_torch(values):
+            values = _f32(values)
+        p, sp = _ptr_space(values)
+        N = values.shape[0]
+        idx = np.empty((B,), np.int64)
+        util = np.empty((B,), np.float32)
+        keys = np.empty((B,), np.uint64)
+        self._check(self._L.alink_topk_values(self._h, p, N, base, B, sp, _ptr_space(idx)[0],
+                                              _ptr_space(util)[0], _ptr_space(keys)[0], HOST))
+        return idx, util, keys
+
+    def topk_keys(self, keys, B):
+        if not _is_torch(keys):
+            keys = np.ascontiguousarray(keys, dtype=np.uint64)
+        p, sp = _ptr_space(keys)
+        out = np.empty((B,), np.uint64)
+        self._check(self._L.alink_topk_keys(self._h, p, keys.shape[0], B, sp, _ptr_space(out)[0], HOST))
+        return out
+
+    def query(self, group, slot_a, slot_b, ia, ib, N, measure, B, base=0, timing=False, out=None):
+        """Fused step. ia/ib: numpy (host) or torch cuda int32. Returns (idx, util, keys[, Timing])."""
+        pia, sp = _ptr_space(ia)
+        pib, _ = _ptr_space(ib)
+        _space_of(ia, ib)
+        if out is None:
+            out = (np.empty((B,), np.int64), np.empty((B,), np.float32), np.empty((B,), np.uint64))
+        idx, util, keys = out
+        t = Timing() if timing else None
+        self._check(self._L.alink_query(self._h, group, slot_a, slot_b, pia, pib, N, sp, MEASURE_ID[measure], B,
+                                        base, _ptr_space(idx)[0], _ptr_space(util)[0], _ptr_space(keys)[0],
+                                        HOST, C.byref(t) if timing else None))
+        return (idx, util, keys, t) if timing else (idx, util, keys)
+
+    def disparity_select(self, p2, p1, ratio=0.25, eps=0.05, blind=False, y=None):
+        p2 = _f32(p2)
+        p1 = _f32(p1)
+        T, N = p2.shape
+        yy = None if y is None else _f32(y).reshape(-1)
+        idx = np.empty((max(N, 1),), np.int64)
+        n_out, active = C.c_int64(0), C.c_int64(0)
+        self._check(self._L.alink_disparity_select(self._h, _ptr_space(p2)[0], _ptr_space(p1)[0], N, T,
+                                                   float(ratio), float(eps), int(bool(blind)),
+                                                   _ptr_space(yy)[0], HOST, _ptr_space(idx)[0], HOST,
+                                                   C.byref(n_out), C.byref(active)))
+        return idx[:n_out.value].copy(), int(active.value)
+
+    def set_stream(self, cuda_stream):
+        """cuda_stream: integer cudaStream_t (torch.cuda.current_stream().cuda_stream) or None."""
+        self._check(self._L.alink_set_stream(self._h, C.c_void_p(cuda_stream) if cuda_stream else None))
+
+    def sync(self):
+        self._check(self._L.alink_sync(self._h))
+
+    @property
+    def launches(self):
+        return int(self._L.alink_launch_count(self._h))
+
+
+_default_ctx = {}
+
+
+def default_context(device: int | None = None) -> Context:
+    """Process-wide context per device (the reference's single global TF session, code/ALINK.py:22-25)."""
+    if device is None:
+        device = int(os.environ.get("LOCAL_RANK", "0")) if os.environ.get("ALINK_USE_LOCAL_RANK", "1") == "1" else 0
+    if device not in _default_ctx:
+        _default_ctx[device] = Context(device)
+    return _default_ctx[device]

@@ -1,0 +1,486 @@
+// alink_b200.cu — C ABI (include/alink_b200.h) over the sm_100a kernels of the query-selection path.
+// Build: alink_b200/csrc/Makefile (nvcc -gencode arch=compute_100a,code=sm_100a -fmad=false -lineinfo).
+// -fmad=false: no implicit contraction anywhere; every fused multiply-add is an explicit __fmaf_rn.
+#include "common.cuh"
+#include "head_ffma.cuh"
+#include "head_tc.cuh"
+#include "utility.cuh"
+#include "topk.cuh"
+#include "disparity.cuh"
+
+#include <math.h>
+#include <new>
+
+extern "C" {
+
+int alink_abi_version(void) { return ALINK_ABI_VERSION; }
+
+int alink_create(alink_ctx **out, int device, unsigned flags) {
+  (void)flags;
+  if (!out) return ALINK_E_INVALID;
+  *out = nullptr;
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0) return ALINK_E_CUDA;  // no CPU fallback
+  if (device < 0 || device >= ndev) return ALINK_E_INVALID;
+  alink_ctx *ctx = new (std::nothrow) alink_ctx();
+  if (!ctx) return ALINK_E_NOMEM;
+  ctx->device = device;
+  if (cudaSetDevice(device) != cudaSuccess ||
+      cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) {
+    delete ctx;
+    return ALINK_E_CUDA;
+  }
+  ctx->own_stream = ctx->stream;
+  cudaDeviceGetAttribute(&ctx->sm_count, cudaDevAttrMultiProcessorCount, device);
+  for (int i = 0; i < 8; ++i) cudaEventCreate(&ctx->ev[i]);
+  *out = ctx;
+  return ALINK_OK;
+}
+
+static void free_group(HeadGroup &g) {
+  void *ptrs[] = {g.W1, g.b1, g.W2, g.b2, g.W3, g.b3, (void *)g.pW1, g.W1t, g.W2t};
+  for (void *p : ptrs)
+    if (p) cudaFree(p);
+  g = HeadGroup();
+}
+
+int alink_destroy(alink_ctx *ctx) {
+  if (!ctx) return ALINK_OK;
+  cudaSetDevice(ctx->device);
+  cudaStreamSynchronize(ctx->stream);
+  for (auto &g : ctx->groups) free_group(g);
+  for (auto &t : ctx->tables) dev_release(t.own);
+  DevBuf *bufs[] = {&ctx->idx_a, &ctx->idx_b, &ctx->h1ws, &ctx->probs, &ctx->cons, &ctx->util, &ctx->sel_state,
+                    &ctx->sel_keys, &ctx->sel_idx, &ctx->sel_util, &ctx->sel_in, &ctx->misc0, &ctx->misc1,
+                    &ctx->misc2, &ctx->misc3};
+  for (DevBuf *b : bufs) dev_release(*b);
+  for (int i = 0; i < 8; ++i)
+    if (ctx->ev[i]) cudaEventDestroy(ctx->ev[i]);
+  cudaStreamDestroy(ctx->own_stream);
+  delete ctx;
+  return ALINK_OK;
+}
+
+const char *alink_last_error(const alink_ctx *ctx) { return ctx ? ctx->err : "null context"; }
+
+int alink_sync(alink_ctx *ctx) {
+  if (!ctx) return ALINK_E_INVALID;
+  ALINK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return ALINK_OK;
+}
+
+int alink_set_stream(alink_ctx *ctx, void *cuda_stream) {
+  if (!ctx) return ALINK_E_INVALID;
+  ALINK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  ctx->stream = cuda_stream ? (cudaStream_t)cuda_stream : ctx->own_stream;
+  return ALINK_OK;
+}
+
+int64_t alink_launch_count(const alink_ctx *ctx) { return ctx ? ctx->launches : 0; }
+
+int alink_host_alloc(void **out, uint64_t bytes) {
+  if (!out) return ALINK_E_INVALID;
+  return cudaMallocHost(out, bytes ? bytes : 1) == cudaSuccess ? ALINK_OK : ALINK_E_NOMEM;
+}
+int alink_host_free(void *p) { return (!p || cudaFreeHost(p) == cudaSuccess) ? ALINK_OK : ALINK_E_CUDA; }
+
+// ------------------------------------------------------------------------------------------ heads
+static int upload_stack(alink_ctx *ctx, const float *const *src, int K, size_t each, float **dst) {
+  ALINK_CUDA(ctx, cudaMalloc((void **)dst, sizeof(float) * each * K));
+  for (int k = 0; k < K; ++k)
+    ALINK_CUDA(ctx, cudaMemcpyAsync(*dst + each * k, src[k], sizeof(float) * each, cudaMemcpyHostToDevice,
+                                    ctx->stream));
+  return ALINK_OK;
+}
+
+int alink_set_heads(alink_ctx *ctx, int group, int K, int D_in, int H1, int H2, int C, int out_act,
+                    int feat_mode, const float *const *W1, const float *const *b1, const float *const *W2,
+                    const float *const *b2, const float *const *W3, const float *const *b3, int compute) {
+  if (!ctx) return ALINK_E_INVALID;
+  if (group < 0 || group >= ALINK_MAX_GROUPS) return alink_fail(ctx, ALINK_E_INVALID, "bad group %d", group);
+  if (K < 1 || K > ALINK_MAX_K) return alink_fail(ctx, ALINK_E_INVALID, "K=%d outside [1,%d]", K, ALINK_MAX_K);
+  if (!((C == 2 && out_act == ALINK_ACT_SOFTMAX) || (C == 1 && out_act == ALINK_ACT_SIGMOID)))
+    return alink_fail(ctx, ALINK_E_INVALID, "head must be softmax/C=2 (siamese.py) or sigmoid/C=1 (siamese3.py)");
+  if (feat_mode != ALINK_FEAT_ABSDIFF && feat_mode != ALINK_FEAT_ABSDIFF_HADAMARD)
+    return alink_fail(ctx, ALINK_E_INVALID, "bad feat_mode %d", feat_mode);
+  if (compute != ALINK_COMPUTE_FP32_EXACT && compute != ALINK_COMPUTE_BF16_TC)
+    return alink_fail(ctx, ALINK_E_INVALID, "bad compute mode %d", compute);
+  if (D_in < 8 || D_in % 8 || H1 < 8 || H1 % 8 || (feat_mode && (D_in % 16)))
+    return alink_fail(ctx, ALINK_E_UNSUPPORTED, "D_in and H1 must be multiples of 8 (got %d, %d)", D_in, H1);
+  if (H2 != 32 && H2 != 64) return alink_fail(ctx, ALINK_E_UNSUPPORTED, "H2 must be 32 or 64 (got %d)", H2);
+  if (!W1 || !b1 || !W2 || !b2 || !W3 || !b3) return alink_fail(ctx, ALINK_E_INVALID, "null weight array");
+  ALINK_CUDA(ctx, cudaSetDevice(ctx->device));
+  ALINK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  HeadGroup &g = ctx->groups[group];
+  free_group(g);
+  g.K = K; g.D_in = D_in; g.H1 = H1; g.H2 = H2; g.C = C; g.act = out_act; g.feat_mode = feat_mode;
+  g.compute = compute;
+  ALINK_TRY(upload_stack(ctx, W1, K, (size_t)D_in * H1, &g.W1));
+  ALINK_TRY(upload_stack(ctx, b1, K, (size_t)H1, &g.b1));
+  ALINK_TRY(upload_stack(ctx, W2, K, (size_t)H1 * H2, &g.W2));
+  ALINK_TRY(upload_stack(ctx, b2, K, (size_t)H2, &g.b2));
+  ALINK_TRY(upload_stack(ctx, W3, K, (size_t)H2 * C, &g.W3));
+  ALINK_TRY(upload_stack(ctx, b3, K, (size_t)C, &g.b3));
+  // pointer tables: 6 arrays of K device pointers in one allocation
+  const float *host_ptrs[6 * ALINK_MAX_K];
+  const float *bases[6] = {g.W1, g.b1, g.W2, g.b2, g.W3, g.b3};
+  const size_t each[6] = {(size_t)D_in * H1, (size_t)H1, (size_t)H1 * H2, (size_t)H2, (size_t)H2 * C, (size_t)C};
+  for (int a = 0; a < 6; ++a)
+    for (int k = 0; k < K; ++k) host_ptrs[a * ALINK_MAX_K + k] = bases[a] + each[a] * k;
+  const float **dptr = nullptr;
+  ALINK_CUDA(ctx, cudaMalloc((void **)&dptr, sizeof(host_ptrs)));
+  ALINK_CUDA(ctx, cudaMemcpyAsync((void *)dptr, host_ptrs, sizeof(host_ptrs), cudaMemcpyHostToDevice, ctx->stream));
+  g.pW1 = dptr;
+  g.pb1 = dptr + 1 * ALINK_MAX_K;
+  g.pW2 = dptr + 2 * ALINK_MAX_K;
+  g.pb2 = dptr + 3 * ALINK_MAX_K;
+  g.pW3 = dptr + 4 * ALINK_MAX_K;
+  g.pb3 = dptr + 5 * ALINK_MAX_K;
+  if (compute == ALINK_COMPUTE_BF16_TC) ALINK_TRY(tc_prepare_heads(ctx, g));
+  ALINK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));  // host_ptrs / caller buffers may go away
+  g.set = true;
+  return ALINK_OK;
+}
+
+// ------------------------------------------------------------------------------------------ tables
+int alink_set_table(alink_ctx *ctx, int slot, const void *emb, int64_t M, int D, int dtype, int space) {
+  if (!ctx) return ALINK_E_INVALID;
+  if (slot < 0 || slot >= ALINK_MAX_SLOTS) return alink_fail(ctx, ALINK_E_INVALID, "bad slot %d", slot);
+  if (!emb || M < 1 || D < 8 || D % 8) return alink_fail(ctx, ALINK_E_INVALID, "bad table (M=%lld, D=%d)", (long long)M, D);
+  if (dtype != ALINK_F32 && dtype != ALINK_BF16) return alink_fail(ctx, ALINK_E_INVALID, "bad dtype %d", dtype);
+  ALINK_CUDA(ctx, cudaSetDevice(ctx->device));
+  Table &t = ctx->tables[slot];
+  const size_t bytes = (size_t)M * D * (dtype == ALINK_F32 ? 4 : 2);
+  if (space == ALINK_DEVICE) {
+    t.p = emb;
+  } else {
+    ALINK_TRY(dev_reserve(ctx, t.own, bytes));
+    ALINK_CUDA(ctx, cudaMemcpyAsync(t.own.p, emb, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    ALINK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    t.p = t.own.p;
+  }
+  t.M = M; t.D = D; t.dtype = dtype;
+  return ALINK_OK;
+}
+
+// ------------------------------------------------------------------------------------------ scoring
+// ia/ib are device pointers (or null = identity). Fills ctx->probs [N][K][C].
+static int score_impl(alink_ctx *ctx, int group, const Table &A, const Table &Bt, const int32_t *ia,
+                      const int32_t *ib, int64_t N) {
+  if (group < 0 || group >= ALINK_MAX_GROUPS || !ctx->groups[group].set)
+    return alink_fail(ctx, ALINK_E_STATE, "head group %d not set (alink_set_heads)", group);
+  const HeadGroup &g = ctx->groups[group];
+  if (!A.p || !Bt.p) return alink_fail(ctx, ALINK_E_STATE, "embedding table slot not set (alink_set_table)");
+  if (A.D != Bt.D || A.dtype != Bt.dtype) return alink_fail(ctx, ALINK_E_INVALID, "table shape/dtype mismatch");
+  const int want = g.feat_mode ? 2 * A.D : A.D;
+  if (want != g.D_in)
+    return alink_fail(ctx, ALINK_E_INVALID, "table D=%d gives fan-in %d but heads expect %d", A.D, want, g.D_in);
+  if (!ia && (N > A.M || N > Bt.M)) return alink_fail(ctx, ALINK_E_INVALID, "identity pairs exceed table rows");
+  if (N < 0 || N > 0xFFFFFFFEll) return alink_fail(ctx, ALINK_E_INVALID, "N out of range");
+  ctx->N = N; ctx->sK = g.K; ctx->sC = g.C; ctx->util_valid = false;
+  ALINK_TRY(dev_reserve(ctx, ctx->probs, sizeof(float) * (size_t)(N ? N : 1) * g.K * g.C));
+  if (N == 0) return ALINK_OK;
+  if (g.compute == ALINK_COMPUTE_BF16_TC)
+    return tc_score(ctx, g, A, Bt, ia, ib, N, (float *)ctx->probs.p);
+  if (A.dtype != ALINK_F32)
+    return alink_fail(ctx, ALINK_E_UNSUPPORTED, "FP32_EXACT mode needs fp32 tables");
+  const int64_t chunk = 65536;
+  const int Mc_max = (int)(N < chunk ? N : chunk);
+  const int64_t lstride = (int64_t)Mc_max * g.H1;
+  ALINK_TRY(dev_reserve(ctx, ctx->h1ws, sizeof(float) * (size_t)lstride * g.K));
+  for (int64_t row0 = 0; row0 < N; row0 += chunk) {
+    const int Mc = (int)((N - row0) < chunk ? (N - row0) : chunk);
+    ALINK_TRY(ffma_head_chunk(ctx, g, (const float *)A.p, (const float *)Bt.p, A.D, ia, ib, row0, Mc,
+                              (float *)ctx->h1ws.p, lstride, (float *)ctx->probs.p));
+  }
+  return ALINK_OK;
+}
+
+static int emit_scores(alink_ctx *ctx, float *per_learner, float *consensus, int out_space) {
+  const int64_t N = ctx->N;
+  if (per_learner)
+    ALINK_TRY(copy_out(ctx, per_learner, ctx->probs.p, sizeof(float) * (size_t)N * ctx->sK * ctx->sC, out_space));
+  if (consensus) {
+    float *dst = consensus;
+    if (out_space == ALINK_HOST) {
+      ALINK_TRY(dev_reserve(ctx, ctx->cons, sizeof(float) * (size_t)(N ? N : 1) * ctx->sC));
+      dst = (float *)ctx->cons.p;
+    }
+    ALINK_TRY(launch_utility(ctx, (const float *)ctx->probs.p, N, ctx->sK, ctx->sC, 0, nullptr, dst));
+    if (out_space == ALINK_HOST)
+      ALINK_TRY(copy_out(ctx, consensus, dst, sizeof(float) * (size_t)N * ctx->sC, ALINK_HOST));
+  }
+  if (out_space == ALINK_HOST && (per_learner || consensus)) ALINK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return ALINK_OK;
+}
+
+int alink_score_indexed(alink_ctx *ctx, int group, int slot_a, int slot_b, const int32_t *ia, const int32_t *ib,
+                        int64_t N, int in_space, float *per_learner, float *consensus, int out_space) {
+  if (!ctx) return ALINK_E_INVALID;
+  if (slot_a < 0 || slot_a >= ALINK_MAX_SLOTS || slot_b < 0 || slot_b >= ALINK_MAX_SLOTS)
+    return alink_fail(ctx, ALINK_E_INVALID, "bad slot");
+  if ((ia == nullptr) != (ib == nullptr)) return alink_fail(ctx, ALINK_E_INVALID, "ia and ib must both be given or both NULL");
+  ALINK_CUDA(ctx, cudaSetDevice(ctx->device));
+  const void *dia, *dib;
+  ALINK_TRY(stage_in(ctx, ia, sizeof(int32_t) * (size_t)N, in_space, ctx->idx_a, &dia));
+  ALINK_TRY(stage_in(ctx, ib, sizeof(int32_t) * (size_t)N, in_space, ctx->idx_b, &dib));
+  ALINK_TRY(score_impl(ctx, group, ctx->tables[slot_a], ctx->tables[slot_b], (const int32_t *)dia,
+                       (const int32_t *)dib, N));
+  return emit_scores(ctx, per_learner, consensus, out_space);
+}
+
+int alink_score_dense(alink_ctx *ctx, int group, const float *XL, const float *XR, int64_t N, int D, int in_space,
+                      float *per_learner, float *consensus, int out_space) {
+  if (!ctx) return ALINK_E_INVALID;
+  if (N < 0 || D < 8 || D % 8) return alink_fail(ctx, ALINK_E_INVALID, "bad dense shape (N=%lld, D=%d)", (long long)N, D);
+  if (N == 0) {
+    ctx->N = 0;
+    return ALINK_OK;
+  }
+  if (!XL || !XR) return alink_fail(ctx, ALINK_E_INVALID, "null XL/XR");
+  ALINK_TRY(alink_set_table(ctx, ALINK_MAX_SLOTS - 2, XL, N, D, ALINK_F32, in_space));
+  ALINK_TRY(alink_set_table(ctx, ALINK_MAX_SLOTS - 1, XR, N, D, ALINK_F32, in_space));
+  ALINK_TRY(score_impl(ctx, group, ctx->tables[ALINK_MAX_SLOTS - 2], ctx->tables[ALINK_MAX_SLOTS - 1], nullptr,
+                       nullptr, N));
+  return emit_scores(ctx, per_learner, consensus, out_space);
+}
+
+// ------------------------------------------------------------------------------------------ utility
+static int utility_impl(alink_ctx *ctx, int measure) {
+  if (measure < 0 || measure >= ALINK_UTIL_COUNT) return alink_fail(ctx, ALINK_E_INVALID, "bad measure %d", measure);
+  if (!ctx->probs.p) return alink_fail(ctx, ALINK_E_STATE, "no scores: call alink_score_* first");
+  ALINK_TRY(dev_reserve(ctx, ctx->util, sizeof(float) * (size_t)(ctx->N ? ctx->N : 1)));
+  ALINK_TRY(launch_utility(ctx, (const float *)ctx->probs.p, ctx->N, ctx->sK, ctx->sC, measure,
+                           (float *)ctx->util.p, nullptr));
+  ctx->util_valid = true;
+  return ALINK_OK;
+}
+
+int alink_utility(alink_ctx *ctx, int measure, float *util, int out_space) {
+  if (!ctx) return ALINK_E_INVALID;
+  ALINK_CUDA(ctx, cudaSetDevice(ctx->device));
+  ALINK_TRY(utility_impl(ctx, measure));
+  ALINK_TRY(copy_out(ctx, util, ctx->util.p, sizeof(float) * (size_t)ctx->N, out_space));
+  if (util && out_space == ALINK_HOST) ALINK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return ALINK_OK;
+}
+
+int alink_utility_from_proba(alink_ctx *ctx, const float *per_learner, int64_t N, int K, int C, int measure,
+                             int in_space, float *util, float *consensus, int out_space) {
+  if (!ctx) return ALINK_E_INVALID;
+  if (N < 0 || K < 1 || K > ALINK_MAX_K || (C != 1 && C != 2) || measure < 0 || measure >= ALINK_UTIL_COUNT)
+    return alink_fail(ctx, ALINK_E_INVALID, "bad arguments (N=%lld K=%d C=%d measure=%d)", (long long)N, K, C, measure);
+  ALINK_CUDA(ctx, cudaSetDevice(ctx->device));
+  const size_t nbytes = sizeof(float) * (size_t)N * K * C;
+  if (N > 0) {
+    if (!per_learner) return alink_fail(ctx, ALINK_E_INVALID, "null per_learner");
+    ALINK_TRY(dev_reserve(ctx, ctx->probs, nbytes));
+    ALINK_CUDA(ctx, cudaMemcpyAsync(ctx->probs.p, per_learner, nbytes,
+                                    in_space == ALINK_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice,
+                                    ctx->stream));
+  }
+  ctx->N = N; ctx->sK = K; ctx->sC = C;
+  ALINK_TRY(utility_impl(ctx, measure));
+  ALINK_TRY(copy_out(ctx, util, ctx->util.p, sizeof(float) * (size_t)N, out_space));
+  if (consensus) ALINK_TRY(emit_scores(ctx, nullptr, consensus, out_space));
+  if (out_space == ALINK_HOST) ALINK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return ALINK_OK;
+}
+
+// ------------------------------------------------------------------------------------------ top-B
+static int emit_selection(alink_ctx *ctx, int64_t B, int64_t *idx_out, float *util_out, uint64_t *keys_out,
+                          int out_space) {
+  if (B == 0) return ALINK_OK;
+  const uint64_t *keys = (const uint64_t *)ctx->sel_keys.p;
+  int64_t *didx = idx_out;
+  float *dutil = util_out;
+  if (out_space == ALINK_HOST) {
+    ALINK_TRY(dev_reserve(ctx, ctx->sel_idx, sizeof(int64_t) * (size_t)B));
+    ALINK_TRY(dev_reserve(ctx, ctx->sel_util, sizeof(float) * (size_t)B));
+    didx = idx_out ? (int64_t *)ctx->sel_idx.p : nullptr;
+    dutil = util_out ? (float *)ctx->sel_util.p : nullptr;
+  }
+  if (didx || dutil) {
+    int64_t blocks = (B + 255) / 256;
+    if (blocks > 1024) blocks = 1024;
+    unpack_keys_kernel<<<(unsigned)blocks, 256, 0, ctx->stream>>>(keys, B, didx, dutil);
+    ALINK_LAUNCHED(ctx);
+  }
+  if (out_space == ALINK_HOST) {
+    ALINK_TRY(copy_out(ctx, idx_out, didx, sizeof(int64_t) * (size_t)B, ALINK_HOST));
+    ALINK_TRY(copy_out(ctx, util_out, dutil, sizeof(float) * (size_t)B, ALINK_HOST));
+  }
+  ALINK_TRY(copy_out(ctx, keys_out, keys, sizeof(uint64_t) * (size_t)B, out_space));
+  if (out_space == ALINK_HOST) ALINK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return ALINK_OK;
+}
+
+int alink_select_topk(alink_ctx *ctx, int64_t B, int64_t base, int64_t *idx_out, float *util_out,
+                      uint64_t *keys_out, int out_space) {
+  if (!ctx) return ALINK_E_INVALID;
+  if (!ctx->util_valid) return alink_fail(ctx, ALINK_E_STATE, "no utilities: call alink_utility first");
+  if (B < 0 || B > ctx->N) return alink_fail(ctx, ALINK_E_INVALID, "B=%lld outside [0, N=%lld]", (long long)B, (long long)ctx->N);
+  if (base < 0 || base + ctx->N > 0xFFFFFFFFll) return alink_fail(ctx, ALINK_E_INVALID, "base + N exceeds 2^32 - 1");
+  if (B == 0) return ALINK_OK;
+  ALINK_CUDA(ctx, cudaSetDevice(ctx->device));
+  KeySrc src{(const float *)ctx->util.p, nullptr, (uint64_t)base};
+  ALINK_TRY(topk_device(ctx, src, ctx->N, B));
+  return emit_selection(ctx, B, idx_out, util_out, keys_out, out_space);
+}
+
+int alink_topk_values(alink_ctx *ctx, const float *util, int64_t N, int64_t base, int64_t B, int in_space,
+                      int64_t *idx_out, float *util_out, uint64_t *keys_out, int out_space) {
+  if (!ctx) return ALINK_E_INVALID;
+  if (N < 0 || B < 0 || B > N) return alink_fail(ctx, ALINK_E_INVALID, "B=%lld outside [0, N=%lld]", (long long)B, (long long)N);
+  if (base < 0 || base + N > 0xFFFFFFFFll) return alink_fail(ctx, ALINK_E_INVALID, "base + N exceeds 2^32 - 1");
+  if (B == 0) return ALINK_OK;
+  if (!util) return alink_fail(ctx, ALINK_E_INVALID, "null util");
+  ALINK_CUDA(ctx, cudaSetDevice(ctx->device));
+  const void *du;
+  ALINK_TRY(stage_in(ctx, util, sizeof(float) * (size_t)N, in_space, ctx->sel_in, &du));
+  KeySrc src{(const float *)du, nullptr, (uint64_t)base};
+  ALINK_TRY(topk_device(ctx, src, N, B));
+  return emit_selection(ctx, B, idx_out, util_out, keys_out, out_space);
+}
+
+int alink_topk_keys(alink_ctx *ctx, const uint64_t *keys, int64_t n, int64_t B, int in_space, uint64_t *keys_out,
+                    int out_space) {
+  if (!ctx) return ALINK_E_INVALID;
+  if (n < 0 || B < 0 || B > n) return alink_fail(ctx, ALINK_E_INVALID, "B=%lld outside [0, n=%lld]", (long long)B, (long long)n);
+  if (B == 0) return ALINK_OK;
+  if (!keys) return alink_fail(ctx, ALINK_E_INVALID, "null keys");
+  ALINK_CUDA(ctx, cudaSetDevice(ctx->device));
+  const void *dk;
+  ALINK_TRY(stage_in(ctx, keys, sizeof(uint64_t) * (size_t)n, in_space, ctx->sel_in, &dk));
+  KeySrc src{nullptr, (const uint64_t *)dk, 0};
+  ALINK_TRY(topk_device(ctx, src, n, B));
+  return emit_selection(ctx, B, nullptr, nullptr, keys_out, out_space);
+}
+
+// ------------------------------------------------------------------------------------------ fused step
+int alink_query(alink_ctx *ctx, int group, int slot_a, int slot_b, const int32_t *ia, const int32_t *ib, int64_t N,
+                int in_space, int measure, int64_t B, int64_t base, int64_t *idx_out, float *util_out,
+                uint64_t *keys_out, int out_space, alink_timing *timing) {
+  if (!ctx) return ALINK_E_INVALID;
+  if (slot_a < 0 || slot_a >= ALINK_MAX_SLOTS || slot_b < 0 || slot_b >= ALINK_MAX_SLOTS)
+    return alink_fail(ctx, ALINK_E_INVALID, "bad slot");
+  if ((ia == nullptr) != (ib == nullptr)) return alink_fail(ctx, ALINK_E_INVALID, "ia and ib must both be given or both NULL");
+  if (B < 0 || B > N) return alink_fail(ctx, ALINK_E_INVALID, "B=%lld outside [0, N=%lld]", (long long)B, (long long)N);
+  if (base < 0 || base + N > 0xFFFFFFFFll) return alink_fail(ctx, ALINK_E_INVALID, "base + N exceeds 2^32 - 1");
+  if (measure < 0 || measure >= ALINK_UTIL_COUNT) return alink_fail(ctx, ALINK_E_INVALID, "bad measure %d", measure);
+  ALINK_CUDA(ctx, cudaSetDevice(ctx->device));
+  const int64_t l0 = ctx->launches;
+  cudaEvent_t *e = ctx->ev;
+  if (timing) ALINK_CUDA(ctx, cudaEventRecord(e[0], ctx->stream));
+  const void *dia, *dib;
+  ALINK_TRY(stage_in(ctx, ia, sizeof(int32_t) * (size_t)N, in_space, ctx->idx_a, &dia));
+  ALINK_TRY(stage_in(ctx, ib, sizeof(int32_t) * (size_t)N, in_space, ctx->idx_b, &dib));
+  if (timing) ALINK_CUDA(ctx, cudaEventRecord(e[1], ctx->stream));
+  ALINK_TRY(score_impl(ctx, group, ctx->tables[slot_a], ctx->tables[slot_b], (const int32_t *)dia,
+                       (const int32_t *)dib, N));
+  if (timing) ALINK_CUDA(ctx, cudaEventRecord(e[2], ctx->stream));
+  ALINK_TRY(utility_impl(ctx, measure));
+  if (timing) ALINK_CUDA(ctx, cudaEventRecord(e[3], ctx->stream));
+  if (B > 0) {
+    KeySrc src{(const float *)ctx->util.p, nullptr, (uint64_t)base};
+    ALINK_TRY(topk_device(ctx, src, N, B));
+  }
+  if (timing) ALINK_CUDA(ctx, cudaEventRecord(e[4], ctx->stream));
+  ALINK_TRY(emit_selection(ctx, B, idx_out, util_out, keys_out, out_space));
+  if (timing) {
+    ALINK_CUDA(ctx, cudaEventRecord(e[5], ctx->stream));
+    ALINK_CUDA(ctx, cudaEventSynchronize(e[5]));
+    cudaEventElapsedTime(&timing->ms_h2d, e[0], e[1]);
+    cudaEventElapsedTime(&timing->ms_score, e[1], e[2]);
+    cudaEventElapsedTime(&timing->ms_utility, e[2], e[3]);
+    cudaEventElapsedTime(&timing->ms_select, e[3], e[4]);
+    cudaEventElapsedTime(&timing->ms_d2h, e[4], e[5]);
+    cudaEventElapsedTime(&timing->ms_total, e[0], e[5]);
+    timing->launches = ctx->launches - l0;
+  }
+  return ALINK_OK;
+}
+
+// ------------------------------------------------------------------------------------------ A-LINK rule
+int alink_disparity_select(alink_ctx *ctx, const float *p2, const float *p1, int64_t N, int T, double ratio,
+                           double eps, int blind, const float *y, int in_space, int64_t *idx_out, int out_space,
+                           int64_t *n_out, int64_t *active_count) {
+  if (!ctx) return ALINK_E_INVALID;
+  if (N < 0 || T < 1 || !n_out) return alink_fail(ctx, ALINK_E_INVALID, "bad arguments (N=%lld, T=%d)", (long long)N, T);
+  if (N > 0xFFFFFFFEll) return alink_fail(ctx, ALINK_E_INVALID, "N out of range");
+  if (!(ratio >= 0.0 && ratio <= 1.0)) return alink_fail(ctx, ALINK_E_INVALID, "ratio outside [0,1]");
+  *n_out = 0;
+  if (active_count) *active_count = 0;
+  if (N == 0) return ALINK_OK;
+  if (!p2 || !p1) return alink_fail(ctx, ALINK_E_INVALID, "null scores");
+  ALINK_CUDA(ctx, cudaSetDevice(ctx->device));
+  const void *dp2, *dp1, *dy;
+  ALINK_TRY(stage_in(ctx, p2, sizeof(float) * (size_t)N * T, in_space, ctx->misc0, &dp2));
+  ALINK_TRY(stage_in(ctx, p1, sizeof(float) * (size_t)N, in_space, ctx->misc1, &dp1));
+  ALINK_TRY(stage_in(ctx, y, sizeof(float) * (size_t)N, in_space, ctx->misc2, &dy));
+  // scratch: cnt[N] int | d[N] float | blk counts | 2 x u64 counters
+  const int nblk = (int)((N + 256 * DISP_ITEMS - 1) / (256 * DISP_ITEMS));
+  const size_t off_d = sizeof(int) * (size_t)N;
+  const size_t off_blk = off_d + sizeof(float) * (size_t)N;
+  const size_t off_cnt = (off_blk + sizeof(unsigned int) * (size_t)nblk + 15) & ~(size_t)15;
+  ALINK_TRY(dev_reserve(ctx, ctx->misc3, off_cnt + 16));
+  ALINK_TRY(dev_reserve(ctx, ctx->sel_state, sizeof(SelectState)));
+  char *scr = (char *)ctx->misc3.p;
+  int *cnt = (int *)scr;
+  float *d = (float *)(scr + off_d);
+  unsigned int *blk = (unsigned int *)(scr + off_blk);
+  unsigned long long *counters = (unsigned long long *)(scr + off_cnt);
+  ALINK_CUDA(ctx, cudaMemsetAsync(cnt, 0, sizeof(int) * (size_t)N, ctx->stream));
+  ALINK_CUDA(ctx, cudaMemsetAsync(counters, 0, 16, ctx->stream));
+  SelectState *st = (SelectState *)ctx->sel_state.p;
+  int64_t sb = (N + 2047) / 2048;
+  const int64_t cap = (int64_t)ctx->sm_count * 8;
+  if (sb > cap) sb = cap;
+  const int64_t m = (int64_t)((double)N * ratio);  // int(len * ratio), code/ALINK.py:183
+  for (int t = 0; t < T; ++t) {
+    const float *q = (const float *)dp2 + (size_t)t * N;
+    if (blind) {
+      disparity_blind_kernel<<<(unsigned)sb, 256, 0, ctx->stream>>>(q, (const float *)dp1, N, cnt);
+      ALINK_LAUNCHED(ctx);
+    } else if (m > 0) {
+      absdiff_vec_kernel<<<(unsigned)sb, 256, 0, ctx->stream>>>(q, (const float *)dp1, N, d);
+      ALINK_LAUNCHED(ctx);
+      KeySrc src{d, nullptr, 0};
+      ALINK_TRY(select_threshold(ctx, src, N, m, st));
+      disparity_mark_kernel<<<(unsigned)sb, 256, 0, ctx->stream>>>(d, N, st, 1, cnt);
+      ALINK_LAUNCHED(ctx);
+    }
+  }
+  // python compares the fp32 score with float64 bounds 0.5 -/+ eps (code/ALINK.py:195): fold the
+  // bounds onto the nearest fp32 values that give the same decisions.
+  const double lo_d = 0.5 - eps, hi_d = 0.5 + eps;
+  float lo = (float)lo_d, hi = (float)hi_d;
+  if ((double)lo > lo_d) lo = nextafterf(lo, -INFINITY);
+  if ((double)hi < hi_d) hi = nextafterf(hi, INFINITY);
+  DispFilter f{cnt, (const float *)dp1, (const float *)dy, T, lo, hi};
+  disparity_count_kernel<<<nblk, 256, 0, ctx->stream>>>(f, N, blk, counters + 0);
+  ALINK_LAUNCHED(ctx);
+  disparity_scan_kernel<<<1, 1024, 0, ctx->stream>>>(blk, nblk, counters + 1);
+  ALINK_LAUNCHED(ctx);
+  int64_t *didx = idx_out;
+  if (idx_out && out_space == ALINK_HOST) {
+    ALINK_TRY(dev_reserve(ctx, ctx->sel_idx, sizeof(int64_t) * (size_t)N));
+    didx = (int64_t *)ctx->sel_idx.p;
+  }
+  if (didx) {
+    disparity_scatter_kernel<<<nblk, 256, 0, ctx->stream>>>(f, N, blk, didx);
+    ALINK_LAUNCHED(ctx);
+  }
+  unsigned long long hc[2];
+  ALINK_CUDA(ctx, cudaMemcpyAsync(hc, counters, 16, cudaMemcpyDeviceToHost, ctx->stream));
+  ALINK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  *n_out = (int64_t)hc[1];
+  if (active_count) *active_count = (int64_t)hc[0];
+  if (idx_out && out_space == ALINK_HOST && hc[1] > 0) {
+    ALINK_CUDA(ctx, cudaMemcpyAsync(idx_out, didx, sizeof(int64_t) * (size_t)hc[1], cudaMemcpyDeviceToHost, ctx->stream));
+    ALINK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  }
+  return ALINK_OK;
+}
+
+}  // extern "C"

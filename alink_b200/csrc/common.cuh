@@ -1,0 +1,147 @@
+// common.cuh — context, error plumbing and device scratch for libalink_b200.so
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+#include <stdarg.h>
+
+#include "../../include/alink_b200.h"
+#include "../../include/alink_math.h"
+
+struct DevBuf {
+  void *p = nullptr;
+  size_t cap = 0;
+};
+
+struct HeadGroup {
+  bool set = false;
+  int K = 0, D_in = 0, H1 = 0, H2 = 0, C = 0, act = 0, feat_mode = 0, compute = 0;
+  // fp32 master copies, one allocation per tensor kind: [K][in][out] contiguous
+  float *W1 = nullptr, *b1 = nullptr, *W2 = nullptr, *b2 = nullptr, *W3 = nullptr, *b3 = nullptr;
+  // device arrays of K pointers into the above
+  const float **pW1 = nullptr, **pb1 = nullptr, **pW2 = nullptr, **pb2 = nullptr, **pW3 = nullptr, **pb3 = nullptr;
+  // bf16 operands for the tcgen05 path, N-major ("[out][in]", K contiguous): W1t [K][H1][D_in], W2t [K][H2][H1]
+  __nv_bfloat16 *W1t = nullptr, *W2t = nullptr;
+};
+
+struct Table {
+  const void *p = nullptr;  // device pointer (owned iff own.p == p)
+  int64_t M = 0;
+  int D = 0;
+  int dtype = ALINK_F32;
+  DevBuf own;
+};
+
+struct SelectState;  // topk.cuh
+
+struct alink_ctx {
+  int device = 0;
+  int sm_count = 148;
+  cudaStream_t stream = nullptr;      // stream in use
+  cudaStream_t own_stream = nullptr;  // private stream created by alink_create
+  cudaEvent_t ev[8] = {};
+  char err[512] = {0};
+  int64_t launches = 0;
+
+  HeadGroup groups[ALINK_MAX_GROUPS];
+  Table tables[ALINK_MAX_SLOTS];
+
+  // last scoring result (device resident)
+  int64_t N = 0;
+  int sK = 0, sC = 0;
+  DevBuf idx_a, idx_b;   // staged pair indices (when given on host)
+  DevBuf h1ws;           // fp32 hidden-1 workspace of one chunk [K][Mc][H1]
+  DevBuf probs;          // [N][K][C] fp32
+  DevBuf cons;           // [N][C] fp32
+  DevBuf util;           // [N] fp32
+  bool util_valid = false;
+  // select scratch
+  DevBuf sel_state, sel_keys, sel_idx, sel_util, sel_in;
+  DevBuf misc0, misc1, misc2, misc3;
+};
+
+static inline int alink_fail(alink_ctx *ctx, int code, const char *fmt, ...) {
+  if (ctx) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(ctx->err, sizeof(ctx->err), fmt, ap);
+    va_end(ap);
+  }
+  return code;
+}
+
+#define ALINK_CUDA(ctx, expr)                                                                     \
+  do {                                                                                            \
+    cudaError_t e__ = (expr);                                                                     \
+    if (e__ != cudaSuccess)                                                                       \
+      return alink_fail((ctx), ALINK_E_CUDA, "%s:%d %s -> %s", __FILE__, __LINE__, #expr,         \
+                        cudaGetErrorString(e__));                                                 \
+  } while (0)
+
+#define ALINK_TRY(expr)            \
+  do {                             \
+    int rc__ = (expr);             \
+    if (rc__ != ALINK_OK) return rc__; \
+  } while (0)
+
+// count + check a kernel launch
+#define ALINK_LAUNCHED(ctx)                                                                       \
+  do {                                                                                            \
+    (ctx)->launches++;                                                                            \
+    cudaError_t e__ = cudaGetLastError();                                                         \
+    if (e__ != cudaSuccess)                                                                       \
+      return alink_fail((ctx), ALINK_E_CUDA, "%s:%d kernel launch -> %s", __FILE__, __LINE__,     \
+                        cudaGetErrorString(e__));                                                 \
+  } while (0)
+
+static inline int dev_reserve(alink_ctx *ctx, DevBuf &b, size_t bytes) {
+  if (bytes <= b.cap && b.p) return ALINK_OK;
+  if (b.p) {
+    ALINK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    ALINK_CUDA(ctx, cudaFree(b.p));
+    b.p = nullptr;
+    b.cap = 0;
+  }
+  size_t want = bytes < 256 ? 256 : bytes;
+  cudaError_t e = cudaMalloc(&b.p, want);
+  if (e != cudaSuccess) {
+    b.p = nullptr;
+    return alink_fail(ctx, ALINK_E_NOMEM, "cudaMalloc(%zu) -> %s", want, cudaGetErrorString(e));
+  }
+  b.cap = want;
+  return ALINK_OK;
+}
+
+static inline void dev_release(DevBuf &b) {
+  if (b.p) cudaFree(b.p);
+  b.p = nullptr;
+  b.cap = 0;
+}
+
+// Bring a caller buffer onto the device: ALINK_DEVICE pointers pass through, ALINK_HOST ones are
+// copied into `stage` on the context stream.
+static inline int stage_in(alink_ctx *ctx, const void *src, size_t bytes, int space, DevBuf &stage,
+                           const void **out) {
+  if (!src) {
+    *out = nullptr;
+    return ALINK_OK;
+  }
+  if (space == ALINK_DEVICE) {
+    *out = src;
+    return ALINK_OK;
+  }
+  ALINK_TRY(dev_reserve(ctx, stage, bytes));
+  ALINK_CUDA(ctx, cudaMemcpyAsync(stage.p, src, bytes, cudaMemcpyHostToDevice, ctx->stream));
+  *out = stage.p;
+  return ALINK_OK;
+}
+
+static inline int copy_out(alink_ctx *ctx, void *dst, const void *src_dev, size_t bytes, int space) {
+  if (!dst || bytes == 0) return ALINK_OK;
+  ALINK_CUDA(ctx, cudaMemcpyAsync(dst, src_dev, bytes,
+                                  space == ALINK_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost,
+                                  ctx->stream));
+  return ALINK_OK;
+}

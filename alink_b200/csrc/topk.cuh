@@ -1,0 +1,227 @@
+// topk.cuh — deterministic top-B selection on packed 64-bit keys (HBM/L2-bound streaming passes).
+//
+// Replaces modAL's multi_argmax = np.argpartition(-v, n-1)[:n] (/root/reference/code/uncertainty.py:155,
+// 183,213) with the north_star tie rule: order = (utility descending, pair index ascending). A key is
+// (orderable(utility) << 32) | (0xFFFFFFFF - index) (include/alink_math.h), so all keys are distinct
+// and plain descending u64 order IS the rule. Algorithm:
+//   1. radix-select the exact B-th largest key: 6 histogram passes (11/11/10 bits of the utility,
+//      11/11/10 bits of the index part). Each pass = shared-memory histogram per CTA -> global
+//      histogram -> the last CTA to finish (ticket) scans it and narrows (prefix, remaining).
+//   2. compact every key >= that threshold (exactly B keys) with one atomic slot counter.
+//   3. bitonic-sort the B keys descending (one CTA in shared memory up to 4096, global passes above).
+//   4. unpack (index, utility).
+// The key source is either a utility vector + base index (keys built on the fly: 4 B/pair per pass)
+// or raw keys (the cross-shard merge after the all-gather).
+#pragma once
+#include "common.cuh"
+
+struct KeySrc {
+  const float *util;
+  const uint64_t *keys;
+  uint64_t base;
+};
+
+struct SelectState {
+  unsigned long long prefix;     // high bits decided so far (value of key >> hi_shift)
+  unsigned long long remaining;  // rank still to find inside the prefix bucket (1-based)
+  unsigned int ticket;
+  unsigned int out_count;
+  unsigned int hist[2048];
+};
+
+__device__ __forceinline__ uint64_t load_key(const KeySrc &s, int64_t i) {
+  return s.keys ? s.keys[i] : alink_pack_key(__ldg(s.util + i), s.base + (uint64_t)i);
+}
+
+__global__ void select_init_kernel(SelectState *st, unsigned long long B) {
+  for (int i = threadIdx.x; i < 2048; i += blockDim.x) st->hist[i] = 0;
+  if (threadIdx.x == 0) {
+    st->prefix = 0;
+    st->remaining = B;
+    st->ticket = 0;
+    st->out_count = 0;
+  }
+}
+
+// One radix pass over `bits` bits at `shift`. first != 0: no prefix filter.
+__global__ void __launch_bounds__(256) radix_pass_kernel(KeySrc src, int64_t n, int shift, int bits, int first,
+                                                         SelectState *st) {
+  __shared__ unsigned int sh[2048];
+  __shared__ unsigned int part[256];
+  __shared__ bool is_last;
+  const int nb = 1 << bits;
+  const unsigned mask = (unsigned)nb - 1u;
+  for (int i = threadIdx.x; i < nb; i += 256) sh[i] = 0;
+  __syncthreads();
+  const unsigned long long prefix = st->prefix;
+  const int hi = shift + bits;
+  for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < n; i += (int64_t)gridDim.x * 256) {
+    const uint64_t key = load_key(src, i);
+    if (first || (key >> hi) == prefix) atomicAdd(&sh[(unsigned)(key >> shift) & mask], 1u);
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < nb; i += 256)
+    if (sh[i]) atomicAdd(&st->hist[i], sh[i]);
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) is_last = (atomicAdd(&st->ticket, 1u) == gridDim.x - 1);
+  __syncthreads();
+  if (!is_last) return;
+  __threadfence();
+  // ---- last CTA: descending scan of the global histogram
+  for (int i = threadIdx.x; i < nb; i += 256) sh[i] = __ldcg(&st->hist[i]);
+  __syncthreads();
+  const int per = nb / 256;  // 8 or 4 bins per thread; thread t owns bins [nb-1-per*t-(per-1), nb-1-per*t]
+  unsigned int mine = 0;
+  for (int j = 0; j < per; ++j) mine += sh[nb - 1 - per * threadIdx.x - j];
+  part[threadIdx.x] = mine;
+  const unsigned long long remaining = st->remaining;  // read before anyone may overwrite it below
+  __syncthreads();
+  for (int off = 1; off < 256; off <<= 1) {  // inclusive Hillis-Steele scan
+    unsigned int v = threadIdx.x >= off ? part[threadIdx.x - off] : 0u;
+    __syncthreads();
+    part[threadIdx.x] += v;
+    __syncthreads();
+  }
+  const unsigned long long incl = part[threadIdx.x];
+  const unsigned long long before = incl - mine;
+  if (before < remaining && remaining <= incl) {
+    unsigned long long cum = before;
+    for (int j = 0; j < per; ++j) {
+      const int bin = nb - 1 - per * threadIdx.x - j;
+      const unsigned int c = sh[bin];
+      if (cum + c >= remaining) {
+        st->prefix = first ? (unsigned long long)bin : ((prefix << bits) | (unsigned long long)bin);
+        st->remaining = remaining - cum;
+        break;
+      }
+      cum += c;
+    }
+  }
+  for (int i = threadIdx.x; i < 2048; i += 256) st->hist[i] = 0;
+  if (threadIdx.x == 0) st->ticket = 0;
+}
+
+// keys >= threshold (st->prefix after the last pass) -> out (exactly B of them, unordered)
+__global__ void __launch_bounds__(256) compact_kernel(KeySrc src, int64_t n, SelectState *st, uint64_t *out,
+                                                      unsigned int cap) {
+  const unsigned long long thr = st->prefix;
+  for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < n; i += (int64_t)gridDim.x * 256) {
+    const uint64_t key = load_key(src, i);
+    if (key >= thr) {
+      const unsigned int pos = atomicAdd(&st->out_count, 1u);
+      if (pos < cap) out[pos] = key;
+    }
+  }
+}
+
+// one-CTA bitonic sort, descending; npad = power of two <= 4096; entries >= n are padded with 0
+// (0 is below every real key: index 0xFFFFFFFF is excluded by the ABI).
+__global__ void __launch_bounds__(1024) bitonic_smem_kernel(uint64_t *keys, int n, int npad) {
+  extern __shared__ uint64_t sk[];
+  for (int i = threadIdx.x; i < npad; i += blockDim.x) sk[i] = i < n ? keys[i] : 0ull;
+  __syncthreads();
+  for (int k = 2; k <= npad; k <<= 1) {
+    for (int j = k >> 1; j > 0; j >>= 1) {
+      for (int i = threadIdx.x; i < npad; i += blockDim.x) {
+        const int ixj = i ^ j;
+        if (ixj > i) {
+          const uint64_t a = sk[i], b = sk[ixj];
+          const bool desc = (i & k) == 0;
+          if (desc ? (a < b) : (a > b)) {
+            sk[i] = b;
+            sk[ixj] = a;
+          }
+        }
+      }
+      __syncthreads();
+    }
+  }
+  for (int i = threadIdx.x; i < n; i += blockDim.x) keys[i] = sk[i];
+}
+
+__global__ void pad_zero_kernel(uint64_t *keys, int64_t n, int64_t npad) {
+  for (int64_t i = n + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < npad;
+       i += (int64_t)gridDim.x * blockDim.x)
+    keys[i] = 0ull;
+}
+
+__global__ void bitonic_global_step_kernel(uint64_t *keys, int64_t npad, int64_t k, int64_t j) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < npad;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t ixj = i ^ j;
+    if (ixj > i) {
+      const uint64_t a = keys[i], b = keys[ixj];
+      const bool desc = (i & k) == 0;
+      if (desc ? (a < b) : (a > b)) {
+        keys[i] = b;
+        keys[ixj] = a;
+      }
+    }
+  }
+}
+
+__global__ void unpack_keys_kernel(const uint64_t *keys, int64_t B, int64_t *idx, float *util) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < B; i += (int64_t)gridDim.x * blockDim.x) {
+    const uint64_t k = keys[i];
+    if (idx) idx[i] = (int64_t)alink_key_index(k);
+    if (util) util[i] = alink_key_utility(k);
+  }
+}
+
+static inline int64_t next_pow2(int64_t v) {
+  int64_t p = 1;
+  while (p < v) p <<= 1;
+  return p;
+}
+
+// Radix-select the B-th largest key; on return st->prefix holds it (device).
+static int select_threshold(alink_ctx *ctx, const KeySrc &src, int64_t n, int64_t B, SelectState *st) {
+  select_init_kernel<<<1, 256, 0, ctx->stream>>>(st, (unsigned long long)B);
+  ALINK_LAUNCHED(ctx);
+  int64_t blocks = (n + 256 * 8 - 1) / (256 * 8);
+  const int64_t cap = (int64_t)ctx->sm_count * 8;
+  if (blocks > cap) blocks = cap;
+  if (blocks < 1) blocks = 1;
+  static const int shifts[6] = {53, 42, 32, 21, 10, 0};
+  static const int nbits[6] = {11, 11, 10, 11, 11, 10};
+  for (int p = 0; p < 6; ++p) {
+    radix_pass_kernel<<<(unsigned)blocks, 256, 0, ctx->stream>>>(src, n, shifts[p], nbits[p], p == 0, st);
+    ALINK_LAUNCHED(ctx);
+  }
+  return ALINK_OK;
+}
+
+// Top-B keys of the source, sorted descending, into ctx->sel_keys (device). B >= 1, B <= n.
+static int topk_device(alink_ctx *ctx, const KeySrc &src, int64_t n, int64_t B) {
+  ALINK_TRY(dev_reserve(ctx, ctx->sel_state, sizeof(SelectState)));
+  const int64_t npad = next_pow2(B);
+  ALINK_TRY(dev_reserve(ctx, ctx->sel_keys, sizeof(uint64_t) * (size_t)npad));
+  SelectState *st = (SelectState *)ctx->sel_state.p;
+  uint64_t *out = (uint64_t *)ctx->sel_keys.p;
+  ALINK_TRY(select_threshold(ctx, src, n, B, st));
+  int64_t blocks = (n + 256 * 8 - 1) / (256 * 8);
+  const int64_t cap = (int64_t)ctx->sm_count * 8;
+  if (blocks > cap) blocks = cap;
+  if (blocks < 1) blocks = 1;
+  compact_kernel<<<(unsigned)blocks, 256, 0, ctx->stream>>>(src, n, st, out, (unsigned int)B);
+  ALINK_LAUNCHED(ctx);
+  if (npad <= 4096) {
+    const int threads = npad >= 2048 ? 1024 : (npad >= 64 ? (int)(npad / 2) : 32);
+    bitonic_smem_kernel<<<1, threads, sizeof(uint64_t) * (size_t)npad, ctx->stream>>>(out, (int)B, (int)npad);
+    ALINK_LAUNCHED(ctx);
+  } else {
+    if (npad > B) {
+      pad_zero_kernel<<<64, 256, 0, ctx->stream>>>(out, B, npad);
+      ALINK_LAUNCHED(ctx);
+    }
+    int64_t gb = npad / 256;
+    if (gb > cap) gb = cap;
+    for (int64_t k = 2; k <= npad; k <<= 1)
+      for (int64_t j = k >> 1; j > 0; j >>= 1) {
+        bitonic_global_step_kernel<<<(unsigned)gb, 256, 0, ctx->stream>>>(out, npad, k, j);
+        ALINK_LAUNCHED(ctx);
+      }
+  }
+  return ALINK_OK;
+}

@@ -1,0 +1,289 @@
+#!/usr/bin/env python
+"""bench.py — candidate pairs scored+selected per second on N B200s (BASELINE.json metric).
+
+One step = one pass of the hot path (score every pair with the K-learner siamese head -> committee
+reduction -> utility -> top-B, + the cross-shard key merge when N > 1) over one batch of synthetic
+input. Workload at N = 1: BASELINE.json configs[1] (1 M pairs, 512-d ArcFace-shaped table, K = 5,
+top-1000, fp32 bit-exact mode); weak scaling: every rank owns a 1 M-pair shard of an N x 1 M pool.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--mode fp32|bf16] [--impl native|reference]
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+from alink_b200 import synth  # noqa: E402
+
+METRIC = "pairs_scored_selected_per_s"
+UNIT = "pairs/s"
+FLOPS_PER_PAIR = lambda K, D, H1, H2, C: 2.0 * K * (D * H1 + H1 * H2 + H2 * C)
+
+
+def load_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return dict(hbm_gbs=d["hbm_gbs"], tf_burst=d["bf16_tflops"], tf_sustained=d["bf16_tflops_sustained"],
+                    source="measured (MEASURED_PEAKS.json)")
+    return dict(hbm_gbs=6650.0, tf_burst=1590.0, tf_sustained=1400.0, source="fallback (B200_PROFILING.md)")
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index=0):
+        self.rows, self.proc, self.gpu = [], None, gpu_index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            pass
+        sm = [float(r[1]) for r in self.rows if len(r) >= 9 and r[1].replace(".", "").isdigit()]
+        mx = [float(r[2]) for r in self.rows if len(r) >= 9 and r[2].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({n for r in self.rows if len(r) >= 9 for n, v in zip(names, r[5:9]) if v.lower() == "active"})
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+def cpu_oracle_throughput(pool, sample_pairs, threads=0, repeats=1):
+    """Oracle (C restatement, oracle/) on the first `sample_pairs` pairs + top-B; returns pairs/s."""
+    from oracle import oracle_ffi
+    n = min(sample_pairs, pool.N)
+    ia, ib = pool.ia[:n], pool.ib[:n]
+    best = None
+    for _ in range(repeats):
+        t0 = time.perf_counter()
+        out = oracle_ffi.score(pool.table, pool.table, ia, ib, pool.heads, measure=pool.measure,
+                               want_per_learner=False, want_consensus=False, threads=threads)
+        oracle_ffi.topk(out["util"], min(pool.B, n))
+        dt = time.perf_counter() - t0
+        best = dt if best is None else min(best, dt)
+    return n / best, n, best, oracle_ffi.lib().alink_oracle_get_threads()
+
+
+def workload_desc(pool, n_gpus, mode):
+    h = pool.heads
+    return {"workload": f"BASELINE configs[1]: {pool.N:,} pairs/GPU x {n_gpus} GPU, {pool.D}-d ArcFace-shaped table "
+                        f"(M={pool.table.shape[0]:,}), K={h.K} committee {h.D_in}->{h.H1}->{h.H2}->{h.C} {h.act}, "
+                        f"measure={pool.measure}, top-{pool.B}",
+            "pairs_per_gpu": pool.N, "D": pool.D, "K": h.K, "B": pool.B, "compute": mode,
+            "sharding": f"dp{n_gpus} by pair index, all-gather of top-B keys" if n_gpus > 1 else "single GPU",
+            "l2": "inputs larger than L2 (table 410 MB + 8 MB indices + hidden workspace; no explicit flush)"}
+
+
+def run_reference(args, rank):
+    """--impl reference: the reference's CPU path for this step. Keras/TF is not installable here, so
+    this is the oracle port (oracle/alink_oracle.c) with all host threads, on a bounded sample."""
+    if rank != 0:
+        return
+    pool = synth.make_pool(2, N=args.ref_sample, measure=args.measure)
+    times = []
+    threads = 0
+    for i in range(args.warmup + args.steps):
+        v, n, dt, threads = cpu_oracle_throughput(pool, args.ref_sample)
+        if i >= args.warmup:
+            times.append(dt)
+    ms = 1e3 * float(np.mean(times))
+    value = args.ref_sample / (ms / 1e3)
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": dict(workload_desc(pool, 1, "cpu-oracle"),
+                           note="Keras/TF reference unavailable on this box; timed path = C oracle port, "
+                                f"bounded sample of {args.ref_sample:,} pairs per step"),
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port",
+                             "sample": f"first {args.ref_sample:,} pairs of configs[1], all {threads} host threads"},
+            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="native", choices=["native", "reference"])
+    ap.add_argument("--mode", default="fp32", choices=["fp32", "bf16"])
+    ap.add_argument("--measure", default="uncertainty")
+    ap.add_argument("--pairs", type=int, default=1_000_000, help="pairs per GPU")
+    ap.add_argument("--ref-sample", type=int, default=100_000)
+    ap.add_argument("--cpu-sample", type=int, default=100_000)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.impl == "reference":
+        run_reference(args, rank)
+        return
+
+    import torch
+    import torch.distributed as dist
+    from alink_b200 import _ffi
+    from alink_b200.dist import decode_keys, merge_shards
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the product has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    n_gpus = world
+    peaks = load_peaks()
+
+    # ---- synthetic workload (identical table/heads on every rank; each rank draws its own shard of pairs)
+    pool = synth.make_pool(2, N=args.pairs, measure=args.measure)
+    if world > 1:
+        ia, ib, _ = synth.make_pairs(args.pairs, pool.table.shape[0], 50_000, seed=synth.BASE_SEED + 102 + 1000 * rank)
+        pool.ia, pool.ib = ia, ib
+    N, B, K = pool.N, pool.B, pool.heads.K
+    base = rank * N  # global pair index of this shard's first pair
+    mode = _ffi.COMPUTE_ID[args.mode]
+
+    ctx = _ffi.Context(local_rank)
+    ctx.set_stream(torch.cuda.current_stream().cuda_stream)
+    ctx.set_heads(0, pool.heads, compute=mode)
+    table_dev = torch.from_numpy(pool.table).to(dev)
+    ia_dev = torch.from_numpy(pool.ia).to(dev)
+    ib_dev = torch.from_numpy(pool.ib).to(dev)
+    table_pin = torch.from_numpy(pool.table).pin_memory()
+    ia_pin = torch.from_numpy(pool.ia).pin_memory()
+    ib_pin = torch.from_numpy(pool.ib).pin_memory()
+    out = (np.empty((B,), np.int64), np.empty((B,), np.float32), np.empty((B,), np.uint64))
+
+    def step_resident():
+        """inputs already in HBM; result (B keys) read back; cross-shard merge when N > 1."""
+        _, _, keys, t = ctx.query(0, 0, 0, ia_dev, ib_dev, N, args.measure, B, base=base, timing=True, out=out)
+        merged = merge_shards(keys, B, ctx.topk_keys, dist=dist if world > 1 else None, device=dev)
+        return merged, t
+
+    def step_e2e():
+        """host buffers in, host result out: table + indices cross PCIe inside the step."""
+        ctx.set_table(1, table_pin)
+        _, _, keys, t = ctx.query(0, 1, 1, ia_pin.numpy(), ib_pin.numpy(), N, args.measure, B, base=base,
+                                  timing=True, out=out)
+        merged = merge_shards(keys, B, ctx.topk_keys, dist=dist if world > 1 else None, device=dev)
+        return merged, t
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(step_fn, steps, warmup, sample_clocks=False):
+        for _ in range(warmup):
+            step_fn()
+        sampler = ClockSampler(local_rank) if sample_clocks else None
+        barrier()
+        if sampler:
+            sampler.start()
+        l0 = ctx.launches
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        stage = {"ms_score": 0.0, "ms_utility": 0.0, "ms_select": 0.0, "ms_h2d": 0.0, "ms_d2h": 0.0}
+        t0 = time.perf_counter()
+        e0.record()
+        for _ in range(steps):
+            merged, t = step_fn()
+            for k_ in stage:
+                stage[k_] += getattr(t, k_)
+        e1.record()
+        barrier()
+        wall_ms = 1e3 * (time.perf_counter() - t0)
+        dev_ms = e0.elapsed_time(e1)
+        clocks = sampler.stop() if sampler else None
+        launches = ctx.launches - l0
+        ms = torch.tensor([max(wall_ms, dev_ms)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item()) / steps, {k_: v / steps for k_, v in stage.items()}, launches, clocks, merged, dev_ms / steps
+
+    ctx.set_table(0, table_dev)
+    ms_step, stage, launches, clocks, merged, dev_ms = timed(step_resident, args.steps, args.warmup, sample_clocks=True)
+    ms_e2e, stage_e2e, _, _, merged_e2e, _ = timed(step_e2e, max(2, min(args.steps, 3)), 1)
+    assert np.array_equal(merged, merged_e2e), "resident and e2e paths selected different pairs"
+
+    value = n_gpus * N / (ms_step / 1e3)
+    e2e_value = n_gpus * N / (ms_e2e / 1e3)
+    h = pool.heads
+    flops = FLOPS_PER_PAIR(K, h.D_in, h.H1, h.H2, h.C) * N
+    head_ms = stage["ms_score"]
+    achieved_tf = flops / (head_ms / 1e3) / 1e12
+    roofline = {"bound": "tensor", "achieved": achieved_tf, "peak": peaks["tf_sustained"], "unit": "TFLOP/s",
+                "frac": achieved_tf / peaks["tf_sustained"], "traffic": None,
+                "kernel": "siamese head (gather+|a-b| fused layer-1 GEMM, layer-2/3 + softmax)",
+                "flops_per_pair": FLOPS_PER_PAIR(K, h.D_in, h.H1, h.H2, h.C), "launch_ms": head_ms,
+                "peak_source": peaks["source"] + ", sustained bf16 (kernel timed inside a long step)"}
+    if args.mode == "fp32":
+        clk = (clocks or {}).get("sm_mhz") or 1965.0
+        ffma_peak = 2 * 128 * 148 * clk * 1e6 / 1e12
+        roofline["note"] = ("FP32_EXACT is the bit-exact correctness mode: CUDA-core FFMA, not tensor cores; "
+                            f"FFMA peak at the sampled {clk:.0f} MHz = {ffma_peak:.1f} TFLOP/s")
+        roofline["frac_of_ffma_peak"] = achieved_tf / ffma_peak
+    h2d = int(pool.table.nbytes + pool.ia.nbytes + pool.ib.nbytes)
+    d2h = int(B * 8)
+    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": n_gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32" if args.mode == "fp32" else "bf16", "data": "synthetic",
+            "config": workload_desc(pool, n_gpus, "FP32_EXACT" if args.mode == "fp32" else "BF16_TC"),
+            "stage_ms": stage, "device_ms_per_step": dev_ms,
+            "roofline": roofline,
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "ms_per_step": ms_e2e, "stage_ms": stage_e2e,
+                    "call": "alink_set_table(HOST) + alink_query(HOST indices) -> host top-B"},
+            "gpu_launches": launches, "clocks": clocks}
+
+    if rank == 0 and n_gpus == 1 and not args.no_cpu_baseline:
+        # bounded CPU sample: calibrate on 10k pairs, then size the sample for ~10-20 s
+        v0, _, dt0, threads = cpu_oracle_throughput(pool, 10_000)
+        n_s = int(min(pool.N, max(20_000, min(args.cpu_sample * 4, v0 * 12.0))))
+        v, n_s, dt, threads = cpu_oracle_throughput(pool, n_s)
+        line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": threads, "kind": "port",
+                                "sample": f"first {n_s:,} pairs of the same workload, {dt:.1f} s, C oracle "
+                                          f"(oracle/alink_oracle.c) on {threads} host threads; Keras/TF reference "
+                                          "unavailable on this box"}
+    if rank == 0:
+        print(json.dumps(line))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,150 @@
+/* alink_b200.h — C ABI of the B200-native A-LINK query-selection path (libalink_b200.so).
+ *
+ * The reference (iamgroot42/A-LINK, under /root/reference) is pure Python; its "FFI" for this path is the
+ * set of Python call sites below. Each entry point names the reference interface it replaces
+ * (paths relative to /root/reference). The Python shims in alink_b200/*.py keep the reference's
+ * class / function names and bind these symbols with ctypes.
+ *
+ * Conventions
+ *   - extern "C"; plain pointers and sizes; no exceptions or aborts cross the ABI.
+ *   - every call returns ALINK_OK (0) or a negative ALINK_E_*; alink_last_error(ctx) gives the text.
+ *   - `in_space` / `out_space` say where the caller's buffers live: ALINK_HOST (the library copies
+ *     over PCIe on the context's stream) or ALINK_DEVICE (device pointers on the context's GPU, used
+ *     as they are: no copy). The caller owns every buffer it passes.
+ *   - a context owns one GPU, one stream and all scratch memory; it is not thread-safe; distinct
+ *     contexts are independent. Calls are synchronous on return when any output is ALINK_HOST,
+ *     and stream-ordered (use alink_sync) when all outputs are ALINK_DEVICE.
+ *   - there is NO CPU fallback: without a CUDA device alink_create fails with ALINK_E_CUDA.
+ *   - probabilities: per_learner is [N][K][C] fp32 (C = 2 softmax head, C = 1 sigmoid head),
+ *     consensus is [N][C]; utilities are computed on rows widened to 2 columns ([1-p, p] for C = 1,
+ *     code/keras_wrapper.py:263-270).
+ *   - selections are ordered by (utility descending, pair index ascending): modAL's multi_argmax
+ *     (code/uncertainty.py:155) with the north_star tie rule. Reported index = base + position,
+ *     base + N <= 2^32 - 1.
+ */
+#ifndef ALINK_B200_H
+#define ALINK_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ALINK_ABI_VERSION 1
+
+enum { ALINK_OK = 0, ALINK_E_INVALID = -1, ALINK_E_CUDA = -2, ALINK_E_STATE = -3, ALINK_E_NOMEM = -4,
+       ALINK_E_UNSUPPORTED = -5 };
+enum { ALINK_HOST = 0, ALINK_DEVICE = 1 };
+enum { ALINK_F32 = 0, ALINK_BF16 = 1 };
+enum { ALINK_FEAT_ABSDIFF = 0, ALINK_FEAT_ABSDIFF_HADAMARD = 1 };
+/* compute modes: FP32_EXACT = CUDA-core FFMA chains in the oracle's summation order (bit-exact with
+ * oracle/); BF16_TC = tcgen05 bf16 tiles with fp32 accumulation in TMEM (|dp| <= 2e-2). */
+enum { ALINK_COMPUTE_FP32_EXACT = 0, ALINK_COMPUTE_BF16_TC = 1 };
+/* activation and utility ids are shared with the oracle: see include/alink_math.h
+ * (ALINK_ACT_SOFTMAX/SIGMOID, ALINK_UTIL_*). */
+
+#define ALINK_MAX_GROUPS 4  /* head groups per context: 0 = M1 committee, 1 = M2 (code/ALINK.py:96-108) */
+#define ALINK_MAX_SLOTS 8   /* embedding-table slots */
+
+typedef struct alink_ctx alink_ctx;
+
+/* device-side milliseconds (CUDA events on the context stream) of the last alink_query */
+typedef struct alink_timing {
+  float ms_h2d;      /* host->device copies of this call's inputs (0 when inputs are ALINK_DEVICE) */
+  float ms_score;    /* gather + head kernels */
+  float ms_utility;  /* K-learner reduction / measure */
+  float ms_select;   /* top-B */
+  float ms_d2h;      /* device->host copy of the results */
+  float ms_total;
+  int64_t launches;  /* kernels launched by this call */
+} alink_timing;
+
+int alink_abi_version(void);
+
+/* Context on CUDA device `device`. Replaces the reference's global TF session
+ * (code/ALINK.py:22-25: ConfigProto(allow_growth) + K.set_session). */
+int alink_create(alink_ctx **out, int device, unsigned flags);
+int alink_destroy(alink_ctx *ctx);
+const char *alink_last_error(const alink_ctx *ctx);
+int alink_sync(alink_ctx *ctx);
+/* Launch on the caller's CUDA stream (a cudaStream_t, e.g. torch.cuda.current_stream().cuda_stream)
+ * instead of the context's own; NULL restores the private stream. Lets the host framework order its
+ * own work and CUDA events with the library's kernels. */
+int alink_set_stream(alink_ctx *ctx, void *cuda_stream);
+/* total kernels launched by this context so far (bench.py's gpu_launches) */
+int64_t alink_launch_count(const alink_ctx *ctx);
+/* pinned host memory for ALINK_HOST buffers that should move at full PCIe rate */
+int alink_host_alloc(void **out, uint64_t bytes);
+int alink_host_free(void *p);
+
+/* Install the K heads of one group. Replaces SiameseNetwork.__init__ + maybeLoadFromMemory
+ * (code/siamese.py:20-35,114-119; code/siamese3.py:15-28) for each learner of Bagging(models, ...)
+ * (code/committee.py:7, code/ALINK.py:90-97). Weights are Keras Dense layout: W (in,out) row-major
+ * fp32, b (out,); W1[k] is (D_in,H1), W2[k] (H1,H2), W3[k] (H2,C). D_in = D (ABSDIFF) or 2*D
+ * (ABSDIFF_HADAMARD). Host pointers; copied. */
+int alink_set_heads(alink_ctx *ctx, int group, int K, int D_in, int H1, int H2, int C, int out_act,
+                    int feat_mode, const float *const *W1, const float *const *b1,
+                    const float *const *W2, const float *const *b2, const float *const *W3,
+                    const float *const *b3, int compute);
+
+/* Install an embedding table (M rows x D) in a slot. Replaces the materialised feature arrays the
+ * reference builds with Python loops (code/readDFW.py:222-244, utilities/generateMatrixDFW.py:25-33).
+ * space = ALINK_HOST: copied to the GPU; ALINK_DEVICE: borrowed (caller keeps it alive). */
+int alink_set_table(alink_ctx *ctx, int slot, const void *emb, int64_t M, int D, int dtype, int space);
+
+/* Score N indexed pairs (row ia[n] of slot_a vs row ib[n] of slot_b) with every learner of `group`.
+ * Replaces SiameseNetwork.predict (code/siamese.py:130-131) called per learner by Bagging.predict
+ * (code/committee.py:13-20) / Committee.vote_proba (code/learners.py:383-416).
+ * ia/ib may be NULL = identity (pair n = row n of both tables). Outputs may be NULL; the scores also
+ * stay on the device inside the context for alink_utility / alink_select_topk. */
+int alink_score_indexed(alink_ctx *ctx, int group, int slot_a, int slot_b, const int32_t *ia,
+                        const int32_t *ib, int64_t N, int in_space, float *per_learner,
+                        float *consensus, int out_space);
+
+/* Same, on materialised [X_left, X_right] (N x D fp32 each): the reference's own calling convention
+ * (code/ALINK.py:160,170; code/existing_al.py:108). Uses slots ALINK_MAX_SLOTS-2/-1 as staging. */
+int alink_score_dense(alink_ctx *ctx, int group, const float *XL, const float *XR, int64_t N, int D,
+                      int in_space, float *per_learner, float *consensus, int out_space);
+
+/* Utility of every scored pair. Replaces classifier_uncertainty / classifier_margin /
+ * classifier_entropy (code/uncertainty.py:63-130) and modAL's vote_entropy / consensus_entropy /
+ * KL_max_disagreement (imported at code/learners.py:12). util (N) may be NULL (kept on device). */
+int alink_utility(alink_ctx *ctx, int measure, float *util, int out_space);
+
+/* Utility from caller-held probabilities ([N][K][C]); same measures. consensus (N*C) may be NULL. */
+int alink_utility_from_proba(alink_ctx *ctx, const float *per_learner, int64_t N, int K, int C,
+                             int measure, int in_space, float *util, float *consensus, int out_space);
+
+/* Top-B of the context's utility vector. Replaces modAL multi_argmax (code/uncertainty.py:155,183,213).
+ * idx_out (B int64), util_out (B fp32), keys_out (B packed u64 keys for cross-shard merging): any may
+ * be NULL. */
+int alink_select_topk(alink_ctx *ctx, int64_t B, int64_t base, int64_t *idx_out, float *util_out,
+                      uint64_t *keys_out, int out_space);
+
+/* Top-B of a caller-held utility vector (N fp32). */
+int alink_topk_values(alink_ctx *ctx, const float *util, int64_t N, int64_t base, int64_t B, int in_space,
+                      int64_t *idx_out, float *util_out, uint64_t *keys_out, int out_space);
+
+/* Top-B of n packed keys (the merge after the per-shard all-gather). keys_out: B keys, descending. */
+int alink_topk_keys(alink_ctx *ctx, const uint64_t *keys, int64_t n, int64_t B, int in_space,
+                    uint64_t *keys_out, int out_space);
+
+/* The whole step: score -> K-learner reduce -> utility -> top-B. Replaces learner.query(X, n_instances)
+ * (code/base.py:179-195 -> code/uncertainty.py:133-159) and the Bagging + selection part of the
+ * A-LINK loop (code/ALINK.py:160). timing may be NULL. */
+int alink_query(alink_ctx *ctx, int group, int slot_a, int slot_b, const int32_t *ia, const int32_t *ib,
+                int64_t N, int in_space, int measure, int64_t B, int64_t base, int64_t *idx_out,
+                float *util_out, uint64_t *keys_out, int out_space, alink_timing *timing);
+
+/* A-LINK disparity selector on column-extracted scores (code/ALINK.py:170-201):
+ * p2 (T*N), p1 (N), y (N fp32 pseudo-oracle labels, may be NULL). idx_out: capacity N int64,
+ * ascending pair indices; n_out / active_count: host scalars. */
+int alink_disparity_select(alink_ctx *ctx, const float *p2, const float *p1, int64_t N, int T,
+                           double ratio, double eps, int blind, const float *y, int in_space,
+                           int64_t *idx_out, int out_space, int64_t *n_out, int64_t *active_count);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ALINK_B200_H */

@@ -1,0 +1,205 @@
+"""ref_numpy.py — line-by-line numpy/scipy transcription of the reference's query-selection path.
+
+TEST INFRASTRUCTURE ONLY (see oracle/alink_oracle.c header): imported by tests/, bench.py's CPU
+baseline legs and tests/golden/make_golden.py; never by the product package.
+
+It is deliberately *independent* of include/alink_math.h: it uses numpy's BLAS matmul, np.exp,
+scipy.stats.entropy and np.argpartition exactly where the reference (Keras 2.1.2 / TF 1.15 /
+numpy / scipy / modAL) does, so agreement between this file and the C oracle (<= 1e-6 on
+probabilities) is the pin that stands in for the un-installable Keras runtime.
+
+Each function cites the reference line(s) it transcribes (paths relative to /root/reference).
+"""
+from __future__ import annotations
+
+import numpy as np
+from scipy.stats import entropy as _scipy_entropy
+
+
+# --------------------------------------------------------------------------- head (L2)
+def head_forward(XL, XR, W1, b1, W2, b2, W3, b3, act="softmax", feat_mode=0, batch_size=1024,
+                 dtype=np.float32):
+    """code/siamese.py:24-33 (softmax-2) / code/siamese3.py:18-26 (sigmoid-1); batched like
+    `predict(..., batch_size=1024)` (code/siamese.py:130-131)."""
+    XL = np.asarray(XL, dtype=dtype)
+    XR = np.asarray(XR, dtype=dtype)
+    W1, b1, W2, b2, W3, b3 = (np.asarray(a, dtype=dtype) for a in (W1, b1, W2, b2, W3, b3))
+    outs = []
+    for s in range(0, len(XL), batch_size):
+        l, r = XL[s:s + batch_size], XR[s:s + batch_size]
+        x = np.abs(l - r)                                   # siamese.py:27-28  K.abs(l - r)
+        if feat_mode:
+            x = np.concatenate([x, l * r], axis=1)          # north_star opt-in feature (not in reference)
+        h1 = np.maximum(x @ W1 + b1, 0)                     # siamese.py:29  Dense(512, relu)
+        h2 = np.maximum(h1 @ W2 + b2, 0)                    # siamese.py:30  Dense(64, relu)
+        z = h2 @ W3 + b3                                    # siamese.py:31  Dense(2) / siamese3.py:25 Dense(1)
+        if act == "softmax":
+            e = np.exp(z - z.max(axis=1, keepdims=True))    # siamese.py:32  softmax
+            p = e / e.sum(axis=1, keepdims=True)
+        else:
+            p = 1.0 / (1.0 + np.exp(-z))                    # siamese3.py:25 sigmoid
+        outs.append(p.astype(dtype))
+    if not outs:
+        return np.zeros((0, W3.shape[1]), dtype=dtype)
+    return np.concatenate(outs, axis=0)
+
+
+def bagging_predict(preds):
+    """code/committee.py:13-20: np.sum(np.array(predictions), axis=0) / len(models)."""
+    return np.array(np.sum(np.array(preds), axis=0) / len(preds))
+
+
+def widen(p):
+    """code/keras_wrapper.py:263-270: (N,1) -> hstack([1-p, p])."""
+    p = np.asarray(p)
+    if p.shape[1] == 1:
+        p = np.hstack([1 - p, p])
+    return p
+
+
+def hard_labels(p):
+    """code/keras_wrapper.py:235-242: argmax if >1 column else p > 0.5."""
+    p = np.asarray(p)
+    if p.shape[-1] > 1:
+        return p.argmax(axis=-1)
+    return (p > 0.5).astype("int32").reshape(-1)
+
+
+def vote_proba(per_learner_probs):
+    """code/learners.py:383-416: (N, K, C) float64 container of per-learner predict_proba."""
+    K = len(per_learner_probs)
+    P0 = widen(per_learner_probs[0])
+    out = np.zeros(shape=(P0.shape[0], K, P0.shape[1]))
+    for k, p in enumerate(per_learner_probs):
+        out[:, k, :] = widen(p)
+    return out
+
+
+def committee_predict_proba(per_learner_probs):
+    """code/learners.py:334-345: np.mean(vote_proba, axis=1)."""
+    return np.mean(vote_proba(per_learner_probs), axis=1)
+
+
+def vote(per_learner_probs):
+    """code/learners.py:365-381: (N, K) float64 of hard labels."""
+    K = len(per_learner_probs)
+    N = len(per_learner_probs[0])
+    out = np.zeros(shape=(N, K))
+    for k, p in enumerate(per_learner_probs):
+        out[:, k] = hard_labels(p)
+    return out
+
+
+# --------------------------------------------------------------------------- measures (L4)
+def proba_uncertainty(proba):
+    """code/uncertainty.py:26,82."""
+    return 1 - np.max(proba, axis=1)
+
+
+def proba_margin(proba):
+    """code/uncertainty.py:40-46,104-110."""
+    if proba.shape[1] == 1:
+        return np.zeros(shape=len(proba))
+    part = np.partition(-proba, 1, axis=1)
+    return -part[:, 0] + part[:, 1]
+
+
+def proba_entropy(proba):
+    """code/uncertainty.py:60,130."""
+    return np.transpose(_scipy_entropy(np.transpose(proba)))
+
+
+def vote_entropy(per_learner_probs, n_classes=2):
+    """modAL.disagreement.vote_entropy [external; SURVEY App. B]: entropy of vote fractions."""
+    votes = vote(per_learner_probs)
+    K = votes.shape[1]
+    p_vote = np.zeros(shape=(votes.shape[0], n_classes))
+    for c in range(n_classes):
+        p_vote[:, c] = (votes == c).sum(axis=1) / K
+    return _scipy_entropy(p_vote, axis=1)
+
+
+def consensus_entropy(per_learner_probs):
+    """modAL.disagreement.consensus_entropy [external]: entropy(transpose(predict_proba))."""
+    return np.transpose(_scipy_entropy(np.transpose(committee_predict_proba(per_learner_probs))))
+
+
+def kl_max_disagreement(per_learner_probs):
+    """modAL.disagreement.KL_max_disagreement [external]: max_k KL(p_k || consensus)."""
+    P = vote_proba(per_learner_probs)
+    cons = np.mean(P, axis=1)
+    K = P.shape[1]
+    kl = np.zeros((P.shape[0], K))
+    for k in range(K):
+        kl[:, k] = _scipy_entropy(np.transpose(P[:, k, :]), qk=np.transpose(cons))
+    return np.max(kl, axis=1)
+
+
+MEASURES = ("uncertainty", "neg_margin", "entropy", "vote_entropy", "consensus_entropy", "kl_max")
+
+
+def utility(measure, per_learner_probs):
+    """Utility vector as the reference's samplers rank it (largest first)."""
+    if measure == "vote_entropy":
+        return vote_entropy(per_learner_probs)
+    if measure == "consensus_entropy":
+        return consensus_entropy(per_learner_probs)
+    if measure == "kl_max":
+        return kl_max_disagreement(per_learner_probs)
+    # single-estimator measures act on predict_proba of the estimator handed to the sampler; for a
+    # Bagging/Committee that is the mean over learners.
+    if len(per_learner_probs) == 1:
+        proba = widen(per_learner_probs[0])
+    else:
+        proba = widen(bagging_predict([widen(p) for p in per_learner_probs]))
+    if measure == "uncertainty":
+        return proba_uncertainty(proba)
+    if measure == "neg_margin":
+        return -proba_margin(proba)                         # uncertainty.py:183 ranks -margin
+    if measure == "entropy":
+        return proba_entropy(proba)
+    raise ValueError(measure)
+
+
+# --------------------------------------------------------------------------- selection
+def multi_argmax(values, n_instances=1):
+    """modAL.utils.selection.multi_argmax [external]: argpartition(-values, n-1)[:n] (unordered)."""
+    assert n_instances <= values.shape[0]
+    return np.argpartition(-values, n_instances - 1, axis=0)[:n_instances]
+
+
+def topk_lowest_index(values, n_instances):
+    """The build's tie rule (north_star): n largest by (value desc, index asc), in that order."""
+    values = np.asarray(values)
+    order = np.lexsort((np.arange(len(values)), -values.astype(np.float64)))
+    return order[:n_instances]
+
+
+# --------------------------------------------------------------------------- A-LINK rule
+def disparity_select(p2, p1, ratio=0.25, eps=0.05, blind=False, y=None):
+    """code/ALINK.py:170-201 on column-extracted scores. p2: (T, N); p1: (N,). Returns
+    (sorted query indices, ACTIVE_COUNT increment). Ties inside argsort follow the build's
+    lowest-index rule (numpy's default quicksort leaves them unspecified)."""
+    p2 = np.asarray(p2)
+    p1 = np.asarray(p1)
+    T, N = p2.shape
+    sets = []
+    for t in range(T):
+        if blind:
+            idx = [j for j in range(N) if (p2[t, j] >= 0.5) != (p1[j] >= 0.5)]      # ALINK.py:177-179
+        else:
+            disparities = -np.absolute(p2[t] - p1)                                   # ALINK.py:181
+            order = np.lexsort((np.arange(N), disparities.astype(np.float64)))
+            idx = order[:int(N * ratio)]                                             # ALINK.py:183
+        sets.append(set(int(j) for j in idx))
+    all_noise_works = sets[0]
+    for s in sets[1:]:
+        all_noise_works = all_noise_works & s                                        # ALINK.py:186-188
+    query, active = [], 0
+    for j in sorted(all_noise_works):
+        ep = p1[j]
+        if ep <= 0.5 - eps or ep >= 0.5 + eps:                                       # ALINK.py:195
+            active += 1                                                              # ALINK.py:198
+            if y is None or ((ep >= 0.5) == (y[j] >= 0.5)):                          # ALINK.py:196-200
+                query.append(j)
+    return np.array(query, dtype=np.int64), active

@@ -1,0 +1,55 @@
+"""The C-ABI library loads and exports every symbol include/alink_b200.h declares (no compute here)."""
+import ctypes
+import os
+import re
+
+import pytest
+
+from alink_b200 import _ffi
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _declared_symbols():
+    src = open(os.path.join(ROOT, "include", "alink_b200.h")).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(alink_[a-z0-9_]+)\s*\(", src)))
+
+
+def test_library_exports_every_declared_symbol():
+    lib = _ffi.load()
+    names = _declared_symbols()
+    assert len(names) >= 19
+    for n in names:
+        assert hasattr(lib, n), f"libalink_b200.so does not export {n}"
+    assert sorted(_ffi.SYMBOLS) == names, "alink_b200/_ffi.py binds a different symbol set than the header declares"
+
+
+def test_abi_version():
+    assert _ffi.load().alink_abi_version() == 1
+
+
+def test_no_cpu_fallback_without_gpu():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    with pytest.raises(_ffi.AlinkError, match="no CPU fallback"):
+        _ffi.Context(0)
+
+
+def test_product_never_imports_oracle():
+    """The oracle is test infrastructure: nothing under alink_b200/ may import, link or execute it."""
+    pkg = os.path.join(ROOT, "alink_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h", "Makefile")):
+                txt = open(os.path.join(dirpath, f)).read()
+                assert "oracle_ffi" not in txt and "libalink_oracle" not in txt and "ref_numpy" not in txt, f
+                assert not re.search(r"^\s*(from|import)\s+oracle", txt, flags=re.M), f
+
+
+def test_sass_is_sm100a():
+    so = _ffi.SO_PATH
+    import subprocess
+    out = subprocess.run(["cuobjdump", "-lelf", so], capture_output=True, text=True).stdout
+    assert "sm_100a" in out
