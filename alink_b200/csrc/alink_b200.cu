@@ -165,8 +165,9 @@ int alink_set_table(alink_ctx *ctx, int slot, const void *emb, int64_t M, int D,
 
 // ------------------------------------------------------------------------------------------ scoring
 // ia/ib are device pointers (or null = identity). Fills ctx->probs [N][K][C].
+// fuse_measure >= 0: a compute mode that can reduce the K learners in its epilogue also fills ctx->util.
 static int score_impl(alink_ctx *ctx, int group, const Table &A, const Table &Bt, const int32_t *ia,
-                      const int32_t *ib, int64_t N) {
+                      const int32_t *ib, int64_t N, int fuse_measure = -1) {
   if (group < 0 || group >= ALINK_MAX_GROUPS || !ctx->groups[group].set)
     return alink_fail(ctx, ALINK_E_STATE, "head group %d not set (alink_set_heads)", group);
   const HeadGroup &g = ctx->groups[group];
@@ -180,8 +181,19 @@ static int score_impl(alink_ctx *ctx, int group, const Table &A, const Table &Bt
   ctx->N = N; ctx->sK = g.K; ctx->sC = g.C; ctx->util_valid = false;
   ALINK_TRY(dev_reserve(ctx, ctx->probs, sizeof(float) * (size_t)(N ? N : 1) * g.K * g.C));
   if (N == 0) return ALINK_OK;
-  if (g.compute == ALINK_COMPUTE_BF16_TC)
-    return tc_score(ctx, g, A, Bt, ia, ib, N, (float *)ctx->probs.p);
+  if (g.compute == ALINK_COMPUTE_BF16_TC) {
+    float *util = nullptr;
+    if (fuse_measure >= 0) {
+      ALINK_TRY(dev_reserve(ctx, ctx->util, sizeof(float) * (size_t)N));
+      util = (float *)ctx->util.p;
+    }
+    ALINK_TRY(tc_score(ctx, g, A, Bt, ia, ib, N, (float *)ctx->probs.p, util, fuse_measure >= 0 ? fuse_measure : 0));
+    if (util) {
+      ctx->util_valid = true;
+      ctx->util_measure = fuse_measure;
+    }
+    return ALINK_OK;
+  }
   if (A.dtype != ALINK_F32)
     return alink_fail(ctx, ALINK_E_UNSUPPORTED, "FP32_EXACT mode needs fp32 tables");
   const int64_t chunk = 65536;
@@ -253,6 +265,7 @@ static int utility_impl(alink_ctx *ctx, int measure) {
   ALINK_TRY(launch_utility(ctx, (const float *)ctx->probs.p, ctx->N, ctx->sK, ctx->sC, measure,
                            (float *)ctx->util.p, nullptr));
   ctx->util_valid = true;
+  ctx->util_measure = measure;
   return ALINK_OK;
 }
 
@@ -377,9 +390,9 @@ int alink_query(alink_ctx *ctx, int group, int slot_a, int slot_b, const int32_t
   ALINK_TRY(stage_in(ctx, ib, sizeof(int32_t) * (size_t)N, in_space, ctx->idx_b, &dib));
   if (timing) ALINK_CUDA(ctx, cudaEventRecord(e[1], ctx->stream));
   ALINK_TRY(score_impl(ctx, group, ctx->tables[slot_a], ctx->tables[slot_b], (const int32_t *)dia,
-                       (const int32_t *)dib, N));
+                       (const int32_t *)dib, N, measure));
   if (timing) ALINK_CUDA(ctx, cudaEventRecord(e[2], ctx->stream));
-  ALINK_TRY(utility_impl(ctx, measure));
+  if (!(ctx->util_valid && ctx->util_measure == measure)) ALINK_TRY(utility_impl(ctx, measure));
   if (timing) ALINK_CUDA(ctx, cudaEventRecord(e[3], ctx->stream));
   if (B > 0) {
     KeySrc src{(const float *)ctx->util.p, nullptr, (uint64_t)base};

@@ -57,6 +57,7 @@ struct alink_ctx {
   DevBuf cons;           // [N][C] fp32
   DevBuf util;           // [N] fp32
   bool util_valid = false;
+  int util_measure = -1;  // measure ctx->util holds
   // select scratch
   DevBuf sel_state, sel_keys, sel_idx, sel_util, sel_in;
   DevBuf misc0, misc1, misc2, misc3;

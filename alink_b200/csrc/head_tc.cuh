@@ -1,12 +1,459 @@
-// head_tc.cuh — BF16_TC siamese head on tcgen05 tensor cores (placeholder until the UMMA path lands).
+// head_tc.cuh — BF16_TC siamese head on the 5th-gen tensor cores (tcgen05, accumulators in TMEM).
+//
+// Replaces, for all K learners of a committee at once, the Keras graph of
+// /root/reference/code/siamese.py:24-33 (|l-r| -> Dense(512,relu) -> Dense(64,relu) -> Dense(2)+softmax),
+// siamese3.py:18-26 (-> Dense(1,sigmoid)), the per-learner loop + mean of Bagging.predict
+// (code/committee.py:13-20) and the utility measures of code/uncertainty.py:63-130, in ONE persistent
+// kernel: index-driven gather -> |a-b| (bf16, swizzled shared memory) -> tcgen05 layer 1 -> fused
+// bias/relu/bf16 epilogue -> tcgen05 layer 2 -> fused layer 3 + softmax/sigmoid + K-learner
+// consensus/vote/entropy epilogue -> probabilities [N][K][C] and the utility [N].
+//
+// One CTA per SM, one 128-pair tile at a time, 512 threads in five roles:
+//   warp 0     : weight producer — streams pre-swizzled bf16 weight images (16 KB per stage) from L2 with
+//                cp.async.bulk (TMA bulk copy) into a 4-stage ring; completion on mbarriers.
+//   warp 1     : MMA issuer — one thread issues every tcgen05.mma (M=128, N=128 layer 1 / N=H2 layer 2,
+//                K=16), commits completion to mbarriers (tcgen05.commit).
+//   warp 2     : TMEM allocator.   warp 3 : L2 prefetcher of the NEXT tile's table rows.
+//   warps 4-7  : epilogue — tcgen05.ld accumulator -> +bias, relu -> bf16 -> swizzled shared (A operand of
+//                layer 2); after a learner's last chunk: layer-2 accumulator -> +bias, relu -> Dense(H2,C)
+//                in fp32 -> activation (include/alink_math.h, same arithmetic as the oracle) -> registers;
+//                after the last learner: Bagging mean + utility -> global.
+//   warps 8-15 : gather producers — rows ia[n] / ib[n] of the embedding tables with 128-bit loads,
+//                |a-b| (or a*b for the opt-in Hadamard half), bf16, 128B-swizzled K-major tile X.
+// The feature tile X (128 x D_in bf16, <= 128 KB) is learner-independent: it stays resident in shared
+// memory while the K learners x (H1/128) weight chunks stream past it. Work items q = (tile, learner,
+// chunk) are software-pipelined on the tensor pipe as L1(q), L2(q-1), with two layer-1 accumulators in
+// TMEM (2 x 128 columns) + one layer-2 accumulator (H2 columns).
+//
+// Rooflines: tensor-bound — 2*K*(D_in*H1 + H1*H2) flop per pair on the tensor pipe; the weight stream is
+// K*(D_in*H1 + H1*H2)*2 bytes of L2->SMEM traffic per tile; HBM: 2*D*s + 8 bytes gathered per pair +
+// 4*K*C + 4 written.
 #pragma once
 #include "common.cuh"
-static int tc_prepare_heads(alink_ctx *ctx, HeadGroup &g) {
-  (void)g;
-  return alink_fail(ctx, ALINK_E_UNSUPPORTED, "BF16_TC mode not built yet");
+#include "ptx.cuh"
+
+namespace tc {
+
+constexpr int TILE_M = 128;
+constexpr int CHUNK_N = 128;
+constexpr int KBLK = 64;            // bf16 per 128-byte swizzle row
+constexpr int STAGE_BYTES = 16384;  // one [128 x 64] bf16 tile
+constexpr int NSTAGE = 4;
+constexpr int MAX_KB = 8;           // D_in <= 512
+constexpr int NTHREADS = 512;
+
+// dynamic shared memory map (bytes)
+constexpr uint32_t XOFF = 0;                                  // feature tile: MAX_KB x 16 KB
+constexpr uint32_t HOFF = XOFF + MAX_KB * STAGE_BYTES;        // hidden-1 chunk: 2 x 16 KB
+constexpr uint32_t ROFF = HOFF + 2 * STAGE_BYTES;             // weight ring: NSTAGE x 16 KB
+constexpr uint32_t POFF = ROFF + NSTAGE * STAGE_BYTES;        // staged biases / last layer
+constexpr uint32_t P_B1 = POFF;                               // float [2][128]
+constexpr uint32_t P_B2 = P_B1 + 2 * 128 * 4;                 // float [2][64]
+constexpr uint32_t P_W3 = P_B2 + 2 * 64 * 4;                  // float [2][128]
+constexpr uint32_t P_B3 = P_W3 + 2 * 128 * 4;                 // float [2][2]
+constexpr uint32_t BOFF = P_B3 + 16;                          // mbarriers
+enum { W_FULL = 0, W_EMPTY = 4, X_FULL = 8, X_EMPTY = 16, A1_FULL = 24, A1_EMPTY = 26, H1_FULL = 28, H1_EMPTY = 29,
+       A2_FULL = 30, A2_EMPTY = 31, NBARS = 32 };
+constexpr uint32_t TOFF = BOFF + NBARS * 8;                   // TMEM base address
+constexpr uint32_t SMEM_BYTES = TOFF + 16;
+static_assert(SMEM_BYTES <= 232448, "exceeds the 227 KB per-CTA shared memory limit");
+static_assert(BOFF % 8 == 0, "mbarriers need 8-byte alignment");
+
+constexpr uint32_t TMEM_COLS = 512;
+constexpr uint32_t ACC2_COL = 256;
+
+struct Args {
+  const void *ta, *tb;       // embedding tables (fp32 or bf16), D columns
+  const int32_t *ia, *ib;    // pair -> row (nullptr = identity)
+  int64_t N;
+  int D, nkb, hadamard;
+  int K, nc, H1, H2, C, act, measure;
+  const uint8_t *w1img;      // [K][nc][nkb] blocks of 16 KB: [128 n x 64 k] bf16, SWIZZLE_128B image
+  const uint8_t *w2img;      // [K][nc] blocks of 2*H2*128 B: 2 x [H2 n x 64 k]
+  const float *b1, *b2, *W3, *b3;  // fp32 [K][H1], [K][H2], [K][H2][C], [K][C]
+  float *probs;              // [N][K][C] or nullptr
+  float *util;               // [N] or nullptr
+  int ntiles;
+};
+
+__device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
+  __nv_bfloat162 h = __floats2bfloat162_rn(lo, hi);
+  return *reinterpret_cast<uint32_t *>(&h);
 }
+__device__ __forceinline__ void sts128(uint32_t addr, uint32_t x, uint32_t y, uint32_t z, uint32_t w) {
+  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(x), "r"(y), "r"(z), "r"(w) : "memory");
+}
+__device__ __forceinline__ void sts64(uint32_t addr, uint32_t x, uint32_t y) {
+  asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(addr), "r"(x), "r"(y) : "memory");
+}
+__device__ __forceinline__ float4 ldg_f4(const float *p) {
+  float4 v;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+               : "l"(p));
+  return v;
+}
+__device__ __forceinline__ float4 ldg_bf4(const __nv_bfloat16 *p) {  // 4 bf16 -> 4 fp32
+  uint32_t lo, hi;
+  asm volatile("ld.global.nc.L1::no_allocate.v2.b32 {%0, %1}, [%2];" : "=r"(lo), "=r"(hi) : "l"(p));
+  float4 v;
+  v.x = __uint_as_float(lo << 16);
+  v.y = __uint_as_float(lo & 0xFFFF0000u);
+  v.z = __uint_as_float(hi << 16);
+  v.w = __uint_as_float(hi & 0xFFFF0000u);
+  return v;
+}
+
+template <bool TAB_BF16>
+__global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  const uint32_t sbase = ptx::smem_u32(smem);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  auto bar = [&](int i) -> uint32_t { return sbase + BOFF + 8u * (uint32_t)i; };
+
+  if (tid == 0) {
+    if (sbase & 1023u) {
+      printf("alink_b200: dynamic shared memory base 0x%x is not 1024-byte aligned\n", sbase);
+      __trap();
+    }
+    for (int s = 0; s < NSTAGE; ++s) {
+      ptx::mbar_init(bar(W_FULL + s), 1);
+      ptx::mbar_init(bar(W_EMPTY + s), 1);
+    }
+    for (int k = 0; k < MAX_KB; ++k) {
+      ptx::mbar_init(bar(X_FULL + k), 256);
+      ptx::mbar_init(bar(X_EMPTY + k), 1);
+    }
+    for (int b = 0; b < 2; ++b) {
+      ptx::mbar_init(bar(A1_FULL + b), 1);
+      ptx::mbar_init(bar(A1_EMPTY + b), 128);
+    }
+    ptx::mbar_init(bar(H1_FULL), 128);
+    ptx::mbar_init(bar(H1_EMPTY), 1);
+    ptx::mbar_init(bar(A2_FULL), 1);
+    ptx::mbar_init(bar(A2_EMPTY), 128);
+    ptx::fence_barrier_init();
+  }
+  if (warp == 2) ptx::tmem_alloc(sbase + TOFF, TMEM_COLS);
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem = *reinterpret_cast<volatile uint32_t *>(smem + TOFF);
+
+  const uint32_t G = (uint32_t)(a.K * a.nc);  // work items per tile
+  const uint32_t T = (uint32_t)a.ntiles > blockIdx.x ? ((uint32_t)a.ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0u;
+  const uint32_t Q = T * G;
+  const uint32_t nkb = (uint32_t)a.nkb;
+  const uint32_t l2bytes = 2u * (uint32_t)a.H2 * 128u;
+
+  if (warp == 0) {
+    // ------------------------------------------------------------------ weight producer (TMA bulk)
+    if (lane == 0) {
+      uint32_t j = 0;
+      for (uint32_t q = 0; q <= Q; ++q) {
+        if (q < Q) {
+          const uint8_t *src = a.w1img + (size_t)(q % G) * nkb * STAGE_BYTES;
+          for (uint32_t kb = 0; kb < nkb; ++kb, ++j) {
+            const uint32_t s = j % NSTAGE, r = j / NSTAGE;
+            ptx::mbar_wait(bar(W_EMPTY + s), (r & 1u) ^ 1u);
+            ptx::mbar_expect_tx(bar(W_FULL + s), STAGE_BYTES);
+            ptx::bulk_g2s(sbase + ROFF + s * STAGE_BYTES, src + (size_t)kb * STAGE_BYTES, STAGE_BYTES, bar(W_FULL + s));
+          }
+        }
+        if (q >= 1) {
+          const uint8_t *src = a.w2img + (size_t)((q - 1) % G) * l2bytes;
+          const uint32_t s = j % NSTAGE, r = j / NSTAGE;
+          ptx::mbar_wait(bar(W_EMPTY + s), (r & 1u) ^ 1u);
+          ptx::mbar_expect_tx(bar(W_FULL + s), l2bytes);
+          ptx::bulk_g2s(sbase + ROFF + s * STAGE_BYTES, src, l2bytes, bar(W_FULL + s));
+          ++j;
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------------------------------------------ MMA issuer
+    if (lane == 0) {
+      const uint32_t idesc1 = ptx::umma_idesc_bf16(TILE_M, CHUNK_N);
+      const uint32_t idesc2 = ptx::umma_idesc_bf16(TILE_M, a.H2);
+      const uint32_t kb2_step = ((uint32_t)a.H2 * 128u) >> 4;  // layer-2 B sub-block stride, 16-byte units
+      uint32_t j = 0;
+      for (uint32_t q = 0; q <= Q; ++q) {
+        if (q < Q) {
+          const uint32_t i = q / G, g = q % G, b = q & 1u, u = q >> 1;
+          ptx::mbar_wait(bar(A1_EMPTY + b), (u & 1u) ^ 1u);
+          const uint32_t d_tmem = tmem + b * CHUNK_N;
+          for (uint32_t kb = 0; kb < nkb; ++kb, ++j) {
+            if (g == 0) ptx::mbar_wait(bar(X_FULL + kb), i & 1u);
+            const uint32_t s = j % NSTAGE, r = j / NSTAGE;
+            ptx::mbar_wait(bar(W_FULL + s), r & 1u);
+            ptx::tc_fence_after();
+            const uint64_t ad = ptx::umma_desc_sw128(sbase + XOFF + kb * STAGE_BYTES);
+            const uint64_t bd = ptx::umma_desc_sw128(sbase + ROFF + s * STAGE_BYTES);
+#pragma unroll
+            for (uint32_t k = 0; k < 4; ++k) ptx::umma_bf16(d_tmem, ad + 2 * k, bd + 2 * k, idesc1, (kb | k) != 0u);
+            ptx::umma_commit(bar(W_EMPTY + s));
+            if (g == G - 1) ptx::umma_commit(bar(X_EMPTY + kb));  // last reader of this tile's X block
+          }
+          ptx::umma_commit(bar(A1_FULL + b));
+        }
+        if (q >= 1) {
+          const uint32_t p = q - 1, i = p / G, g = p % G, l = g / (uint32_t)a.nc, c = g % (uint32_t)a.nc;
+          ptx::mbar_wait(bar(H1_FULL), p & 1u);
+          if (c == 0) ptx::mbar_wait(bar(A2_EMPTY), ((i * (uint32_t)a.K + l) & 1u) ^ 1u);
+          const uint32_t s = j % NSTAGE, r = j / NSTAGE;
+          ptx::mbar_wait(bar(W_FULL + s), r & 1u);
+          ++j;
+          ptx::tc_fence_after();
+          const uint64_t bd = ptx::umma_desc_sw128(sbase + ROFF + s * STAGE_BYTES);
+#pragma unroll
+          for (uint32_t kb2 = 0; kb2 < 2; ++kb2) {
+            const uint64_t ad = ptx::umma_desc_sw128(sbase + HOFF + kb2 * STAGE_BYTES);
+#pragma unroll
+            for (uint32_t k = 0; k < 4; ++k)
+              ptx::umma_bf16(tmem + ACC2_COL, ad + 2 * k, bd + kb2 * kb2_step + 2 * k, idesc2, (c | kb2 | k) != 0u);
+          }
+          ptx::umma_commit(bar(W_EMPTY + s));
+          ptx::umma_commit(bar(H1_EMPTY));
+          if (c == (uint32_t)a.nc - 1) ptx::umma_commit(bar(A2_FULL));
+        }
+      }
+    }
+  } else if (warp == 3) {
+    // ------------------------------------------------------------------ L2 prefetch of the next tile's rows
+    const uint32_t rowbytes = (uint32_t)a.D * (TAB_BF16 ? 2u : 4u);
+    for (uint32_t i = 0; i + 1 < T; ++i) {
+      ptx::mbar_wait(bar(X_FULL + 0), i & 1u);  // tile i is being consumed: fetch tile i + 1
+      const int64_t tile = (int64_t)blockIdx.x + (int64_t)(i + 1) * gridDim.x;
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        int64_t n = tile * TILE_M + lane * 4 + e;
+        if (n >= a.N) n = a.N - 1;
+        const int64_t ra = a.ia ? (int64_t)__ldg(a.ia + n) : n;
+        const int64_t rb = a.ib ? (int64_t)__ldg(a.ib + n) : n;
+        ptx::bulk_prefetch_l2((const uint8_t *)a.ta + (size_t)ra * rowbytes, rowbytes);
+        ptx::bulk_prefetch_l2((const uint8_t *)a.tb + (size_t)rb * rowbytes, rowbytes);
+      }
+    }
+  } else if (warp >= 4 && warp < 8) {
+    // ------------------------------------------------------------------ epilogue
+    const int et = tid - 128;             // 0..127 = row of the tile = TMEM lane
+    const uint32_t quad = (uint32_t)(warp & 3);
+    const uint32_t trow = tmem + ((quad * 32u) << 16);
+    float *b1s = reinterpret_cast<float *>(smem + P_B1);
+    float *b2s = reinterpret_cast<float *>(smem + P_B2);
+    float *w3s = reinterpret_cast<float *>(smem + P_W3);
+    float *b3s = reinterpret_cast<float *>(smem + P_B3);
+    float rows[2 * ALINK_MAX_K];
+    for (uint32_t q = 0; q < Q; ++q) {
+      const uint32_t i = q / G, g = q % G, l = g / (uint32_t)a.nc, c = g % (uint32_t)a.nc, b = q & 1u, u = q >> 1;
+      // stage this chunk's bias (and, at a learner's first chunk, its layer-2 bias and last layer)
+      b1s[b * 128 + et] = __ldg(a.b1 + (size_t)l * a.H1 + c * CHUNK_N + et);
+      if (c == 0) {
+        const uint32_t lb = l & 1u;
+        if (et < a.H2) b2s[lb * 64 + et] = __ldg(a.b2 + (size_t)l * a.H2 + et);
+        if (et < a.H2 * a.C) w3s[lb * 128 + et] = __ldg(a.W3 + (size_t)l * a.H2 * a.C + et);
+        if (et < a.C) b3s[lb * 2 + et] = __ldg(a.b3 + (size_t)l * a.C + et);
+      }
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      ptx::mbar_wait(bar(A1_FULL + b), u & 1u);
+      ptx::tc_fence_after();
+      ptx::mbar_wait(bar(H1_EMPTY), (q & 1u) ^ 1u);  // layer 2 of the previous item has read the h1 buffer
+#pragma unroll 1
+      for (uint32_t jj = 0; jj < 4; ++jj) {
+        uint32_t v[32];
+        ptx::tmem_ld32(trow + b * CHUNK_N + jj * 32, v);
+        ptx::tc_wait_ld();
+        const float *bias = b1s + b * 128 + jj * 32;
+        const uint32_t hbase = sbase + HOFF + (jj >> 1) * STAGE_BYTES;
+#pragma unroll
+        for (uint32_t e = 0; e < 4; ++e) {
+          uint32_t w[4];
+#pragma unroll
+          for (uint32_t h = 0; h < 4; ++h) {
+            const float x0 = fmaxf(__fadd_rn(__uint_as_float(v[e * 8 + 2 * h]), bias[e * 8 + 2 * h]), 0.0f);
+            const float x1 = fmaxf(__fadd_rn(__uint_as_float(v[e * 8 + 2 * h + 1]), bias[e * 8 + 2 * h + 1]), 0.0f);
+            w[h] = pack_bf16(x0, x1);
+          }
+          sts128(hbase + ptx::sw128_offset((uint32_t)et, (jj & 1u) * 4 + e), w[0], w[1], w[2], w[3]);
+        }
+      }
+      ptx::fence_proxy_async_smem();
+      ptx::tc_fence_before();
+      ptx::mbar_arrive(bar(A1_EMPTY + b));
+      ptx::mbar_arrive(bar(H1_FULL));
+
+      if (c == (uint32_t)a.nc - 1) {
+        // ---- learner l is complete for this tile: layer-2 accumulator -> Dense(H2, C) -> activation
+        const uint32_t lb = l & 1u;
+        ptx::mbar_wait(bar(A2_FULL), (i * (uint32_t)a.K + l) & 1u);
+        ptx::tc_fence_after();
+        float z0 = 0.0f, z1 = 0.0f;
+        for (int jj = 0; jj < a.H2 / 32; ++jj) {
+          uint32_t v[32];
+          ptx::tmem_ld32(trow + ACC2_COL + jj * 32, v);
+          ptx::tc_wait_ld();
+#pragma unroll
+          for (int e = 0; e < 32; ++e) {
+            const int jn = jj * 32 + e;
+            const float h = fmaxf(__fadd_rn(__uint_as_float(v[e]), b2s[lb * 64 + jn]), 0.0f);
+            if (a.C == 2) {
+              z0 = __fmaf_rn(h, w3s[lb * 128 + 2 * jn], z0);
+              z1 = __fmaf_rn(h, w3s[lb * 128 + 2 * jn + 1], z1);
+            } else {
+              z0 = __fmaf_rn(h, w3s[lb * 128 + jn], z0);
+            }
+          }
+        }
+        ptx::tc_fence_before();
+        ptx::mbar_arrive(bar(A2_EMPTY));
+        const int64_t n = ((int64_t)blockIdx.x + (int64_t)i * gridDim.x) * TILE_M + et;
+        float p0, p1;
+        if (a.C == 2) {
+          alink_softmax2(__fadd_rn(z0, b3s[lb * 2 + 0]), __fadd_rn(z1, b3s[lb * 2 + 1]), &p0, &p1);
+          if (a.probs && n < a.N)
+            *reinterpret_cast<float2 *>(a.probs + ((size_t)n * a.K + l) * 2) = make_float2(p0, p1);
+        } else {
+          p1 = alink_sigmoid(__fadd_rn(z0, b3s[lb * 2 + 0]));
+          p0 = __fsub_rn(1.0f, p1);  // code/keras_wrapper.py:268
+          if (a.probs && n < a.N) a.probs[(size_t)n * a.K + l] = p1;
+        }
+        rows[2 * l] = p0;
+        rows[2 * l + 1] = p1;
+        if (l == (uint32_t)a.K - 1 && a.util && n < a.N) {
+          float c0, c1;
+          alink_consensus2(rows, a.K, &c0, &c1);
+          a.util[n] = alink_utility2(a.measure, rows, a.K, c0, c1);
+        }
+      }
+    }
+  } else if (warp >= 8) {
+    // ------------------------------------------------------------------ gather producers
+    const int pt = tid - 256, sub = pt & 15, rbase = pt >> 4;
+    const uint32_t nkb_feat = (uint32_t)a.D / KBLK;  // k-blocks of the |a-b| half
+    for (uint32_t i = 0; i < T; ++i) {
+      const int64_t tile = (int64_t)blockIdx.x + (int64_t)i * gridDim.x;
+      int64_t ra[8], rb[8];
+#pragma unroll
+      for (int ii = 0; ii < 8; ++ii) {
+        int64_t n = tile * TILE_M + rbase + 16 * ii;
+        if (n >= a.N) n = a.N - 1;
+        ra[ii] = (a.ia ? (int64_t)__ldg(a.ia + n) : n) * a.D;
+        rb[ii] = (a.ib ? (int64_t)__ldg(a.ib + n) : n) * a.D;
+      }
+      for (uint32_t kb = 0; kb < nkb; ++kb) {
+        const bool had = kb >= nkb_feat;
+        const int col = (int)(had ? kb - nkb_feat : kb) * KBLK + sub * 4;
+        float4 va[8], vb[8];
+#pragma unroll
+        for (int ii = 0; ii < 8; ++ii) {
+          if (TAB_BF16) {
+            va[ii] = ldg_bf4((const __nv_bfloat16 *)a.ta + ra[ii] + col);
+            vb[ii] = ldg_bf4((const __nv_bfloat16 *)a.tb + rb[ii] + col);
+          } else {
+            va[ii] = ldg_f4((const float *)a.ta + ra[ii] + col);
+            vb[ii] = ldg_f4((const float *)a.tb + rb[ii] + col);
+          }
+        }
+        ptx::mbar_wait(bar(X_EMPTY + kb), (i & 1u) ^ 1u);  // previous tile's MMAs have read this block
+        const uint32_t xb = sbase + XOFF + kb * STAGE_BYTES;
+#pragma unroll
+        for (int ii = 0; ii < 8; ++ii) {
+          float x0, x1, x2, x3;
+          if (had) {
+            x0 = __fmul_rn(va[ii].x, vb[ii].x); x1 = __fmul_rn(va[ii].y, vb[ii].y);
+            x2 = __fmul_rn(va[ii].z, vb[ii].z); x3 = __fmul_rn(va[ii].w, vb[ii].w);
+          } else {  // K.abs(l - r), code/siamese.py:27
+            x0 = fabsf(__fsub_rn(va[ii].x, vb[ii].x)); x1 = fabsf(__fsub_rn(va[ii].y, vb[ii].y));
+            x2 = fabsf(__fsub_rn(va[ii].z, vb[ii].z)); x3 = fabsf(__fsub_rn(va[ii].w, vb[ii].w));
+          }
+          const uint32_t r = (uint32_t)(rbase + 16 * ii);
+          sts64(xb + ptx::sw128_offset(r, (uint32_t)sub >> 1) + ((uint32_t)sub & 1u) * 8u, pack_bf16(x0, x1),
+                pack_bf16(x2, x3));
+        }
+        ptx::fence_proxy_async_smem();
+        ptx::mbar_arrive(bar(X_FULL + kb));
+      }
+    }
+  }
+
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc(tmem, TMEM_COLS);
+  }
+}
+
+// ---- one-time weight repack: Keras (in,out) fp32 -> bf16 UMMA operand images (N rows x 64 k, swizzled)
+__global__ void prep_w1_kernel(const float *__restrict__ W1, uint8_t *__restrict__ img, int K, int Din, int H1) {
+  const int nc = H1 / CHUNK_N, nkb = Din / KBLK;
+  const int64_t total = (int64_t)K * nc * nkb * 1024;  // 16-byte chunks
+  for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (int64_t)gridDim.x * blockDim.x) {
+    const int chunk = (int)(idx & 7), r = (int)((idx >> 3) & 127);
+    const int64_t blk = idx >> 10;
+    const int kb = (int)(blk % nkb), c = (int)((blk / nkb) % nc), l = (int)(blk / ((int64_t)nkb * nc));
+    const float *src = W1 + ((size_t)l * Din + (size_t)kb * KBLK + chunk * 8) * H1 + c * CHUNK_N + r;
+    uint32_t w[4];
+    for (int h = 0; h < 4; ++h) w[h] = pack_bf16(src[(size_t)(2 * h) * H1], src[(size_t)(2 * h + 1) * H1]);
+    *reinterpret_cast<uint4 *>(img + (size_t)blk * STAGE_BYTES + ptx::sw128_offset((uint32_t)r, (uint32_t)chunk)) =
+        make_uint4(w[0], w[1], w[2], w[3]);
+  }
+}
+__global__ void prep_w2_kernel(const float *__restrict__ W2, uint8_t *__restrict__ img, int K, int H1, int H2) {
+  const int nc = H1 / CHUNK_N;
+  const int64_t total = (int64_t)K * nc * 2 * H2 * 8;
+  for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (int64_t)gridDim.x * blockDim.x) {
+    const int chunk = (int)(idx & 7);
+    const int n = (int)((idx >> 3) % H2);
+    const int64_t sb = (idx >> 3) / H2;  // (l * nc + c) * 2 + kb2
+    const int kb2 = (int)(sb & 1);
+    const int64_t blk = sb >> 1;
+    const int c = (int)(blk % nc), l = (int)(blk / nc);
+    const float *src = W2 + ((size_t)l * H1 + (size_t)c * CHUNK_N + kb2 * KBLK + chunk * 8) * H2 + n;
+    uint32_t w[4];
+    for (int h = 0; h < 4; ++h) w[h] = pack_bf16(src[(size_t)(2 * h) * H2], src[(size_t)(2 * h + 1) * H2]);
+    *reinterpret_cast<uint4 *>(img + (size_t)blk * (2 * H2 * 128) + (size_t)kb2 * (H2 * 128) +
+                               ptx::sw128_offset((uint32_t)n, (uint32_t)chunk)) = make_uint4(w[0], w[1], w[2], w[3]);
+  }
+}
+
+}  // namespace tc
+
+static int tc_prepare_heads(alink_ctx *ctx, HeadGroup &g) {
+  if (g.D_in % tc::KBLK || g.D_in > tc::MAX_KB * tc::KBLK)
+    return alink_fail(ctx, ALINK_E_UNSUPPORTED, "BF16_TC head needs fan-in %% 64 == 0 and <= %d (got %d)",
+                      tc::MAX_KB * tc::KBLK, g.D_in);
+  if (g.H1 % tc::CHUNK_N || g.H1 > 4096)
+    return alink_fail(ctx, ALINK_E_UNSUPPORTED, "BF16_TC head needs H1 %% 128 == 0 (got %d)", g.H1);
+  if (g.H2 != 32 && g.H2 != 64) return alink_fail(ctx, ALINK_E_UNSUPPORTED, "BF16_TC head needs H2 in {32, 64}");
+  const size_t w1b = (size_t)g.K * g.D_in * g.H1 * 2, w2b = (size_t)g.K * g.H1 * g.H2 * 2;
+  ALINK_CUDA(ctx, cudaMalloc((void **)&g.W1t, w1b));
+  ALINK_CUDA(ctx, cudaMalloc((void **)&g.W2t, w2b));
+  tc::prep_w1_kernel<<<ctx->sm_count * 4, 256, 0, ctx->stream>>>(g.W1, (uint8_t *)g.W1t, g.K, g.D_in, g.H1);
+  ALINK_LAUNCHED(ctx);
+  tc::prep_w2_kernel<<<ctx->sm_count, 256, 0, ctx->stream>>>(g.W2, (uint8_t *)g.W2t, g.K, g.H1, g.H2);
+  ALINK_LAUNCHED(ctx);
+  return ALINK_OK;
+}
+
+// Scores N pairs with every learner; probs [N][K][C] and/or util [N] (measure) are written by the
+// kernel's epilogue. ia/ib are device pointers or null.
 static int tc_score(alink_ctx *ctx, const HeadGroup &g, const Table &A, const Table &B, const int32_t *ia,
-                    const int32_t *ib, int64_t N, float *probs) {
-  (void)g; (void)A; (void)B; (void)ia; (void)ib; (void)N; (void)probs;
-  return alink_fail(ctx, ALINK_E_UNSUPPORTED, "BF16_TC mode not built yet");
+                    const int32_t *ib, int64_t N, float *probs, float *util, int measure) {
+  if (!g.W1t || !g.W2t) return alink_fail(ctx, ALINK_E_STATE, "BF16_TC weights were not prepared");
+  tc::Args a;
+  memset(&a, 0, sizeof(a));
+  a.ta = A.p; a.tb = B.p; a.ia = ia; a.ib = ib; a.N = N; a.D = A.D;
+  a.nkb = g.D_in / tc::KBLK; a.hadamard = g.feat_mode == ALINK_FEAT_ABSDIFF_HADAMARD;
+  a.K = g.K; a.nc = g.H1 / tc::CHUNK_N; a.H1 = g.H1; a.H2 = g.H2; a.C = g.C; a.act = g.act; a.measure = measure;
+  a.w1img = (const uint8_t *)g.W1t; a.w2img = (const uint8_t *)g.W2t;
+  a.b1 = g.b1; a.b2 = g.b2; a.W3 = g.W3; a.b3 = g.b3;
+  a.probs = probs; a.util = util;
+  a.ntiles = (int)((N + tc::TILE_M - 1) / tc::TILE_M);
+  const int grid = a.ntiles < ctx->sm_count ? a.ntiles : ctx->sm_count;
+  auto kern = A.dtype == ALINK_BF16 ? tc::head_kernel<true> : tc::head_kernel<false>;
+  ALINK_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tc::SMEM_BYTES));
+  kern<<<grid, tc::NTHREADS, tc::SMEM_BYTES, ctx->stream>>>(a);
+  ALINK_LAUNCHED(ctx);
+  return ALINK_OK;
 }
