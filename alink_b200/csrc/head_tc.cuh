@@ -138,7 +138,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
   ptx::tc_fence_before();
   __syncthreads();
   ptx::tc_fence_after();
-  const uint32_t tmem = *reinterpret_cast<volatile uint32_t *>(smem + TOFF);
+  const uint32_t tmem = __shfl_sync(0xffffffffu, *reinterpret_cast<volatile uint32_t *>(smem + TOFF), 0);
 
   const uint32_t G = (uint32_t)(a.K * a.nc);  // work items per tile
   const uint32_t T = (uint32_t)a.ntiles > blockIdx.x ? ((uint32_t)a.ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0u;
@@ -148,74 +148,93 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
 
   if (warp == 0) {
     // ------------------------------------------------------------------ weight producer (TMA bulk)
-    if (lane == 0) {
-      uint32_t j = 0;
-      for (uint32_t q = 0; q <= Q; ++q) {
-        if (q < Q) {
-          const uint8_t *src = a.w1img + (size_t)(q % G) * nkb * STAGE_BYTES;
-          for (uint32_t kb = 0; kb < nkb; ++kb, ++j) {
-            const uint32_t s = j % NSTAGE, r = j / NSTAGE;
-            ptx::mbar_wait(bar(W_EMPTY + s), (r & 1u) ^ 1u);
-            ptx::mbar_expect_tx(bar(W_FULL + s), STAGE_BYTES);
-            ptx::bulk_g2s(sbase + ROFF + s * STAGE_BYTES, src + (size_t)kb * STAGE_BYTES, STAGE_BYTES, bar(W_FULL + s));
-          }
-        }
-        if (q >= 1) {
-          const uint8_t *src = a.w2img + (size_t)((q - 1) % G) * l2bytes;
+    // The whole warp runs the loop converged; one elected lane issues the copies.
+    const uint32_t leader = ptx::elect_one();
+    const uint32_t ring = sbase + ROFF;
+    uint32_t j = 0;
+    for (uint32_t q = 0; q <= Q; ++q) {
+      if (q < Q) {
+        const uint8_t *src = a.w1img + (size_t)(q % G) * nkb * STAGE_BYTES;
+        for (uint32_t kb = 0; kb < nkb; ++kb, ++j) {
           const uint32_t s = j % NSTAGE, r = j / NSTAGE;
           ptx::mbar_wait(bar(W_EMPTY + s), (r & 1u) ^ 1u);
-          ptx::mbar_expect_tx(bar(W_FULL + s), l2bytes);
-          ptx::bulk_g2s(sbase + ROFF + s * STAGE_BYTES, src, l2bytes, bar(W_FULL + s));
-          ++j;
+          if (leader) {
+            ptx::mbar_expect_tx(bar(W_FULL + s), STAGE_BYTES);
+            ptx::bulk_g2s(ring + s * STAGE_BYTES, src + (size_t)kb * STAGE_BYTES, STAGE_BYTES, bar(W_FULL + s));
+          }
+          __syncwarp();
         }
+      }
+      if (q >= 1) {
+        const uint8_t *src = a.w2img + (size_t)((q - 1) % G) * l2bytes;
+        const uint32_t s = j % NSTAGE, r = j / NSTAGE;
+        ptx::mbar_wait(bar(W_EMPTY + s), (r & 1u) ^ 1u);
+        if (leader) {
+          ptx::mbar_expect_tx(bar(W_FULL + s), l2bytes);
+          ptx::bulk_g2s(ring + s * STAGE_BYTES, src, l2bytes, bar(W_FULL + s));
+        }
+        __syncwarp();
+        ++j;
       }
     }
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer
-    if (lane == 0) {
-      const uint32_t idesc1 = ptx::umma_idesc_bf16(TILE_M, CHUNK_N);
-      const uint32_t idesc2 = ptx::umma_idesc_bf16(TILE_M, a.H2);
-      const uint32_t kb2_step = ((uint32_t)a.H2 * 128u) >> 4;  // layer-2 B sub-block stride, 16-byte units
-      uint32_t j = 0;
-      for (uint32_t q = 0; q <= Q; ++q) {
-        if (q < Q) {
-          const uint32_t i = q / G, g = q % G, b = q & 1u, u = q >> 1;
-          ptx::mbar_wait(bar(A1_EMPTY + b), (u & 1u) ^ 1u);
-          const uint32_t d_tmem = tmem + b * CHUNK_N;
-          for (uint32_t kb = 0; kb < nkb; ++kb, ++j) {
-            if (g == 0) ptx::mbar_wait(bar(X_FULL + kb), i & 1u);
-            const uint32_t s = j % NSTAGE, r = j / NSTAGE;
-            ptx::mbar_wait(bar(W_FULL + s), r & 1u);
-            ptx::tc_fence_after();
-            const uint64_t ad = ptx::umma_desc_sw128(sbase + XOFF + kb * STAGE_BYTES);
-            const uint64_t bd = ptx::umma_desc_sw128(sbase + ROFF + s * STAGE_BYTES);
+    // Converged warp, uniform control flow; one elected lane issues tcgen05.mma / tcgen05.commit.
+    const uint32_t leader = ptx::elect_one();
+    const uint32_t idesc1 = ptx::umma_idesc_bf16(TILE_M, CHUNK_N);
+    const uint32_t idesc2 = ptx::umma_idesc_bf16(TILE_M, a.H2);
+    const uint32_t kb2_step = ((uint32_t)a.H2 * 128u) >> 4;  // layer-2 B sub-block stride, 16-byte units
+    constexpr uint64_t STAGE_STEP = STAGE_BYTES >> 4;
+    const uint64_t xdesc0 = ptx::umma_desc_sw128(sbase + XOFF);
+    const uint64_t hdesc0 = ptx::umma_desc_sw128(sbase + HOFF);
+    const uint64_t rdesc0 = ptx::umma_desc_sw128(sbase + ROFF);
+    const uint32_t acc2 = tmem + ACC2_COL;
+    uint32_t j = 0;
+    for (uint32_t q = 0; q <= Q; ++q) {
+      if (q < Q) {
+        const uint32_t i = q / G, g = q % G, b = q & 1u, u = q >> 1;
+        ptx::mbar_wait(bar(A1_EMPTY + b), (u & 1u) ^ 1u);
+        const uint32_t d_tmem = tmem + b * CHUNK_N;
+        for (uint32_t kb = 0; kb < nkb; ++kb, ++j) {
+          if (g == 0) ptx::mbar_wait(bar(X_FULL + kb), i & 1u);
+          const uint32_t s = j % NSTAGE, r = j / NSTAGE;
+          ptx::mbar_wait(bar(W_FULL + s), r & 1u);
+          ptx::tc_fence_after();
+          if (leader) {
+            const uint64_t ad = xdesc0 + kb * STAGE_STEP;
+            const uint64_t bd = rdesc0 + s * STAGE_STEP;
 #pragma unroll
             for (uint32_t k = 0; k < 4; ++k) ptx::umma_bf16(d_tmem, ad + 2 * k, bd + 2 * k, idesc1, (kb | k) != 0u);
             ptx::umma_commit(bar(W_EMPTY + s));
             if (g == G - 1) ptx::umma_commit(bar(X_EMPTY + kb));  // last reader of this tile's X block
           }
-          ptx::umma_commit(bar(A1_FULL + b));
+          __syncwarp();
         }
-        if (q >= 1) {
-          const uint32_t p = q - 1, i = p / G, g = p % G, l = g / (uint32_t)a.nc, c = g % (uint32_t)a.nc;
-          ptx::mbar_wait(bar(H1_FULL), p & 1u);
-          if (c == 0) ptx::mbar_wait(bar(A2_EMPTY), ((i * (uint32_t)a.K + l) & 1u) ^ 1u);
-          const uint32_t s = j % NSTAGE, r = j / NSTAGE;
-          ptx::mbar_wait(bar(W_FULL + s), r & 1u);
-          ++j;
-          ptx::tc_fence_after();
-          const uint64_t bd = ptx::umma_desc_sw128(sbase + ROFF + s * STAGE_BYTES);
+        if (leader) ptx::umma_commit(bar(A1_FULL + b));
+        __syncwarp();
+      }
+      if (q >= 1) {
+        const uint32_t p = q - 1, i = p / G, g = p % G, l = g / (uint32_t)a.nc, c = g % (uint32_t)a.nc;
+        ptx::mbar_wait(bar(H1_FULL), p & 1u);
+        if (c == 0) ptx::mbar_wait(bar(A2_EMPTY), ((i * (uint32_t)a.K + l) & 1u) ^ 1u);
+        const uint32_t s = j % NSTAGE, r = j / NSTAGE;
+        ptx::mbar_wait(bar(W_FULL + s), r & 1u);
+        ++j;
+        ptx::tc_fence_after();
+        if (leader) {
+          const uint64_t bd = rdesc0 + s * STAGE_STEP;
 #pragma unroll
           for (uint32_t kb2 = 0; kb2 < 2; ++kb2) {
-            const uint64_t ad = ptx::umma_desc_sw128(sbase + HOFF + kb2 * STAGE_BYTES);
+            const uint64_t ad = hdesc0 + kb2 * STAGE_STEP;
 #pragma unroll
             for (uint32_t k = 0; k < 4; ++k)
-              ptx::umma_bf16(tmem + ACC2_COL, ad + 2 * k, bd + kb2 * kb2_step + 2 * k, idesc2, (c | kb2 | k) != 0u);
+              ptx::umma_bf16(acc2, ad + 2 * k, bd + kb2 * kb2_step + 2 * k, idesc2, (c | kb2 | k) != 0u);
           }
           ptx::umma_commit(bar(W_EMPTY + s));
           ptx::umma_commit(bar(H1_EMPTY));
           if (c == (uint32_t)a.nc - 1) ptx::umma_commit(bar(A2_FULL));
         }
+        __syncwarp();
       }
     }
   } else if (warp == 3) {
