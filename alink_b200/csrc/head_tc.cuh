@@ -31,6 +31,7 @@
 #pragma once
 #include "common.cuh"
 #include "ptx.cuh"
+#include <stdlib.h>
 
 namespace tc {
 
@@ -52,8 +53,11 @@ constexpr uint32_t P_B2 = P_B1 + 2 * 128 * 4;                 // float [2][64]
 constexpr uint32_t P_W3 = P_B2 + 2 * 64 * 4;                  // float [2][128]
 constexpr uint32_t P_B3 = P_W3 + 2 * 128 * 4;                 // float [2][2]
 constexpr uint32_t BOFF = P_B3 + 16;                          // mbarriers
-enum { W_FULL = 0, W_EMPTY = 4, X_FULL = 8, X_EMPTY = 16, A1_FULL = 24, A1_EMPTY = 26, H1_FULL = 28, H1_EMPTY = 29,
-       A2_FULL = 30, A2_EMPTY = 31, NBARS = 32 };
+// "*P" barriers exist in the leader CTA of a pair: the peer CTA forwards its local readiness to them.
+constexpr int MAX_STAGES = 8;
+enum { W_FULL = 0, W_EMPTY = 8, W_FULLP = 16, X_FULL = 24, X_EMPTY = 32, X_FULLP = 40, A1_FULL = 48, A1_EMPTY = 50,
+       A1_EMPTYP = 52, H1_FULL = 54, H1_EMPTY = 55, H1_FULLP = 56, A2_FULL = 57, A2_EMPTY = 58, A2_EMPTYP = 59,
+       NBARS = 60 };
 constexpr uint32_t TOFF = BOFF + NBARS * 8;                   // TMEM base address
 constexpr uint32_t SMEM_BYTES = TOFF + 16;
 static_assert(SMEM_BYTES <= 232448, "exceeds the 227 KB per-CTA shared memory limit");
@@ -104,8 +108,16 @@ __device__ __forceinline__ float4 ldg_bf4(const __nv_bfloat16 *p) {  // 4 bf16 -
   return v;
 }
 
-template <bool TAB_BF16>
+// NCTA = 1: every CTA is independent (tcgen05 cta_group::1, M = 128).
+// NCTA = 2: CTA pairs (cluster of 2, tcgen05 cta_group::2, M = 256): each CTA keeps its own 128-pair tile,
+//           loads HALF of every weight block, and the leader's MMAs read both halves — half the TMA
+//           traffic and half the B-operand shared-memory reads per CTA.
+template <bool TAB_BF16, int NCTA>
 __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
+  constexpr uint32_t SB = STAGE_BYTES / NCTA;   // bytes of one ring slot in this CTA
+  constexpr uint32_t NS = NSTAGE * NCTA;        // ring slots
+  const uint32_t rank = NCTA == 2 ? ptx::cluster_ctarank() : 0u;
+  const uint32_t unit0 = blockIdx.x / NCTA, nunit = gridDim.x / NCTA;  // tile (pair) scheduling units
   extern __shared__ __align__(1024) uint8_t smem[];
   const uint32_t sbase = ptx::smem_u32(smem);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -116,32 +128,43 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
       printf("alink_b200: dynamic shared memory base 0x%x is not 1024-byte aligned\n", sbase);
       __trap();
     }
-    for (int s = 0; s < NSTAGE; ++s) {
+    for (int s = 0; s < MAX_STAGES; ++s) {
       ptx::mbar_init(bar(W_FULL + s), 1);
       ptx::mbar_init(bar(W_EMPTY + s), 1);
+      ptx::mbar_init(bar(W_FULLP + s), 1);
     }
     for (int k = 0; k < MAX_KB; ++k) {
       ptx::mbar_init(bar(X_FULL + k), 256);
       ptx::mbar_init(bar(X_EMPTY + k), 1);
+      ptx::mbar_init(bar(X_FULLP + k), 1);
     }
     for (int b = 0; b < 2; ++b) {
       ptx::mbar_init(bar(A1_FULL + b), 1);
       ptx::mbar_init(bar(A1_EMPTY + b), 128);
+      ptx::mbar_init(bar(A1_EMPTYP + b), 1);
     }
     ptx::mbar_init(bar(H1_FULL), 128);
     ptx::mbar_init(bar(H1_EMPTY), 1);
+    ptx::mbar_init(bar(H1_FULLP), 1);
     ptx::mbar_init(bar(A2_FULL), 1);
     ptx::mbar_init(bar(A2_EMPTY), 128);
+    ptx::mbar_init(bar(A2_EMPTYP), 1);
     ptx::fence_barrier_init();
   }
-  if (warp == 2) ptx::tmem_alloc(sbase + TOFF, TMEM_COLS);
+  if (warp == 2) {
+    if (NCTA == 2) ptx::tmem_alloc2(sbase + TOFF, TMEM_COLS);
+    else ptx::tmem_alloc(sbase + TOFF, TMEM_COLS);
+  }
   ptx::tc_fence_before();
-  __syncthreads();
+  if (NCTA == 2) ptx::cluster_sync();
+  else __syncthreads();
   ptx::tc_fence_after();
   const uint32_t tmem = __shfl_sync(0xffffffffu, *reinterpret_cast<volatile uint32_t *>(smem + TOFF), 0);
 
   const uint32_t G = (uint32_t)(a.K * a.nc);  // work items per tile
-  const uint32_t T = (uint32_t)a.ntiles > blockIdx.x ? ((uint32_t)a.ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0u;
+  const uint32_t nunits = ((uint32_t)a.ntiles + NCTA - 1) / NCTA;
+  const uint32_t T = nunits > unit0 ? (nunits - unit0 + nunit - 1) / nunit : 0u;
+  auto tile_of = [&](uint32_t i) -> int64_t { return ((int64_t)unit0 + (int64_t)i * nunit) * NCTA + rank; };
   const uint32_t Q = T * G;
   const uint32_t nkb = (uint32_t)a.nkb;
   const uint32_t l2bytes = 2u * (uint32_t)a.H2 * 128u;
@@ -154,87 +177,145 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
     uint32_t j = 0;
     for (uint32_t q = 0; q <= Q; ++q) {
       if (q < Q) {
-        const uint8_t *src = a.w1img + (size_t)(q % G) * nkb * STAGE_BYTES;
+        // this CTA's rows of the [128 n x 64 k] block: all of them, or the half [64 * rank, +64)
+        const uint8_t *src = a.w1img + (size_t)(q % G) * nkb * STAGE_BYTES + rank * SB;
         for (uint32_t kb = 0; kb < nkb; ++kb, ++j) {
-          const uint32_t s = j % NSTAGE, r = j / NSTAGE;
+          const uint32_t s = j % NS, r = j / NS;
           ptx::mbar_wait(bar(W_EMPTY + s), (r & 1u) ^ 1u);
           if (leader) {
-            ptx::mbar_expect_tx(bar(W_FULL + s), STAGE_BYTES);
-            ptx::bulk_g2s(ring + s * STAGE_BYTES, src + (size_t)kb * STAGE_BYTES, STAGE_BYTES, bar(W_FULL + s));
+            ptx::mbar_expect_tx(bar(W_FULL + s), SB);
+            ptx::bulk_g2s(ring + s * SB, src + (size_t)kb * STAGE_BYTES, SB, bar(W_FULL + s));
           }
           __syncwarp();
         }
       }
       if (q >= 1) {
+        // layer-2 slice: 2 k-blocks of [H2 n x 64 k]; a pair CTA takes rows [H2/2 * rank, +H2/2) of each
         const uint8_t *src = a.w2img + (size_t)((q - 1) % G) * l2bytes;
-        const uint32_t s = j % NSTAGE, r = j / NSTAGE;
+        const uint32_t s = j % NS, r = j / NS;
         ptx::mbar_wait(bar(W_EMPTY + s), (r & 1u) ^ 1u);
         if (leader) {
-          ptx::mbar_expect_tx(bar(W_FULL + s), l2bytes);
-          ptx::bulk_g2s(ring + s * STAGE_BYTES, src, l2bytes, bar(W_FULL + s));
+          ptx::mbar_expect_tx(bar(W_FULL + s), l2bytes / NCTA);
+          if (NCTA == 1) {
+            ptx::bulk_g2s(ring + s * SB, src, l2bytes, bar(W_FULL + s));
+          } else {
+            const uint32_t piece = l2bytes / 4;  // H2/2 rows x 128 B
+            ptx::bulk_g2s(ring + s * SB, src + rank * piece, piece, bar(W_FULL + s));
+            ptx::bulk_g2s(ring + s * SB + piece, src + 2 * piece + rank * piece, piece, bar(W_FULL + s));
+          }
         }
         __syncwarp();
         ++j;
       }
     }
-  } else if (warp == 1) {
-    // ------------------------------------------------------------------ MMA issuer
+  } else if (warp == 1 && rank == 0) {
+    // ------------------------------------------------------------------ MMA issuer (leader CTA of a pair)
     // Converged warp, uniform control flow; one elected lane issues tcgen05.mma / tcgen05.commit.
     const uint32_t leader = ptx::elect_one();
-    const uint32_t idesc1 = ptx::umma_idesc_bf16(TILE_M, CHUNK_N);
-    const uint32_t idesc2 = ptx::umma_idesc_bf16(TILE_M, a.H2);
-    const uint32_t kb2_step = ((uint32_t)a.H2 * 128u) >> 4;  // layer-2 B sub-block stride, 16-byte units
+    const uint32_t idesc1 = ptx::umma_idesc_bf16(TILE_M * NCTA, CHUNK_N);
+    const uint32_t idesc2 = ptx::umma_idesc_bf16(TILE_M * NCTA, a.H2);
+    const uint32_t kb2_step = ((uint32_t)a.H2 * 128u / NCTA) >> 4;  // layer-2 B sub-block stride, 16-byte units
     constexpr uint64_t STAGE_STEP = STAGE_BYTES >> 4;
+    constexpr uint64_t SLOT_STEP = SB >> 4;
     const uint64_t xdesc0 = ptx::umma_desc_sw128(sbase + XOFF);
     const uint64_t hdesc0 = ptx::umma_desc_sw128(sbase + HOFF);
     const uint64_t rdesc0 = ptx::umma_desc_sw128(sbase + ROFF);
     const uint32_t acc2 = tmem + ACC2_COL;
+    auto mma = [&](uint32_t d, uint64_t ad, uint64_t bd, uint32_t idesc, uint32_t acc) {
+      if (NCTA == 2) ptx::umma2_bf16(d, ad, bd, idesc, acc);
+      else ptx::umma_bf16(d, ad, bd, idesc, acc);
+    };
+    auto commit = [&](int b_) {
+      if (NCTA == 2) ptx::umma2_commit_mc(bar(b_));
+      else ptx::umma_commit(bar(b_));
+    };
+    // wait for this CTA's producer and (pair mode) for the peer's, forwarded to the *P barrier
+    auto wait2 = [&](int local, int fwd, uint32_t parity) {
+      ptx::mbar_wait(bar(local), parity);
+      if (NCTA == 2) ptx::mbar_wait_cluster(bar(fwd), parity);
+    };
     uint32_t j = 0;
     for (uint32_t q = 0; q <= Q; ++q) {
       if (q < Q) {
         const uint32_t i = q / G, g = q % G, b = q & 1u, u = q >> 1;
+        // "empty" barriers pass freely on their first use: nothing is forwarded for it
         ptx::mbar_wait(bar(A1_EMPTY + b), (u & 1u) ^ 1u);
+        if (NCTA == 2 && u > 0) ptx::mbar_wait_cluster(bar(A1_EMPTYP + b), (u & 1u) ^ 1u);
         const uint32_t d_tmem = tmem + b * CHUNK_N;
         for (uint32_t kb = 0; kb < nkb; ++kb, ++j) {
-          if (g == 0) ptx::mbar_wait(bar(X_FULL + kb), i & 1u);
-          const uint32_t s = j % NSTAGE, r = j / NSTAGE;
-          ptx::mbar_wait(bar(W_FULL + s), r & 1u);
+          if (g == 0) wait2(X_FULL + kb, X_FULLP + kb, i & 1u);
+          const uint32_t s = j % NS, r = j / NS;
+          wait2(W_FULL + s, W_FULLP + s, r & 1u);
           ptx::tc_fence_after();
           if (leader) {
             const uint64_t ad = xdesc0 + kb * STAGE_STEP;
-            const uint64_t bd = rdesc0 + s * STAGE_STEP;
+            const uint64_t bd = rdesc0 + s * SLOT_STEP;
 #pragma unroll
-            for (uint32_t k = 0; k < 4; ++k) ptx::umma_bf16(d_tmem, ad + 2 * k, bd + 2 * k, idesc1, (kb | k) != 0u);
-            ptx::umma_commit(bar(W_EMPTY + s));
-            if (g == G - 1) ptx::umma_commit(bar(X_EMPTY + kb));  // last reader of this tile's X block
+            for (uint32_t k = 0; k < 4; ++k) mma(d_tmem, ad + 2 * k, bd + 2 * k, idesc1, (kb | k) != 0u);
+            commit(W_EMPTY + s);
+            if (g == G - 1) commit(X_EMPTY + kb);  // last reader of this tile's X block
           }
           __syncwarp();
         }
-        if (leader) ptx::umma_commit(bar(A1_FULL + b));
+        if (leader) commit(A1_FULL + b);
         __syncwarp();
       }
       if (q >= 1) {
         const uint32_t p = q - 1, i = p / G, g = p % G, l = g / (uint32_t)a.nc, c = g % (uint32_t)a.nc;
-        ptx::mbar_wait(bar(H1_FULL), p & 1u);
-        if (c == 0) ptx::mbar_wait(bar(A2_EMPTY), ((i * (uint32_t)a.K + l) & 1u) ^ 1u);
-        const uint32_t s = j % NSTAGE, r = j / NSTAGE;
-        ptx::mbar_wait(bar(W_FULL + s), r & 1u);
+        wait2(H1_FULL, H1_FULLP, p & 1u);
+        if (c == 0) {
+          const uint32_t v = i * (uint32_t)a.K + l;
+          ptx::mbar_wait(bar(A2_EMPTY), (v & 1u) ^ 1u);
+          if (NCTA == 2 && v > 0) ptx::mbar_wait_cluster(bar(A2_EMPTYP), (v & 1u) ^ 1u);
+        }
+        const uint32_t s = j % NS, r = j / NS;
+        wait2(W_FULL + s, W_FULLP + s, r & 1u);
         ++j;
         ptx::tc_fence_after();
         if (leader) {
-          const uint64_t bd = rdesc0 + s * STAGE_STEP;
+          const uint64_t bd = rdesc0 + s * SLOT_STEP;
 #pragma unroll
           for (uint32_t kb2 = 0; kb2 < 2; ++kb2) {
             const uint64_t ad = hdesc0 + kb2 * STAGE_STEP;
 #pragma unroll
             for (uint32_t k = 0; k < 4; ++k)
-              ptx::umma_bf16(acc2, ad + 2 * k, bd + kb2 * kb2_step + 2 * k, idesc2, (c | kb2 | k) != 0u);
+              mma(acc2, ad + 2 * k, bd + kb2 * kb2_step + 2 * k, idesc2, (c | kb2 | k) != 0u);
           }
-          ptx::umma_commit(bar(W_EMPTY + s));
-          ptx::umma_commit(bar(H1_EMPTY));
-          if (c == (uint32_t)a.nc - 1) ptx::umma_commit(bar(A2_FULL));
+          commit(W_EMPTY + s);
+          commit(H1_EMPTY);
+          if (c == (uint32_t)a.nc - 1) commit(A2_FULL);
         }
         __syncwarp();
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------------------------------------------ readiness relay (peer CTA of a pair)
+    // Mirrors the leader's MMA loop: wherever the leader needs this CTA's operands or buffers, wait for
+    // the local barrier and forward ONE arrive to the leader's *P barrier.
+    const uint32_t leader = ptx::elect_one();
+    auto relay = [&](int local, int fwd, uint32_t parity) {
+      ptx::mbar_wait(bar(local), parity);
+      if (leader) ptx::mbar_arrive_remote(ptx::mapa(bar(fwd), 0));
+      __syncwarp();
+    };
+    uint32_t j = 0;
+    for (uint32_t q = 0; q <= Q; ++q) {
+      if (q < Q) {
+        const uint32_t i = q / G, g = q % G, b = q & 1u, u = q >> 1;
+        if (u > 0) relay(A1_EMPTY + b, A1_EMPTYP + b, (u & 1u) ^ 1u);
+        for (uint32_t kb = 0; kb < nkb; ++kb, ++j) {
+          if (g == 0) relay(X_FULL + kb, X_FULLP + kb, i & 1u);
+          const uint32_t s = j % NS, r = j / NS;
+          relay(W_FULL + s, W_FULLP + s, r & 1u);
+        }
+      }
+      if (q >= 1) {
+        const uint32_t p = q - 1, i = p / G, g = p % G, l = g / (uint32_t)a.nc, c = g % (uint32_t)a.nc;
+        relay(H1_FULL, H1_FULLP, p & 1u);
+        if (c == 0 && i * (uint32_t)a.K + l > 0) relay(A2_EMPTY, A2_EMPTYP, ((i * (uint32_t)a.K + l) & 1u) ^ 1u);
+        const uint32_t s = j % NS, r = j / NS;
+        relay(W_FULL + s, W_FULLP + s, r & 1u);
+        ++j;
       }
     }
   } else if (warp == 3) {
@@ -242,7 +323,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
     const uint32_t rowbytes = (uint32_t)a.D * (TAB_BF16 ? 2u : 4u);
     for (uint32_t i = 0; i + 1 < T; ++i) {
       ptx::mbar_wait(bar(X_FULL + 0), i & 1u);  // tile i is being consumed: fetch tile i + 1
-      const int64_t tile = (int64_t)blockIdx.x + (int64_t)(i + 1) * gridDim.x;
+      const int64_t tile = tile_of(i + 1);
 #pragma unroll
       for (int e = 0; e < 4; ++e) {
         int64_t n = tile * TILE_M + lane * 4 + e;
@@ -282,18 +363,21 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
         uint32_t v[32];
         ptx::tmem_ld32(trow + b * CHUNK_N + jj * 32, v);
         ptx::tc_wait_ld();
-        const float *bias = b1s + b * 128 + jj * 32;
+        const float4 *bias = reinterpret_cast<const float4 *>(b1s + b * 128 + jj * 32);  // 128-bit broadcast loads
         const uint32_t hbase = sbase + HOFF + (jj >> 1) * STAGE_BYTES;
 #pragma unroll
         for (uint32_t e = 0; e < 4; ++e) {
-          uint32_t w[4];
-#pragma unroll
-          for (uint32_t h = 0; h < 4; ++h) {
-            const float x0 = fmaxf(__fadd_rn(__uint_as_float(v[e * 8 + 2 * h]), bias[e * 8 + 2 * h]), 0.0f);
-            const float x1 = fmaxf(__fadd_rn(__uint_as_float(v[e * 8 + 2 * h + 1]), bias[e * 8 + 2 * h + 1]), 0.0f);
-            w[h] = pack_bf16(x0, x1);
-          }
-          sts128(hbase + ptx::sw128_offset((uint32_t)et, (jj & 1u) * 4 + e), w[0], w[1], w[2], w[3]);
+          const float4 ba = bias[2 * e], bb = bias[2 * e + 1];
+          const float x0 = fmaxf(__fadd_rn(__uint_as_float(v[e * 8 + 0]), ba.x), 0.0f);
+          const float x1 = fmaxf(__fadd_rn(__uint_as_float(v[e * 8 + 1]), ba.y), 0.0f);
+          const float x2 = fmaxf(__fadd_rn(__uint_as_float(v[e * 8 + 2]), ba.z), 0.0f);
+          const float x3 = fmaxf(__fadd_rn(__uint_as_float(v[e * 8 + 3]), ba.w), 0.0f);
+          const float x4 = fmaxf(__fadd_rn(__uint_as_float(v[e * 8 + 4]), bb.x), 0.0f);
+          const float x5 = fmaxf(__fadd_rn(__uint_as_float(v[e * 8 + 5]), bb.y), 0.0f);
+          const float x6 = fmaxf(__fadd_rn(__uint_as_float(v[e * 8 + 6]), bb.z), 0.0f);
+          const float x7 = fmaxf(__fadd_rn(__uint_as_float(v[e * 8 + 7]), bb.w), 0.0f);
+          sts128(hbase + ptx::sw128_offset((uint32_t)et, (jj & 1u) * 4 + e), pack_bf16(x0, x1), pack_bf16(x2, x3),
+                 pack_bf16(x4, x5), pack_bf16(x6, x7));
         }
       }
       ptx::fence_proxy_async_smem();
@@ -325,7 +409,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
         }
         ptx::tc_fence_before();
         ptx::mbar_arrive(bar(A2_EMPTY));
-        const int64_t n = ((int64_t)blockIdx.x + (int64_t)i * gridDim.x) * TILE_M + et;
+        const int64_t n = tile_of(i) * TILE_M + et;
         float p0, p1;
         if (a.C == 2) {
           alink_softmax2(__fadd_rn(z0, b3s[lb * 2 + 0]), __fadd_rn(z1, b3s[lb * 2 + 1]), &p0, &p1);
@@ -350,7 +434,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
     const int pt = tid - 256, sub = pt & 15, rbase = pt >> 4;
     const uint32_t nkb_feat = (uint32_t)a.D / KBLK;  // k-blocks of the |a-b| half
     for (uint32_t i = 0; i < T; ++i) {
-      const int64_t tile = (int64_t)blockIdx.x + (int64_t)i * gridDim.x;
+      const int64_t tile = tile_of(i);
       int64_t ra[8], rb[8];
 #pragma unroll
       for (int ii = 0; ii < 8; ++ii) {
@@ -396,10 +480,12 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
   }
 
   ptx::tc_fence_before();
-  __syncthreads();
+  if (NCTA == 2) ptx::cluster_sync();  // the peer may still be signalling / reading this CTA's shared memory
+  else __syncthreads();
   if (warp == 2) {
     ptx::tc_fence_after();
-    ptx::tmem_dealloc(tmem, TMEM_COLS);
+    if (NCTA == 2) ptx::tmem_dealloc2(tmem, TMEM_COLS);
+    else ptx::tmem_dealloc(tmem, TMEM_COLS);
   }
 }
 
@@ -469,10 +555,33 @@ static int tc_score(alink_ctx *ctx, const HeadGroup &g, const Table &A, const Ta
   a.b1 = g.b1; a.b2 = g.b2; a.W3 = g.W3; a.b3 = g.b3;
   a.probs = probs; a.util = util;
   a.ntiles = (int)((N + tc::TILE_M - 1) / tc::TILE_M);
-  const int grid = a.ntiles < ctx->sm_count ? a.ntiles : ctx->sm_count;
-  auto kern = A.dtype == ALINK_BF16 ? tc::head_kernel<true> : tc::head_kernel<false>;
+  // CTA pairs (cta_group::2) by default; ALINK_TC_NCTA=1 selects the independent-CTA variant.
+  static const int ncta_env = [] { const char *e = getenv("ALINK_TC_NCTA"); return e ? atoi(e) : 2; }();
+  const int ncta = (ncta_env == 1 || ctx->sm_count < 2) ? 1 : 2;
+  const bool tb16 = A.dtype == ALINK_BF16;
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.blockDim = dim3(tc::NTHREADS);
+  cfg.dynamicSmemBytes = tc::SMEM_BYTES;
+  cfg.stream = ctx->stream;
+  cudaLaunchAttribute attr[1];
+  void (*kern)(const tc::Args);
+  if (ncta == 2) {
+    const int units = (a.ntiles + 1) / 2, max_units = ctx->sm_count / 2;
+    cfg.gridDim = dim3(2u * (unsigned)(units < max_units ? units : max_units));
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    kern = tb16 ? tc::head_kernel<true, 2> : tc::head_kernel<false, 2>;
+  } else {
+    cfg.gridDim = dim3((unsigned)(a.ntiles < ctx->sm_count ? a.ntiles : ctx->sm_count));
+    kern = tb16 ? tc::head_kernel<true, 1> : tc::head_kernel<false, 1>;
+  }
   ALINK_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tc::SMEM_BYTES));
-  kern<<<grid, tc::NTHREADS, tc::SMEM_BYTES, ctx->stream>>>(a);
+  ALINK_CUDA(ctx, cudaLaunchKernelEx(&cfg, kern, a));
   ALINK_LAUNCHED(ctx);
   return ALINK_OK;
 }
