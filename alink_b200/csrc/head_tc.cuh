@@ -53,11 +53,8 @@ constexpr uint32_t P_B2 = P_B1 + 2 * 128 * 4;                 // float [2][64]
 constexpr uint32_t P_W3 = P_B2 + 2 * 64 * 4;                  // float [2][128]
 constexpr uint32_t P_B3 = P_W3 + 2 * 128 * 4;                 // float [2][2]
 constexpr uint32_t BOFF = P_B3 + 16;                          // mbarriers
-// "*P" barriers exist in the leader CTA of a pair: the peer CTA forwards its local readiness to them.
-constexpr int MAX_STAGES = 8;
-enum { W_FULL = 0, W_EMPTY = 8, W_FULLP = 16, X_FULL = 24, X_EMPTY = 32, X_FULLP = 40, A1_FULL = 48, A1_EMPTY = 50,
-       A1_EMPTYP = 52, H1_FULL = 54, H1_EMPTY = 55, H1_FULLP = 56, A2_FULL = 57, A2_EMPTY = 58, A2_EMPTYP = 59,
-       NBARS = 60 };
+enum { W_FULL = 0, W_EMPTY = 4, X_FULL = 8, X_EMPTY = 16, A1_FULL = 24, A1_EMPTY = 26, H1_FULL = 28, H1_EMPTY = 29,
+       A2_FULL = 30, A2_EMPTY = 31, NBARS = 32 };
 constexpr uint32_t TOFF = BOFF + NBARS * 8;                   // TMEM base address
 constexpr uint32_t SMEM_BYTES = TOFF + 16;
 static_assert(SMEM_BYTES <= 232448, "exceeds the 227 KB per-CTA shared memory limit");
@@ -114,8 +111,9 @@ __device__ __forceinline__ float4 ldg_bf4(const __nv_bfloat16 *p) {  // 4 bf16 -
 //           traffic and half the B-operand shared-memory reads per CTA.
 template <bool TAB_BF16, int NCTA>
 __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
-  constexpr uint32_t SB = STAGE_BYTES / NCTA;   // bytes of one ring slot in this CTA
-  constexpr uint32_t NS = NSTAGE * NCTA;        // ring slots
+  constexpr uint32_t KPS = NCTA;                // k-blocks per ring slot (a pair CTA holds half of each block)
+  constexpr uint32_t HB = STAGE_BYTES / NCTA;   // bytes of this CTA's part of one [128 n x 64 k] weight block
+  constexpr uint32_t NS = NSTAGE;               // ring slots of STAGE_BYTES
   const uint32_t rank = NCTA == 2 ? ptx::cluster_ctarank() : 0u;
   const uint32_t unit0 = blockIdx.x / NCTA, nunit = gridDim.x / NCTA;  // tile (pair) scheduling units
   extern __shared__ __align__(1024) uint8_t smem[];
@@ -128,27 +126,25 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
       printf("alink_b200: dynamic shared memory base 0x%x is not 1024-byte aligned\n", sbase);
       __trap();
     }
-    for (int s = 0; s < MAX_STAGES; ++s) {
-      ptx::mbar_init(bar(W_FULL + s), 1);
+    // The leader CTA of a pair also needs the peer's operands: the peer's relay warp forwards one
+    // arrive per phase onto the leader's "operand ready" / "buffer free" barriers (count + 1).
+    const uint32_t fwd = (NCTA == 2 && rank == 0) ? 1u : 0u;
+    for (int s = 0; s < NSTAGE; ++s) {
+      ptx::mbar_init(bar(W_FULL + s), 1 + fwd);
       ptx::mbar_init(bar(W_EMPTY + s), 1);
-      ptx::mbar_init(bar(W_FULLP + s), 1);
     }
     for (int k = 0; k < MAX_KB; ++k) {
-      ptx::mbar_init(bar(X_FULL + k), 256);
+      ptx::mbar_init(bar(X_FULL + k), 256 + fwd);
       ptx::mbar_init(bar(X_EMPTY + k), 1);
-      ptx::mbar_init(bar(X_FULLP + k), 1);
     }
     for (int b = 0; b < 2; ++b) {
       ptx::mbar_init(bar(A1_FULL + b), 1);
-      ptx::mbar_init(bar(A1_EMPTY + b), 128);
-      ptx::mbar_init(bar(A1_EMPTYP + b), 1);
+      ptx::mbar_init(bar(A1_EMPTY + b), 128 + fwd);
     }
-    ptx::mbar_init(bar(H1_FULL), 128);
+    ptx::mbar_init(bar(H1_FULL), 128 + fwd);
     ptx::mbar_init(bar(H1_EMPTY), 1);
-    ptx::mbar_init(bar(H1_FULLP), 1);
     ptx::mbar_init(bar(A2_FULL), 1);
-    ptx::mbar_init(bar(A2_EMPTY), 128);
-    ptx::mbar_init(bar(A2_EMPTYP), 1);
+    ptx::mbar_init(bar(A2_EMPTY), 128 + fwd);
     ptx::fence_barrier_init();
   }
   if (warp == 2) {
@@ -171,41 +167,42 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
 
   if (warp == 0) {
     // ------------------------------------------------------------------ weight producer (TMA bulk)
-    // The whole warp runs the loop converged; one elected lane issues the copies.
+    // The whole warp runs the loop converged; one elected lane issues the copies. One ring slot holds
+    // KPS k-blocks of this CTA's rows: all 128 of each block, or the half [64 * rank, +64) in pair mode.
     const uint32_t leader = ptx::elect_one();
     const uint32_t ring = sbase + ROFF;
-    uint32_t j = 0;
+    uint32_t s = 0, ph = 0;  // ring slot and its phase parity
     for (uint32_t q = 0; q <= Q; ++q) {
       if (q < Q) {
-        // this CTA's rows of the [128 n x 64 k] block: all of them, or the half [64 * rank, +64)
-        const uint8_t *src = a.w1img + (size_t)(q % G) * nkb * STAGE_BYTES + rank * SB;
-        for (uint32_t kb = 0; kb < nkb; ++kb, ++j) {
-          const uint32_t s = j % NS, r = j / NS;
-          ptx::mbar_wait(bar(W_EMPTY + s), (r & 1u) ^ 1u);
+        const uint8_t *src = a.w1img + (size_t)(q % G) * nkb * STAGE_BYTES + rank * HB;
+        for (uint32_t kb = 0; kb < nkb; kb += KPS) {
+          ptx::mbar_wait(bar(W_EMPTY + s), ph ^ 1u);
           if (leader) {
-            ptx::mbar_expect_tx(bar(W_FULL + s), SB);
-            ptx::bulk_g2s(ring + s * SB, src + (size_t)kb * STAGE_BYTES, SB, bar(W_FULL + s));
+            ptx::mbar_expect_tx(bar(W_FULL + s), KPS * HB);
+#pragma unroll
+            for (uint32_t kk = 0; kk < KPS; ++kk)
+              ptx::bulk_g2s(ring + s * STAGE_BYTES + kk * HB, src + (size_t)(kb + kk) * STAGE_BYTES, HB, bar(W_FULL + s));
           }
           __syncwarp();
+          if (++s == NS) { s = 0; ph ^= 1u; }
         }
       }
       if (q >= 1) {
         // layer-2 slice: 2 k-blocks of [H2 n x 64 k]; a pair CTA takes rows [H2/2 * rank, +H2/2) of each
         const uint8_t *src = a.w2img + (size_t)((q - 1) % G) * l2bytes;
-        const uint32_t s = j % NS, r = j / NS;
-        ptx::mbar_wait(bar(W_EMPTY + s), (r & 1u) ^ 1u);
+        ptx::mbar_wait(bar(W_EMPTY + s), ph ^ 1u);
         if (leader) {
           ptx::mbar_expect_tx(bar(W_FULL + s), l2bytes / NCTA);
           if (NCTA == 1) {
-            ptx::bulk_g2s(ring + s * SB, src, l2bytes, bar(W_FULL + s));
+            ptx::bulk_g2s(ring + s * STAGE_BYTES, src, l2bytes, bar(W_FULL + s));
           } else {
             const uint32_t piece = l2bytes / 4;  // H2/2 rows x 128 B
-            ptx::bulk_g2s(ring + s * SB, src + rank * piece, piece, bar(W_FULL + s));
-            ptx::bulk_g2s(ring + s * SB + piece, src + 2 * piece + rank * piece, piece, bar(W_FULL + s));
+            ptx::bulk_g2s(ring + s * STAGE_BYTES, src + rank * piece, piece, bar(W_FULL + s));
+            ptx::bulk_g2s(ring + s * STAGE_BYTES + piece, src + 2 * piece + rank * piece, piece, bar(W_FULL + s));
           }
         }
         __syncwarp();
-        ++j;
+        if (++s == NS) { s = 0; ph ^= 1u; }
       }
     }
   } else if (warp == 1 && rank == 0) {
@@ -216,7 +213,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
     const uint32_t idesc2 = ptx::umma_idesc_bf16(TILE_M * NCTA, a.H2);
     const uint32_t kb2_step = ((uint32_t)a.H2 * 128u / NCTA) >> 4;  // layer-2 B sub-block stride, 16-byte units
     constexpr uint64_t STAGE_STEP = STAGE_BYTES >> 4;
-    constexpr uint64_t SLOT_STEP = SB >> 4;
+    constexpr uint64_t HB_STEP = HB >> 4;
     const uint64_t xdesc0 = ptx::umma_desc_sw128(sbase + XOFF);
     const uint64_t hdesc0 = ptx::umma_desc_sw128(sbase + HOFF);
     const uint64_t rdesc0 = ptx::umma_desc_sw128(sbase + ROFF);
@@ -226,54 +223,51 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
       else ptx::umma_bf16(d, ad, bd, idesc, acc);
     };
     auto commit = [&](int b_) {
-      if (NCTA == 2) ptx::umma2_commit_mc(bar(b_));
+      if (NCTA == 2) ptx::umma2_commit_mc(bar(b_));  // arrives in both CTAs of the pair
       else ptx::umma_commit(bar(b_));
     };
-    // wait for this CTA's producer and (pair mode) for the peer's, forwarded to the *P barrier
-    auto wait2 = [&](int local, int fwd, uint32_t parity) {
-      ptx::mbar_wait(bar(local), parity);
-      if (NCTA == 2) ptx::mbar_wait_cluster(bar(fwd), parity);
-    };
-    uint32_t j = 0;
+    uint32_t s = 0, ph = 0;
     for (uint32_t q = 0; q <= Q; ++q) {
       if (q < Q) {
         const uint32_t i = q / G, g = q % G, b = q & 1u, u = q >> 1;
-        // "empty" barriers pass freely on their first use: nothing is forwarded for it
         ptx::mbar_wait(bar(A1_EMPTY + b), (u & 1u) ^ 1u);
-        if (NCTA == 2 && u > 0) ptx::mbar_wait_cluster(bar(A1_EMPTYP + b), (u & 1u) ^ 1u);
         const uint32_t d_tmem = tmem + b * CHUNK_N;
-        for (uint32_t kb = 0; kb < nkb; ++kb, ++j) {
-          if (g == 0) wait2(X_FULL + kb, X_FULLP + kb, i & 1u);
-          const uint32_t s = j % NS, r = j / NS;
-          wait2(W_FULL + s, W_FULLP + s, r & 1u);
+        for (uint32_t kb = 0; kb < nkb; kb += KPS) {
+          if (g == 0) {
+#pragma unroll
+            for (uint32_t kk = 0; kk < KPS; ++kk) ptx::mbar_wait(bar(X_FULL + kb + kk), i & 1u);
+          }
+          ptx::mbar_wait(bar(W_FULL + s), ph);
           ptx::tc_fence_after();
           if (leader) {
             const uint64_t ad = xdesc0 + kb * STAGE_STEP;
-            const uint64_t bd = rdesc0 + s * SLOT_STEP;
+            const uint64_t bd = rdesc0 + s * STAGE_STEP;
 #pragma unroll
-            for (uint32_t k = 0; k < 4; ++k) mma(d_tmem, ad + 2 * k, bd + 2 * k, idesc1, (kb | k) != 0u);
+            for (uint32_t kk = 0; kk < KPS; ++kk) {
+#pragma unroll
+              for (uint32_t k = 0; k < 4; ++k)
+                mma(d_tmem, ad + kk * STAGE_STEP + 2 * k, bd + kk * HB_STEP + 2 * k, idesc1, (kb | kk | k) != 0u);
+            }
             commit(W_EMPTY + s);
-            if (g == G - 1) commit(X_EMPTY + kb);  // last reader of this tile's X block
+            if (g == G - 1) {  // last reader of this tile's X blocks
+#pragma unroll
+              for (uint32_t kk = 0; kk < KPS; ++kk) commit(X_EMPTY + kb + kk);
+            }
           }
           __syncwarp();
+          if (++s == NS) { s = 0; ph ^= 1u; }
         }
         if (leader) commit(A1_FULL + b);
         __syncwarp();
       }
       if (q >= 1) {
         const uint32_t p = q - 1, i = p / G, g = p % G, l = g / (uint32_t)a.nc, c = g % (uint32_t)a.nc;
-        wait2(H1_FULL, H1_FULLP, p & 1u);
-        if (c == 0) {
-          const uint32_t v = i * (uint32_t)a.K + l;
-          ptx::mbar_wait(bar(A2_EMPTY), (v & 1u) ^ 1u);
-          if (NCTA == 2 && v > 0) ptx::mbar_wait_cluster(bar(A2_EMPTYP), (v & 1u) ^ 1u);
-        }
-        const uint32_t s = j % NS, r = j / NS;
-        wait2(W_FULL + s, W_FULLP + s, r & 1u);
-        ++j;
+        ptx::mbar_wait(bar(H1_FULL), p & 1u);
+        if (c == 0) ptx::mbar_wait(bar(A2_EMPTY), ((i * (uint32_t)a.K + l) & 1u) ^ 1u);
+        ptx::mbar_wait(bar(W_FULL + s), ph);
         ptx::tc_fence_after();
         if (leader) {
-          const uint64_t bd = rdesc0 + s * SLOT_STEP;
+          const uint64_t bd = rdesc0 + s * STAGE_STEP;
 #pragma unroll
           for (uint32_t kb2 = 0; kb2 < 2; ++kb2) {
             const uint64_t ad = hdesc0 + kb2 * STAGE_STEP;
@@ -286,36 +280,41 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
           if (c == (uint32_t)a.nc - 1) commit(A2_FULL);
         }
         __syncwarp();
+        if (++s == NS) { s = 0; ph ^= 1u; }
       }
     }
   } else if (warp == 1) {
     // ------------------------------------------------------------------ readiness relay (peer CTA of a pair)
     // Mirrors the leader's MMA loop: wherever the leader needs this CTA's operands or buffers, wait for
-    // the local barrier and forward ONE arrive to the leader's *P barrier.
+    // the local barrier and forward ONE arrive to the same barrier of the leader. "Buffer free" barriers
+    // pass freely on their first use, so nothing is forwarded for it.
     const uint32_t leader = ptx::elect_one();
-    auto relay = [&](int local, int fwd, uint32_t parity) {
-      ptx::mbar_wait(bar(local), parity);
-      if (leader) ptx::mbar_arrive_remote(ptx::mapa(bar(fwd), 0));
+    auto relay = [&](int bi, uint32_t parity) {
+      ptx::mbar_wait(bar(bi), parity);
+      if (leader) ptx::mbar_arrive_remote(ptx::mapa(bar(bi), 0));
       __syncwarp();
     };
-    uint32_t j = 0;
+    uint32_t s = 0, ph = 0;
     for (uint32_t q = 0; q <= Q; ++q) {
       if (q < Q) {
         const uint32_t i = q / G, g = q % G, b = q & 1u, u = q >> 1;
-        if (u > 0) relay(A1_EMPTY + b, A1_EMPTYP + b, (u & 1u) ^ 1u);
-        for (uint32_t kb = 0; kb < nkb; ++kb, ++j) {
-          if (g == 0) relay(X_FULL + kb, X_FULLP + kb, i & 1u);
-          const uint32_t s = j % NS, r = j / NS;
-          relay(W_FULL + s, W_FULLP + s, r & 1u);
+        if (u > 0) relay(A1_EMPTY + b, (u & 1u) ^ 1u);
+        for (uint32_t kb = 0; kb < nkb; kb += KPS) {
+          if (g == 0) {
+#pragma unroll
+            for (uint32_t kk = 0; kk < KPS; ++kk) relay(X_FULL + kb + kk, i & 1u);
+          }
+          relay(W_FULL + s, ph);
+          if (++s == NS) { s = 0; ph ^= 1u; }
         }
       }
       if (q >= 1) {
         const uint32_t p = q - 1, i = p / G, g = p % G, l = g / (uint32_t)a.nc, c = g % (uint32_t)a.nc;
-        relay(H1_FULL, H1_FULLP, p & 1u);
-        if (c == 0 && i * (uint32_t)a.K + l > 0) relay(A2_EMPTY, A2_EMPTYP, ((i * (uint32_t)a.K + l) & 1u) ^ 1u);
-        const uint32_t s = j % NS, r = j / NS;
-        relay(W_FULL + s, W_FULLP + s, r & 1u);
-        ++j;
+        relay(H1_FULL, p & 1u);
+        const uint32_t v = i * (uint32_t)a.K + l;
+        if (c == 0 && v > 0) relay(A2_EMPTY, (v & 1u) ^ 1u);
+        relay(W_FULL + s, ph);
+        if (++s == NS) { s = 0; ph ^= 1u; }
       }
     }
   } else if (warp == 3) {
@@ -557,7 +556,7 @@ static int tc_score(alink_ctx *ctx, const HeadGroup &g, const Table &A, const Ta
   a.ntiles = (int)((N + tc::TILE_M - 1) / tc::TILE_M);
   // CTA pairs (cta_group::2) by default; ALINK_TC_NCTA=1 selects the independent-CTA variant.
   static const int ncta_env = [] { const char *e = getenv("ALINK_TC_NCTA"); return e ? atoi(e) : 2; }();
-  const int ncta = (ncta_env == 1 || ctx->sm_count < 2) ? 1 : 2;
+  const int ncta = (ncta_env == 1 || ctx->sm_count < 2 || (a.nkb & 1)) ? 1 : 2;  // a pair slot holds 2 k-blocks
   const bool tb16 = A.dtype == ALINK_BF16;
   cudaLaunchConfig_t cfg;
   memset(&cfg, 0, sizeof(cfg));
