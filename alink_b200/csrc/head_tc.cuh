@@ -122,10 +122,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
   auto bar = [&](int i) -> uint32_t { return sbase + BOFF + 8u * (uint32_t)i; };
 
   if (tid == 0) {
-    if (sbase & 1023u) {
-      printf("alink_b200: dynamic shared memory base 0x%x is not 1024-byte aligned\n", sbase);
-      __trap();
-    }
+    if (sbase & 1023u) __trap();  // the swizzled operand tiles need a 1024-byte aligned base
     // The leader CTA of a pair also needs the peer's operands: the peer's relay warp forwards one
     // arrive per phase onto the leader's "operand ready" / "buffer free" barriers (count + 1).
     const uint32_t fwd = (NCTA == 2 && rank == 0) ? 1u : 0u;
@@ -165,10 +162,15 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
   const uint32_t nkb = (uint32_t)a.nkb;
   const uint32_t l2bytes = 2u * (uint32_t)a.H2 * 128u;
 
+  // Register budget per warpgroup: light control warps and the epilogue give registers to the gather
+  // producers, which keep two k-blocks of loads in flight (56*128 + 112*128 + 168*256 <= 64 K).
+  // (each role branch starts with its warpgroup's setmaxnreg so that ptxas budgets the branch with it)
+
   if (warp == 0) {
     // ------------------------------------------------------------------ weight producer (TMA bulk)
     // The whole warp runs the loop converged; one elected lane issues the copies. One ring slot holds
     // KPS k-blocks of this CTA's rows: all 128 of each block, or the half [64 * rank, +64) in pair mode.
+    ptx::setmaxnreg_dec<56>();
     const uint32_t leader = ptx::elect_one();
     const uint32_t ring = sbase + ROFF;
     uint32_t s = 0, ph = 0;  // ring slot and its phase parity
@@ -208,6 +210,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
   } else if (warp == 1 && rank == 0) {
     // ------------------------------------------------------------------ MMA issuer (leader CTA of a pair)
     // Converged warp, uniform control flow; one elected lane issues tcgen05.mma / tcgen05.commit.
+    ptx::setmaxnreg_dec<56>();
     const uint32_t leader = ptx::elect_one();
     const uint32_t idesc1 = ptx::umma_idesc_bf16(TILE_M * NCTA, CHUNK_N);
     const uint32_t idesc2 = ptx::umma_idesc_bf16(TILE_M * NCTA, a.H2);
@@ -288,6 +291,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
     // Mirrors the leader's MMA loop: wherever the leader needs this CTA's operands or buffers, wait for
     // the local barrier and forward ONE arrive to the same barrier of the leader. "Buffer free" barriers
     // pass freely on their first use, so nothing is forwarded for it.
+    ptx::setmaxnreg_dec<56>();
     const uint32_t leader = ptx::elect_one();
     auto relay = [&](int bi, uint32_t parity) {
       ptx::mbar_wait(bar(bi), parity);
@@ -317,7 +321,10 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
         if (++s == NS) { s = 0; ph ^= 1u; }
       }
     }
+  } else if (warp == 2) {
+    ptx::setmaxnreg_dec<56>();
   } else if (warp == 3) {
+    ptx::setmaxnreg_dec<56>();
     // ------------------------------------------------------------------ L2 prefetch of the next tile's rows
     const uint32_t rowbytes = (uint32_t)a.D * (TAB_BF16 ? 2u : 4u);
     for (uint32_t i = 0; i + 1 < T; ++i) {
@@ -335,6 +342,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
     }
   } else if (warp >= 4 && warp < 8) {
     // ------------------------------------------------------------------ epilogue
+    ptx::setmaxnreg_dec<112>();
     const int et = tid - 128;             // 0..127 = row of the tile = TMEM lane
     const uint32_t quad = (uint32_t)(warp & 3);
     const uint32_t trow = tmem + ((quad * 32u) << 16);
@@ -430,50 +438,75 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
     }
   } else if (warp >= 8) {
     // ------------------------------------------------------------------ gather producers
+    // 16 lanes per row segment (64 features = 256 B of fp32), 8 rows per thread and k-block. Loads run
+    // two k-blocks deep (the registers come from setmaxnreg): while block kb is converted and stored,
+    // the loads of block kb + 1 — possibly of the NEXT tile — are already in flight.
+    ptx::setmaxnreg_inc<168>();
     const int pt = tid - 256, sub = pt & 15, rbase = pt >> 4;
     const uint32_t nkb_feat = (uint32_t)a.D / KBLK;  // k-blocks of the |a-b| half
-    for (uint32_t i = 0; i < T; ++i) {
+    uint32_t ra[8], rb[8];                           // table rows of this thread's 8 pairs
+    auto load_rows = [&](uint32_t i) __attribute__((always_inline)) {
       const int64_t tile = tile_of(i);
-      int64_t ra[8], rb[8];
 #pragma unroll
       for (int ii = 0; ii < 8; ++ii) {
         int64_t n = tile * TILE_M + rbase + 16 * ii;
         if (n >= a.N) n = a.N - 1;
-        ra[ii] = (a.ia ? (int64_t)__ldg(a.ia + n) : n) * a.D;
-        rb[ii] = (a.ib ? (int64_t)__ldg(a.ib + n) : n) * a.D;
+        ra[ii] = a.ia ? (uint32_t)__ldg(a.ia + n) : (uint32_t)n;
+        rb[ii] = a.ib ? (uint32_t)__ldg(a.ib + n) : (uint32_t)n;
       }
-      for (uint32_t kb = 0; kb < nkb; ++kb) {
-        const bool had = kb >= nkb_feat;
-        const int col = (int)(had ? kb - nkb_feat : kb) * KBLK + sub * 4;
-        float4 va[8], vb[8];
+    };
+    auto issue = [&](float4(&va)[8], float4(&vb)[8], uint32_t kb) __attribute__((always_inline)) {
+      const uint32_t col = (kb >= nkb_feat ? kb - nkb_feat : kb) * KBLK + (uint32_t)sub * 4;
 #pragma unroll
-        for (int ii = 0; ii < 8; ++ii) {
-          if (TAB_BF16) {
-            va[ii] = ldg_bf4((const __nv_bfloat16 *)a.ta + ra[ii] + col);
-            vb[ii] = ldg_bf4((const __nv_bfloat16 *)a.tb + rb[ii] + col);
-          } else {
-            va[ii] = ldg_f4((const float *)a.ta + ra[ii] + col);
-            vb[ii] = ldg_f4((const float *)a.tb + rb[ii] + col);
-          }
+      for (int ii = 0; ii < 8; ++ii) {
+        const size_t oa = (size_t)ra[ii] * (uint32_t)a.D + col, ob = (size_t)rb[ii] * (uint32_t)a.D + col;
+        if (TAB_BF16) {
+          va[ii] = ldg_bf4((const __nv_bfloat16 *)a.ta + oa);
+          vb[ii] = ldg_bf4((const __nv_bfloat16 *)a.tb + ob);
+        } else {
+          va[ii] = ldg_f4((const float *)a.ta + oa);
+          vb[ii] = ldg_f4((const float *)a.tb + ob);
         }
-        ptx::mbar_wait(bar(X_EMPTY + kb), (i & 1u) ^ 1u);  // previous tile's MMAs have read this block
-        const uint32_t xb = sbase + XOFF + kb * STAGE_BYTES;
+      }
+    };
+    auto finish = [&](const float4(&va)[8], const float4(&vb)[8], uint32_t i, uint32_t kb) __attribute__((always_inline)) {
+      const bool had = kb >= nkb_feat;
+      ptx::mbar_wait(bar(X_EMPTY + kb), (i & 1u) ^ 1u);  // the previous tile's MMAs have read this block
+      const uint32_t xb = sbase + XOFF + kb * STAGE_BYTES;
 #pragma unroll
-        for (int ii = 0; ii < 8; ++ii) {
-          float x0, x1, x2, x3;
-          if (had) {
-            x0 = __fmul_rn(va[ii].x, vb[ii].x); x1 = __fmul_rn(va[ii].y, vb[ii].y);
-            x2 = __fmul_rn(va[ii].z, vb[ii].z); x3 = __fmul_rn(va[ii].w, vb[ii].w);
-          } else {  // K.abs(l - r), code/siamese.py:27
-            x0 = fabsf(__fsub_rn(va[ii].x, vb[ii].x)); x1 = fabsf(__fsub_rn(va[ii].y, vb[ii].y));
-            x2 = fabsf(__fsub_rn(va[ii].z, vb[ii].z)); x3 = fabsf(__fsub_rn(va[ii].w, vb[ii].w));
-          }
-          const uint32_t r = (uint32_t)(rbase + 16 * ii);
-          sts64(xb + ptx::sw128_offset(r, (uint32_t)sub >> 1) + ((uint32_t)sub & 1u) * 8u, pack_bf16(x0, x1),
-                pack_bf16(x2, x3));
+      for (int ii = 0; ii < 8; ++ii) {
+        float x0, x1, x2, x3;
+        if (had) {
+          x0 = __fmul_rn(va[ii].x, vb[ii].x); x1 = __fmul_rn(va[ii].y, vb[ii].y);
+          x2 = __fmul_rn(va[ii].z, vb[ii].z); x3 = __fmul_rn(va[ii].w, vb[ii].w);
+        } else {  // K.abs(l - r), code/siamese.py:27
+          x0 = fabsf(__fsub_rn(va[ii].x, vb[ii].x)); x1 = fabsf(__fsub_rn(va[ii].y, vb[ii].y));
+          x2 = fabsf(__fsub_rn(va[ii].z, vb[ii].z)); x3 = fabsf(__fsub_rn(va[ii].w, vb[ii].w));
         }
-        ptx::fence_proxy_async_smem();
-        ptx::mbar_arrive(bar(X_FULL + kb));
+        const uint32_t r = (uint32_t)(rbase + 16 * ii);
+        sts64(xb + ptx::sw128_offset(r, (uint32_t)sub >> 1) + ((uint32_t)sub & 1u) * 8u, pack_bf16(x0, x1),
+              pack_bf16(x2, x3));
+      }
+      ptx::fence_proxy_async_smem();
+      ptx::mbar_arrive(bar(X_FULL + kb));
+    };
+    float4 va0[8], vb0[8], va1[8], vb1[8];
+    if (T > 0) {
+      load_rows(0);
+      issue(va0, vb0, 0);
+    }
+    for (uint32_t i = 0; i < T; ++i) {
+      for (uint32_t kb = 0; kb < nkb; kb += 2) {
+        const bool has1 = kb + 1 < nkb;
+        if (has1) issue(va1, vb1, kb + 1);
+        finish(va0, vb0, i, kb);
+        if (kb + 2 < nkb) {
+          issue(va0, vb0, kb + 2);
+        } else if (i + 1 < T) {
+          load_rows(i + 1);
+          issue(va0, vb0, 0);
+        }
+        if (has1) finish(va1, vb1, i, kb + 1);
       }
     }
   }

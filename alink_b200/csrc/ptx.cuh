@@ -23,6 +23,11 @@ __device__ __forceinline__ uint32_t elect_one() {
   return pred;
 }
 
+template <int N>
+__device__ __forceinline__ void setmaxnreg_inc() { asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(N)); }
+template <int N>
+__device__ __forceinline__ void setmaxnreg_dec() { asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(N)); }
+
 // ---------------------------------------------------------------------------------------- mbarrier
 __device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
   asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
@@ -47,18 +52,14 @@ __device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
       : "memory");
   return ok != 0;
 }
-// A wait that never completes would hang the GPU: after ~2 s of polling report and trap instead
-// (the context dies with an error; the C ABI reports ALINK_E_CUDA).
-__device__ __noinline__ void mbar_timeout(uint32_t bar, uint32_t parity) {
-  printf("alink_b200: mbarrier wait timed out (block %d thread %d bar 0x%x parity %u)\n", (int)blockIdx.x,
-         (int)threadIdx.x, bar, parity);
-  __trap();
-}
+// A wait that never completes would hang the GPU: after ~2 s of polling trap instead (the context dies
+// with an error and the C ABI reports ALINK_E_CUDA). No printf / function call here: a call inside the
+// kernel makes ptxas ignore the per-warpgroup register budgets of setmaxnreg.
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   if (mbar_try_wait(bar, parity)) return;
   const long long t0 = clock64();
   while (!mbar_try_wait(bar, parity)) {
-    if (clock64() - t0 > 4000000000LL) mbar_timeout(bar, parity);
+    if (clock64() - t0 > 4000000000LL) __trap();
   }
 }
 
@@ -154,7 +155,7 @@ __device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity)
   if (mbar_try_wait_cluster(bar, parity)) return;
   const long long t0 = clock64();
   while (!mbar_try_wait_cluster(bar, parity)) {
-    if (clock64() - t0 > 4000000000LL) mbar_timeout(bar, parity);
+    if (clock64() - t0 > 4000000000LL) __trap();
   }
 }
 // cta_group::2 flavours: issued in both CTAs of the pair (alloc / dealloc) or by the leader CTA (mma / commit)
