@@ -17,11 +17,12 @@ SO_PATH = os.path.join(_HERE, "csrc", "libalink_b200.so")
 HOST, DEVICE = 0, 1
 F32, BF16 = 0, 1
 FEAT_ABSDIFF, FEAT_ABSDIFF_HADAMARD = 0, 1
-FP32_EXACT, BF16_TC = 0, 1
+FP32_EXACT, BF16_TC, FP32_REFINE = 0, 1, 2
 ACT_ID = {"softmax": 0, "sigmoid": 1}
 MEASURE_ID = {"uncertainty": 0, "neg_margin": 1, "entropy": 2, "vote_entropy": 3,
               "consensus_entropy": 4, "kl_max": 5}
-COMPUTE_ID = {"fp32": FP32_EXACT, "fp32_exact": FP32_EXACT, "bf16": BF16_TC, "bf16_tc": BF16_TC}
+COMPUTE_ID = {"fp32": FP32_EXACT, "fp32_exact": FP32_EXACT, "bf16": BF16_TC, "bf16_tc": BF16_TC,
+              "refine": FP32_REFINE, "fp32_refine": FP32_REFINE}
 MAX_SLOTS = 8
 
 # every symbol include/alink_b200.h declares (tests/test_abi.py checks the .so exports them all)
@@ -30,6 +31,7 @@ SYMBOLS = (
     "alink_set_stream", "alink_launch_count", "alink_host_alloc", "alink_host_free", "alink_set_heads", "alink_set_table",
     "alink_score_indexed", "alink_score_dense", "alink_utility", "alink_utility_from_proba",
     "alink_select_topk", "alink_topk_values", "alink_topk_keys", "alink_query", "alink_disparity_select",
+    "alink_set_refine_eps", "alink_refine_stats",
 )
 
 
@@ -102,6 +104,10 @@ def load():
     L.alink_disparity_select.restype = i32
     L.alink_disparity_select.argtypes = [vp, vp, vp, i64, i32, dbl, dbl, i32, vp, i32, vp, i32,
                                          C.POINTER(i64), C.POINTER(i64)]
+    L.alink_set_refine_eps.restype = i32
+    L.alink_set_refine_eps.argtypes = [vp, dbl]
+    L.alink_refine_stats.restype = i32
+    L.alink_refine_stats.argtypes = [vp, C.POINTER(i64), C.POINTER(C.c_float)]
     _lib = L
     return L
 
@@ -295,6 +301,15 @@ class Context:
                                                    _ptr_space(yy)[0], HOST, _ptr_space(idx)[0], HOST,
                                                    C.byref(n_out), C.byref(active)))
         return idx[:n_out.value].copy(), int(active.value)
+
+    def set_refine_eps(self, eps):
+        self._check(self._L.alink_set_refine_eps(self._h, float(eps)))
+
+    def refine_stats(self):
+        """(candidates re-scored exactly, max |approx - exact| utility among them) of the last query."""
+        n, e = C.c_int64(0), C.c_float(0)
+        self._check(self._L.alink_refine_stats(self._h, C.byref(n), C.byref(e)))
+        return int(n.value), float(e.value)
 
     def set_stream(self, cuda_stream):
         """cuda_stream: integer cudaStream_t (torch.cuda.current_stream().cuda_stream) or None."""

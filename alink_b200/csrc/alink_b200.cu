@@ -7,6 +7,7 @@
 #include "utility.cuh"
 #include "topk.cuh"
 #include "disparity.cuh"
+#include "refine.cuh"
 
 #include <math.h>
 #include <new>
@@ -52,7 +53,7 @@ int alink_destroy(alink_ctx *ctx) {
   for (auto &t : ctx->tables) dev_release(t.own);
   DevBuf *bufs[] = {&ctx->idx_a, &ctx->idx_b, &ctx->h1ws, &ctx->probs, &ctx->cons, &ctx->util, &ctx->sel_state,
                     &ctx->sel_keys, &ctx->sel_idx, &ctx->sel_util, &ctx->sel_in, &ctx->misc0, &ctx->misc1,
-                    &ctx->misc2, &ctx->misc3};
+                    &ctx->misc2, &ctx->misc3, &ctx->cand, &ctx->cia, &ctx->cib, &ctx->util_c, &ctx->rstat};
   for (DevBuf *b : bufs) dev_release(*b);
   for (int i = 0; i < 8; ++i)
     if (ctx->ev[i]) cudaEventDestroy(ctx->ev[i]);
@@ -103,7 +104,7 @@ int alink_set_heads(alink_ctx *ctx, int group, int K, int D_in, int H1, int H2, 
     return alink_fail(ctx, ALINK_E_INVALID, "head must be softmax/C=2 (siamese.py) or sigmoid/C=1 (siamese3.py)");
   if (feat_mode != ALINK_FEAT_ABSDIFF && feat_mode != ALINK_FEAT_ABSDIFF_HADAMARD)
     return alink_fail(ctx, ALINK_E_INVALID, "bad feat_mode %d", feat_mode);
-  if (compute != ALINK_COMPUTE_FP32_EXACT && compute != ALINK_COMPUTE_BF16_TC)
+  if (compute != ALINK_COMPUTE_FP32_EXACT && compute != ALINK_COMPUTE_BF16_TC && compute != ALINK_COMPUTE_FP32_REFINE)
     return alink_fail(ctx, ALINK_E_INVALID, "bad compute mode %d", compute);
   if (D_in < 8 || D_in % 8 || H1 < 8 || H1 % 8 || (feat_mode && (D_in % 16)))
     return alink_fail(ctx, ALINK_E_UNSUPPORTED, "D_in and H1 must be multiples of 8 (got %d, %d)", D_in, H1);
@@ -136,7 +137,13 @@ int alink_set_heads(alink_ctx *ctx, int group, int K, int D_in, int H1, int H2, 
   g.pb2 = dptr + 3 * ALINK_MAX_K;
   g.pW3 = dptr + 4 * ALINK_MAX_K;
   g.pb3 = dptr + 5 * ALINK_MAX_K;
-  if (compute == ALINK_COMPUTE_BF16_TC) ALINK_TRY(tc_prepare_heads(ctx, g));
+  if (compute == ALINK_COMPUTE_BF16_TC) {
+    ALINK_TRY(tc_prepare_heads(ctx, g));
+    g.tc_ok = true;
+  } else if (compute == ALINK_COMPUTE_FP32_REFINE) {
+    g.tc_ok = tc_prepare_heads(ctx, g) == ALINK_OK;  // shapes the tensor-core head cannot take run fully exact
+    if (!g.tc_ok) ctx->err[0] = 0;
+  }
   ALINK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));  // host_ptrs / caller buffers may go away
   g.set = true;
   return ALINK_OK;
@@ -178,7 +185,7 @@ static int score_impl(alink_ctx *ctx, int group, const Table &A, const Table &Bt
     return alink_fail(ctx, ALINK_E_INVALID, "table D=%d gives fan-in %d but heads expect %d", A.D, want, g.D_in);
   if (!ia && (N > A.M || N > Bt.M)) return alink_fail(ctx, ALINK_E_INVALID, "identity pairs exceed table rows");
   if (N < 0 || N > 0xFFFFFFFEll) return alink_fail(ctx, ALINK_E_INVALID, "N out of range");
-  ctx->N = N; ctx->sK = g.K; ctx->sC = g.C; ctx->util_valid = false;
+  ctx->N = N; ctx->sK = g.K; ctx->sC = g.C; ctx->util_valid = false; ctx->probs_full = true;
   ALINK_TRY(dev_reserve(ctx, ctx->probs, sizeof(float) * (size_t)(N ? N : 1) * g.K * g.C));
   if (N == 0) return ALINK_OK;
   if (g.compute == ALINK_COMPUTE_BF16_TC) {
@@ -260,7 +267,8 @@ int alink_score_dense(alink_ctx *ctx, int group, const float *XL, const float *X
 // ------------------------------------------------------------------------------------------ utility
 static int utility_impl(alink_ctx *ctx, int measure) {
   if (measure < 0 || measure >= ALINK_UTIL_COUNT) return alink_fail(ctx, ALINK_E_INVALID, "bad measure %d", measure);
-  if (!ctx->probs.p) return alink_fail(ctx, ALINK_E_STATE, "no scores: call alink_score_* first");
+  if (!ctx->probs.p || !ctx->probs_full)
+    return alink_fail(ctx, ALINK_E_STATE, "no scores: call alink_score_* first");
   ALINK_TRY(dev_reserve(ctx, ctx->util, sizeof(float) * (size_t)(ctx->N ? ctx->N : 1)));
   ALINK_TRY(launch_utility(ctx, (const float *)ctx->probs.p, ctx->N, ctx->sK, ctx->sC, measure,
                            (float *)ctx->util.p, nullptr));
@@ -371,6 +379,89 @@ int alink_topk_keys(alink_ctx *ctx, const uint64_t *keys, int64_t n, int64_t B, 
 }
 
 // ------------------------------------------------------------------------------------------ fused step
+// FP32_REFINE (refine.cuh): bf16 tensor-core filter over all N pairs, bit-exact re-score of the candidates.
+// On return ctx->sel_keys holds the B selected keys (device, sorted). ev (6 events) may be null.
+static int refine_query(alink_ctx *ctx, const HeadGroup &g, const Table &A, const Table &Bt, const int32_t *ia,
+                        const int32_t *ib, int64_t N, int measure, int64_t B, int64_t base, cudaEvent_t *ev) {
+  ctx->N = N; ctx->sK = g.K; ctx->sC = g.C; ctx->util_valid = false; ctx->probs_full = false;
+  ALINK_TRY(dev_reserve(ctx, ctx->util, sizeof(float) * (size_t)N));
+  ALINK_TRY(dev_reserve(ctx, ctx->sel_state, sizeof(SelectState)));
+  ALINK_TRY(dev_reserve(ctx, ctx->cand, sizeof(uint32_t) * (size_t)N));
+  ALINK_TRY(dev_reserve(ctx, ctx->rstat, 16));
+  float *util_a = (float *)ctx->util.p;
+  SelectState *st = (SelectState *)ctx->sel_state.p;
+  unsigned int *rstat = (unsigned int *)ctx->rstat.p;  // [0] candidate count, [1] max error bits
+  // (1) approximate utilities of every pair, fused K-learner reduction in the kernel's epilogue
+  ALINK_TRY(tc_score(ctx, g, A, Bt, ia, ib, N, nullptr, util_a, measure));
+  if (ev) ALINK_CUDA(ctx, cudaEventRecord(ev[2], ctx->stream));
+  // (2) B-th largest approximate utility, (3) candidates within 2 eps of it
+  KeySrc asrc{util_a, nullptr, 0, nullptr};
+  ALINK_TRY(select_threshold(ctx, asrc, N, B, st));
+  ALINK_CUDA(ctx, cudaMemsetAsync(rstat, 0, 16, ctx->stream));
+  int64_t blocks = (N + 2047) / 2048;
+  const int64_t cap = (int64_t)ctx->sm_count * 8;
+  if (blocks > cap) blocks = cap;
+  // eps bounds the error of a PROBABILITY; a measure moves by at most `scale` times that near the top
+  // (margin = p(1) - p(2) doubles it; KL-max compares a learner with the mean: measured 4.3x)
+  static const double scale[ALINK_UTIL_COUNT] = {1.0, 2.0, 1.25, 1.0, 1.25, 5.0};
+  refine_mark_kernel<<<(unsigned)blocks, 256, 0, ctx->stream>>>(util_a, N, st, (float)(2.0 * ctx->refine_eps * scale[measure]),
+                                                                (uint32_t *)ctx->cand.p, rstat);
+  ALINK_LAUNCHED(ctx);
+  unsigned int hM = 0;
+  ALINK_CUDA(ctx, cudaMemcpyAsync(&hM, rstat, 4, cudaMemcpyDeviceToHost, ctx->stream));
+  ALINK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  const int64_t M = (int64_t)hM;
+  if (M < B) return alink_fail(ctx, ALINK_E_STATE, "refine: %lld candidates < B=%lld", (long long)M, (long long)B);
+  // (4) exact re-score of the candidates (oracle summation order, CUDA cores)
+  ALINK_TRY(dev_reserve(ctx, ctx->cia, sizeof(int32_t) * (size_t)M));
+  ALINK_TRY(dev_reserve(ctx, ctx->cib, sizeof(int32_t) * (size_t)M));
+  ALINK_TRY(dev_reserve(ctx, ctx->util_c, sizeof(float) * (size_t)M));
+  ALINK_TRY(dev_reserve(ctx, ctx->probs, sizeof(float) * (size_t)M * g.K * g.C));
+  int64_t cb = (M + 255) / 256;
+  if (cb > cap) cb = cap;
+  refine_compose_kernel<<<(unsigned)cb, 256, 0, ctx->stream>>>((const uint32_t *)ctx->cand.p, (unsigned)M, ia, ib,
+                                                               (int32_t *)ctx->cia.p, (int32_t *)ctx->cib.p);
+  ALINK_LAUNCHED(ctx);
+  const int64_t chunk = 65536;
+  const int Mc_max = (int)(M < chunk ? M : chunk);
+  const int64_t lstride = (int64_t)Mc_max * g.H1;
+  ALINK_TRY(dev_reserve(ctx, ctx->h1ws, sizeof(float) * (size_t)lstride * g.K));
+  for (int64_t row0 = 0; row0 < M; row0 += chunk) {
+    const int Mc = (int)((M - row0) < chunk ? (M - row0) : chunk);
+    ALINK_TRY(ffma_head_chunk(ctx, g, (const float *)A.p, (const float *)Bt.p, A.D, (const int32_t *)ctx->cia.p,
+                              (const int32_t *)ctx->cib.p, row0, Mc, (float *)ctx->h1ws.p, lstride,
+                              (float *)ctx->probs.p));
+  }
+  ALINK_TRY(launch_utility(ctx, (const float *)ctx->probs.p, M, g.K, g.C, measure, (float *)ctx->util_c.p, nullptr));
+  refine_maxerr_kernel<<<(unsigned)cb, 256, 0, ctx->stream>>>((const float *)ctx->util_c.p, util_a,
+                                                              (const uint32_t *)ctx->cand.p, (unsigned)M, rstat + 1);
+  ALINK_LAUNCHED(ctx);
+  if (ev) ALINK_CUDA(ctx, cudaEventRecord(ev[3], ctx->stream));
+  // (5) exact top-B among the candidates, keyed by the pairs' original indices
+  KeySrc csrc{(const float *)ctx->util_c.p, nullptr, (uint64_t)base, (const uint32_t *)ctx->cand.p};
+  ALINK_TRY(topk_device(ctx, csrc, M, B));
+  unsigned int hbits = 0;
+  ALINK_CUDA(ctx, cudaMemcpyAsync(&hbits, rstat + 1, 4, cudaMemcpyDeviceToHost, ctx->stream));
+  ALINK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  ctx->refine_survivors = M;
+  memcpy(&ctx->refine_max_err, &hbits, 4);
+  return ALINK_OK;
+}
+
+int alink_set_refine_eps(alink_ctx *ctx, double eps) {
+  if (!ctx) return ALINK_E_INVALID;
+  if (!(eps > 0.0 && eps < 1.0)) return alink_fail(ctx, ALINK_E_INVALID, "eps outside (0, 1)");
+  ctx->refine_eps = eps;
+  return ALINK_OK;
+}
+
+int alink_refine_stats(const alink_ctx *ctx, int64_t *survivors, float *max_err) {
+  if (!ctx) return ALINK_E_INVALID;
+  if (survivors) *survivors = ctx->refine_survivors;
+  if (max_err) *max_err = ctx->refine_max_err;
+  return ALINK_OK;
+}
+
 int alink_query(alink_ctx *ctx, int group, int slot_a, int slot_b, const int32_t *ia, const int32_t *ib, int64_t N,
                 int in_space, int measure, int64_t B, int64_t base, int64_t *idx_out, float *util_out,
                 uint64_t *keys_out, int out_space, alink_timing *timing) {
@@ -389,6 +480,34 @@ int alink_query(alink_ctx *ctx, int group, int slot_a, int slot_b, const int32_t
   ALINK_TRY(stage_in(ctx, ia, sizeof(int32_t) * (size_t)N, in_space, ctx->idx_a, &dia));
   ALINK_TRY(stage_in(ctx, ib, sizeof(int32_t) * (size_t)N, in_space, ctx->idx_b, &dib));
   if (timing) ALINK_CUDA(ctx, cudaEventRecord(e[1], ctx->stream));
+  ctx->refine_survivors = 0;
+  ctx->refine_max_err = 0.0f;
+  if (group >= 0 && group < ALINK_MAX_GROUPS && ctx->groups[group].set &&
+      ctx->groups[group].compute == ALINK_COMPUTE_FP32_REFINE && ctx->groups[group].tc_ok &&
+      measure != ALINK_UTIL_VOTE_ENTROPY && B > 0 && N >= 8192) {
+    const HeadGroup &g = ctx->groups[group];
+    const Table &TA = ctx->tables[slot_a], &TB = ctx->tables[slot_b];
+    if (!TA.p || !TB.p) return alink_fail(ctx, ALINK_E_STATE, "embedding table slot not set (alink_set_table)");
+    if (TA.D != TB.D || TA.dtype != ALINK_F32 || TB.dtype != ALINK_F32 || (g.feat_mode ? 2 * TA.D : TA.D) != g.D_in)
+      return alink_fail(ctx, ALINK_E_INVALID, "FP32_REFINE needs fp32 tables matching the heads' fan-in");
+    if (!dia && (N > TA.M || N > TB.M)) return alink_fail(ctx, ALINK_E_INVALID, "identity pairs exceed table rows");
+    ALINK_TRY(refine_query(ctx, g, TA, TB, (const int32_t *)dia, (const int32_t *)dib, N, measure, B, base,
+                           timing ? e : nullptr));
+    if (timing) ALINK_CUDA(ctx, cudaEventRecord(e[4], ctx->stream));
+    ALINK_TRY(emit_selection(ctx, B, idx_out, util_out, keys_out, out_space));
+    if (timing) {
+      ALINK_CUDA(ctx, cudaEventRecord(e[5], ctx->stream));
+      ALINK_CUDA(ctx, cudaEventSynchronize(e[5]));
+      cudaEventElapsedTime(&timing->ms_h2d, e[0], e[1]);
+      cudaEventElapsedTime(&timing->ms_score, e[1], e[2]);    // tensor-core filter
+      cudaEventElapsedTime(&timing->ms_utility, e[2], e[3]);  // candidate marking + exact re-score
+      cudaEventElapsedTime(&timing->ms_select, e[3], e[4]);
+      cudaEventElapsedTime(&timing->ms_d2h, e[4], e[5]);
+      cudaEventElapsedTime(&timing->ms_total, e[0], e[5]);
+      timing->launches = ctx->launches - l0;
+    }
+    return ALINK_OK;
+  }
   ALINK_TRY(score_impl(ctx, group, ctx->tables[slot_a], ctx->tables[slot_b], (const int32_t *)dia,
                        (const int32_t *)dib, N, measure));
   if (timing) ALINK_CUDA(ctx, cudaEventRecord(e[2], ctx->stream));

@@ -24,6 +24,7 @@ struct HeadGroup {
   const float **pW1 = nullptr, **pb1 = nullptr, **pW2 = nullptr, **pb2 = nullptr, **pW3 = nullptr, **pb3 = nullptr;
   // bf16 operands for the tcgen05 path, N-major ("[out][in]", K contiguous): W1t [K][H1][D_in], W2t [K][H2][H1]
   __nv_bfloat16 *W1t = nullptr, *W2t = nullptr;
+  bool tc_ok = false;  // the tensor-core images exist (shape supported by head_tc.cuh)
 };
 
 struct Table {
@@ -61,6 +62,12 @@ struct alink_ctx {
   // select scratch
   DevBuf sel_state, sel_keys, sel_idx, sel_util, sel_in;
   DevBuf misc0, misc1, misc2, misc3;
+  // FP32_REFINE (refine.cuh)
+  double refine_eps = 6e-3;       // assumed bound on |bf16 utility - fp32 utility|
+  int64_t refine_survivors = 0;   // candidates re-scored exactly by the last alink_query
+  float refine_max_err = 0.0f;    // max |approx - exact| utility over those candidates
+  bool probs_full = true;         // ctx->probs holds all N pairs (false after a refine query)
+  DevBuf cand, cia, cib, util_c, rstat;
 };
 
 static inline int alink_fail(alink_ctx *ctx, int code, const char *fmt, ...) {

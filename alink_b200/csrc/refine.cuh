@@ -1,0 +1,57 @@
+// refine.cuh — FP32_REFINE: bit-exact fp32 selection at tensor-core speed (filter and refine).
+//
+// The fp32 selection of /root/reference/code/uncertainty.py:154-159 (top-n of the utility) only depends
+// on the pairs near the top. So: (1) the tcgen05 bf16 head scores EVERY pair and yields approximate
+// utilities u~ with |u~ - u| <= eps; (2) radix-select the B-th largest u~ (tau); (3) keep the candidates
+// {n : u~[n] >= tau - 2 eps} — every pair of the exact top-B is among them, because the exact B-th value
+// is >= tau - eps and a pair outside has u < tau - 2 eps + eps; (4) re-score only the candidates with the
+// bit-exact FFMA head (head_ffma.cuh, the oracle's summation order) and (5) select the top-B of the exact
+// utilities with the pairs' ORIGINAL indices in the keys. The result is identical to FP32_EXACT whenever
+// the error bound holds; the observed max |u~ - u| over the candidates is reported next to the survivor
+// count (alink_refine_stats) so the caller can check the bound it chose.
+#pragma once
+#include "common.cuh"
+#include "topk.cuh"
+
+// candidates = pairs whose approximate utility is within `margin` of the B-th largest (st->prefix = its key)
+__global__ void __launch_bounds__(256) refine_mark_kernel(const float *__restrict__ util, int64_t N, const SelectState *st,
+                                                          float margin, uint32_t *__restrict__ cand,
+                                                          unsigned int *__restrict__ count) {
+  const float thr = __fsub_rn(alink_key_utility(st->prefix), margin);
+  const int lane = threadIdx.x & 31;
+  // warp-uniform loop bound: every lane takes part in the ballot
+  for (int64_t n0 = (int64_t)blockIdx.x * 256 + (threadIdx.x & ~31); n0 < N; n0 += (int64_t)gridDim.x * 256) {
+    const int64_t n = n0 + lane;
+    const bool keep = n < N && __ldg(util + n) >= thr;
+    const unsigned int m = __ballot_sync(0xffffffffu, keep);  // one atomic per warp
+    if (m) {
+      const int first = __ffs(m) - 1;
+      unsigned int basepos = 0;
+      if (lane == first) basepos = atomicAdd(count, (unsigned int)__popc(m));
+      basepos = __shfl_sync(0xffffffffu, basepos, first);
+      if (keep) cand[basepos + __popc(m & ((1u << lane) - 1u))] = (uint32_t)n;
+    }
+  }
+}
+
+// table rows of the candidates: cia[j] = ia[cand[j]] (or cand[j] for identity pairs)
+__global__ void __launch_bounds__(256) refine_compose_kernel(const uint32_t *__restrict__ cand, unsigned int M,
+                                                             const int32_t *__restrict__ ia, const int32_t *__restrict__ ib,
+                                                             int32_t *__restrict__ cia, int32_t *__restrict__ cib) {
+  for (unsigned int j = blockIdx.x * 256 + threadIdx.x; j < M; j += gridDim.x * 256) {
+    const uint32_t n = cand[j];
+    cia[j] = ia ? __ldg(ia + n) : (int32_t)n;
+    cib[j] = ib ? __ldg(ib + n) : (int32_t)n;
+  }
+}
+
+// max over the candidates of |exact - approximate| utility (as ordered uint bits: values are >= 0)
+__global__ void __launch_bounds__(256) refine_maxerr_kernel(const float *__restrict__ exact, const float *__restrict__ approx,
+                                                            const uint32_t *__restrict__ cand, unsigned int M,
+                                                            unsigned int *__restrict__ out_bits) {
+  float m = 0.0f;
+  for (unsigned int j = blockIdx.x * 256 + threadIdx.x; j < M; j += gridDim.x * 256)
+    m = fmaxf(m, fabsf(__fsub_rn(exact[j], __ldg(approx + cand[j]))));
+  for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+  if ((threadIdx.x & 31) == 0) atomicMax(out_bits, __float_as_uint(m));
+}

@@ -19,6 +19,7 @@ struct KeySrc {
   const float *util;
   const uint64_t *keys;
   uint64_t base;
+  const uint32_t *map;  // optional: index reported for element i is base + map[i] (refine.cuh)
 };
 
 struct SelectState {
@@ -30,7 +31,8 @@ struct SelectState {
 };
 
 __device__ __forceinline__ uint64_t load_key(const KeySrc &s, int64_t i) {
-  return s.keys ? s.keys[i] : alink_pack_key(__ldg(s.util + i), s.base + (uint64_t)i);
+  if (s.keys) return s.keys[i];
+  return alink_pack_key(__ldg(s.util + i), s.base + (s.map ? (uint64_t)__ldg(s.map + i) : (uint64_t)i));
 }
 
 __global__ void select_init_kernel(SelectState *st, unsigned long long B) {

@@ -6,7 +6,7 @@ reduction -> utility -> top-B, + the cross-shard key merge when N > 1) over one 
 input. Workload at N = 1: BASELINE.json configs[1] (1 M pairs, 512-d ArcFace-shaped table, K = 5,
 top-1000, fp32 bit-exact mode); weak scaling: every rank owns a 1 M-pair shard of an N x 1 M pool.
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--mode fp32|bf16] [--impl native|reference]
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--mode refine|fp32|bf16] [--impl native|reference]
 """
 from __future__ import annotations
 
@@ -138,12 +138,15 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="native", choices=["native", "reference"])
-    ap.add_argument("--mode", default="fp32", choices=["fp32", "bf16"])
+    ap.add_argument("--mode", default="refine", choices=["refine", "fp32", "bf16"],
+                    help="refine = fp32 bit-exact selection via tensor-core filter + exact re-score (default: "
+                         "BASELINE configs[1] is the fp32 bit-exact mode); fp32 = CUDA-core exact; bf16 = tensor cores only")
     ap.add_argument("--measure", default="uncertainty")
     ap.add_argument("--pairs", type=int, default=1_000_000, help="pairs per GPU")
     ap.add_argument("--ref-sample", type=int, default=100_000)
     ap.add_argument("--cpu-sample", type=int, default=100_000)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-mode-compare", action="store_true")
     args = ap.parse_args()
 
     rank = int(os.environ.get("RANK", "0"))
@@ -236,6 +239,7 @@ def main():
 
     ctx.set_table(0, table_dev)
     ms_step, stage, launches, clocks, merged, dev_ms = timed(step_resident, args.steps, args.warmup, sample_clocks=True)
+    refine_stats = ctx.refine_stats() if args.mode == "refine" else None
     ms_e2e, stage_e2e, _, _, merged_e2e, _ = timed(step_e2e, max(2, min(args.steps, 3)), 1)
     assert np.array_equal(merged, merged_e2e), "resident and e2e paths selected different pairs"
 
@@ -243,13 +247,17 @@ def main():
     e2e_value = n_gpus * N / (ms_e2e / 1e3)
     h = pool.heads
     flops = FLOPS_PER_PAIR(K, h.D_in, h.H1, h.H2, h.C) * N
-    head_ms = stage["ms_score"]
+    head_ms = stage["ms_score"]  # fp32 / bf16: the head kernel(s); refine: the tensor-core filter over all N pairs
     achieved_tf = flops / (head_ms / 1e3) / 1e12
     roofline = {"bound": "tensor", "achieved": achieved_tf, "peak": peaks["tf_sustained"], "unit": "TFLOP/s",
                 "frac": achieved_tf / peaks["tf_sustained"], "traffic": None,
                 "kernel": "siamese head (gather+|a-b| fused layer-1 GEMM, layer-2/3 + softmax)",
                 "flops_per_pair": FLOPS_PER_PAIR(K, h.D_in, h.H1, h.H2, h.C), "launch_ms": head_ms,
                 "peak_source": peaks["source"] + ", sustained bf16 (kernel timed inside a long step)"}
+    mode_name = {"fp32": "FP32_EXACT", "bf16": "BF16_TC", "refine": "FP32_REFINE"}[args.mode]
+    if args.mode == "refine":
+        roofline["kernel"] = "tc::head_kernel (tcgen05 bf16 filter over every pair; the exact re-score of the survivors is extra, non-algorithmic work)"
+        roofline["share_of_step"] = head_ms / ms_step
     if args.mode == "fp32":
         clk = (clocks or {}).get("sm_mhz") or 1965.0
         ffma_peak = 2 * 128 * 148 * clk * 1e6 / 1e12
@@ -260,8 +268,8 @@ def main():
     d2h = int(B * 8)
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": n_gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "f32" if args.mode == "fp32" else "bf16", "data": "synthetic",
-            "config": workload_desc(pool, n_gpus, "FP32_EXACT" if args.mode == "fp32" else "BF16_TC"),
+            "vs_baseline": None, "dtype": "bf16" if args.mode == "bf16" else "f32", "data": "synthetic",
+            "config": workload_desc(pool, n_gpus, mode_name),
             "stage_ms": stage, "device_ms_per_step": dev_ms,
             "roofline": roofline,
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
@@ -269,6 +277,25 @@ def main():
                     "call": "alink_set_table(HOST) + alink_query(HOST indices) -> host top-B"},
             "gpu_launches": launches, "clocks": clocks}
 
+    if refine_stats is not None:
+        line["refine"] = {"survivors_rescored_exactly": refine_stats[0], "max_abs_utility_error_seen": refine_stats[1],
+                          "eps": 6e-3, "stage_ms": {"tc_filter": stage["ms_score"], "mark_and_exact_rescore": stage["ms_utility"],
+                                                    "select": stage["ms_select"]}}
+    if n_gpus == 1 and not args.no_mode_compare:
+        # outside the timed region: the same step in the other compute modes, and how the selections compare
+        cmp_ = {}
+        sel = {}
+        for name, cid in (("fp32_exact", _ffi.FP32_EXACT), ("bf16_tc", _ffi.BF16_TC), ("fp32_refine", _ffi.FP32_REFINE)):
+            ctx.set_heads(1, pool.heads, compute=cid)
+            best = None
+            for _ in range(3):
+                idx_m, _, keys_m, t = ctx.query(1, 0, 0, ia_dev, ib_dev, N, args.measure, B, base=base, timing=True)
+                best = t.ms_total if best is None else min(best, t.ms_total)
+            sel[name] = set(idx_m.tolist())
+            cmp_[name] = {"ms_per_step": best, "pairs_per_s": N / (best / 1e3)}
+        cmp_["fp32_refine"]["selection_identical_to_fp32_exact"] = sel["fp32_refine"] == sel["fp32_exact"]
+        cmp_["bf16_tc"]["top_B_overlap_with_fp32_exact"] = len(sel["bf16_tc"] & sel["fp32_exact"]) / max(B, 1)
+        line["modes"] = cmp_
     if rank == 0 and n_gpus == 1 and not args.no_cpu_baseline:
         # bounded CPU sample: calibrate on 10k pairs, then size the sample for ~10-20 s
         v0, _, dt0, threads = cpu_oracle_throughput(pool, 10_000)

@@ -40,7 +40,11 @@ enum { ALINK_F32 = 0, ALINK_BF16 = 1 };
 enum { ALINK_FEAT_ABSDIFF = 0, ALINK_FEAT_ABSDIFF_HADAMARD = 1 };
 /* compute modes: FP32_EXACT = CUDA-core FFMA chains in the oracle's summation order (bit-exact with
  * oracle/); BF16_TC = tcgen05 bf16 tiles with fp32 accumulation in TMEM (|dp| <= 2e-2). */
-enum { ALINK_COMPUTE_FP32_EXACT = 0, ALINK_COMPUTE_BF16_TC = 1 };
+enum { ALINK_COMPUTE_FP32_EXACT = 0, ALINK_COMPUTE_BF16_TC = 1, ALINK_COMPUTE_FP32_REFINE = 2 };
+/* FP32_REFINE: alink_score_* behave as FP32_EXACT; alink_query filters with the BF16_TC head and re-scores
+ * only the pairs within 2*eps of the B-th best approximate utility with the bit-exact head, so the
+ * selection is identical to FP32_EXACT whenever |bf16 utility - fp32 utility| <= eps (alink_set_refine_eps;
+ * survivors and the observed error: alink_refine_stats). VOTE_ENTROPY (discrete plateaus) runs exactly. */
 /* activation and utility ids are shared with the oracle: see include/alink_math.h
  * (ALINK_ACT_SOFTMAX/SIGMOID, ALINK_UTIL_*). */
 
@@ -115,6 +119,14 @@ int alink_utility(alink_ctx *ctx, int measure, float *util, int out_space);
 /* Utility from caller-held probabilities ([N][K][C]); same measures. consensus (N*C) may be NULL. */
 int alink_utility_from_proba(alink_ctx *ctx, const float *per_learner, int64_t N, int K, int C,
                              int measure, int in_space, float *util, float *consensus, int out_space);
+
+/* FP32_REFINE knobs: eps = assumed bound on the bf16 utility error (default 6e-3; measured max 4.9e-3 over
+ * 1 M pairs of BASELINE configs[1]); stats of the last alink_query: candidates re-scored exactly and the
+ * largest |approximate - exact| utility seen among them (survivors = 0 when the query ran fully exact).
+ * eps bounds a probability error; the candidate margin is 2 * eps * scale(measure), scale = 1 (uncertainty),
+ * 2 (margin), 1.25 (entropy, consensus entropy), 5 (KL-max). */
+int alink_set_refine_eps(alink_ctx *ctx, double eps);
+int alink_refine_stats(const alink_ctx *ctx, int64_t *survivors, float *max_err);
 
 /* Top-B of the context's utility vector. Replaces modAL multi_argmax (code/uncertainty.py:155,183,213).
  * idx_out (B int64), util_out (B fp32), keys_out (B packed u64 keys for cross-shard merging): any may

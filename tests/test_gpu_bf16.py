@@ -79,3 +79,37 @@ def test_bf16_hadamard_d256(ctx, oracle):
     per, _ = ctx.score_indexed(1, 0, 0, pool.ia, pool.ib, pool.N, pool.heads.K, pool.heads.C)
     ref = oracle.score(pool.table, pool.table, pool.ia, pool.ib, pool.heads, feat_mode=1)
     assert np.abs(per - ref["per_learner"]).max() <= TOL
+
+
+# ---- FP32_REFINE: tensor-core filter + bit-exact re-score of the survivors (csrc/refine.cuh)
+@pytest.mark.parametrize("measure", ["uncertainty", "neg_margin", "entropy", "consensus_entropy", "kl_max", "vote_entropy"])
+def test_refine_selection_is_bit_identical_to_fp32(ctx, oracle, measure):
+    pool = synth.make_pool(2, N=60000, M=20000)
+    ctx.set_heads(2, pool.heads, compute=_ffi.FP32_REFINE)
+    ctx.set_table(0, pool.table)
+    idx, util, keys = ctx.query(2, 0, 0, pool.ia, pool.ib, pool.N, measure, pool.B, base=5)
+    survivors, max_err = ctx.refine_stats()
+    ref = oracle.score(pool.table, pool.table, pool.ia, pool.ib, pool.heads, measure=measure)
+    ridx, rutil, rkeys = oracle.topk(ref["util"], pool.B, base=5)
+    np.testing.assert_array_equal(keys, rkeys)
+    np.testing.assert_array_equal(idx, ridx)
+    np.testing.assert_array_equal(util.view(np.uint32), rutil.view(np.uint32))
+    if measure == "vote_entropy":
+        assert survivors == 0  # discrete plateaus: runs fully exact
+    else:
+        assert pool.B <= survivors < pool.N
+        scale = {"uncertainty": 1.0, "neg_margin": 2.0, "entropy": 1.25, "consensus_entropy": 1.25, "kl_max": 5.0}[measure]
+        assert max_err <= 6e-3 * scale, f"observed bf16 utility error {max_err} exceeds the assumed bound"
+        print(f"refine[{measure}]: {survivors} of {pool.N} pairs re-scored exactly, max err {max_err:.2e}")
+
+
+def test_refine_small_pool_and_scores_are_exact(ctx, oracle):
+    pool = synth.make_pool(1)  # 2,000 pairs: below the filter's minimum, runs the exact path
+    ctx.set_heads(2, pool.heads, compute=_ffi.FP32_REFINE)
+    ctx.set_table(0, pool.table)
+    idx, util, keys = ctx.query(2, 0, 0, pool.ia, pool.ib, pool.N, "uncertainty", pool.B)
+    ref = oracle.score(pool.table, pool.table, pool.ia, pool.ib, pool.heads, measure="uncertainty")
+    ridx, _, rkeys = oracle.topk(ref["util"], pool.B)
+    np.testing.assert_array_equal(keys, rkeys)
+    per, cons = ctx.score_indexed(2, 0, 0, pool.ia, pool.ib, pool.N, pool.heads.K, pool.heads.C)
+    np.testing.assert_array_equal(per.view(np.uint32), ref["per_learner"].view(np.uint32))  # score calls stay exact
