@@ -105,7 +105,7 @@ def workload_desc(pool, n_gpus, mode):
             "l2": "inputs larger than L2 (table 410 MB + 8 MB indices + hidden workspace; no explicit flush)"}
 
 
-def run_reference(args, rank):
+def run_reference(args, rank, emit):
     """--impl reference: the reference's CPU path for this step. Keras/TF is not installable here, so
     this is the oracle port (oracle/alink_oracle.c) with all host threads, on a bounded sample."""
     if rank != 0:
@@ -129,10 +129,18 @@ def run_reference(args, rank):
                              "sample": f"first {args.ref_sample:,} pairs of configs[1], all {threads} host threads"},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line))
+    emit(line)
 
 
 def main():
+    # stdout carries exactly ONE JSON line: libraries that print banners there (NCCL) go to stderr instead
+    json_fd = os.dup(1)
+    os.dup2(2, 1)
+    sys.stdout = os.fdopen(os.dup(2), "w")
+
+    def emit(obj):
+        os.write(json_fd, (json.dumps(obj) + "\n").encode())
+
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
@@ -153,7 +161,7 @@ def main():
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     if args.impl == "reference":
-        run_reference(args, rank)
+        run_reference(args, rank, emit)
         return
 
     import torch
@@ -306,7 +314,7 @@ def main():
                                           f"(oracle/alink_oracle.c) on {threads} host threads; Keras/TF reference "
                                           "unavailable on this box"}
     if rank == 0:
-        print(json.dumps(line))
+        emit(line)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
