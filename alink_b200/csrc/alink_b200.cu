@@ -4,6 +4,7 @@
 #include "common.cuh"
 #include "head_ffma.cuh"
 #include "head_tc.cuh"
+#include "head_tc_ko.cuh"
 #include "utility.cuh"
 #include "topk.cuh"
 #include "disparity.cuh"
@@ -53,7 +54,7 @@ int alink_destroy(alink_ctx *ctx) {
   for (auto &t : ctx->tables) dev_release(t.own);
   DevBuf *bufs[] = {&ctx->idx_a, &ctx->idx_b, &ctx->h1ws, &ctx->probs, &ctx->cons, &ctx->util, &ctx->sel_state,
                     &ctx->sel_keys, &ctx->sel_idx, &ctx->sel_util, &ctx->sel_in, &ctx->misc0, &ctx->misc1,
-                    &ctx->misc2, &ctx->misc3, &ctx->cand, &ctx->cia, &ctx->cib, &ctx->util_c, &ctx->rstat};
+                    &ctx->misc2, &ctx->misc3, &ctx->cand, &ctx->cia, &ctx->cib, &ctx->util_c, &ctx->rstat, &ctx->xscratch};
   for (DevBuf *b : bufs) dev_release(*b);
   for (int i = 0; i < 8; ++i)
     if (ctx->ev[i]) cudaEventDestroy(ctx->ev[i]);

@@ -68,6 +68,7 @@ struct alink_ctx {
   float refine_max_err = 0.0f;    // max |approx - exact| utility over those candidates
   bool probs_full = true;         // ctx->probs holds all N pairs (false after a refine query)
   DevBuf cand, cia, cib, util_c, rstat;
+  DevBuf xscratch;  // head_tc_ko.cuh: per-CTA bf16 feature-tile images
 };
 
 static inline int alink_fail(alink_ctx *ctx, int code, const char *fmt, ...) {

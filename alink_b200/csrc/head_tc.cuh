@@ -557,9 +557,10 @@ __global__ void prep_w2_kernel(const float *__restrict__ W2, uint8_t *__restrict
 }  // namespace tc
 
 static int tc_prepare_heads(alink_ctx *ctx, HeadGroup &g) {
-  if (g.D_in % tc::KBLK || g.D_in > tc::MAX_KB * tc::KBLK)
-    return alink_fail(ctx, ALINK_E_UNSUPPORTED, "BF16_TC head needs fan-in %% 64 == 0 and <= %d (got %d)",
-                      tc::MAX_KB * tc::KBLK, g.D_in);
+  if (g.D_in % tc::KBLK || g.D_in > 8192)
+    return alink_fail(ctx, ALINK_E_UNSUPPORTED, "BF16_TC head needs fan-in %% 64 == 0 and <= 8192 (got %d)", g.D_in);
+  if (g.D_in > tc::MAX_KB * tc::KBLK && g.H1 > 512)
+    return alink_fail(ctx, ALINK_E_UNSUPPORTED, "BF16_TC head with fan-in > 512 needs H1 <= 512 (got %d)", g.H1);
   if (g.H1 % tc::CHUNK_N || g.H1 > 4096)
     return alink_fail(ctx, ALINK_E_UNSUPPORTED, "BF16_TC head needs H1 %% 128 == 0 (got %d)", g.H1);
   if (g.H2 != 32 && g.H2 != 64) return alink_fail(ctx, ALINK_E_UNSUPPORTED, "BF16_TC head needs H2 in {32, 64}");
@@ -572,6 +573,8 @@ static int tc_prepare_heads(alink_ctx *ctx, HeadGroup &g) {
   ALINK_LAUNCHED(ctx);
   return ALINK_OK;
 }
+
+static int tc_score_ko(alink_ctx *ctx, const HeadGroup &g, const tc::Args &a0, bool tb16);  // head_tc_ko.cuh
 
 // Scores N pairs with every learner; probs [N][K][C] and/or util [N] (measure) are written by the
 // kernel's epilogue. ia/ib are device pointers or null.
@@ -587,6 +590,9 @@ static int tc_score(alink_ctx *ctx, const HeadGroup &g, const Table &A, const Ta
   a.b1 = g.b1; a.b2 = g.b2; a.W3 = g.W3; a.b3 = g.b3;
   a.probs = probs; a.util = util;
   a.ntiles = (int)((N + tc::TILE_M - 1) / tc::TILE_M);
+  // Wide features (the tile does not fit in shared memory) take the k-outer kernel; ALINK_TC_KO=1 forces it.
+  static const int ko_env = [] { const char *e = getenv("ALINK_TC_KO"); return e ? atoi(e) : 0; }();
+  if (a.nkb > tc::MAX_KB || (ko_env == 1 && g.H1 <= 512)) return tc_score_ko(ctx, g, a, A.dtype == ALINK_BF16);
   // CTA pairs (cta_group::2) by default; ALINK_TC_NCTA=1 selects the independent-CTA variant.
   static const int ncta_env = [] { const char *e = getenv("ALINK_TC_NCTA"); return e ? atoi(e) : 2; }();
   const int ncta = (ncta_env == 1 || ctx->sm_count < 2 || (a.nkb & 1)) ? 1 : 2;  // a pair slot holds 2 k-blocks

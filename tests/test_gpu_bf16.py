@@ -113,3 +113,29 @@ def test_refine_small_pool_and_scores_are_exact(ctx, oracle):
     np.testing.assert_array_equal(keys, rkeys)
     per, cons = ctx.score_indexed(2, 0, 0, pool.ia, pool.ib, pool.N, pool.heads.K, pool.heads.C)
     np.testing.assert_array_equal(per.view(np.uint32), ref["per_learner"].view(np.uint32))  # score calls stay exact
+
+
+# ---- wide features: the k-outer tensor-core kernel (csrc/head_tc_ko.cuh)
+@pytest.mark.parametrize("act", ["softmax", "sigmoid"])
+@pytest.mark.parametrize("N", [1, 129, 700, 40000])
+def test_bf16_d2048_resnet_pool(ctx, oracle, act, N):
+    """2048-d VGGFace-ResNet50-shaped features (code/siamese.py:203-216), K = 2 learners."""
+    pool = synth.make_pool(1, N=max(N, 64), D=2048, kind="resnet50", K=2, act=act, M=800)
+    ia, ib = pool.ia[:N].copy(), pool.ib[:N].copy()
+    _install(ctx, pool)
+    per, cons = ctx.score_indexed(1, 0, 0, ia, ib, N, pool.heads.K, pool.heads.C)
+    ref = oracle.score(pool.table, pool.table, ia, ib, pool.heads)
+    err = np.abs(per - ref["per_learner"]).max()
+    assert err <= TOL, f"max |dp| = {err}"
+    assert np.abs(cons - ref["consensus"]).max() <= TOL
+
+
+def test_bf16_d1024_h256_fused_utility(ctx, oracle):
+    pool = synth.make_pool(1, N=5000, D=1024, kind="resnet50", K=3, H1=256, H2=32, M=700)
+    _install(ctx, pool)
+    idx, util, keys = ctx.query(1, 0, 0, pool.ia, pool.ib, pool.N, "entropy", 64)
+    per, _ = ctx.score_indexed(1, 0, 0, pool.ia, pool.ib, pool.N, pool.heads.K, pool.heads.C)
+    ref = oracle.score(pool.table, pool.table, pool.ia, pool.ib, pool.heads)
+    assert np.abs(per - ref["per_learner"]).max() <= TOL
+    _, _, keys2 = ctx.topk_values(ctx.utility_from_proba(per, "entropy"), 64)
+    np.testing.assert_array_equal(keys, keys2)
