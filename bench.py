@@ -95,14 +95,18 @@ def cpu_oracle_throughput(pool, sample_pairs, threads=0, repeats=1):
     return n / best, n, best, oracle_ffi.lib().alink_oracle_get_threads()
 
 
-def workload_desc(pool, n_gpus, mode):
+def workload_desc(pool, n_gpus, mode, cfg=2, table_rows=None):
     h = pool.heads
-    return {"workload": f"BASELINE configs[1]: {pool.N:,} pairs/GPU x {n_gpus} GPU, {pool.D}-d ArcFace-shaped table "
-                        f"(M={pool.table.shape[0]:,}), K={h.K} committee {h.D_in}->{h.H1}->{h.H2}->{h.C} {h.act}, "
+    rows = table_rows or pool.table.shape[0]
+    shape = "ArcFace-shaped fp32" if cfg == 2 else "ResNet-50-shaped bf16"
+    tbytes = rows * pool.D * (4 if cfg == 2 else 2)
+    return {"workload": f"BASELINE configs[{cfg - 1}]: {pool.N:,} pairs/GPU x {n_gpus} GPU, {pool.D}-d {shape} table "
+                        f"(M={rows:,}), K={h.K} committee {h.D_in}->{h.H1}->{h.H2}->{h.C} {h.act}, "
                         f"measure={pool.measure}, top-{pool.B}",
             "pairs_per_gpu": pool.N, "D": pool.D, "K": h.K, "B": pool.B, "compute": mode,
             "sharding": f"dp{n_gpus} by pair index, all-gather of top-B keys" if n_gpus > 1 else "single GPU",
-            "l2": "inputs larger than L2 (table 410 MB + 8 MB indices + hidden workspace; no explicit flush)"}
+            "l2": f"inputs larger than L2 (table {tbytes / 1e6:.0f} MB + {pool.N * 8 / 1e6:.0f} MB indices, random row "
+                  "gather; no explicit flush)"}
 
 
 def run_reference(args, rank, emit):
@@ -110,7 +114,10 @@ def run_reference(args, rank, emit):
     this is the oracle port (oracle/alink_oracle.c) with all host threads, on a bounded sample."""
     if rank != 0:
         return
-    pool = synth.make_pool(2, N=args.ref_sample, measure=args.measure)
+    if args.config == 3:
+        pool = synth.make_pool(3, N=args.ref_sample, M=20_000, measure=args.measure)
+    else:
+        pool = synth.make_pool(2, N=args.ref_sample, measure=args.measure)
     times = []
     threads = 0
     for i in range(args.warmup + args.steps):
@@ -122,7 +129,7 @@ def run_reference(args, rank, emit):
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": dict(workload_desc(pool, 1, "cpu-oracle"),
+            "config": dict(workload_desc(pool, 1, "cpu-oracle", args.config),
                            note="Keras/TF reference unavailable on this box; timed path = C oracle port, "
                                 f"bounded sample of {args.ref_sample:,} pairs per step"),
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port",
@@ -150,7 +157,11 @@ def main():
                     help="refine = fp32 bit-exact selection via tensor-core filter + exact re-score (default: "
                          "BASELINE configs[1] is the fp32 bit-exact mode); fp32 = CUDA-core exact; bf16 = tensor cores only")
     ap.add_argument("--measure", default="uncertainty")
-    ap.add_argument("--pairs", type=int, default=1_000_000, help="pairs per GPU")
+    ap.add_argument("--pairs", type=int, default=None, help="pairs per GPU (default 1,000,000; config 3: 1,250,000)")
+    ap.add_argument("--config", type=int, default=2, choices=[2, 3],
+                    help="BASELINE.json configs ordinal: 2 = 1 M pairs x 512-d (default, the N=1 workload); "
+                         "3 = 10 M pairs x 2048-d bf16 over 8 GPUs (1.25 M pairs per GPU, bf16 table, BF16_TC)")
+    ap.add_argument("--table-rows", type=int, default=None)
     ap.add_argument("--ref-sample", type=int, default=100_000)
     ap.add_argument("--cpu-sample", type=int, default=100_000)
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -180,10 +191,33 @@ def main():
     peaks = load_peaks()
 
     # ---- synthetic workload (identical table/heads on every rank; each rank draws its own shard of pairs)
-    pool = synth.make_pool(2, N=args.pairs, measure=args.measure)
-    if world > 1:
-        ia, ib, _ = synth.make_pairs(args.pairs, pool.table.shape[0], 50_000, seed=synth.BASE_SEED + 102 + 1000 * rank)
-        pool.ia, pool.ib = ia, ib
+    if args.pairs is None:
+        args.pairs = 1_250_000 if args.config == 3 else 1_000_000
+    table_dev = None
+    if args.config == 3:
+        # 2048-d ResNet-50-shaped features: generated ON THE DEVICE (500 k x 2048), stored bf16 (2 GB); the host
+        # only holds a small fp32 slice for head calibration and the CPU sample
+        args.mode = "bf16"
+        M, D, I = args.table_rows or 500_000, 2048, 125_000
+        gen = torch.Generator(device=dev).manual_seed(synth.BASE_SEED + 3)
+        cen = torch.randn((I, D), generator=gen, device=dev, dtype=torch.float32)
+        table_dev = torch.empty((M, D), device=dev, dtype=torch.bfloat16)
+        per = max(M // I, 1)
+        for lo in range(0, M, 50_000):
+            hi = min(lo + 50_000, M)
+            ident = torch.clamp(torch.arange(lo, hi, device=dev) // per, max=I - 1)
+            table_dev[lo:hi] = torch.relu(cen[ident] + 0.5 * torch.randn((hi - lo, D), generator=gen, device=dev)).to(torch.bfloat16)
+        del cen
+        small = table_dev[:20_000].float().cpu().numpy()
+        ia, ib, genuine = synth.make_pairs(args.pairs, M, I, seed=synth.BASE_SEED + 103 + 1000 * rank)
+        cal_a, cal_b, _ = synth.make_pairs(4096, 20_000, 5_000, seed=7)
+        heads = synth.make_heads(5, D, synth.pair_features(small, small, cal_a, cal_b))
+        pool = synth.Pool("cfg3", small, ia, ib, heads, 1000, args.measure, genuine)
+    else:
+        pool = synth.make_pool(2, N=args.pairs, measure=args.measure)
+        if world > 1:
+            ia, ib, _ = synth.make_pairs(args.pairs, pool.table.shape[0], 50_000, seed=synth.BASE_SEED + 102 + 1000 * rank)
+            pool.ia, pool.ib = ia, ib
     N, B, K = pool.N, pool.B, pool.heads.K
     base = rank * N  # global pair index of this shard's first pair
     mode = _ffi.COMPUTE_ID[args.mode]
@@ -191,10 +225,11 @@ def main():
     ctx = _ffi.Context(local_rank)
     ctx.set_stream(torch.cuda.current_stream().cuda_stream)
     ctx.set_heads(0, pool.heads, compute=mode)
-    table_dev = torch.from_numpy(pool.table).to(dev)
+    if table_dev is None:
+        table_dev = torch.from_numpy(pool.table).to(dev)
     ia_dev = torch.from_numpy(pool.ia).to(dev)
     ib_dev = torch.from_numpy(pool.ib).to(dev)
-    table_pin = torch.from_numpy(pool.table).pin_memory()
+    table_pin = table_dev.cpu().pin_memory() if args.config == 3 else torch.from_numpy(pool.table).pin_memory()
     ia_pin = torch.from_numpy(pool.ia).pin_memory()
     ib_pin = torch.from_numpy(pool.ib).pin_memory()
     out = (np.empty((B,), np.int64), np.empty((B,), np.float32), np.empty((B,), np.uint64))
@@ -272,12 +307,12 @@ def main():
         roofline["note"] = ("FP32_EXACT is the bit-exact correctness mode: CUDA-core FFMA, not tensor cores; "
                             f"FFMA peak at the sampled {clk:.0f} MHz = {ffma_peak:.1f} TFLOP/s")
         roofline["frac_of_ffma_peak"] = achieved_tf / ffma_peak
-    h2d = int(pool.table.nbytes + pool.ia.nbytes + pool.ib.nbytes)
+    h2d = int(table_pin.numel() * table_pin.element_size() + pool.ia.nbytes + pool.ib.nbytes)
     d2h = int(B * 8)
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": n_gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "bf16" if args.mode == "bf16" else "f32", "data": "synthetic",
-            "config": workload_desc(pool, n_gpus, mode_name),
+            "config": workload_desc(pool, n_gpus, mode_name, args.config, int(table_dev.shape[0])),
             "stage_ms": stage, "device_ms_per_step": dev_ms,
             "roofline": roofline,
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
@@ -289,7 +324,7 @@ def main():
         line["refine"] = {"survivors_rescored_exactly": refine_stats[0], "max_abs_utility_error_seen": refine_stats[1],
                           "eps": 6e-3, "stage_ms": {"tc_filter": stage["ms_score"], "mark_and_exact_rescore": stage["ms_utility"],
                                                     "select": stage["ms_select"]}}
-    if n_gpus == 1 and not args.no_mode_compare:
+    if n_gpus == 1 and not args.no_mode_compare and args.config == 2:
         # outside the timed region: the same step in the other compute modes, and how the selections compare
         cmp_ = {}
         sel = {}
@@ -306,6 +341,9 @@ def main():
         line["modes"] = cmp_
     if rank == 0 and n_gpus == 1 and not args.no_cpu_baseline:
         # bounded CPU sample: calibrate on 10k pairs, then size the sample for ~10-20 s
+        if args.config == 3:  # the host only holds a 20 k-row fp32 slice: same per-pair work on folded indices
+            pool = synth.Pool(pool.name, pool.table, pool.ia % 20_000, pool.ib % 20_000, pool.heads, pool.B, pool.measure,
+                              pool.genuine)
         v0, _, dt0, threads = cpu_oracle_throughput(pool, 10_000)
         n_s = int(min(pool.N, max(20_000, min(args.cpu_sample * 4, v0 * 12.0))))
         v, n_s, dt, threads = cpu_oracle_throughput(pool, n_s)
