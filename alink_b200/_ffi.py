@@ -31,7 +31,7 @@ SYMBOLS = (
     "alink_set_stream", "alink_launch_count", "alink_host_alloc", "alink_host_free", "alink_set_heads", "alink_set_table",
     "alink_score_indexed", "alink_score_dense", "alink_utility", "alink_utility_from_proba",
     "alink_select_topk", "alink_topk_values", "alink_topk_keys", "alink_query", "alink_disparity_select",
-    "alink_set_refine_eps", "alink_refine_stats",
+    "alink_set_refine_eps", "alink_refine_stats", "alink_score_allpairs", "alink_query_allpairs",
 )
 
 
@@ -104,6 +104,10 @@ def load():
     L.alink_disparity_select.restype = i32
     L.alink_disparity_select.argtypes = [vp, vp, vp, i64, i32, dbl, dbl, i32, vp, i32, vp, i32,
                                          C.POINTER(i64), C.POINTER(i64)]
+    L.alink_score_allpairs.restype = i32
+    L.alink_score_allpairs.argtypes = [vp, i32, i32, i32, i64, i64, vp, vp, i32]
+    L.alink_query_allpairs.restype = i32
+    L.alink_query_allpairs.argtypes = [vp, i32, i32, i32, i64, i64, i32, i64, vp, vp, vp, i32, C.POINTER(Timing)]
     L.alink_set_refine_eps.restype = i32
     L.alink_set_refine_eps.argtypes = [vp, dbl]
     L.alink_refine_stats.restype = i32
@@ -301,6 +305,21 @@ class Context:
                                                    _ptr_space(yy)[0], HOST, _ptr_space(idx)[0], HOST,
                                                    C.byref(n_out), C.byref(active)))
         return idx[:n_out.value].copy(), int(active.value)
+
+    def score_allpairs(self, group, slot_probe, slot_gallery, row0, nrows, G, K, Cc, want_per=False, want_cons=True):
+        """Scores of probe rows [row0, row0+nrows) against all G gallery rows: consensus (nrows*G, C)."""
+        per, cons = self._outs(nrows * G, K, Cc, want_per, want_cons, False)
+        self._check(self._L.alink_score_allpairs(self._h, group, slot_probe, slot_gallery, row0, nrows,
+                                                 _ptr_space(per)[0], _ptr_space(cons)[0], HOST))
+        return per, cons
+
+    def query_allpairs(self, group, slot_probe, slot_gallery, row0, nrows, measure, B, timing=False):
+        idx, util, keys = np.empty((B,), np.int64), np.empty((B,), np.float32), np.empty((B,), np.uint64)
+        t = Timing() if timing else None
+        self._check(self._L.alink_query_allpairs(self._h, group, slot_probe, slot_gallery, row0, nrows,
+                                                 MEASURE_ID[measure], B, _ptr_space(idx)[0], _ptr_space(util)[0],
+                                                 _ptr_space(keys)[0], HOST, C.byref(t) if timing else None))
+        return (idx, util, keys, t) if timing else (idx, util, keys)
 
     def set_refine_eps(self, eps):
         self._check(self._L.alink_set_refine_eps(self._h, float(eps)))

@@ -184,18 +184,22 @@ static int score_impl(alink_ctx *ctx, int group, const Table &A, const Table &Bt
   const int want = g.feat_mode ? 2 * A.D : A.D;
   if (want != g.D_in)
     return alink_fail(ctx, ALINK_E_INVALID, "table D=%d gives fan-in %d but heads expect %d", A.D, want, g.D_in);
-  if (!ia && (N > A.M || N > Bt.M)) return alink_fail(ctx, ALINK_E_INVALID, "identity pairs exceed table rows");
+  if (!ia && !ctx->ap_G && (N > A.M || N > Bt.M)) return alink_fail(ctx, ALINK_E_INVALID, "identity pairs exceed table rows");
   if (N < 0 || N > 0xFFFFFFFEll) return alink_fail(ctx, ALINK_E_INVALID, "N out of range");
   ctx->N = N; ctx->sK = g.K; ctx->sC = g.C; ctx->util_valid = false; ctx->probs_full = true;
-  ALINK_TRY(dev_reserve(ctx, ctx->probs, sizeof(float) * (size_t)(N ? N : 1) * g.K * g.C));
+  // an all-pairs query whose K-learner reduction is fused needs no [N][K][C] probabilities (100 GB at 50k x 50k)
+  const bool skip_probs = ctx->ap_G && fuse_measure >= 0 && g.compute == ALINK_COMPUTE_BF16_TC;
+  if (!skip_probs) ALINK_TRY(dev_reserve(ctx, ctx->probs, sizeof(float) * (size_t)(N ? N : 1) * g.K * g.C));
   if (N == 0) return ALINK_OK;
   if (g.compute == ALINK_COMPUTE_BF16_TC) {
     float *util = nullptr;
+    ctx->probs_full = !skip_probs;
     if (fuse_measure >= 0) {
       ALINK_TRY(dev_reserve(ctx, ctx->util, sizeof(float) * (size_t)N));
       util = (float *)ctx->util.p;
     }
-    ALINK_TRY(tc_score(ctx, g, A, Bt, ia, ib, N, (float *)ctx->probs.p, util, fuse_measure >= 0 ? fuse_measure : 0));
+    ALINK_TRY(tc_score(ctx, g, A, Bt, ia, ib, N, skip_probs ? nullptr : (float *)ctx->probs.p, util,
+                       fuse_measure >= 0 ? fuse_measure : 0));
     if (util) {
       ctx->util_valid = true;
       ctx->util_measure = fuse_measure;
@@ -421,6 +425,7 @@ static int refine_query(alink_ctx *ctx, const HeadGroup &g, const Table &A, cons
   int64_t cb = (M + 255) / 256;
   if (cb > cap) cb = cap;
   refine_compose_kernel<<<(unsigned)cb, 256, 0, ctx->stream>>>((const uint32_t *)ctx->cand.p, (unsigned)M, ia, ib,
+                                                               ia ? 0u : ctx->ap_G, ctx->ap_pair0,
                                                                (int32_t *)ctx->cia.p, (int32_t *)ctx->cib.p);
   ALINK_LAUNCHED(ctx);
   const int64_t chunk = 65536;
@@ -491,7 +496,8 @@ int alink_query(alink_ctx *ctx, int group, int slot_a, int slot_b, const int32_t
     if (!TA.p || !TB.p) return alink_fail(ctx, ALINK_E_STATE, "embedding table slot not set (alink_set_table)");
     if (TA.D != TB.D || TA.dtype != ALINK_F32 || TB.dtype != ALINK_F32 || (g.feat_mode ? 2 * TA.D : TA.D) != g.D_in)
       return alink_fail(ctx, ALINK_E_INVALID, "FP32_REFINE needs fp32 tables matching the heads' fan-in");
-    if (!dia && (N > TA.M || N > TB.M)) return alink_fail(ctx, ALINK_E_INVALID, "identity pairs exceed table rows");
+    if (!dia && !ctx->ap_G && (N > TA.M || N > TB.M))
+      return alink_fail(ctx, ALINK_E_INVALID, "identity pairs exceed table rows");
     ALINK_TRY(refine_query(ctx, g, TA, TB, (const int32_t *)dia, (const int32_t *)dib, N, measure, B, base,
                            timing ? e : nullptr));
     if (timing) ALINK_CUDA(ctx, cudaEventRecord(e[4], ctx->stream));
@@ -532,6 +538,52 @@ int alink_query(alink_ctx *ctx, int group, int slot_a, int slot_b, const int32_t
     timing->launches = ctx->launches - l0;
   }
   return ALINK_OK;
+}
+
+// ------------------------------------------------------------------------------------------ all pairs
+// Probe rows [row0, row0 + nrows) of slot_probe against EVERY row of slot_gallery, pair index = i * G + j:
+// the row-at-a-time loops of utilities/generateMatrixDFW.py:28-35 and code/ALINK_MTP.py:279-288.
+static int allpairs_begin(alink_ctx *ctx, int slot_probe, int slot_gallery, int64_t row0, int64_t nrows, int64_t *N,
+                          int64_t *base) {
+  if (slot_probe < 0 || slot_probe >= ALINK_MAX_SLOTS || slot_gallery < 0 || slot_gallery >= ALINK_MAX_SLOTS)
+    return alink_fail(ctx, ALINK_E_INVALID, "bad slot");
+  const Table &P = ctx->tables[slot_probe], &G = ctx->tables[slot_gallery];
+  if (!P.p || !G.p) return alink_fail(ctx, ALINK_E_STATE, "embedding table slot not set (alink_set_table)");
+  if (row0 < 0 || nrows < 0 || row0 + nrows > P.M) return alink_fail(ctx, ALINK_E_INVALID, "probe rows outside the table");
+  if ((double)(row0 + nrows) * (double)G.M > 4294967294.0)
+    return alink_fail(ctx, ALINK_E_INVALID, "pair index (row0 + nrows) * G exceeds 2^32 - 2");
+  *N = nrows * G.M;
+  *base = row0 * G.M;
+  ctx->ap_G = (uint32_t)G.M;
+  ctx->ap_pair0 = *base;
+  return ALINK_OK;
+}
+
+int alink_score_allpairs(alink_ctx *ctx, int group, int slot_probe, int slot_gallery, int64_t row0, int64_t nrows,
+                         float *per_learner, float *consensus, int out_space) {
+  if (!ctx) return ALINK_E_INVALID;
+  ALINK_CUDA(ctx, cudaSetDevice(ctx->device));
+  int64_t N, base;
+  ALINK_TRY(allpairs_begin(ctx, slot_probe, slot_gallery, row0, nrows, &N, &base));
+  int rc = score_impl(ctx, group, ctx->tables[slot_probe], ctx->tables[slot_gallery], nullptr, nullptr, N);
+  ctx->ap_G = 0;
+  ctx->ap_pair0 = 0;
+  if (rc != ALINK_OK) return rc;
+  return emit_scores(ctx, per_learner, consensus, out_space);
+}
+
+int alink_query_allpairs(alink_ctx *ctx, int group, int slot_probe, int slot_gallery, int64_t row0, int64_t nrows,
+                         int measure, int64_t B, int64_t *idx_out, float *util_out, uint64_t *keys_out, int out_space,
+                         alink_timing *timing) {
+  if (!ctx) return ALINK_E_INVALID;
+  ALINK_CUDA(ctx, cudaSetDevice(ctx->device));
+  int64_t N, base;
+  ALINK_TRY(allpairs_begin(ctx, slot_probe, slot_gallery, row0, nrows, &N, &base));
+  const int rc = alink_query(ctx, group, slot_probe, slot_gallery, nullptr, nullptr, N, ALINK_DEVICE, measure, B, base,
+                             idx_out, util_out, keys_out, out_space, timing);
+  ctx->ap_G = 0;
+  ctx->ap_pair0 = 0;
+  return rc;
 }
 
 // ------------------------------------------------------------------------------------------ A-LINK rule

@@ -68,6 +68,9 @@ struct alink_ctx {
   float refine_max_err = 0.0f;    // max |approx - exact| utility over those candidates
   bool probs_full = true;         // ctx->probs holds all N pairs (false after a refine query)
   DevBuf cand, cia, cib, util_c, rstat;
+  // all-pairs enumeration (alink_*_allpairs): pair n = (probe row (ap_pair0 + n) / ap_G, gallery row (..) % ap_G)
+  uint32_t ap_G = 0;
+  int64_t ap_pair0 = 0;
   DevBuf xscratch;  // head_tc_ko.cuh: per-CTA bf16 feature-tile images
 };
 

@@ -23,7 +23,9 @@ struct FfmaArgs {
   const float *A;              // AMODE 0: A + learner * a_learner_stride + row * lda
   int64_t lda, a_learner_stride;
   const float *ta, *tb;        // AMODE 1/2: fp32 tables, D columns
-  const int32_t *ia, *ib;      // pair -> row (nullptr = identity)
+  const int32_t *ia, *ib;      // pair -> row (nullptr = identity, or the all-pairs enumeration when G > 0)
+  uint32_t G;                  // all-pairs: gallery rows; pair p = (p / G, p % G)
+  int64_t pair0;               // all-pairs: enumeration index of pair 0
   int D;
   int64_t row0;                // first pair of this chunk
   int M;                       // rows (pairs) in this chunk
@@ -64,8 +66,17 @@ __global__ void __launch_bounds__(256, 2) ffma_layer_kernel(const FfmaArgs a) {
     pa = a.A + (size_t)learner * a.a_learner_stride + (size_t)grow * a.lda;
   } else {
     const int64_t pair = a.row0 + grow;
-    const int64_t ra = a.ia ? (int64_t)__ldg(a.ia + pair) : pair;
-    const int64_t rb = a.ib ? (int64_t)__ldg(a.ib + pair) : pair;
+    int64_t ra, rb;
+    if (a.ia) {
+      ra = (int64_t)__ldg(a.ia + pair);
+      rb = (int64_t)__ldg(a.ib + pair);
+    } else if (a.G) {  // utilities/generateMatrixDFW.py:28-33: row-major (probe i, every gallery j)
+      const int64_t p = a.pair0 + pair;
+      ra = p / a.G;
+      rb = p - ra * a.G;
+    } else {
+      ra = rb = pair;
+    }
     pa = a.ta + (size_t)ra * a.D;
     pb = a.tb + (size_t)rb * a.D;
   }
@@ -237,6 +248,7 @@ static int ffma_head_chunk(alink_ctx *ctx, const HeadGroup &g, const float *ta, 
   FfmaArgs a;
   memset(&a, 0, sizeof(a));
   a.ta = ta; a.tb = tb; a.ia = ia; a.ib = ib; a.D = D;
+  a.G = ia ? 0u : ctx->ap_G; a.pair0 = ctx->ap_pair0;
   a.row0 = row0; a.M = Mc; a.Kdim = g.D_in; a.Ncols = g.H1;
   a.ntiles = (g.H1 + 127) / 128;
   a.W = g.pW1; a.bias = g.pb1;

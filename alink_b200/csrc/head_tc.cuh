@@ -65,7 +65,9 @@ constexpr uint32_t ACC2_COL = 256;
 
 struct Args {
   const void *ta, *tb;       // embedding tables (fp32 or bf16), D columns
-  const int32_t *ia, *ib;    // pair -> row (nullptr = identity)
+  const int32_t *ia, *ib;    // pair -> row (nullptr = identity, or the all-pairs enumeration when G > 0)
+  uint32_t G;                // all-pairs: gallery rows; pair p = (probe p / G, gallery p % G)
+  int64_t pair0;             // all-pairs: enumeration index of pair 0
   int64_t N;
   int D, nkb, hadamard;
   int K, nc, H1, H2, C, act, measure;
@@ -76,6 +78,20 @@ struct Args {
   float *util;               // [N] or nullptr
   int ntiles;
 };
+
+// table rows of pair n: explicit indices, the all-pairs enumeration, or identity
+__device__ __forceinline__ void pair_rows(const Args &a, int64_t n, int64_t &ra, int64_t &rb) {
+  if (a.ia) {
+    ra = (int64_t)__ldg(a.ia + n);
+    rb = (int64_t)__ldg(a.ib + n);
+  } else if (a.G) {
+    const int64_t p = a.pair0 + n;
+    ra = p / a.G;
+    rb = p - ra * a.G;
+  } else {
+    ra = rb = n;
+  }
+}
 
 __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
   __nv_bfloat162 h = __floats2bfloat162_rn(lo, hi);
@@ -334,8 +350,8 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
       for (int e = 0; e < 4; ++e) {
         int64_t n = tile * TILE_M + lane * 4 + e;
         if (n >= a.N) n = a.N - 1;
-        const int64_t ra = a.ia ? (int64_t)__ldg(a.ia + n) : n;
-        const int64_t rb = a.ib ? (int64_t)__ldg(a.ib + n) : n;
+        int64_t ra, rb;
+        pair_rows(a, n, ra, rb);
         ptx::bulk_prefetch_l2((const uint8_t *)a.ta + (size_t)ra * rowbytes, rowbytes);
         ptx::bulk_prefetch_l2((const uint8_t *)a.tb + (size_t)rb * rowbytes, rowbytes);
       }
@@ -451,8 +467,10 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
       for (int ii = 0; ii < 8; ++ii) {
         int64_t n = tile * TILE_M + rbase + 16 * ii;
         if (n >= a.N) n = a.N - 1;
-        ra[ii] = a.ia ? (uint32_t)__ldg(a.ia + n) : (uint32_t)n;
-        rb[ii] = a.ib ? (uint32_t)__ldg(a.ib + n) : (uint32_t)n;
+        int64_t r0, r1;
+        pair_rows(a, n, r0, r1);
+        ra[ii] = (uint32_t)r0;
+        rb[ii] = (uint32_t)r1;
       }
     };
     auto issue = [&](float4(&va)[8], float4(&vb)[8], uint32_t kb) __attribute__((always_inline)) {
@@ -584,6 +602,7 @@ static int tc_score(alink_ctx *ctx, const HeadGroup &g, const Table &A, const Ta
   tc::Args a;
   memset(&a, 0, sizeof(a));
   a.ta = A.p; a.tb = B.p; a.ia = ia; a.ib = ib; a.N = N; a.D = A.D;
+  a.G = ia ? 0u : ctx->ap_G; a.pair0 = ctx->ap_pair0;
   a.nkb = g.D_in / tc::KBLK; a.hadamard = g.feat_mode == ALINK_FEAT_ABSDIFF_HADAMARD;
   a.K = g.K; a.nc = g.H1 / tc::CHUNK_N; a.H1 = g.H1; a.H2 = g.H2; a.C = g.C; a.act = g.act; a.measure = measure;
   a.w1img = (const uint8_t *)g.W1t; a.w2img = (const uint8_t *)g.W2t;

@@ -340,8 +340,10 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel_ko(const KoArgs ka) {
       for (int ii = 0; ii < 8; ++ii) {
         int64_t n = tile * TILE_M + rbase + 16 * ii;
         if (n >= a.N) n = a.N - 1;
-        ra[ii] = a.ia ? (uint32_t)__ldg(a.ia + n) : (uint32_t)n;
-        rb[ii] = a.ib ? (uint32_t)__ldg(a.ib + n) : (uint32_t)n;
+        int64_t r0, r1;
+        tc::pair_rows(a, n, r0, r1);
+        ra[ii] = (uint32_t)r0;
+        rb[ii] = (uint32_t)r1;
       }
     };
     auto issue = [&](float4(&va)[8], float4(&vb)[8], uint32_t kb) __attribute__((always_inline)) {

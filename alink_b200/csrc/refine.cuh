@@ -37,11 +37,21 @@ __global__ void __launch_bounds__(256) refine_mark_kernel(const float *__restric
 // table rows of the candidates: cia[j] = ia[cand[j]] (or cand[j] for identity pairs)
 __global__ void __launch_bounds__(256) refine_compose_kernel(const uint32_t *__restrict__ cand, unsigned int M,
                                                              const int32_t *__restrict__ ia, const int32_t *__restrict__ ib,
-                                                             int32_t *__restrict__ cia, int32_t *__restrict__ cib) {
+                                                             uint32_t G, int64_t pair0, int32_t *__restrict__ cia,
+                                                             int32_t *__restrict__ cib) {
   for (unsigned int j = blockIdx.x * 256 + threadIdx.x; j < M; j += gridDim.x * 256) {
     const uint32_t n = cand[j];
-    cia[j] = ia ? __ldg(ia + n) : (int32_t)n;
-    cib[j] = ib ? __ldg(ib + n) : (int32_t)n;
+    if (ia) {
+      cia[j] = __ldg(ia + n);
+      cib[j] = __ldg(ib + n);
+    } else if (G) {
+      const int64_t p = pair0 + n;
+      const int64_t ra = p / G;
+      cia[j] = (int32_t)ra;
+      cib[j] = (int32_t)(p - ra * G);
+    } else {
+      cia[j] = cib[j] = (int32_t)n;
+    }
   }
 }
 

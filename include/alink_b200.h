@@ -149,6 +149,18 @@ int alink_query(alink_ctx *ctx, int group, int slot_a, int slot_b, const int32_t
                 int64_t N, int in_space, int measure, int64_t B, int64_t base, int64_t *idx_out,
                 float *util_out, uint64_t *keys_out, int out_space, alink_timing *timing);
 
+/* All pairs: probe rows [row0, row0 + nrows) of slot_probe against EVERY row of slot_gallery (G rows), without
+ * index arrays; pair index = i * G + j (row-major, the order of the reference's loops), (row0 + nrows) * G
+ * <= 2^32 - 2. Replaces the row-at-a-time scoring of utilities/generateMatrixDFW.py:27-35 (DFW score
+ * matrix), code/ALINK_MTP.py:279-288 and code/siamese.py:60-79. alink_score_allpairs: consensus is the
+ * [nrows * G][C] score matrix block; alink_query_allpairs: top-B of the utility over the block (sharding by
+ * probe-row block across GPUs: keys carry the global pair index). */
+int alink_score_allpairs(alink_ctx *ctx, int group, int slot_probe, int slot_gallery, int64_t row0, int64_t nrows,
+                         float *per_learner, float *consensus, int out_space);
+int alink_query_allpairs(alink_ctx *ctx, int group, int slot_probe, int slot_gallery, int64_t row0, int64_t nrows,
+                         int measure, int64_t B, int64_t *idx_out, float *util_out, uint64_t *keys_out, int out_space,
+                         alink_timing *timing);
+
 /* A-LINK disparity selector on column-extracted scores (code/ALINK.py:170-201):
  * p2 (T*N), p1 (N), y (N fp32 pseudo-oracle labels, may be NULL). idx_out: capacity N int64,
  * ascending pair indices; n_out / active_count: host scalars. */
