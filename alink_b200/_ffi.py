@@ -31,7 +31,7 @@ SYMBOLS = (
     "alink_set_stream", "alink_launch_count", "alink_host_alloc", "alink_host_free", "alink_set_heads", "alink_set_table",
     "alink_score_indexed", "alink_score_dense", "alink_utility", "alink_utility_from_proba",
     "alink_select_topk", "alink_topk_values", "alink_topk_keys", "alink_query", "alink_disparity_select",
-    "alink_set_refine_eps", "alink_refine_stats", "alink_score_allpairs", "alink_query_allpairs",
+    "alink_set_refine_eps", "alink_refine_stats", "alink_refine_detail", "alink_score_allpairs", "alink_query_allpairs",
 )
 
 
@@ -112,6 +112,8 @@ def load():
     L.alink_set_refine_eps.argtypes = [vp, dbl]
     L.alink_refine_stats.restype = i32
     L.alink_refine_stats.argtypes = [vp, C.POINTER(i64), C.POINTER(C.c_float)]
+    L.alink_refine_detail.restype = i32
+    L.alink_refine_detail.argtypes = [vp, C.POINTER(C.c_int), C.POINTER(dbl), C.POINTER(C.c_float), C.POINTER(C.c_int)]
     _lib = L
     return L
 
@@ -329,6 +331,13 @@ class Context:
         n, e = C.c_int64(0), C.c_float(0)
         self._check(self._L.alink_refine_stats(self._h, C.byref(n), C.byref(e)))
         return int(n.value), float(e.value)
+
+    def refine_detail(self):
+        """dict(filter, eps_used, rms_err, rounds) of the last FP32_REFINE query."""
+        f, e, r, n = C.c_int(0), C.c_double(0), C.c_float(0), C.c_int(0)
+        self._check(self._L.alink_refine_detail(self._h, C.byref(f), C.byref(e), C.byref(r), C.byref(n)))
+        return {"filter": "f16" if f.value else "bf16", "eps_used": float(e.value), "rms_err": float(r.value),
+                "rounds": int(n.value)}
 
     def set_stream(self, cuda_stream):
         """cuda_stream: integer cudaStream_t (torch.cuda.current_stream().cuda_stream) or None."""

@@ -12,6 +12,8 @@
 
 #include <math.h>
 #include <new>
+#include <vector>
+#include <algorithm>
 
 extern "C" {
 
@@ -40,7 +42,7 @@ int alink_create(alink_ctx **out, int device, unsigned flags) {
 }
 
 static void free_group(HeadGroup &g) {
-  void *ptrs[] = {g.W1, g.b1, g.W2, g.b2, g.W3, g.b3, (void *)g.pW1, g.W1t, g.W2t};
+  void *ptrs[] = {g.W1, g.b1, g.W2, g.b2, g.W3, g.b3, (void *)g.pW1, g.W1t, g.W2t, g.W1h, g.W2h};
   for (void *p : ptrs)
     if (p) cudaFree(p);
   g = HeadGroup();
@@ -142,8 +144,27 @@ int alink_set_heads(alink_ctx *ctx, int group, int K, int D_in, int H1, int H2, 
     ALINK_TRY(tc_prepare_heads(ctx, g));
     g.tc_ok = true;
   } else if (compute == ALINK_COMPUTE_FP32_REFINE) {
-    g.tc_ok = tc_prepare_heads(ctx, g) == ALINK_OK;  // shapes the tensor-core head cannot take run fully exact
+    // bf16 and half operand images (the query picks half when it cannot overflow, refine.cuh);
+    // shapes the tensor-core head cannot take run fully exact
+    g.tc_ok = tc_prepare_heads(ctx, g, 3) == ALINK_OK;
     if (!g.tc_ok) ctx->err[0] = 0;
+    std::vector<double> col((size_t)H1);
+    for (int k = 0; k < K; ++k) {
+      std::fill(col.begin(), col.end(), 0.0);
+      for (int i = 0; i < D_in; ++i) {
+        const float *row = W1[k] + (size_t)i * H1;
+        for (int j = 0; j < H1; ++j) col[j] += fabs((double)row[j]);
+      }
+      for (int j = 0; j < H1; ++j) {
+        if (!(col[j] <= g.w1_col_l1)) g.w1_col_l1 = col[j];  // NaN-propagating max
+        const double b = fabs((double)b1[k][j]);
+        if (!(b <= g.b1_absmax)) g.b1_absmax = b;
+      }
+      for (size_t i = 0; i < (size_t)H1 * H2; ++i) {
+        const double w = fabs((double)W2[k][i]);
+        if (!(w <= g.w_absmax)) g.w_absmax = w;
+      }
+    }
   }
   ALINK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));  // host_ptrs / caller buffers may go away
   g.set = true;
@@ -168,6 +189,7 @@ int alink_set_table(alink_ctx *ctx, int slot, const void *emb, int64_t M, int D,
     t.p = t.own.p;
   }
   t.M = M; t.D = D; t.dtype = dtype;
+  t.absmax = -1.0;
   return ALINK_OK;
 }
 
@@ -386,77 +408,125 @@ int alink_topk_keys(alink_ctx *ctx, const uint64_t *keys, int64_t n, int64_t B, 
 // ------------------------------------------------------------------------------------------ fused step
 // FP32_REFINE (refine.cuh): bf16 tensor-core filter over all N pairs, bit-exact re-score of the candidates.
 // On return ctx->sel_keys holds the B selected keys (device, sorted). ev (6 events) may be null.
-static int refine_query(alink_ctx *ctx, const HeadGroup &g, const Table &A, const Table &Bt, const int32_t *ia,
+// max |element| of an fp32 table, computed once per alink_set_table (one streaming pass)
+static int table_absmax(alink_ctx *ctx, Table &t, double *out) {
+  if (t.absmax < 0.0) {
+    ALINK_TRY(dev_reserve(ctx, ctx->rstat, 32));
+    unsigned int *bits = (unsigned int *)ctx->rstat.p;
+    ALINK_CUDA(ctx, cudaMemsetAsync(bits, 0, 4, ctx->stream));
+    absmax_kernel<<<ctx->sm_count * 8, 256, 0, ctx->stream>>>((const float4 *)t.p, t.M * t.D / 4, bits);
+    ALINK_LAUNCHED(ctx);
+    unsigned int h = 0;
+    ALINK_CUDA(ctx, cudaMemcpyAsync(&h, bits, 4, cudaMemcpyDeviceToHost, ctx->stream));
+    ALINK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    float f;
+    memcpy(&f, &h, 4);
+    t.absmax = (double)f;  // +inf stays +inf (fails the bound); NaN inputs never reach a finite utility anyway
+  }
+  *out = t.absmax;
+  return ALINK_OK;
+}
+
+static const double REFINE_EPS_BF16 = 1.2e-2;  // measured max |dp| 9.0e-3 (profiles/r1_refine_filter_error.txt)
+static const double REFINE_EPS_F16 = 1.5e-3;   // measured max |dp| 8.4e-4, rms 1.2e-4 (same file)
+
+static int refine_query(alink_ctx *ctx, const HeadGroup &g, Table &A, Table &Bt, const int32_t *ia,
                         const int32_t *ib, int64_t N, int measure, int64_t B, int64_t base, cudaEvent_t *ev) {
   ctx->N = N; ctx->sK = g.K; ctx->sC = g.C; ctx->util_valid = false; ctx->probs_full = false;
+  // operand format of the filter: half unless a feature or hidden activation could exceed its range
+  static const int fmt_env = [] { const char *e = getenv("ALINK_REFINE_FMT"); return e ? atoi(e) : 0; }();  // 1 = force bf16
+  bool f16 = g.W1h && g.W2h && fmt_env != 1;
+  if (f16) {
+    double ma, mb;
+    ALINK_TRY(table_absmax(ctx, A, &ma));
+    ALINK_TRY(table_absmax(ctx, Bt, &mb));
+    double xmax = ma + mb;
+    if (g.feat_mode == ALINK_FEAT_ABSDIFF_HADAMARD && ma * mb > xmax) xmax = ma * mb;
+    const double h1max = xmax * g.w1_col_l1 + g.b1_absmax;
+    f16 = xmax < 6.0e4 && h1max < 6.0e4 && g.w_absmax < 6.0e4;  // false for NaN / inf
+  }
   ALINK_TRY(dev_reserve(ctx, ctx->util, sizeof(float) * (size_t)N));
   ALINK_TRY(dev_reserve(ctx, ctx->sel_state, sizeof(SelectState)));
   ALINK_TRY(dev_reserve(ctx, ctx->cand, sizeof(uint32_t) * (size_t)N));
-  ALINK_TRY(dev_reserve(ctx, ctx->rstat, 16));
+  ALINK_TRY(dev_reserve(ctx, ctx->rstat, 32));
   float *util_a = (float *)ctx->util.p;
   SelectState *st = (SelectState *)ctx->sel_state.p;
-  unsigned int *rstat = (unsigned int *)ctx->rstat.p;  // [0] candidate count, [1] max error bits
+  unsigned int *rstat = (unsigned int *)ctx->rstat.p;  // [0] candidate count, [1] max error bits, [2..3] sum sq
   // (1) approximate utilities of every pair, fused K-learner reduction in the kernel's epilogue
-  ALINK_TRY(tc_score(ctx, g, A, Bt, ia, ib, N, nullptr, util_a, measure));
+  ALINK_TRY(tc_score(ctx, g, A, Bt, ia, ib, N, nullptr, util_a, measure, f16));
   if (ev) ALINK_CUDA(ctx, cudaEventRecord(ev[2], ctx->stream));
-  // (2) B-th largest approximate utility, (3) candidates within 2 eps of it
+  // (2) B-th largest approximate utility
   KeySrc asrc{util_a, nullptr, 0, nullptr};
   ALINK_TRY(select_threshold(ctx, asrc, N, B, st));
-  ALINK_CUDA(ctx, cudaMemsetAsync(rstat, 0, 16, ctx->stream));
   int64_t blocks = (N + 2047) / 2048;
   const int64_t cap = (int64_t)ctx->sm_count * 8;
   if (blocks > cap) blocks = cap;
   // eps bounds the error of a PROBABILITY; a measure moves by at most `scale` times that near the top
   // (margin = p(1) - p(2) doubles it; KL-max compares a learner with the mean: measured 4.3x)
   static const double scale[ALINK_UTIL_COUNT] = {1.0, 2.0, 1.25, 1.0, 1.25, 5.0};
-  refine_mark_kernel<<<(unsigned)blocks, 256, 0, ctx->stream>>>(util_a, N, st, (float)(2.0 * ctx->refine_eps * scale[measure]),
-                                                                (uint32_t *)ctx->cand.p, rstat);
-  ALINK_LAUNCHED(ctx);
-  unsigned int hM = 0;
-  ALINK_CUDA(ctx, cudaMemcpyAsync(&hM, rstat, 4, cudaMemcpyDeviceToHost, ctx->stream));
-  ALINK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-  const int64_t M = (int64_t)hM;
-  if (M < B) return alink_fail(ctx, ALINK_E_STATE, "refine: %lld candidates < B=%lld", (long long)M, (long long)B);
-  // (4) exact re-score of the candidates (oracle summation order, CUDA cores)
-  ALINK_TRY(dev_reserve(ctx, ctx->cia, sizeof(int32_t) * (size_t)M));
-  ALINK_TRY(dev_reserve(ctx, ctx->cib, sizeof(int32_t) * (size_t)M));
-  ALINK_TRY(dev_reserve(ctx, ctx->util_c, sizeof(float) * (size_t)M));
-  ALINK_TRY(dev_reserve(ctx, ctx->probs, sizeof(float) * (size_t)M * g.K * g.C));
-  int64_t cb = (M + 255) / 256;
-  if (cb > cap) cb = cap;
-  refine_compose_kernel<<<(unsigned)cb, 256, 0, ctx->stream>>>((const uint32_t *)ctx->cand.p, (unsigned)M, ia, ib,
-                                                               ia ? 0u : ctx->ap_G, ctx->ap_pair0,
-                                                               (int32_t *)ctx->cia.p, (int32_t *)ctx->cib.p);
-  ALINK_LAUNCHED(ctx);
-  const int64_t chunk = 65536;
-  const int Mc_max = (int)(M < chunk ? M : chunk);
-  const int64_t lstride = (int64_t)Mc_max * g.H1;
-  ALINK_TRY(dev_reserve(ctx, ctx->h1ws, sizeof(float) * (size_t)lstride * g.K));
-  for (int64_t row0 = 0; row0 < M; row0 += chunk) {
-    const int Mc = (int)((M - row0) < chunk ? (M - row0) : chunk);
-    ALINK_TRY(ffma_head_chunk(ctx, g, (const float *)A.p, (const float *)Bt.p, A.D, (const int32_t *)ctx->cia.p,
-                              (const int32_t *)ctx->cib.p, row0, Mc, (float *)ctx->h1ws.p, lstride,
-                              (float *)ctx->probs.p));
+  double eps = ctx->refine_eps > 0.0 ? ctx->refine_eps : (f16 ? REFINE_EPS_F16 : REFINE_EPS_BF16);
+  ctx->refine_f16 = f16 ? 1 : 0;
+  for (int round = 1;; ++round) {
+    // (3) candidates within 2 eps of the threshold
+    ALINK_CUDA(ctx, cudaMemsetAsync(rstat, 0, 32, ctx->stream));
+    refine_mark_kernel<<<(unsigned)blocks, 256, 0, ctx->stream>>>(util_a, N, st, (float)(2.0 * eps * scale[measure]),
+                                                                  (uint32_t *)ctx->cand.p, rstat);
+    ALINK_LAUNCHED(ctx);
+    unsigned int hM = 0;
+    ALINK_CUDA(ctx, cudaMemcpyAsync(&hM, rstat, 4, cudaMemcpyDeviceToHost, ctx->stream));
+    ALINK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    const int64_t M = (int64_t)hM;
+    if (M < B) return alink_fail(ctx, ALINK_E_STATE, "refine: %lld candidates < B=%lld", (long long)M, (long long)B);
+    // (4) exact re-score of the candidates (oracle summation order, CUDA cores)
+    ALINK_TRY(dev_reserve(ctx, ctx->cia, sizeof(int32_t) * (size_t)M));
+    ALINK_TRY(dev_reserve(ctx, ctx->cib, sizeof(int32_t) * (size_t)M));
+    ALINK_TRY(dev_reserve(ctx, ctx->util_c, sizeof(float) * (size_t)M));
+    ALINK_TRY(dev_reserve(ctx, ctx->probs, sizeof(float) * (size_t)M * g.K * g.C));
+    int64_t cb = (M + 255) / 256;
+    if (cb > cap) cb = cap;
+    refine_compose_kernel<<<(unsigned)cb, 256, 0, ctx->stream>>>((const uint32_t *)ctx->cand.p, (unsigned)M, ia, ib,
+                                                                 ia ? 0u : ctx->ap_G, ctx->ap_pair0,
+                                                                 (int32_t *)ctx->cia.p, (int32_t *)ctx->cib.p);
+    ALINK_LAUNCHED(ctx);
+    const int64_t chunk = 65536;
+    const int Mc_max = (int)(M < chunk ? M : chunk);
+    const int64_t lstride = (int64_t)Mc_max * g.H1;
+    ALINK_TRY(dev_reserve(ctx, ctx->h1ws, sizeof(float) * (size_t)lstride * g.K));
+    for (int64_t row0 = 0; row0 < M; row0 += chunk) {
+      const int Mc = (int)((M - row0) < chunk ? (M - row0) : chunk);
+      ALINK_TRY(ffma_head_chunk(ctx, g, (const float *)A.p, (const float *)Bt.p, A.D, (const int32_t *)ctx->cia.p,
+                                (const int32_t *)ctx->cib.p, row0, Mc, (float *)ctx->h1ws.p, lstride,
+                                (float *)ctx->probs.p));
+    }
+    ALINK_TRY(launch_utility(ctx, (const float *)ctx->probs.p, M, g.K, g.C, measure, (float *)ctx->util_c.p, nullptr));
+    refine_maxerr_kernel<<<(unsigned)cb, 256, 0, ctx->stream>>>((const float *)ctx->util_c.p, util_a,
+                                                                (const uint32_t *)ctx->cand.p, (unsigned)M, rstat);
+    ALINK_LAUNCHED(ctx);
+    if (ev) ALINK_CUDA(ctx, cudaEventRecord(ev[3], ctx->stream));
+    // (5) exact top-B among the candidates, keyed by the pairs' original indices
+    KeySrc csrc{(const float *)ctx->util_c.p, nullptr, (uint64_t)base, (const uint32_t *)ctx->cand.p};
+    ALINK_TRY(topk_device(ctx, csrc, M, B));
+    unsigned int hs[4] = {0, 0, 0, 0};
+    ALINK_CUDA(ctx, cudaMemcpyAsync(hs, rstat, 16, cudaMemcpyDeviceToHost, ctx->stream));
+    ALINK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    double sumsq;
+    memcpy(&sumsq, hs + 2, 8);
+    ctx->refine_survivors = M;
+    memcpy(&ctx->refine_max_err, hs + 1, 4);
+    ctx->refine_rms_err = (float)sqrt(sumsq / (double)M);
+    ctx->refine_eps_used = eps;
+    ctx->refine_rounds = round;
+    // the bound must hold on every candidate we can check; if not, widen it and redo (3)-(5)
+    const double seen = (double)ctx->refine_max_err / scale[measure];
+    if (seen <= eps || M >= N || round >= 4) break;
+    eps = 2.0 * (seen > eps ? seen : eps);
   }
-  ALINK_TRY(launch_utility(ctx, (const float *)ctx->probs.p, M, g.K, g.C, measure, (float *)ctx->util_c.p, nullptr));
-  refine_maxerr_kernel<<<(unsigned)cb, 256, 0, ctx->stream>>>((const float *)ctx->util_c.p, util_a,
-                                                              (const uint32_t *)ctx->cand.p, (unsigned)M, rstat + 1);
-  ALINK_LAUNCHED(ctx);
-  if (ev) ALINK_CUDA(ctx, cudaEventRecord(ev[3], ctx->stream));
-  // (5) exact top-B among the candidates, keyed by the pairs' original indices
-  KeySrc csrc{(const float *)ctx->util_c.p, nullptr, (uint64_t)base, (const uint32_t *)ctx->cand.p};
-  ALINK_TRY(topk_device(ctx, csrc, M, B));
-  unsigned int hbits = 0;
-  ALINK_CUDA(ctx, cudaMemcpyAsync(&hbits, rstat + 1, 4, cudaMemcpyDeviceToHost, ctx->stream));
-  ALINK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-  ctx->refine_survivors = M;
-  memcpy(&ctx->refine_max_err, &hbits, 4);
   return ALINK_OK;
 }
 
 int alink_set_refine_eps(alink_ctx *ctx, double eps) {
   if (!ctx) return ALINK_E_INVALID;
-  if (!(eps > 0.0 && eps < 1.0)) return alink_fail(ctx, ALINK_E_INVALID, "eps outside (0, 1)");
+  if (!(eps >= 0.0 && eps < 1.0)) return alink_fail(ctx, ALINK_E_INVALID, "eps outside [0, 1) (0 = per-format default)");
   ctx->refine_eps = eps;
   return ALINK_OK;
 }
@@ -465,6 +535,15 @@ int alink_refine_stats(const alink_ctx *ctx, int64_t *survivors, float *max_err)
   if (!ctx) return ALINK_E_INVALID;
   if (survivors) *survivors = ctx->refine_survivors;
   if (max_err) *max_err = ctx->refine_max_err;
+  return ALINK_OK;
+}
+
+int alink_refine_detail(const alink_ctx *ctx, int *filter_f16, double *eps_used, float *rms_err, int *rounds) {
+  if (!ctx) return ALINK_E_INVALID;
+  if (filter_f16) *filter_f16 = ctx->refine_f16;
+  if (eps_used) *eps_used = ctx->refine_eps_used;
+  if (rms_err) *rms_err = ctx->refine_rms_err;
+  if (rounds) *rounds = ctx->refine_rounds;
   return ALINK_OK;
 }
 
@@ -492,7 +571,7 @@ int alink_query(alink_ctx *ctx, int group, int slot_a, int slot_b, const int32_t
       ctx->groups[group].compute == ALINK_COMPUTE_FP32_REFINE && ctx->groups[group].tc_ok &&
       measure != ALINK_UTIL_VOTE_ENTROPY && B > 0 && N >= 8192) {
     const HeadGroup &g = ctx->groups[group];
-    const Table &TA = ctx->tables[slot_a], &TB = ctx->tables[slot_b];
+    Table &TA = ctx->tables[slot_a], &TB = ctx->tables[slot_b];
     if (!TA.p || !TB.p) return alink_fail(ctx, ALINK_E_STATE, "embedding table slot not set (alink_set_table)");
     if (TA.D != TB.D || TA.dtype != ALINK_F32 || TB.dtype != ALINK_F32 || (g.feat_mode ? 2 * TA.D : TA.D) != g.D_in)
       return alink_fail(ctx, ALINK_E_INVALID, "FP32_REFINE needs fp32 tables matching the heads' fan-in");

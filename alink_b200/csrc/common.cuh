@@ -2,6 +2,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <cuda_bf16.h>
+#include <cuda_fp16.h>
 #include <stdint.h>
 #include <stdio.h>
 #include <string.h>
@@ -24,7 +25,11 @@ struct HeadGroup {
   const float **pW1 = nullptr, **pb1 = nullptr, **pW2 = nullptr, **pb2 = nullptr, **pW3 = nullptr, **pb3 = nullptr;
   // bf16 operands for the tcgen05 path, N-major ("[out][in]", K contiguous): W1t [K][H1][D_in], W2t [K][H2][H1]
   __nv_bfloat16 *W1t = nullptr, *W2t = nullptr;
+  // the same images in IEEE half (FP32_REFINE's default filter format)
+  __half *W1h = nullptr, *W2h = nullptr;
   bool tc_ok = false;  // the tensor-core images exist (shape supported by head_tc.cuh)
+  // bound for "no half overflow": max_j sum_k |W1[k][j]| over learners, max |b1| (host, at alink_set_heads)
+  double w1_col_l1 = 0.0, b1_absmax = 0.0, w_absmax = 0.0;
 };
 
 struct Table {
@@ -33,6 +38,7 @@ struct Table {
   int D = 0;
   int dtype = ALINK_F32;
   DevBuf own;
+  double absmax = -1.0;  // max |element| (lazy, refine.cuh; reset by alink_set_table)
 };
 
 struct SelectState;  // topk.cuh
@@ -63,9 +69,13 @@ struct alink_ctx {
   DevBuf sel_state, sel_keys, sel_idx, sel_util, sel_in;
   DevBuf misc0, misc1, misc2, misc3;
   // FP32_REFINE (refine.cuh)
-  double refine_eps = 6e-3;       // assumed bound on |bf16 utility - fp32 utility|
+  double refine_eps = 0.0;        // caller's bound on |filter probability - fp32 probability| (0 = per-format default)
   int64_t refine_survivors = 0;   // candidates re-scored exactly by the last alink_query
   float refine_max_err = 0.0f;    // max |approx - exact| utility over those candidates
+  float refine_rms_err = 0.0f;    // rms of the same
+  double refine_eps_used = 0.0;   // bound the last query ran with (after any widening)
+  int refine_rounds = 0;          // mark + re-score rounds of the last query (> 1: the bound had to be widened)
+  int refine_f16 = 0;             // the last query's filter ran on half (1) or bf16 (0) operands
   bool probs_full = true;         // ctx->probs holds all N pairs (false after a refine query)
   DevBuf cand, cia, cib, util_c, rstat;
   // all-pairs enumeration (alink_*_allpairs): pair n = (probe row (ap_pair0 + n) / ap_G, gallery row (..) % ap_G)

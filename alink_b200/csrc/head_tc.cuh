@@ -97,6 +97,16 @@ __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
   __nv_bfloat162 h = __floats2bfloat162_rn(lo, hi);
   return *reinterpret_cast<uint32_t *>(&h);
 }
+__device__ __forceinline__ uint32_t pack_f16(float lo, float hi) {
+  __half2 h = __floats2half2_rn(lo, hi);
+  return *reinterpret_cast<uint32_t *>(&h);
+}
+// operand format of the tensor-core path: bf16 (BF16_TC, and the fallback filter of FP32_REFINE) or IEEE
+// half (the default FP32_REFINE filter: 8x smaller rounding error, so 8x fewer candidates to re-score)
+template <bool F16>
+__device__ __forceinline__ uint32_t pack16(float lo, float hi) {
+  return F16 ? pack_f16(lo, hi) : pack_bf16(lo, hi);
+}
 __device__ __forceinline__ void sts128(uint32_t addr, uint32_t x, uint32_t y, uint32_t z, uint32_t w) {
   asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(x), "r"(y), "r"(z), "r"(w) : "memory");
 }
@@ -125,7 +135,7 @@ __device__ __forceinline__ float4 ldg_bf4(const __nv_bfloat16 *p) {  // 4 bf16 -
 // NCTA = 2: CTA pairs (cluster of 2, tcgen05 cta_group::2, M = 256): each CTA keeps its own 128-pair tile,
 //           loads HALF of every weight block, and the leader's MMAs read both halves — half the TMA
 //           traffic and half the B-operand shared-memory reads per CTA.
-template <bool TAB_BF16, int NCTA>
+template <bool TAB_BF16, int NCTA, bool F16>
 __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
   constexpr uint32_t KPS = NCTA;                // k-blocks per ring slot (a pair CTA holds half of each block)
   constexpr uint32_t HB = STAGE_BYTES / NCTA;   // bytes of this CTA's part of one [128 n x 64 k] weight block
@@ -228,8 +238,8 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
     // Converged warp, uniform control flow; one elected lane issues tcgen05.mma / tcgen05.commit.
     ptx::setmaxnreg_dec<56>();
     const uint32_t leader = ptx::elect_one();
-    const uint32_t idesc1 = ptx::umma_idesc_bf16(TILE_M * NCTA, CHUNK_N);
-    const uint32_t idesc2 = ptx::umma_idesc_bf16(TILE_M * NCTA, a.H2);
+    const uint32_t idesc1 = F16 ? ptx::umma_idesc_f16(TILE_M * NCTA, CHUNK_N) : ptx::umma_idesc_bf16(TILE_M * NCTA, CHUNK_N);
+    const uint32_t idesc2 = F16 ? ptx::umma_idesc_f16(TILE_M * NCTA, a.H2) : ptx::umma_idesc_bf16(TILE_M * NCTA, a.H2);
     const uint32_t kb2_step = ((uint32_t)a.H2 * 128u / NCTA) >> 4;  // layer-2 B sub-block stride, 16-byte units
     constexpr uint64_t STAGE_STEP = STAGE_BYTES >> 4;
     constexpr uint64_t HB_STEP = HB >> 4;
@@ -399,8 +409,8 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
           const float x5 = fmaxf(__fadd_rn(__uint_as_float(v[e * 8 + 5]), bb.y), 0.0f);
           const float x6 = fmaxf(__fadd_rn(__uint_as_float(v[e * 8 + 6]), bb.z), 0.0f);
           const float x7 = fmaxf(__fadd_rn(__uint_as_float(v[e * 8 + 7]), bb.w), 0.0f);
-          sts128(hbase + ptx::sw128_offset((uint32_t)et, (jj & 1u) * 4 + e), pack_bf16(x0, x1), pack_bf16(x2, x3),
-                 pack_bf16(x4, x5), pack_bf16(x6, x7));
+          sts128(hbase + ptx::sw128_offset((uint32_t)et, (jj & 1u) * 4 + e), pack16<F16>(x0, x1), pack16<F16>(x2, x3),
+                 pack16<F16>(x4, x5), pack16<F16>(x6, x7));
         }
       }
       ptx::fence_proxy_async_smem();
@@ -502,8 +512,8 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
           x2 = fabsf(__fsub_rn(va[ii].z, vb[ii].z)); x3 = fabsf(__fsub_rn(va[ii].w, vb[ii].w));
         }
         const uint32_t r = (uint32_t)(rbase + 16 * ii);
-        sts64(xb + ptx::sw128_offset(r, (uint32_t)sub >> 1) + ((uint32_t)sub & 1u) * 8u, pack_bf16(x0, x1),
-              pack_bf16(x2, x3));
+        sts64(xb + ptx::sw128_offset(r, (uint32_t)sub >> 1) + ((uint32_t)sub & 1u) * 8u, pack16<F16>(x0, x1),
+              pack16<F16>(x2, x3));
       }
       ptx::fence_proxy_async_smem();
       ptx::mbar_arrive(bar(X_FULL + kb));
@@ -540,6 +550,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
 }
 
 // ---- one-time weight repack: Keras (in,out) fp32 -> bf16 UMMA operand images (N rows x 64 k, swizzled)
+template <bool F16>
 __global__ void prep_w1_kernel(const float *__restrict__ W1, uint8_t *__restrict__ img, int K, int Din, int H1) {
   const int nc = H1 / CHUNK_N, nkb = Din / KBLK;
   const int64_t total = (int64_t)K * nc * nkb * 1024;  // 16-byte chunks
@@ -549,11 +560,12 @@ __global__ void prep_w1_kernel(const float *__restrict__ W1, uint8_t *__restrict
     const int kb = (int)(blk % nkb), c = (int)((blk / nkb) % nc), l = (int)(blk / ((int64_t)nkb * nc));
     const float *src = W1 + ((size_t)l * Din + (size_t)kb * KBLK + chunk * 8) * H1 + c * CHUNK_N + r;
     uint32_t w[4];
-    for (int h = 0; h < 4; ++h) w[h] = pack_bf16(src[(size_t)(2 * h) * H1], src[(size_t)(2 * h + 1) * H1]);
+    for (int h = 0; h < 4; ++h) w[h] = pack16<F16>(src[(size_t)(2 * h) * H1], src[(size_t)(2 * h + 1) * H1]);
     *reinterpret_cast<uint4 *>(img + (size_t)blk * STAGE_BYTES + ptx::sw128_offset((uint32_t)r, (uint32_t)chunk)) =
         make_uint4(w[0], w[1], w[2], w[3]);
   }
 }
+template <bool F16>
 __global__ void prep_w2_kernel(const float *__restrict__ W2, uint8_t *__restrict__ img, int K, int H1, int H2) {
   const int nc = H1 / CHUNK_N;
   const int64_t total = (int64_t)K * nc * 2 * H2 * 8;
@@ -566,7 +578,7 @@ __global__ void prep_w2_kernel(const float *__restrict__ W2, uint8_t *__restrict
     const int c = (int)(blk % nc), l = (int)(blk / nc);
     const float *src = W2 + ((size_t)l * H1 + (size_t)c * CHUNK_N + kb2 * KBLK + chunk * 8) * H2 + n;
     uint32_t w[4];
-    for (int h = 0; h < 4; ++h) w[h] = pack_bf16(src[(size_t)(2 * h) * H2], src[(size_t)(2 * h + 1) * H2]);
+    for (int h = 0; h < 4; ++h) w[h] = pack16<F16>(src[(size_t)(2 * h) * H2], src[(size_t)(2 * h + 1) * H2]);
     *reinterpret_cast<uint4 *>(img + (size_t)blk * (2 * H2 * 128) + (size_t)kb2 * (H2 * 128) +
                                ptx::sw128_offset((uint32_t)n, (uint32_t)chunk)) = make_uint4(w[0], w[1], w[2], w[3]);
   }
@@ -574,7 +586,8 @@ __global__ void prep_w2_kernel(const float *__restrict__ W2, uint8_t *__restrict
 
 }  // namespace tc
 
-static int tc_prepare_heads(alink_ctx *ctx, HeadGroup &g) {
+// formats: bit 0 = bf16 images, bit 1 = half images
+static int tc_prepare_heads(alink_ctx *ctx, HeadGroup &g, int formats = 1) {
   if (g.D_in % tc::KBLK || g.D_in > 8192)
     return alink_fail(ctx, ALINK_E_UNSUPPORTED, "BF16_TC head needs fan-in %% 64 == 0 and <= 8192 (got %d)", g.D_in);
   if (g.D_in > tc::MAX_KB * tc::KBLK && g.H1 > 512)
@@ -583,35 +596,47 @@ static int tc_prepare_heads(alink_ctx *ctx, HeadGroup &g) {
     return alink_fail(ctx, ALINK_E_UNSUPPORTED, "BF16_TC head needs H1 %% 128 == 0 (got %d)", g.H1);
   if (g.H2 != 32 && g.H2 != 64) return alink_fail(ctx, ALINK_E_UNSUPPORTED, "BF16_TC head needs H2 in {32, 64}");
   const size_t w1b = (size_t)g.K * g.D_in * g.H1 * 2, w2b = (size_t)g.K * g.H1 * g.H2 * 2;
-  ALINK_CUDA(ctx, cudaMalloc((void **)&g.W1t, w1b));
-  ALINK_CUDA(ctx, cudaMalloc((void **)&g.W2t, w2b));
-  tc::prep_w1_kernel<<<ctx->sm_count * 4, 256, 0, ctx->stream>>>(g.W1, (uint8_t *)g.W1t, g.K, g.D_in, g.H1);
-  ALINK_LAUNCHED(ctx);
-  tc::prep_w2_kernel<<<ctx->sm_count, 256, 0, ctx->stream>>>(g.W2, (uint8_t *)g.W2t, g.K, g.H1, g.H2);
-  ALINK_LAUNCHED(ctx);
+  if (formats & 1) {
+    ALINK_CUDA(ctx, cudaMalloc((void **)&g.W1t, w1b));
+    ALINK_CUDA(ctx, cudaMalloc((void **)&g.W2t, w2b));
+    tc::prep_w1_kernel<false><<<ctx->sm_count * 4, 256, 0, ctx->stream>>>(g.W1, (uint8_t *)g.W1t, g.K, g.D_in, g.H1);
+    ALINK_LAUNCHED(ctx);
+    tc::prep_w2_kernel<false><<<ctx->sm_count, 256, 0, ctx->stream>>>(g.W2, (uint8_t *)g.W2t, g.K, g.H1, g.H2);
+    ALINK_LAUNCHED(ctx);
+  }
+  if (formats & 2) {
+    ALINK_CUDA(ctx, cudaMalloc((void **)&g.W1h, w1b));
+    ALINK_CUDA(ctx, cudaMalloc((void **)&g.W2h, w2b));
+    tc::prep_w1_kernel<true><<<ctx->sm_count * 4, 256, 0, ctx->stream>>>(g.W1, (uint8_t *)g.W1h, g.K, g.D_in, g.H1);
+    ALINK_LAUNCHED(ctx);
+    tc::prep_w2_kernel<true><<<ctx->sm_count, 256, 0, ctx->stream>>>(g.W2, (uint8_t *)g.W2h, g.K, g.H1, g.H2);
+    ALINK_LAUNCHED(ctx);
+  }
   return ALINK_OK;
 }
 
-static int tc_score_ko(alink_ctx *ctx, const HeadGroup &g, const tc::Args &a0, bool tb16);  // head_tc_ko.cuh
+static int tc_score_ko(alink_ctx *ctx, const HeadGroup &g, const tc::Args &a0, bool tb16, bool f16);  // head_tc_ko.cuh
 
 // Scores N pairs with every learner; probs [N][K][C] and/or util [N] (measure) are written by the
 // kernel's epilogue. ia/ib are device pointers or null.
 static int tc_score(alink_ctx *ctx, const HeadGroup &g, const Table &A, const Table &B, const int32_t *ia,
-                    const int32_t *ib, int64_t N, float *probs, float *util, int measure) {
-  if (!g.W1t || !g.W2t) return alink_fail(ctx, ALINK_E_STATE, "BF16_TC weights were not prepared");
+                    const int32_t *ib, int64_t N, float *probs, float *util, int measure, bool f16 = false) {
+  if (f16 ? (!g.W1h || !g.W2h || A.dtype != ALINK_F32) : (!g.W1t || !g.W2t))
+    return alink_fail(ctx, ALINK_E_STATE, "tensor-core weight images were not prepared");
   tc::Args a;
   memset(&a, 0, sizeof(a));
   a.ta = A.p; a.tb = B.p; a.ia = ia; a.ib = ib; a.N = N; a.D = A.D;
   a.G = ia ? 0u : ctx->ap_G; a.pair0 = ctx->ap_pair0;
   a.nkb = g.D_in / tc::KBLK; a.hadamard = g.feat_mode == ALINK_FEAT_ABSDIFF_HADAMARD;
   a.K = g.K; a.nc = g.H1 / tc::CHUNK_N; a.H1 = g.H1; a.H2 = g.H2; a.C = g.C; a.act = g.act; a.measure = measure;
-  a.w1img = (const uint8_t *)g.W1t; a.w2img = (const uint8_t *)g.W2t;
+  a.w1img = (const uint8_t *)(f16 ? (void *)g.W1h : (void *)g.W1t);
+  a.w2img = (const uint8_t *)(f16 ? (void *)g.W2h : (void *)g.W2t);
   a.b1 = g.b1; a.b2 = g.b2; a.W3 = g.W3; a.b3 = g.b3;
   a.probs = probs; a.util = util;
   a.ntiles = (int)((N + tc::TILE_M - 1) / tc::TILE_M);
   // Wide features (the tile does not fit in shared memory) take the k-outer kernel; ALINK_TC_KO=1 forces it.
   static const int ko_env = [] { const char *e = getenv("ALINK_TC_KO"); return e ? atoi(e) : 0; }();
-  if (a.nkb > tc::MAX_KB || (ko_env == 1 && g.H1 <= 512)) return tc_score_ko(ctx, g, a, A.dtype == ALINK_BF16);
+  if (a.nkb > tc::MAX_KB || (ko_env == 1 && g.H1 <= 512)) return tc_score_ko(ctx, g, a, A.dtype == ALINK_BF16, f16);
   // CTA pairs (cta_group::2) by default; ALINK_TC_NCTA=1 selects the independent-CTA variant.
   static const int ncta_env = [] { const char *e = getenv("ALINK_TC_NCTA"); return e ? atoi(e) : 2; }();
   const int ncta = (ncta_env == 1 || ctx->sm_count < 2 || (a.nkb & 1)) ? 1 : 2;  // a pair slot holds 2 k-blocks
@@ -632,10 +657,10 @@ static int tc_score(alink_ctx *ctx, const HeadGroup &g, const Table &A, const Ta
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    kern = tb16 ? tc::head_kernel<true, 2> : tc::head_kernel<false, 2>;
+    kern = f16 ? tc::head_kernel<false, 2, true> : tb16 ? tc::head_kernel<true, 2, false> : tc::head_kernel<false, 2, false>;
   } else {
     cfg.gridDim = dim3((unsigned)(a.ntiles < ctx->sm_count ? a.ntiles : ctx->sm_count));
-    kern = tb16 ? tc::head_kernel<true, 1> : tc::head_kernel<false, 1>;
+    kern = f16 ? tc::head_kernel<false, 1, true> : tb16 ? tc::head_kernel<true, 1, false> : tc::head_kernel<false, 1, false>;
   }
   ALINK_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tc::SMEM_BYTES));
   ALINK_CUDA(ctx, cudaLaunchKernelEx(&cfg, kern, a));

@@ -55,7 +55,7 @@ __device__ __forceinline__ void stg64(void *p, uint32_t x, uint32_t y) {
   asm volatile("st.global.v2.b32 [%0], {%1, %2};" ::"l"(p), "r"(x), "r"(y) : "memory");
 }
 
-template <bool TAB_BF16>
+template <bool TAB_BF16, bool F16>
 __global__ void __launch_bounds__(NTHREADS, 1) head_kernel_ko(const KoArgs ka) {
   const Args &a = ka.a;
   const uint32_t rank = ptx::cluster_ctarank();
@@ -153,8 +153,8 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel_ko(const KoArgs ka) {
     // ------------------------------------------------------------------ MMA issuer (leader CTA)
     ptx::setmaxnreg_dec<56>();
     const uint32_t leader = ptx::elect_one();
-    const uint32_t idesc1 = ptx::umma_idesc_bf16(2 * TILE_M, CHUNK_N);
-    const uint32_t idesc2 = ptx::umma_idesc_bf16(2 * TILE_M, a.H2);
+    const uint32_t idesc1 = F16 ? ptx::umma_idesc_f16(2 * TILE_M, CHUNK_N) : ptx::umma_idesc_bf16(2 * TILE_M, CHUNK_N);
+    const uint32_t idesc2 = F16 ? ptx::umma_idesc_f16(2 * TILE_M, a.H2) : ptx::umma_idesc_bf16(2 * TILE_M, a.H2);
     const uint32_t kb2_step = ((uint32_t)a.H2 * 64u) >> 4;  // this CTA's half of a layer-2 k-block, 16-byte units
     const uint64_t rdesc0 = ptx::umma_desc_sw128(sbase + ROFF);
     const uint64_t hdesc0 = ptx::umma_desc_sw128(sbase + HOFF);
@@ -275,8 +275,8 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel_ko(const KoArgs ka) {
               const float x5 = fmaxf(__fadd_rn(__uint_as_float(r[e * 8 + 5]), bb.y), 0.0f);
               const float x6 = fmaxf(__fadd_rn(__uint_as_float(r[e * 8 + 6]), bb.z), 0.0f);
               const float x7 = fmaxf(__fadd_rn(__uint_as_float(r[e * 8 + 7]), bb.w), 0.0f);
-              tc::sts128(hbase + ptx::sw128_offset((uint32_t)et, (jj & 1u) * 4 + e), tc::pack_bf16(x0, x1),
-                         tc::pack_bf16(x2, x3), tc::pack_bf16(x4, x5), tc::pack_bf16(x6, x7));
+              tc::sts128(hbase + ptx::sw128_offset((uint32_t)et, (jj & 1u) * 4 + e), tc::pack16<F16>(x0, x1),
+                         tc::pack16<F16>(x2, x3), tc::pack16<F16>(x4, x5), tc::pack16<F16>(x6, x7));
             }
           }
           ptx::fence_proxy_async_smem();
@@ -374,8 +374,8 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel_ko(const KoArgs ka) {
           x2 = fabsf(__fsub_rn(va[ii].z, vb[ii].z)); x3 = fabsf(__fsub_rn(va[ii].w, vb[ii].w));
         }
         const uint32_t r = (uint32_t)(rbase + 16 * ii);
-        stg64(xb + ptx::sw128_offset(r, (uint32_t)sub >> 1) + ((uint32_t)sub & 1u) * 8u, tc::pack_bf16(x0, x1),
-              tc::pack_bf16(x2, x3));
+        stg64(xb + ptx::sw128_offset(r, (uint32_t)sub >> 1) + ((uint32_t)sub & 1u) * 8u, tc::pack16<F16>(x0, x1),
+              tc::pack16<F16>(x2, x3));
       }
     };
     float4 va0[8], vb0[8], va1[8], vb1[8];
@@ -407,7 +407,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel_ko(const KoArgs ka) {
 }  // namespace tcko
 
 // Wide-feature scoring (D_in > 512 or when forced): same contract as tc_score.
-static int tc_score_ko(alink_ctx *ctx, const HeadGroup &g, const tc::Args &a0, bool tb16) {
+static int tc_score_ko(alink_ctx *ctx, const HeadGroup &g, const tc::Args &a0, bool tb16, bool f16) {
   if (ctx->sm_count < 2) return alink_fail(ctx, ALINK_E_UNSUPPORTED, "the wide-feature tensor-core head needs CTA pairs");
   tcko::KoArgs ka;
   ka.a = a0;
@@ -428,7 +428,8 @@ static int tc_score_ko(alink_ctx *ctx, const HeadGroup &g, const tc::Args &a0, b
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  void (*kern)(const tcko::KoArgs) = tb16 ? tcko::head_kernel_ko<true> : tcko::head_kernel_ko<false>;
+  void (*kern)(const tcko::KoArgs) = f16 ? tcko::head_kernel_ko<false, true>
+                                     : tb16 ? tcko::head_kernel_ko<true, false> : tcko::head_kernel_ko<false, false>;
   ALINK_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tcko::SMEM_BYTES));
   ALINK_CUDA(ctx, cudaLaunchKernelEx(&cfg, kern, ka));
   ALINK_LAUNCHED(ctx);

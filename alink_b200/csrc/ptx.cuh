@@ -201,6 +201,10 @@ __device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t smem_addr) {
 __host__ __device__ constexpr uint32_t umma_idesc_bf16(int M, int N) {
   return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
 }
+// same with IEEE half operands (a_format = b_format = 0): 11 significant bits instead of 8, same rate
+__host__ __device__ constexpr uint32_t umma_idesc_f16(int M, int N) {
+  return (1u << 4) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
 
 // byte offset of element (row r, 16-byte chunk c) inside a [rows x 64 bf16] SWIZZLE_128B tile
 __host__ __device__ __forceinline__ uint32_t sw128_offset(uint32_t r, uint32_t c) {

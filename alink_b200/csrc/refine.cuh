@@ -7,8 +7,14 @@
 // is >= tau - eps and a pair outside has u < tau - 2 eps + eps; (4) re-score only the candidates with the
 // bit-exact FFMA head (head_ffma.cuh, the oracle's summation order) and (5) select the top-B of the exact
 // utilities with the pairs' ORIGINAL indices in the keys. The result is identical to FP32_EXACT whenever
-// the error bound holds; the observed max |u~ - u| over the candidates is reported next to the survivor
-// count (alink_refine_stats) so the caller can check the bound it chose.
+// the error bound holds. The bound is checked on every query: the observed max |u~ - u| over the
+// candidates must stay below it, otherwise it is widened and steps (3)-(5) are repeated (alink_refine_stats
+// / alink_refine_detail report survivors, max and rms error, the bound used and the number of rounds).
+//
+// Filter operand format: IEEE half by default (11 significant bits: the rounding error of the features,
+// weights and hidden activations is 8x smaller than bf16's, so the candidate band is 8x narrower and the
+// exact re-score 8x cheaper) — used only when it provably cannot overflow: |x| <= |a|max + |b|max and
+// |h1| <= xmax * max_j sum_k |W1[k][j]| + |b1|max must stay below 6e4; otherwise the bf16 images are used.
 #pragma once
 #include "common.cuh"
 #include "topk.cuh"
@@ -55,13 +61,35 @@ __global__ void __launch_bounds__(256) refine_compose_kernel(const uint32_t *__r
   }
 }
 
-// max over the candidates of |exact - approximate| utility (as ordered uint bits: values are >= 0)
+// max and sum of squares over the candidates of |exact - approximate| utility
+// stat: [0] candidate count, [1] max error (ordered uint bits: values are >= 0), [2..3] double sum of squares
 __global__ void __launch_bounds__(256) refine_maxerr_kernel(const float *__restrict__ exact, const float *__restrict__ approx,
                                                             const uint32_t *__restrict__ cand, unsigned int M,
-                                                            unsigned int *__restrict__ out_bits) {
+                                                            unsigned int *__restrict__ stat) {
+  float m = 0.0f, ss = 0.0f;
+  for (unsigned int j = blockIdx.x * 256 + threadIdx.x; j < M; j += gridDim.x * 256) {
+    const float e = fabsf(__fsub_rn(exact[j], __ldg(approx + cand[j])));
+    m = fmaxf(m, e);
+    ss = __fmaf_rn(e, e, ss);
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+    ss += __shfl_xor_sync(0xffffffffu, ss, o);
+  }
+  if ((threadIdx.x & 31) == 0) {
+    atomicMax(stat + 1, __float_as_uint(m));
+    atomicAdd(reinterpret_cast<double *>(stat + 2), (double)ss);
+  }
+}
+
+// max |element| of a table (fp32): decides whether the half-precision filter can overflow (65504)
+__global__ void __launch_bounds__(256) absmax_kernel(const float4 *__restrict__ x, int64_t n4, unsigned int *__restrict__ out_bits) {
   float m = 0.0f;
-  for (unsigned int j = blockIdx.x * 256 + threadIdx.x; j < M; j += gridDim.x * 256)
-    m = fmaxf(m, fabsf(__fsub_rn(exact[j], __ldg(approx + cand[j]))));
+  for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < n4; i += (int64_t)gridDim.x * 256) {
+    const float4 v = __ldg(x + i);
+    m = fmaxf(m, fmaxf(fmaxf(fabsf(v.x), fabsf(v.y)), fmaxf(fabsf(v.z), fabsf(v.w))));
+  }
   for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+  // NaN/Inf elements: fmaxf drops NaN, so test the bit pattern of what remains and flag non-finite separately
   if ((threadIdx.x & 31) == 0) atomicMax(out_bits, __float_as_uint(m));
 }

@@ -283,6 +283,7 @@ def main():
     ctx.set_table(0, table_dev)
     ms_step, stage, launches, clocks, merged, dev_ms = timed(step_resident, args.steps, args.warmup, sample_clocks=True)
     refine_stats = ctx.refine_stats() if args.mode == "refine" else None
+    refine_detail = ctx.refine_detail() if args.mode == "refine" else None
     ms_e2e, stage_e2e, _, _, merged_e2e, _ = timed(step_e2e, max(2, min(args.steps, 3)), 1)
     assert np.array_equal(merged, merged_e2e), "resident and e2e paths selected different pairs"
 
@@ -298,8 +299,18 @@ def main():
                 "flops_per_pair": FLOPS_PER_PAIR(K, h.D_in, h.H1, h.H2, h.C), "launch_ms": head_ms,
                 "peak_source": peaks["source"] + ", sustained bf16 (kernel timed inside a long step)"}
     mode_name = {"fp32": "FP32_EXACT", "bf16": "BF16_TC", "refine": "FP32_REFINE"}[args.mode]
+    if args.config == 2 and args.mode != "fp32" and N == 1_000_000:
+        # DRAM bytes of one launch of this kernel on this workload, from the committed ncu --set full capture
+        try:
+            with open(os.path.join(ROOT, "profiles", "r1_ncu_head_full_summary.json")) as f:
+                roofline["traffic"] = json.load(f)["traffic_bytes_per_launch"]
+            roofline["traffic_source"] = "profiles/r1_ncu_head_full_summary.json (dram__bytes_read.sum + dram__bytes_write.sum)"
+        except Exception:
+            pass
     if args.mode == "refine":
-        roofline["kernel"] = "tc::head_kernel (tcgen05 bf16 filter over every pair; the exact re-score of the survivors is extra, non-algorithmic work)"
+        roofline["kernel"] = ("tc::head_kernel (tcgen05 kind::f16 filter over every pair, "
+                              f"{refine_detail['filter']} operands / fp32 accumulate; the exact re-score of the "
+                              "survivors is extra, non-algorithmic work)")
         roofline["share_of_step"] = head_ms / ms_step
     if args.mode == "fp32":
         clk = (clocks or {}).get("sm_mhz") or 1965.0
@@ -322,7 +333,7 @@ def main():
 
     if refine_stats is not None:
         line["refine"] = {"survivors_rescored_exactly": refine_stats[0], "max_abs_utility_error_seen": refine_stats[1],
-                          "eps": 6e-3, "stage_ms": {"tc_filter": stage["ms_score"], "mark_and_exact_rescore": stage["ms_utility"],
+                          **refine_detail, "stage_ms": {"tc_filter": stage["ms_score"], "mark_and_exact_rescore": stage["ms_utility"],
                                                     "select": stage["ms_select"]}}
     if n_gpus == 1 and not args.no_mode_compare and args.config == 2:
         # outside the timed region: the same step in the other compute modes, and how the selections compare

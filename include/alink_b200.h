@@ -41,10 +41,13 @@ enum { ALINK_FEAT_ABSDIFF = 0, ALINK_FEAT_ABSDIFF_HADAMARD = 1 };
 /* compute modes: FP32_EXACT = CUDA-core FFMA chains in the oracle's summation order (bit-exact with
  * oracle/); BF16_TC = tcgen05 bf16 tiles with fp32 accumulation in TMEM (|dp| <= 2e-2). */
 enum { ALINK_COMPUTE_FP32_EXACT = 0, ALINK_COMPUTE_BF16_TC = 1, ALINK_COMPUTE_FP32_REFINE = 2 };
-/* FP32_REFINE: alink_score_* behave as FP32_EXACT; alink_query filters with the BF16_TC head and re-scores
- * only the pairs within 2*eps of the B-th best approximate utility with the bit-exact head, so the
- * selection is identical to FP32_EXACT whenever |bf16 utility - fp32 utility| <= eps (alink_set_refine_eps;
- * survivors and the observed error: alink_refine_stats). VOTE_ENTROPY (discrete plateaus) runs exactly. */
+/* FP32_REFINE: alink_score_* behave as FP32_EXACT; alink_query filters with the tensor-core head (IEEE
+ * half operands when the features and hidden activations provably stay below 6e4, else bf16) and
+ * re-scores only the pairs within 2*eps of the B-th best approximate utility with the bit-exact head, so
+ * the selection is identical to FP32_EXACT whenever |filter utility - fp32 utility| <= eps. The bound is
+ * verified on every candidate of every query and widened (re-marking, re-scoring) when it fails
+ * (alink_set_refine_eps, alink_refine_stats, alink_refine_detail). VOTE_ENTROPY (discrete plateaus)
+ * runs exactly. */
 /* activation and utility ids are shared with the oracle: see include/alink_math.h
  * (ALINK_ACT_SOFTMAX/SIGMOID, ALINK_UTIL_*). */
 
@@ -120,13 +123,16 @@ int alink_utility(alink_ctx *ctx, int measure, float *util, int out_space);
 int alink_utility_from_proba(alink_ctx *ctx, const float *per_learner, int64_t N, int K, int C,
                              int measure, int in_space, float *util, float *consensus, int out_space);
 
-/* FP32_REFINE knobs: eps = assumed bound on the bf16 utility error (default 6e-3; measured max 4.9e-3 over
- * 1 M pairs of BASELINE configs[1]); stats of the last alink_query: candidates re-scored exactly and the
- * largest |approximate - exact| utility seen among them (survivors = 0 when the query ran fully exact).
- * eps bounds a probability error; the candidate margin is 2 * eps * scale(measure), scale = 1 (uncertainty),
- * 2 (margin), 1.25 (entropy, consensus entropy), 5 (KL-max). */
+/* FP32_REFINE knobs: eps = assumed bound on the filter's probability error (0 = the per-format default:
+ * 1e-3 half, 6e-3 bf16; see DESIGN.md for the measured errors); stats of the last alink_query: candidates
+ * re-scored exactly and the largest |approximate - exact| utility seen among them (survivors = 0 when the
+ * query ran fully exact). eps bounds a probability error; the candidate margin is 2 * eps * scale(measure),
+ * scale = 1 (uncertainty), 2 (margin), 1.25 (entropy, consensus entropy), 5 (KL-max).
+ * alink_refine_detail: operand format of the last filter (1 = half, 0 = bf16), the bound it ended with,
+ * the rms error over the candidates, and the number of mark + re-score rounds (1 unless widened). */
 int alink_set_refine_eps(alink_ctx *ctx, double eps);
 int alink_refine_stats(const alink_ctx *ctx, int64_t *survivors, float *max_err);
+int alink_refine_detail(const alink_ctx *ctx, int *filter_f16, double *eps_used, float *rms_err, int *rounds);
 
 /* Top-B of the context's utility vector. Replaces modAL multi_argmax (code/uncertainty.py:155,183,213).
  * idx_out (B int64), util_out (B fp32), keys_out (B packed u64 keys for cross-shard merging): any may

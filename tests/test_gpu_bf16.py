@@ -99,8 +99,45 @@ def test_refine_selection_is_bit_identical_to_fp32(ctx, oracle, measure):
     else:
         assert pool.B <= survivors < pool.N
         scale = {"uncertainty": 1.0, "neg_margin": 2.0, "entropy": 1.25, "consensus_entropy": 1.25, "kl_max": 5.0}[measure]
-        assert max_err <= 6e-3 * scale, f"observed bf16 utility error {max_err} exceeds the assumed bound"
-        print(f"refine[{measure}]: {survivors} of {pool.N} pairs re-scored exactly, max err {max_err:.2e}")
+        d = ctx.refine_detail()
+        assert d["filter"] == "f16"  # unit-norm embeddings cannot overflow half: the narrow-band filter runs
+        assert d["rounds"] == 1, f"the default bound had to be widened: {d}, max err {max_err}"
+        assert max_err <= d["eps_used"] * scale, f"observed filter utility error {max_err} exceeds the bound {d}"
+        print(f"refine[{measure}]: {survivors} of {pool.N} pairs re-scored exactly, max err {max_err:.2e}, {d}")
+
+
+def test_refine_falls_back_to_bf16_when_half_could_overflow(ctx, oracle):
+    """Features beyond the half range (|a| + |b| >= 6e4 after scaling the table by 1e6): the filter must use the bf16 images; selection stays exact."""
+    pool = synth.make_pool(2, N=30000, M=5000)
+    table = (pool.table * np.float32(1.0e6)).astype(np.float32)
+    import copy
+    heads = copy.deepcopy(pool.heads)
+    heads.W1 = [np.ascontiguousarray(w * np.float32(1.0 / 1.0e6), dtype=np.float32) for w in heads.W1]
+    ctx.set_heads(2, heads, compute=_ffi.FP32_REFINE)
+    ctx.set_table(0, table)
+    idx, util, keys = ctx.query(2, 0, 0, pool.ia, pool.ib, pool.N, "uncertainty", pool.B)
+    assert ctx.refine_detail()["filter"] == "bf16"
+    ref = oracle.score(table, table, pool.ia, pool.ib, heads, measure="uncertainty")
+    ridx, rutil, rkeys = oracle.topk(ref["util"], pool.B)
+    np.testing.assert_array_equal(keys, rkeys)
+    np.testing.assert_array_equal(util.view(np.uint32), rutil.view(np.uint32))
+
+
+def test_refine_widens_a_bound_that_is_too_tight(ctx, oracle):
+    """A caller-supplied eps far below the real filter error is detected on the candidates and widened."""
+    pool = synth.make_pool(2, N=60000, M=20000)
+    ctx.set_heads(2, pool.heads, compute=_ffi.FP32_REFINE)
+    ctx.set_table(0, pool.table)
+    ctx.set_refine_eps(1e-6)
+    try:
+        idx, util, keys = ctx.query(2, 0, 0, pool.ia, pool.ib, pool.N, "uncertainty", pool.B)
+        d = ctx.refine_detail()
+    finally:
+        ctx.set_refine_eps(0.0)
+    assert d["rounds"] > 1 and d["eps_used"] > 1e-6
+    ref = oracle.score(pool.table, pool.table, pool.ia, pool.ib, pool.heads, measure="uncertainty")
+    _, _, rkeys = oracle.topk(ref["util"], pool.B)
+    np.testing.assert_array_equal(keys, rkeys)
 
 
 def test_refine_small_pool_and_scores_are_exact(ctx, oracle):

@@ -134,8 +134,11 @@ def test_errors_are_reported_not_fatal(ctx):
     _install(ctx, pool)
     with pytest.raises(_ffi.AlinkError):
         ctx.query(0, 0, 0, pool.ia, pool.ib, pool.N, "uncertainty", pool.N + 1)
+    fresh = _ffi.Context(0)  # the session context is shared: other test files may have filled its groups
+    fresh.set_table(0, pool.table)
     with pytest.raises(_ffi.AlinkError):
-        ctx.query(3, 0, 0, pool.ia, pool.ib, pool.N, "uncertainty", 1)  # group 3 never set
+        fresh.query(3, 0, 0, pool.ia, pool.ib, pool.N, "uncertainty", 1)  # group 3 never set
+    fresh.close()
     # the context is still usable afterwards
     idx, _, _ = ctx.query(0, 0, 0, pool.ia, pool.ib, pool.N, "uncertainty", 8)
     assert len(idx) == 8
