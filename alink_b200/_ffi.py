@@ -32,6 +32,7 @@ SYMBOLS = (
     "alink_score_indexed", "alink_score_dense", "alink_utility", "alink_utility_from_proba",
     "alink_select_topk", "alink_topk_values", "alink_topk_keys", "alink_query", "alink_disparity_select",
     "alink_set_refine_eps", "alink_refine_stats", "alink_refine_detail", "alink_score_allpairs", "alink_query_allpairs",
+    "alink_disparity_hist", "alink_disparity_select_sharded",
 )
 
 
@@ -112,6 +113,11 @@ def load():
     L.alink_set_refine_eps.argtypes = [vp, dbl]
     L.alink_refine_stats.restype = i32
     L.alink_refine_stats.argtypes = [vp, C.POINTER(i64), C.POINTER(C.c_float)]
+    L.alink_disparity_hist.restype = i32
+    L.alink_disparity_hist.argtypes = [vp, vp, vp, i64, i64, u64, i32, i32, vp]
+    L.alink_disparity_select_sharded.restype = i32
+    L.alink_disparity_select_sharded.argtypes = [vp, vp, vp, i64, i32, i64, vp, dbl, i32, vp, i32, vp, i32,
+                                                 C.POINTER(i64), C.POINTER(i64)]
     L.alink_refine_detail.restype = i32
     L.alink_refine_detail.argtypes = [vp, C.POINTER(C.c_int), C.POINTER(dbl), C.POINTER(C.c_float), C.POINTER(C.c_int)]
     _lib = L
@@ -288,11 +294,12 @@ class Context:
         _space_of(ia, ib)
         if out is None:
             out = (np.empty((B,), np.int64), np.empty((B,), np.float32), np.empty((B,), np.uint64))
-        idx, util, keys = out
+        idx, util, keys = out  # numpy (host) or torch cuda tensors (left on the device; any may be None)
+        osp = _space_of(idx, util, keys)
         t = Timing() if timing else None
         self._check(self._L.alink_query(self._h, group, slot_a, slot_b, pia, pib, N, sp, MEASURE_ID[measure], B,
                                         base, _ptr_space(idx)[0], _ptr_space(util)[0], _ptr_space(keys)[0],
-                                        HOST, C.byref(t) if timing else None))
+                                        osp, C.byref(t) if timing else None))
         return (idx, util, keys, t) if timing else (idx, util, keys)
 
     def disparity_select(self, p2, p1, ratio=0.25, eps=0.05, blind=False, y=None):
@@ -306,6 +313,34 @@ class Context:
                                                    float(ratio), float(eps), int(bool(blind)),
                                                    _ptr_space(yy)[0], HOST, _ptr_space(idx)[0], HOST,
                                                    C.byref(n_out), C.byref(active)))
+        return idx[:n_out.value].copy(), int(active.value)
+
+    def disparity_hist(self, q, p1, base, prefix, pass_):
+        """One radix-select histogram pass (2048 uint32 counters) over this shard's keys (|q - p1|, base + j)."""
+        N = int(q.shape[0])
+        (pq, sq), (pp, sp) = _ptr_space(q), _ptr_space(p1)
+        if N and sq != sp:
+            raise ValueError("q and p1 must live in the same memory space")
+        hist = np.zeros((2048,), np.uint32)
+        self._check(self._L.alink_disparity_hist(self._h, pq, pp, N, int(base), int(prefix), int(pass_), sq,
+                                                 hist.ctypes.data))
+        return hist
+
+    def disparity_select_sharded(self, p2, p1, base, thr_keys, eps=0.05, blind=False, y=None):
+        """Shard-local part of the A-LINK rule against GLOBAL per-noise threshold keys; returns
+        (global indices ascending, ACTIVE_COUNT of this shard)."""
+        T, N = int(p2.shape[0]), int(p2.shape[1])
+        thr = np.ascontiguousarray(thr_keys, dtype=np.uint64)
+        assert thr.shape == (T,)
+        (pp2, s2), (pp1, s1) = _ptr_space(p2), _ptr_space(p1)
+        py, sy = _ptr_space(y) if y is not None else (None, s2)
+        if N and not (s2 == s1 == sy):
+            raise ValueError("p2, p1 and y must live in the same memory space")
+        idx = np.empty((max(N, 1),), np.int64)
+        n_out, active = C.c_int64(0), C.c_int64(0)
+        self._check(self._L.alink_disparity_select_sharded(self._h, pp2, pp1, N, T, int(base), thr.ctypes.data,
+                                                           float(eps), int(bool(blind)), py, s2, idx.ctypes.data, HOST,
+                                                           C.byref(n_out), C.byref(active)))
         return idx[:n_out.value].copy(), int(active.value)
 
     def score_allpairs(self, group, slot_probe, slot_gallery, row0, nrows, G, K, Cc, want_per=False, want_cons=True):

@@ -666,12 +666,14 @@ int alink_query_allpairs(alink_ctx *ctx, int group, int slot_probe, int slot_gal
 }
 
 // ------------------------------------------------------------------------------------------ A-LINK rule
-int alink_disparity_select(alink_ctx *ctx, const float *p2, const float *p1, int64_t N, int T, double ratio,
-                           double eps, int blind, const float *y, int in_space, int64_t *idx_out, int out_space,
-                           int64_t *n_out, int64_t *active_count) {
+// thr != null: sharded pool — thr[t] is the GLOBAL threshold key of noise t (0 = nothing passes), keys and
+// the returned indices carry base + j; thr == null: single shard, the threshold is selected here.
+static int disparity_impl(alink_ctx *ctx, const float *p2, const float *p1, int64_t N, int T, double ratio,
+                          double eps, int blind, const float *y, int in_space, int64_t *idx_out, int out_space,
+                          int64_t *n_out, int64_t *active_count, int64_t base, const uint64_t *thr) {
   if (!ctx) return ALINK_E_INVALID;
   if (N < 0 || T < 1 || !n_out) return alink_fail(ctx, ALINK_E_INVALID, "bad arguments (N=%lld, T=%d)", (long long)N, T);
-  if (N > 0xFFFFFFFEll) return alink_fail(ctx, ALINK_E_INVALID, "N out of range");
+  if (N > 0xFFFFFFFEll || base < 0 || base + N > 0xFFFFFFFFll) return alink_fail(ctx, ALINK_E_INVALID, "N / base out of range");
   if (!(ratio >= 0.0 && ratio <= 1.0)) return alink_fail(ctx, ALINK_E_INVALID, "ratio outside [0,1]");
   *n_out = 0;
   if (active_count) *active_count = 0;
@@ -706,6 +708,12 @@ int alink_disparity_select(alink_ctx *ctx, const float *p2, const float *p1, int
     if (blind) {
       disparity_blind_kernel<<<(unsigned)sb, 256, 0, ctx->stream>>>(q, (const float *)dp1, N, cnt);
       ALINK_LAUNCHED(ctx);
+    } else if (thr) {
+      if (thr[t]) {
+        disparity_mark_thr_kernel<<<(unsigned)sb, 256, 0, ctx->stream>>>(q, (const float *)dp1, N, (uint64_t)base,
+                                                                          (unsigned long long)thr[t], cnt);
+        ALINK_LAUNCHED(ctx);
+      }
     } else if (m > 0) {
       absdiff_vec_kernel<<<(unsigned)sb, 256, 0, ctx->stream>>>(q, (const float *)dp1, N, d);
       ALINK_LAUNCHED(ctx);
@@ -734,6 +742,10 @@ int alink_disparity_select(alink_ctx *ctx, const float *p2, const float *p1, int
   if (didx) {
     disparity_scatter_kernel<<<nblk, 256, 0, ctx->stream>>>(f, N, blk, didx);
     ALINK_LAUNCHED(ctx);
+    if (base) {
+      offset_i64_kernel<<<ctx->sm_count, 256, 0, ctx->stream>>>(didx, N, counters + 1, base);
+      ALINK_LAUNCHED(ctx);
+    }
   }
   unsigned long long hc[2];
   ALINK_CUDA(ctx, cudaMemcpyAsync(hc, counters, 16, cudaMemcpyDeviceToHost, ctx->stream));
@@ -744,6 +756,52 @@ int alink_disparity_select(alink_ctx *ctx, const float *p2, const float *p1, int
     ALINK_CUDA(ctx, cudaMemcpyAsync(idx_out, didx, sizeof(int64_t) * (size_t)hc[1], cudaMemcpyDeviceToHost, ctx->stream));
     ALINK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
   }
+  return ALINK_OK;
+}
+
+int alink_disparity_select(alink_ctx *ctx, const float *p2, const float *p1, int64_t N, int T, double ratio,
+                           double eps, int blind, const float *y, int in_space, int64_t *idx_out, int out_space,
+                           int64_t *n_out, int64_t *active_count) {
+  return disparity_impl(ctx, p2, p1, N, T, ratio, eps, blind, y, in_space, idx_out, out_space, n_out, active_count, 0,
+                        nullptr);
+}
+
+int alink_disparity_select_sharded(alink_ctx *ctx, const float *p2, const float *p1, int64_t N, int T, int64_t base,
+                                   const uint64_t *thr_keys, double eps, int blind, const float *y, int in_space,
+                                   int64_t *idx_out, int out_space, int64_t *n_out, int64_t *active_count) {
+  if (!ctx) return ALINK_E_INVALID;
+  if (!blind && !thr_keys) return alink_fail(ctx, ALINK_E_INVALID, "null thr_keys");
+  static const uint64_t none[1] = {0};
+  return disparity_impl(ctx, p2, p1, N, T, 1.0, eps, blind, y, in_space, idx_out, out_space, n_out, active_count, base,
+                        blind ? none : thr_keys);
+}
+
+int alink_disparity_hist(alink_ctx *ctx, const float *q, const float *p1, int64_t N, int64_t base, uint64_t prefix,
+                         int pass, int in_space, uint32_t *hist_out) {
+  if (!ctx) return ALINK_E_INVALID;
+  if (N < 0 || base < 0 || base + N > 0xFFFFFFFFll || pass < 0 || pass > 5 || !hist_out)
+    return alink_fail(ctx, ALINK_E_INVALID, "bad arguments (N=%lld, base=%lld, pass=%d)", (long long)N, (long long)base, pass);
+  static const int shifts[6] = {53, 42, 32, 21, 10, 0};
+  static const int nbits[6] = {11, 11, 10, 11, 11, 10};
+  ALINK_CUDA(ctx, cudaSetDevice(ctx->device));
+  const void *dq, *dp1;
+  ALINK_TRY(stage_in(ctx, N ? q : nullptr, sizeof(float) * (size_t)N, in_space, ctx->misc0, &dq));
+  ALINK_TRY(stage_in(ctx, N ? p1 : nullptr, sizeof(float) * (size_t)N, in_space, ctx->misc1, &dp1));
+  ALINK_TRY(dev_reserve(ctx, ctx->sel_state, sizeof(SelectState)));
+  unsigned int *hist = ((SelectState *)ctx->sel_state.p)->hist;
+  ALINK_CUDA(ctx, cudaMemsetAsync(hist, 0, sizeof(unsigned int) * 2048, ctx->stream));
+  if (N > 0) {
+    if (!dq || !dp1) return alink_fail(ctx, ALINK_E_INVALID, "null scores");
+    int64_t sb = (N + 2047) / 2048;
+    const int64_t cap = (int64_t)ctx->sm_count * 8;
+    if (sb > cap) sb = cap;
+    disparity_hist_kernel<<<(unsigned)sb, 256, 0, ctx->stream>>>((const float *)dq, (const float *)dp1, N, (uint64_t)base,
+                                                                  (unsigned long long)prefix, shifts[pass], nbits[pass],
+                                                                  pass == 0, hist);
+    ALINK_LAUNCHED(ctx);
+  }
+  ALINK_CUDA(ctx, cudaMemcpyAsync(hist_out, hist, sizeof(unsigned int) * 2048, cudaMemcpyDeviceToHost, ctx->stream));
+  ALINK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
   return ALINK_OK;
 }
 

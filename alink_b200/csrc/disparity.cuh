@@ -28,6 +28,34 @@ __global__ void __launch_bounds__(256) disparity_mark_kernel(const float *__rest
     if (has_thr && alink_pack_key(d[j], (uint64_t)j) >= thr) cnt[j] += 1;
 }
 
+// sharded pools (alink_b200/dist.py): membership against an explicit GLOBAL threshold key, keys carry base + j
+__global__ void __launch_bounds__(256) disparity_mark_thr_kernel(const float *__restrict__ q, const float *__restrict__ p1,
+                                                                 int64_t N, uint64_t base, unsigned long long thr,
+                                                                 int *__restrict__ cnt) {
+  for (int64_t j = (int64_t)blockIdx.x * 256 + threadIdx.x; j < N; j += (int64_t)gridDim.x * 256)
+    if (alink_pack_key(fabsf(__fsub_rn(__ldg(q + j), __ldg(p1 + j))), base + (uint64_t)j) >= thr) cnt[j] += 1;
+}
+
+// one radix-select histogram pass over this shard's keys (|q - p1|, base + j): the ranks sum the
+// histograms (all-reduce) and pick the bin on the host, so the threshold is the global order statistic
+__global__ void __launch_bounds__(256) disparity_hist_kernel(const float *__restrict__ q, const float *__restrict__ p1,
+                                                             int64_t N, uint64_t base, unsigned long long prefix, int shift,
+                                                             int bits, int first, unsigned int *__restrict__ hist) {
+  __shared__ unsigned int sh[2048];
+  const int nb = 1 << bits;
+  const unsigned mask = (unsigned)nb - 1u;
+  for (int i = threadIdx.x; i < nb; i += 256) sh[i] = 0;
+  __syncthreads();
+  const int hi = shift + bits;
+  for (int64_t j = (int64_t)blockIdx.x * 256 + threadIdx.x; j < N; j += (int64_t)gridDim.x * 256) {
+    const uint64_t key = alink_pack_key(fabsf(__fsub_rn(__ldg(q + j), __ldg(p1 + j))), base + (uint64_t)j);
+    if (first || (key >> hi) == prefix) atomicAdd(&sh[(unsigned)(key >> shift) & mask], 1u);
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < nb; i += 256)
+    if (sh[i]) atomicAdd(&hist[i], sh[i]);
+}
+
 __global__ void __launch_bounds__(256) disparity_blind_kernel(const float *__restrict__ q,
                                                               const float *__restrict__ p1, int64_t N,
                                                               int *__restrict__ cnt) {
@@ -124,4 +152,10 @@ __global__ void __launch_bounds__(256) disparity_scatter_kernel(DispFilter f, in
   unsigned int pos = blk_off[blockIdx.x] + part[threadIdx.x] - mine;
   for (int i = 0; i < DISP_ITEMS; ++i)
     if (fl[i]) idx_out[pos++] = j0 + i;
+}
+
+// idx[i] += base for the first *n entries (shard-local -> global pair indices)
+__global__ void __launch_bounds__(256) offset_i64_kernel(int64_t *idx, int64_t cap, const unsigned long long *n, int64_t base) {
+  const int64_t m = (int64_t)*n < cap ? (int64_t)*n : cap;
+  for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < m; i += (int64_t)gridDim.x * 256) idx[i] += base;
 }

@@ -40,15 +40,45 @@ def load_peaks():
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+    """SM clock / throttle reasons DURING the timed region (B200_PROFILING.md recipe). The timed region of
+    this step is tens of milliseconds, too short for `nvidia-smi -lms`, so the same NVML counters are polled
+    in-process every 2 ms (pynvml); `nvidia-smi` is the fallback when pynvml cannot be loaded."""
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
          "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    BITS = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap"}
 
-    def __init__(self, gpu_index=0):
+    def __init__(self, gpu_index=0, uuid=None):
         self.rows, self.proc, self.gpu = [], None, gpu_index
+        self.sm, self.mask, self.h, self.nv, self._stop = [], 0, None, None, False
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            try:
+                self.h = pynvml.nvmlDeviceGetHandleByUUID(("GPU-" + str(uuid)) if uuid and not str(uuid).startswith("GPU-") else str(uuid))
+            except Exception:
+                self.h = pynvml.nvmlDeviceGetHandleByIndex(gpu_index)
+            self.max_sm = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+        except Exception:
+            self.h = None
+
+    def _poll(self):
+        nv = self.nv
+        reasons = getattr(nv, "nvmlDeviceGetCurrentClocksEventReasons", None) or nv.nvmlDeviceGetCurrentClocksThrottleReasons
+        while not self._stop:
+            try:
+                self.sm.append(float(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)))
+                self.mask |= int(reasons(self.h))
+            except Exception:
+                pass
+            time.sleep(0.002)
 
     def start(self):
+        if self.h is not None:
+            self.t = threading.Thread(target=self._poll, daemon=True)
+            self.t.start()
+            return
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu), f"--query-gpu={self.Q}",
                                           "--format=csv,noheader,nounits", "-lms", "100"],
@@ -63,6 +93,12 @@ class ClockSampler:
             self.rows.append([c.strip() for c in line.split(",")])
 
     def stop(self):
+        if self.h is not None:
+            self._stop = True
+            self.t.join(timeout=1)
+            return {"sm_mhz": float(np.median(self.sm)) if self.sm else None, "sm_max_mhz": self.max_sm,
+                    "reasons": sorted(n for b, n in self.BITS.items() if self.mask & b), "samples": len(self.sm),
+                    "source": "NVML polled in-process every 2 ms"}
         if not self.proc:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         time.sleep(0.15)
@@ -76,7 +112,7 @@ class ClockSampler:
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         reasons = sorted({n for r in self.rows if len(r) >= 9 for n, v in zip(names, r[5:9]) if v.lower() == "active"})
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": reasons, "samples": len(sm)}
+                "reasons": reasons, "samples": len(sm), "source": "nvidia-smi -lms 100"}
 
 
 def cpu_oracle_throughput(pool, sample_pairs, threads=0, repeats=1):
@@ -234,19 +270,28 @@ def main():
     ib_pin = torch.from_numpy(pool.ib).pin_memory()
     out = (np.empty((B,), np.int64), np.empty((B,), np.float32), np.empty((B,), np.uint64))
 
+    keys_dev = torch.zeros((B,), dtype=torch.int64, device=dev)  # u64 key bit patterns, left on the device
+    out_dev = (None, None, keys_dev)
+
     def step_resident():
-        """inputs already in HBM; result (B keys) read back; cross-shard merge when N > 1."""
-        _, _, keys, t = ctx.query(0, 0, 0, ia_dev, ib_dev, N, args.measure, B, base=base, timing=True, out=out)
-        merged = merge_shards(keys, B, ctx.topk_keys, dist=dist if world > 1 else None, device=dev)
-        return merged, t
+        """inputs already in HBM; per-shard keys stay on the device, one all-gather + merge when N > 1, and
+        the merged B keys are read back."""
+        if world == 1:
+            _, _, keys, t = ctx.query(0, 0, 0, ia_dev, ib_dev, N, args.measure, B, base=base, timing=True, out=out)
+            return keys, t
+        _, _, keys, t = ctx.query(0, 0, 0, ia_dev, ib_dev, N, args.measure, B, base=base, timing=True, out=out_dev)
+        return merge_shards(keys, B, ctx.topk_keys, dist=dist, device=dev), t
 
     def step_e2e():
         """host buffers in, host result out: table + indices cross PCIe inside the step."""
         ctx.set_table(1, table_pin)
+        if world == 1:
+            _, _, keys, t = ctx.query(0, 1, 1, ia_pin.numpy(), ib_pin.numpy(), N, args.measure, B, base=base,
+                                      timing=True, out=out)
+            return keys, t
         _, _, keys, t = ctx.query(0, 1, 1, ia_pin.numpy(), ib_pin.numpy(), N, args.measure, B, base=base,
-                                  timing=True, out=out)
-        merged = merge_shards(keys, B, ctx.topk_keys, dist=dist if world > 1 else None, device=dev)
-        return merged, t
+                                  timing=True, out=out_dev)
+        return merge_shards(keys, B, ctx.topk_keys, dist=dist, device=dev), t
 
     def barrier():
         if world > 1:
@@ -256,7 +301,7 @@ def main():
     def timed(step_fn, steps, warmup, sample_clocks=False):
         for _ in range(warmup):
             step_fn()
-        sampler = ClockSampler(local_rank) if sample_clocks else None
+        sampler = ClockSampler(local_rank, getattr(torch.cuda.get_device_properties(local_rank), "uuid", None)) if sample_clocks else None
         barrier()
         if sampler:
             sampler.start()

@@ -174,6 +174,21 @@ int alink_disparity_select(alink_ctx *ctx, const float *p2, const float *p1, int
                            double ratio, double eps, int blind, const float *y, int in_space,
                            int64_t *idx_out, int out_space, int64_t *n_out, int64_t *active_count);
 
+/* The same rule on a pool sharded by pair index (one process per GPU). The per-noise prefix
+ * argsort(d)[:int(N_total*ratio)] (code/ALINK.py:181-183) is a GLOBAL order statistic:
+ *   alink_disparity_hist  : one radix-select pass (pass 0..5: 11/11/10 bits of |q - p1|, 11/11/10 bits of the
+ *                           index part) over this shard's keys (|q[j] - p1[j]|, base + j) that match `prefix`
+ *                           (ignored in pass 0); hist_out = 2048 host counters. The ranks sum the histograms
+ *                           (all-reduce), pick the bin, extend the prefix; after pass 5 the prefix IS the
+ *                           global threshold key of that noise type (alink_b200/dist.py).
+ *   alink_disparity_select_sharded : thr_keys[t] (host, T of them; 0 = nothing passes) replace the local
+ *                           selection; idx_out holds GLOBAL indices base + j, ascending. */
+int alink_disparity_hist(alink_ctx *ctx, const float *q, const float *p1, int64_t N, int64_t base, uint64_t prefix,
+                         int pass, int in_space, uint32_t *hist_out);
+int alink_disparity_select_sharded(alink_ctx *ctx, const float *p2, const float *p1, int64_t N, int T, int64_t base,
+                                   const uint64_t *thr_keys, double eps, int blind, const float *y, int in_space,
+                                   int64_t *idx_out, int out_space, int64_t *n_out, int64_t *active_count);
+
 #ifdef __cplusplus
 }
 #endif

@@ -84,3 +84,79 @@ def test_decode_keys_roundtrip():
     di, du = decode_keys(keys)
     np.testing.assert_array_equal(di, idx)
     np.testing.assert_array_equal(du, np.where(u == 0, np.float32(0.0), u))
+
+
+# ---- sharded A-LINK disparity rule (dist.sharded_disparity_select) ---------------------------------------
+def _pack_keys(d, idx):
+    """numpy twin of alink_pack_key (include/alink_math.h) for d >= 0."""
+    bits = np.ascontiguousarray(d, np.float32).view(np.uint32).astype(np.uint64)
+    o = bits | np.uint64(0x80000000)
+    return (o << np.uint64(32)) | (np.uint64(0xFFFFFFFF) - idx.astype(np.uint64))
+
+
+class _NumpyShard:
+    """Stand-in for the two Context calls dist.sharded_disparity_select makes (the kernels are tested on the GPU;
+    this file is about the host-side exchange)."""
+
+    def disparity_hist(self, q, p1, base, prefix, pass_):
+        from alink_b200.dist import RADIX_BITS, RADIX_SHIFTS
+        shift, bits = RADIX_SHIFTS[pass_], RADIX_BITS[pass_]
+        keys = _pack_keys(np.abs(q - p1), base + np.arange(len(q)))
+        if pass_ > 0:
+            keys = keys[(keys >> np.uint64(shift + bits)) == np.uint64(prefix)]
+        return np.bincount(((keys >> np.uint64(shift)) & np.uint64((1 << bits) - 1)).astype(np.int64), minlength=2048)
+
+    def disparity_select_sharded(self, p2, p1, base, thr, eps, blind, y):
+        T, n = p2.shape
+        cnt = np.zeros(n, np.int64)
+        for t in range(T):
+            if blind:
+                cnt += (p2[t] >= 0.5) != (p1 >= 0.5)
+            elif thr[t]:
+                cnt += _pack_keys(np.abs(p2[t] - p1), base + np.arange(n)) >= thr[t]
+        p = p1.astype(np.float64)
+        q = (cnt == T) & ((p <= 0.5 - eps) | (p >= 0.5 + eps))
+        sel = q if y is None else q & ((p1 >= 0.5) == (y >= 0.5))
+        return base + np.nonzero(sel)[0].astype(np.int64), int(q.sum())
+
+
+def _disp_inputs(N, T, seed=3):
+    rng = np.random.default_rng(seed)
+    p1 = rng.random(N).astype(np.float32)
+    p2 = np.clip(p1[None, :] + 0.2 * rng.standard_normal((T, N)), 0, 1).astype(np.float32)
+    p2[:, ::7] = p1[::7]  # exact ties at d = 0
+    p2[0, 5:40] = p1[5:40] + np.float32(0.25)  # a plateau of equal disparities across the shard boundary
+    y = (rng.random(N) < 0.5).astype(np.float32)
+    return p2, p1, y
+
+
+def _disp_worker(rank, world, port, N, T, ratio, blind, out_dir):
+    import torch.distributed as dist
+    from alink_b200.dist import shard_range, sharded_disparity_select
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    p2, p1, y = _disp_inputs(N, T)
+    lo, hi = shard_range(N, rank, world)
+    idx, active = sharded_disparity_select(_NumpyShard(), np.ascontiguousarray(p2[:, lo:hi]), p1[lo:hi], lo, N, ratio,
+                                           0.05, blind, y[lo:hi], dist=dist)
+    np.savez(os.path.join(out_dir, f"d{rank}.npz"), idx=idx, active=active)
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("N,T,ratio,blind", [(1003, 3, 0.25, False), (400, 2, 0.9, False), (257, 2, 0.25, True),
+                                             (64, 2, 0.001, False)])
+def test_two_rank_disparity_equals_single_shot(tmp_path, N, T, ratio, blind):
+    import torch.multiprocessing as mp
+    from oracle import oracle_ffi
+
+    oracle_ffi.build()
+    world, port = 2, _free_port()
+    mp.spawn(_disp_worker, args=(world, port, N, T, ratio, blind, str(tmp_path)), nprocs=world, join=True)
+    p2, p1, y = _disp_inputs(N, T)
+    ridx, ractive = oracle_ffi.disparity_select(p2, p1, ratio, 0.05, blind, y)
+    for r in range(world):
+        z = np.load(tmp_path / f"d{r}.npz")
+        np.testing.assert_array_equal(z["idx"], ridx)
+        assert int(z["active"]) == ractive

@@ -106,3 +106,39 @@ def test_a2link_noise_pool_disparity_at_scale(ctx, oracle, blind):
     np.testing.assert_array_equal(idx, ridx)
     assert active == ractive
     assert np.all(np.diff(idx) > 0)
+
+
+@pytest.mark.parametrize("blind", [False, True])
+@pytest.mark.parametrize("shards", [2, 3])
+def test_sharded_disparity_equals_single_shot(ctx, oracle, blind, shards):
+    """the per-noise prefix is a GLOBAL order statistic. Shards of one pool (here: in one process, the
+    histograms summed by hand where dist.py all-reduces them) must select exactly the single-shot set."""
+    import torch
+    from alink_b200.dist import global_threshold_key, shard_range
+    rng = np.random.default_rng(11)
+    N, T = 150_001, 4
+    p1 = rng.random(N).astype(np.float32)
+    p2 = np.clip(p1[None, :] + 0.2 * rng.standard_normal((T, N)), 0, 1).astype(np.float32)
+    p2[:, ::501] = p1[::501]
+    p2[1, 70_000:80_500] = p1[70_000:80_500] + np.float32(0.25)  # a plateau of ties across a shard boundary
+    y = (rng.random(N) < 0.5).astype(np.float32)
+    ridx, ractive = oracle.disparity_select(p2, p1, 0.25, 0.05, blind, y)
+    edges = [shard_range(N, r, shards) for r in range(shards)]
+    # device-resident shards (what a rank holds after scoring)
+    dp2 = [torch.from_numpy(np.ascontiguousarray(p2[:, lo:hi])).cuda() for lo, hi in edges]
+    dp1 = [torch.from_numpy(p1[lo:hi].copy()).cuda() for lo, hi in edges]
+    dy = [torch.from_numpy(y[lo:hi].copy()).cuda() for lo, hi in edges]
+    m = int(N * 0.25)
+    thr = np.zeros((T,), np.uint64)
+    if not blind:
+        for t in range(T):
+            hist = lambda pre, ps: sum(ctx.disparity_hist(dp2[r][t], dp1[r], edges[r][0], pre, ps).astype(np.int64)
+                                       for r in range(shards))
+            thr[t] = np.uint64(global_threshold_key(hist, m))
+    parts, active = [], 0
+    for r in range(shards):
+        idx, a = ctx.disparity_select_sharded(dp2[r], dp1[r], edges[r][0], thr, 0.05, blind, dy[r])
+        parts.append(idx)
+        active += a
+    np.testing.assert_array_equal(np.concatenate(parts), ridx)
+    assert active == ractive
