@@ -12,12 +12,18 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-SO_PATH = os.path.join(_HERE, "csrc", "libalink_b200.so")
+# ALINK_LIB_DEBUG=1 loads the debug build (same ABI; role-delay injection and the multi-record watchdog of the
+# tensor-core head: tools/stress_roles.py, tests/test_gpu_stress.py)
+SO_PATH = os.path.join(_HERE, "csrc", "libalink_b200_dbg.so" if os.environ.get("ALINK_LIB_DEBUG") == "1"
+                       else "libalink_b200.so")
+if os.environ.get("ALINK_LIB_PATH"):  # A/B runs of two builds inside one GPU session (tools/)
+    SO_PATH = os.environ["ALINK_LIB_PATH"]
 
 HOST, DEVICE = 0, 1
 F32, BF16 = 0, 1
 FEAT_ABSDIFF, FEAT_ABSDIFF_HADAMARD = 0, 1
 FP32_EXACT, BF16_TC, FP32_REFINE = 0, 1, 2
+E_CUDA = -2
 ACT_ID = {"softmax": 0, "sigmoid": 1}
 MEASURE_ID = {"uncertainty": 0, "neg_margin": 1, "entropy": 2, "vote_entropy": 3,
               "consensus_entropy": 4, "kl_max": 5}
@@ -28,7 +34,7 @@ MAX_SLOTS = 8
 # every symbol include/alink_b200.h declares (tests/test_abi.py checks the .so exports them all)
 SYMBOLS = (
     "alink_abi_version", "alink_create", "alink_destroy", "alink_last_error", "alink_sync",
-    "alink_set_stream", "alink_launch_count", "alink_host_alloc", "alink_host_free", "alink_set_heads", "alink_set_table",
+    "alink_set_stream", "alink_launch_count", "alink_watchdog_record", "alink_host_alloc", "alink_host_free", "alink_set_heads", "alink_set_table",
     "alink_score_indexed", "alink_score_dense", "alink_utility", "alink_utility_from_proba",
     "alink_select_topk", "alink_topk_values", "alink_topk_keys", "alink_query", "alink_disparity_select",
     "alink_set_refine_eps", "alink_refine_stats", "alink_refine_detail", "alink_score_allpairs", "alink_query_allpairs",
@@ -113,6 +119,8 @@ def load():
     L.alink_set_refine_eps.argtypes = [vp, dbl]
     L.alink_refine_stats.restype = i32
     L.alink_refine_stats.argtypes = [vp, C.POINTER(i64), C.POINTER(C.c_float)]
+    L.alink_watchdog_record.restype = i32
+    L.alink_watchdog_record.argtypes = [vp, C.POINTER(u64)]
     L.alink_disparity_hist.restype = i32
     L.alink_disparity_hist.argtypes = [vp, vp, vp, i64, i64, u64, i32, i32, vp]
     L.alink_disparity_select_sharded.restype = i32
@@ -180,9 +188,30 @@ class Context:
         except Exception:
             pass
 
+    def watchdog_record(self):
+        """None, or the records timed-out device waits left behind (list of dicts; see include/alink_b200.h)."""
+        r = (C.c_uint64 * 256)()
+        self._L.alink_watchdog_record(self._h, r)
+        if not r[0]:
+            return None
+        out = []
+        for i in range(min(int(r[0]), 63)):
+            w, b = int(r[1 + 2 * i]), int(r[2 + 2 * i])
+            out.append({"block": w >> 32, "warp": (w & 0xFFFFFFFF) >> 5, "lane": w & 31, "barrier_smem_addr": b >> 32,
+                        "parity": (b >> 8) & 1, "cluster_rank": b & 0xFF})
+        prog = [int(r[128 + i]) for i in range(64)]
+        if any(prog):
+            out.append({"progress(block x role: 0 producer,1 L1,2 L2,4-7 epilogue,8-15 gather)": [prog[16 * b:16 * b + 16] for b in range(4)]})
+        return out
+
     def _check(self, rc):
         if rc != 0:
-            raise AlinkError(f"[{rc}] {self._L.alink_last_error(self._h).decode()}")
+            msg = f"[{rc}] {self._L.alink_last_error(self._h).decode()}"
+            if rc == E_CUDA:
+                wd = self.watchdog_record()
+                if wd:
+                    msg += f" | device watchdog: a wait timed out: {wd}"
+            raise AlinkError(msg)
 
     # ---- state
     def set_heads(self, group, heads, feat_mode=FEAT_ABSDIFF, compute=FP32_EXACT):

@@ -37,6 +37,16 @@ int alink_create(alink_ctx **out, int device, unsigned flags) {
   ctx->own_stream = ctx->stream;
   cudaDeviceGetAttribute(&ctx->sm_count, cudaDevAttrMultiProcessorCount, device);
   for (int i = 0; i < 8; ++i) cudaEventCreate(&ctx->ev[i]);
+  // watchdog record: written by a kernel whose mbarrier wait times out (a protocol deadlock), readable
+  // from the host even after the launch failure has poisoned the CUDA context
+  if (cudaHostAlloc((void **)&ctx->wd_host, 2048, cudaHostAllocMapped) == cudaSuccess) {
+    memset(ctx->wd_host, 0, 2048);
+    unsigned long long *dptr = nullptr;
+    if (cudaHostGetDevicePointer((void **)&dptr, ctx->wd_host, 0) == cudaSuccess)
+      cudaMemcpyToSymbol(ptx::g_alink_wd, &dptr, sizeof(dptr));
+  } else {
+    ctx->wd_host = nullptr;
+  }
   *out = ctx;
   return ALINK_OK;
 }
@@ -81,6 +91,12 @@ int alink_set_stream(alink_ctx *ctx, void *cuda_stream) {
 }
 
 int64_t alink_launch_count(const alink_ctx *ctx) { return ctx ? ctx->launches : 0; }
+
+int alink_watchdog_record(const alink_ctx *ctx, uint64_t out[256]) {
+  if (!ctx || !out) return ALINK_E_INVALID;
+  for (int i = 0; i < 256; ++i) out[i] = ctx->wd_host ? (uint64_t)((volatile unsigned long long *)ctx->wd_host)[i] : 0;
+  return ALINK_OK;
+}
 
 int alink_host_alloc(void **out, uint64_t bytes) {
   if (!out) return ALINK_E_INVALID;

@@ -82,6 +82,7 @@ struct alink_ctx {
   uint32_t ap_G = 0;
   int64_t ap_pair0 = 0;
   DevBuf xscratch;  // head_tc_ko.cuh: per-CTA bf16 feature-tile images
+  unsigned long long *wd_host = nullptr;  // host-mapped watchdog record (ptx.cuh: mbar_timeout)
 };
 
 static inline int alink_fail(alink_ctx *ctx, int code, const char *fmt, ...) {

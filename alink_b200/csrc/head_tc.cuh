@@ -77,6 +77,10 @@ struct Args {
   float *probs;              // [N][K][C] or nullptr
   float *util;               // [N] or nullptr
   int ntiles;
+  // debug build only (-DALINK_TC_DEBUG): bits 0-5 slow down one role per loop iteration by (dbg >> 8) ns —
+  // 1 weight producer, 2 MMA issuer, 8 epilogue, 16 gather producers, 32 peer relay, 128 L2 prefetcher;
+  // bit 6 publishes per-role progress counters in the watchdog buffer (ptx.cuh)
+  uint32_t dbg;
 };
 
 // table rows of pair n: explicit indices, the all-pairs enumeration, or identity
@@ -146,6 +150,21 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
   const uint32_t sbase = ptx::smem_u32(smem);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   auto bar = [&](int i) -> uint32_t { return sbase + BOFF + 8u * (uint32_t)i; };
+#ifdef ALINK_TC_DEBUG
+  // the first two clusters publish each role's loop counter in the host-mapped watchdog buffer
+  // (words 128 + 16 * block + role), so a deadlock report also says how far everyone got
+  auto progress = [&](uint32_t role, uint32_t v) {
+    if ((a.dbg & 64u) && blockIdx.x < 4 && (threadIdx.x & 31) == 0 && ptx::g_alink_wd)
+      reinterpret_cast<volatile unsigned long long *>(ptx::g_alink_wd)[128 + 16 * blockIdx.x + role] = v + 1;
+  };
+#define ALINK_DBG_ROLE(bit, role, v)                      \
+  do {                                                    \
+    if (a.dbg & (bit)) __nanosleep(a.dbg >> 8);           \
+    progress((role), (v));                                \
+  } while (0)
+#else
+#define ALINK_DBG_ROLE(bit, role, v) do { } while (0)
+#endif
 
   if (tid == 0) {
     if (sbase & 1023u) __trap();  // the swizzled operand tiles need a 1024-byte aligned base
@@ -201,6 +220,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
     const uint32_t ring = sbase + ROFF;
     uint32_t s = 0, ph = 0;  // ring slot and its phase parity
     for (uint32_t q = 0; q <= Q; ++q) {
+      ALINK_DBG_ROLE(1u, 0, q);
       if (q < Q) {
         const uint8_t *src = a.w1img + (size_t)(q % G) * nkb * STAGE_BYTES + rank * HB;
         for (uint32_t kb = 0; kb < nkb; kb += KPS) {
@@ -256,15 +276,20 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
       else ptx::umma_commit(bar(b_));
     };
     uint32_t s = 0, ph = 0;
+    // work-item coordinates as running counters (no integer division in the issue loop — this one warp's
+    // instruction stream is the critical path of the kernel): g1 / xpar for layer 1 of item q,
+    // c2 / vpar (parity of tile * K + learner) for layer 2 of item q - 1
+    uint32_t g1 = 0, xpar = 0, c2 = 0, vpar = 0;
     for (uint32_t q = 0; q <= Q; ++q) {
+      ALINK_DBG_ROLE(2u, 1, q);
       if (q < Q) {
-        const uint32_t i = q / G, g = q % G, b = q & 1u, u = q >> 1;
+        const uint32_t g = g1, b = q & 1u, u = q >> 1;
         ptx::mbar_wait(bar(A1_EMPTY + b), (u & 1u) ^ 1u);
         const uint32_t d_tmem = tmem + b * CHUNK_N;
         for (uint32_t kb = 0; kb < nkb; kb += KPS) {
           if (g == 0) {
 #pragma unroll
-            for (uint32_t kk = 0; kk < KPS; ++kk) ptx::mbar_wait(bar(X_FULL + kb + kk), i & 1u);
+            for (uint32_t kk = 0; kk < KPS; ++kk) ptx::mbar_wait(bar(X_FULL + kb + kk), xpar);
           }
           ptx::mbar_wait(bar(W_FULL + s), ph);
           ptx::tc_fence_after();
@@ -288,11 +313,12 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
         }
         if (leader) commit(A1_FULL + b);
         __syncwarp();
+        if (++g1 == G) { g1 = 0; xpar ^= 1u; }
       }
       if (q >= 1) {
-        const uint32_t p = q - 1, i = p / G, g = p % G, l = g / (uint32_t)a.nc, c = g % (uint32_t)a.nc;
+        const uint32_t p = q - 1, c = c2;
         ptx::mbar_wait(bar(H1_FULL), p & 1u);
-        if (c == 0) ptx::mbar_wait(bar(A2_EMPTY), ((i * (uint32_t)a.K + l) & 1u) ^ 1u);
+        if (c == 0) ptx::mbar_wait(bar(A2_EMPTY), vpar ^ 1u);
         ptx::mbar_wait(bar(W_FULL + s), ph);
         ptx::tc_fence_after();
         if (leader) {
@@ -310,6 +336,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
         }
         __syncwarp();
         if (++s == NS) { s = 0; ph ^= 1u; }
+        if (++c2 == (uint32_t)a.nc) { c2 = 0; vpar ^= 1u; }
       }
     }
   } else if (warp == 1) {
@@ -325,26 +352,29 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
       __syncwarp();
     };
     uint32_t s = 0, ph = 0;
+    uint32_t g1 = 0, xpar = 0, c2 = 0, v2 = 0;  // the leader's running counters (v2 = tile * K + learner)
     for (uint32_t q = 0; q <= Q; ++q) {
+      ALINK_DBG_ROLE(32u, 1, q);
       if (q < Q) {
-        const uint32_t i = q / G, g = q % G, b = q & 1u, u = q >> 1;
+        const uint32_t g = g1, b = q & 1u, u = q >> 1;
         if (u > 0) relay(A1_EMPTY + b, (u & 1u) ^ 1u);
         for (uint32_t kb = 0; kb < nkb; kb += KPS) {
           if (g == 0) {
 #pragma unroll
-            for (uint32_t kk = 0; kk < KPS; ++kk) relay(X_FULL + kb + kk, i & 1u);
+            for (uint32_t kk = 0; kk < KPS; ++kk) relay(X_FULL + kb + kk, xpar);
           }
           relay(W_FULL + s, ph);
           if (++s == NS) { s = 0; ph ^= 1u; }
         }
+        if (++g1 == G) { g1 = 0; xpar ^= 1u; }
       }
       if (q >= 1) {
-        const uint32_t p = q - 1, i = p / G, g = p % G, l = g / (uint32_t)a.nc, c = g % (uint32_t)a.nc;
+        const uint32_t p = q - 1;
         relay(H1_FULL, p & 1u);
-        const uint32_t v = i * (uint32_t)a.K + l;
-        if (c == 0 && v > 0) relay(A2_EMPTY, (v & 1u) ^ 1u);
+        if (c2 == 0 && v2 > 0) relay(A2_EMPTY, (v2 & 1u) ^ 1u);
         relay(W_FULL + s, ph);
         if (++s == NS) { s = 0; ph ^= 1u; }
+        if (++c2 == (uint32_t)a.nc) { c2 = 0; ++v2; }
       }
     }
   } else if (warp == 2) {
@@ -354,7 +384,10 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
     // ------------------------------------------------------------------ L2 prefetch of the next tile's rows
     const uint32_t rowbytes = (uint32_t)a.D * (TAB_BF16 ? 2u : 4u);
     for (uint32_t i = 0; i + 1 < T; ++i) {
-      ptx::mbar_wait(bar(X_FULL + 0), i & 1u);  // tile i is being consumed: fetch tile i + 1
+      ALINK_DBG_ROLE(128u, 3, i);
+      // tile i is being consumed: fetch tile i + 1. This warp only observes X_FULL (it neither fills nor frees
+      // the block), so the wait is bounded: a lagging prefetcher skips a tile instead of waiting on a stale parity.
+      if (!ptx::mbar_wait_soft(bar(X_FULL + 0), i & 1u, 2000000)) continue;
       const int64_t tile = tile_of(i + 1);
 #pragma unroll
       for (int e = 0; e < 4; ++e) {
@@ -378,6 +411,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
     float *b3s = reinterpret_cast<float *>(smem + P_B3);
     float rows[2 * ALINK_MAX_K];
     for (uint32_t q = 0; q < Q; ++q) {
+      ALINK_DBG_ROLE(8u, 4 + (warp & 3), q);
       const uint32_t i = q / G, g = q % G, l = g / (uint32_t)a.nc, c = g % (uint32_t)a.nc, b = q & 1u, u = q >> 1;
       // stage this chunk's bias (and, at a learner's first chunk, its layer-2 bias and last layer)
       b1s[b * 128 + et] = __ldg(a.b1 + (size_t)l * a.H1 + c * CHUNK_N + et);
@@ -524,6 +558,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
       issue(va0, vb0, 0);
     }
     for (uint32_t i = 0; i < T; ++i) {
+      ALINK_DBG_ROLE(16u, 8 + ((warp - 8) & 7), i);
       for (uint32_t kb = 0; kb < nkb; kb += 2) {
         const bool has1 = kb + 1 < nkb;
         if (has1) issue(va1, vb1, kb + 1);
@@ -634,6 +669,11 @@ static int tc_score(alink_ctx *ctx, const HeadGroup &g, const Table &A, const Ta
   a.b1 = g.b1; a.b2 = g.b2; a.W3 = g.W3; a.b3 = g.b3;
   a.probs = probs; a.util = util;
   a.ntiles = (int)((N + tc::TILE_M - 1) / tc::TILE_M);
+  {
+    const char *e = getenv("ALINK_TC_DBG_DELAY");  // "<role bits>:<ns>", read per launch; acts in the debug build only
+    unsigned bits = 0, ns = 0;
+    if (e && sscanf(e, "%u:%u", &bits, &ns) == 2) a.dbg = (bits & 255u) | (ns << 8);
+  }
   // Wide features (the tile does not fit in shared memory) take the k-outer kernel; ALINK_TC_KO=1 forces it.
   static const int ko_env = [] { const char *e = getenv("ALINK_TC_KO"); return e ? atoi(e) : 0; }();
   if (a.nkb > tc::MAX_KB || (ko_env == 1 && g.H1 <= 512)) return tc_score_ko(ctx, g, a, A.dtype == ALINK_BF16, f16);

@@ -55,12 +55,49 @@ __device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
 // A wait that never completes would hang the GPU: after ~2 s of polling trap instead (the context dies
 // with an error and the C ABI reports ALINK_E_CUDA). No printf / function call here: a call inside the
 // kernel makes ptxas ignore the per-warpgroup register budgets of setmaxnreg.
+// Watchdog record (failure detection): a wait that exceeds ~2 s writes WHO waited on WHAT into host-mapped
+// memory before it traps, so a protocol deadlock is reported instead of hanging the GPU (alink_watchdog_record).
+// Release build: the wait only traps (measured: even a one-record cold path costs 7 % of the head kernel —
+// registers and instruction cache in every warp role; the host then points at the debug build).
+// Debug build (-DALINK_TC_DEBUG, libalink_b200_dbg.so, ALINK_LIB_DEBUG=1): up to 63
+// waiting warps (r[0] = count; 2 words each) — every role stuck in the same deadlock times out within
+// microseconds of the first one, and the trap is delayed ~0.1 s so that they all get to report.
+__device__ unsigned long long *g_alink_wd = nullptr;
+__device__ __forceinline__ void mbar_timeout(uint32_t bar, uint32_t parity) {
+#ifdef ALINK_TC_DEBUG
+  unsigned long long *r = g_alink_wd;
+  if (r && (threadIdx.x & 31u) == 0u) {  // one record per warp
+    const unsigned long long slot = atomicAdd(r, 1ull);
+    if (slot < 63) {
+      uint32_t rank;
+      asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(rank));
+      r[1 + 2 * slot] = ((unsigned long long)blockIdx.x << 32) | threadIdx.x;
+      r[2 + 2 * slot] = ((unsigned long long)bar << 32) | (parity << 8) | rank;
+      __threadfence_system();
+    }
+  }
+  const long long t1 = clock64();
+  while (clock64() - t1 < 200000000LL) {}
+#endif
+  __trap();
+}
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   if (mbar_try_wait(bar, parity)) return;
   const long long t0 = clock64();
   while (!mbar_try_wait(bar, parity)) {
-    if (clock64() - t0 > 4000000000LL) __trap();
+    if (clock64() - t0 > 4000000000LL) mbar_timeout(bar, parity);
   }
+}
+
+// bounded wait without a trap, for roles that only FOLLOW a barrier they do not own (the L2 prefetcher): an
+// observer can fall two phases behind, where a parity wait would never return; it gives up and moves on instead
+__device__ __forceinline__ bool mbar_wait_soft(uint32_t bar, uint32_t parity, long long max_cycles) {
+  if (mbar_try_wait(bar, parity)) return true;
+  const long long t0 = clock64();
+  while (!mbar_try_wait(bar, parity)) {
+    if (clock64() - t0 > max_cycles) return false;
+  }
+  return true;
 }
 
 // generic-proxy writes (st.shared) -> visible to the async proxy (tcgen05.mma / TMA reads)

@@ -202,6 +202,7 @@ def main():
     ap.add_argument("--cpu-sample", type=int, default=100_000)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-mode-compare", action="store_true")
+    ap.add_argument("--no-clock-sampling", action="store_true", help="for runs under ncu: no NVML polling thread")
     args = ap.parse_args()
 
     rank = int(os.environ.get("RANK", "0"))
@@ -326,7 +327,7 @@ def main():
         return float(ms.item()) / steps, {k_: v / steps for k_, v in stage.items()}, launches, clocks, merged, dev_ms / steps
 
     ctx.set_table(0, table_dev)
-    ms_step, stage, launches, clocks, merged, dev_ms = timed(step_resident, args.steps, args.warmup, sample_clocks=True)
+    ms_step, stage, launches, clocks, merged, dev_ms = timed(step_resident, args.steps, args.warmup, sample_clocks=not args.no_clock_sampling)
     refine_stats = ctx.refine_stats() if args.mode == "refine" else None
     refine_detail = ctx.refine_detail() if args.mode == "refine" else None
     ms_e2e, stage_e2e, _, _, merged_e2e, _ = timed(step_e2e, max(2, min(args.steps, 3)), 1)

@@ -81,6 +81,11 @@ int alink_sync(alink_ctx *ctx);
 int alink_set_stream(alink_ctx *ctx, void *cuda_stream);
 /* total kernels launched by this context so far (bench.py's gpu_launches) */
 int64_t alink_launch_count(const alink_ctx *ctx);
+/* Failure detection: a device-side wait that exceeds ~2 s (a protocol deadlock) records itself in host-mapped
+ * memory and traps, instead of hanging the GPU. out[0] = number of waiters that timed out; for the first 63 of
+ * them, out[1 + 2 i] = blockIdx << 32 | threadIdx, out[2 + 2 i] = shared-memory barrier address << 32 |
+ * parity << 8 | cluster rank. Readable after the launch failure. */
+int alink_watchdog_record(const alink_ctx *ctx, uint64_t out[256]);  /* words 128.. = debug progress counters (ALINK_TC_DBG_DELAY bit 6) */
 /* pinned host memory for ALINK_HOST buffers that should move at full PCIe rate */
 int alink_host_alloc(void **out, uint64_t bytes);
 int alink_host_free(void *p);
