@@ -38,7 +38,7 @@ SYMBOLS = (
     "alink_score_indexed", "alink_score_dense", "alink_utility", "alink_utility_from_proba",
     "alink_select_topk", "alink_topk_values", "alink_topk_keys", "alink_query", "alink_disparity_select",
     "alink_set_refine_eps", "alink_refine_stats", "alink_refine_detail", "alink_score_allpairs", "alink_query_allpairs",
-    "alink_disparity_hist", "alink_disparity_select_sharded",
+    "alink_disparity_hist", "alink_disparity_select_sharded", "alink_roc_counts",
 )
 
 
@@ -119,6 +119,8 @@ def load():
     L.alink_set_refine_eps.argtypes = [vp, dbl]
     L.alink_refine_stats.restype = i32
     L.alink_refine_stats.argtypes = [vp, C.POINTER(i64), C.POINTER(C.c_float)]
+    L.alink_roc_counts.restype = i32
+    L.alink_roc_counts.argtypes = [vp, vp, vp, i64, i64, i64, i32, vp, i32, i32, vp, vp, C.POINTER(u64), C.POINTER(u64)]
     L.alink_watchdog_record.restype = i32
     L.alink_watchdog_record.argtypes = [vp, C.POINTER(u64)]
     L.alink_disparity_hist.restype = i32
@@ -371,6 +373,22 @@ class Context:
                                                            float(eps), int(bool(blind)), py, s2, idx.ctypes.data, HOST,
                                                            C.byref(n_out), C.byref(active)))
         return idx[:n_out.value].copy(), int(active.value)
+
+    def roc_counts(self, scores, mask, thresholds, roc_case, row0=0):
+        """(tp[nthr], fp[nthr], n_genuine, n_impostor) over the strict upper triangle of a score-matrix block."""
+        P, G = int(scores.shape[0]), int(scores.shape[1])
+        thr = np.ascontiguousarray(thresholds, dtype=np.float64).reshape(-1)
+        if not _is_torch(scores):
+            scores = np.ascontiguousarray(scores, dtype=np.float32)
+        if not _is_torch(mask):
+            mask = np.ascontiguousarray(mask, dtype=np.int32)
+        sp = _space_of(scores, mask)
+        tp, fp = np.zeros(len(thr), np.uint64), np.zeros(len(thr), np.uint64)
+        ng, ni = C.c_uint64(0), C.c_uint64(0)
+        self._check(self._L.alink_roc_counts(self._h, _ptr_space(scores)[0], _ptr_space(mask)[0], P, G, int(row0),
+                                             int(roc_case), thr.ctypes.data, len(thr), sp, tp.ctypes.data, fp.ctypes.data,
+                                             C.byref(ng), C.byref(ni)))
+        return tp, fp, int(ng.value), int(ni.value)
 
     def score_allpairs(self, group, slot_probe, slot_gallery, row0, nrows, G, K, Cc, want_per=False, want_cons=True):
         """Scores of probe rows [row0, row0+nrows) against all G gallery rows: consensus (nrows*G, C)."""

@@ -9,6 +9,7 @@
 #include "topk.cuh"
 #include "disparity.cuh"
 #include "refine.cuh"
+#include "roc.cuh"
 
 #include <math.h>
 #include <new>
@@ -679,6 +680,63 @@ int alink_query_allpairs(alink_ctx *ctx, int group, int slot_probe, int slot_gal
   ctx->ap_G = 0;
   ctx->ap_pair0 = 0;
   return rc;
+}
+
+// ------------------------------------------------------------------------------------------ ROC counts
+int alink_roc_counts(alink_ctx *ctx, const float *scores, const int32_t *mask, int64_t P, int64_t G, int64_t row0,
+                     int roc_case, const double *thresholds, int nthr, int in_space, uint64_t *tp, uint64_t *fp,
+                     uint64_t *n_genuine, uint64_t *n_impostor) {
+  if (!ctx) return ALINK_E_INVALID;
+  if (P < 0 || G < 0 || row0 < 0 || nthr < 0 || nthr > ROC_MAX_THR || roc_case < 1 || roc_case > 3 || (nthr && (!thresholds || !tp || !fp)))
+    return alink_fail(ctx, ALINK_E_INVALID, "bad arguments (P=%lld G=%lld row0=%lld nthr=%d case=%d)", (long long)P,
+                      (long long)G, (long long)row0, nthr, roc_case);
+  if ((double)P * (double)G > 9.0e18) return alink_fail(ctx, ALINK_E_INVALID, "matrix too large");
+  // sorted copy of the thresholds + where each one came from
+  std::vector<int> order((size_t)nthr);
+  for (int i = 0; i < nthr; ++i) {
+    if (thresholds[i] != thresholds[i]) return alink_fail(ctx, ALINK_E_INVALID, "threshold %d is NaN", i);
+    order[i] = i;
+  }
+  std::stable_sort(order.begin(), order.end(), [&](int x, int y) { return thresholds[x] < thresholds[y]; });
+  std::vector<double> sorted((size_t)nthr);
+  for (int i = 0; i < nthr; ++i) sorted[i] = thresholds[order[i]];
+  const int nb = nthr + 1;
+  std::vector<unsigned long long> hist((size_t)2 * nb, 0ull);
+  if (P > 0 && G > 0) {
+    if (!scores || !mask) return alink_fail(ctx, ALINK_E_INVALID, "null scores / mask");
+    ALINK_CUDA(ctx, cudaSetDevice(ctx->device));
+    const void *ds, *dm;
+    ALINK_TRY(stage_in(ctx, scores, sizeof(float) * (size_t)P * G, in_space, ctx->misc0, &ds));
+    ALINK_TRY(stage_in(ctx, mask, sizeof(int32_t) * (size_t)P * G, in_space, ctx->misc1, &dm));
+    const size_t thr_bytes = sizeof(double) * (size_t)(nthr ? nthr : 1), hist_bytes = sizeof(unsigned long long) * 2 * nb;
+    ALINK_TRY(dev_reserve(ctx, ctx->misc2, thr_bytes));
+    ALINK_TRY(dev_reserve(ctx, ctx->misc3, hist_bytes));
+    if (nthr) ALINK_CUDA(ctx, cudaMemcpyAsync(ctx->misc2.p, sorted.data(), sizeof(double) * nthr, cudaMemcpyHostToDevice, ctx->stream));
+    ALINK_CUDA(ctx, cudaMemsetAsync(ctx->misc3.p, 0, hist_bytes, ctx->stream));
+    int64_t blocks = (P * G + 256 * 16 - 1) / (256 * 16);
+    const int64_t cap = (int64_t)ctx->sm_count * 8;
+    if (blocks > cap) blocks = cap;
+    const size_t smem = thr_bytes + sizeof(unsigned int) * 2 * nb;
+    roc_hist_kernel<<<(unsigned)blocks, 256, smem, ctx->stream>>>((const float *)ds, (const int32_t *)dm, P, G, row0, roc_case,
+                                                                 (const double *)ctx->misc2.p, nthr,
+                                                                 (unsigned long long *)ctx->misc3.p);
+    ALINK_LAUNCHED(ctx);
+    ALINK_CUDA(ctx, cudaMemcpyAsync(hist.data(), ctx->misc3.p, hist_bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    ALINK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  }
+  // bin k = #thresholds <= score; score >= sorted[t]  <=>  k >= t + 1
+  for (int cls = 0; cls < 2; ++cls) {
+    unsigned long long run = 0, all = hist[(size_t)cls * nb];
+    uint64_t *out = cls == 0 ? tp : fp;
+    for (int t = nthr - 1; t >= 0; --t) {
+      run += hist[(size_t)cls * nb + t + 1];
+      out[order[t]] = (uint64_t)run;
+    }
+    all += run;
+    if (cls == 0 && n_genuine) *n_genuine = (uint64_t)all;
+    if (cls == 1 && n_impostor) *n_impostor = (uint64_t)all;
+  }
+  return ALINK_OK;
 }
 
 // ------------------------------------------------------------------------------------------ A-LINK rule

@@ -19,7 +19,8 @@ _COMPUTE = {"mode": _ffi.FP32_EXACT}
 
 
 def set_compute_mode(mode: str) -> None:
-    """'fp32' (bit-exact with the oracle, CUDA cores) or 'bf16' (tcgen05 tensor cores)."""
+    """'fp32' (bit-exact with the oracle, CUDA cores), 'bf16' (tcgen05 tensor cores) or 'refine' (queries: tensor-core
+    filter + bit-exact re-score, selection identical to 'fp32'; score calls stay exact)."""
     _COMPUTE["mode"] = _ffi.COMPUTE_ID[mode]
     _GroupCache.invalidate_all()
 

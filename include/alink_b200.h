@@ -194,6 +194,16 @@ int alink_disparity_select_sharded(alink_ctx *ctx, const float *p2, const float 
                                    const uint64_t *thr_keys, double eps, int blind, const float *y, int in_space,
                                    int64_t *idx_out, int out_space, int64_t *n_out, int64_t *active_count);
 
+/* Verification-curve counts on a block of the all-pairs score matrix. Replaces the loops of
+ * utilities/ROC_precompute.py:19-63: over the strict upper triangle (j > row0 + r) of scores[P][G], mask codes
+ * pick the genuine / impostor pairs of a protocol (roc_case 1: code 1 vs 3; 2: 2 vs 4; 3: {1,2} vs {3,4});
+ * tp[t] / fp[t] = number of genuine / impostor scores >= thresholds[t] (compared in double, like the reference's
+ * float64 matrix); n_genuine / n_impostor = the denominators of TPR / FPR. thresholds, tp, fp and the scalars
+ * are host arrays (nthr <= 2047, any order); scores / mask follow in_space. Blocks of probe rows add up. */
+int alink_roc_counts(alink_ctx *ctx, const float *scores, const int32_t *mask, int64_t P, int64_t G, int64_t row0,
+                     int roc_case, const double *thresholds, int nthr, int in_space, uint64_t *tp, uint64_t *fp,
+                     uint64_t *n_genuine, uint64_t *n_impostor);
+
 #ifdef __cplusplus
 }
 #endif

@@ -172,3 +172,21 @@ def logf(x):
 
 def pack_key(u, idx):
     return int(lib().alink_oracle_pack_key(float(u), int(idx)))
+
+
+def roc_counts(scores, mask, thresholds, roc_case, row0=0):
+    """(tp, fp, n_genuine, n_impostor) — utilities/ROC_precompute.py:19-63 on a block of the score matrix."""
+    L = lib()
+    L.alink_oracle_roc_counts.restype = C.c_int
+    L.alink_oracle_roc_counts.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_int, C.c_void_p,
+                                          C.c_int, C.c_void_p, C.c_void_p, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
+    s = _f32(scores)
+    m = np.ascontiguousarray(mask, dtype=np.int32)
+    thr = np.ascontiguousarray(thresholds, dtype=np.float64).reshape(-1)
+    tp, fp = np.zeros(len(thr), np.uint64), np.zeros(len(thr), np.uint64)
+    ng, ni = C.c_uint64(0), C.c_uint64(0)
+    rc = L.alink_oracle_roc_counts(_ptr(s), _ptr(m), s.shape[0], s.shape[1], int(row0), int(roc_case), _ptr(thr),
+                                   len(thr), _ptr(tp), _ptr(fp), C.byref(ng), C.byref(ni))
+    if rc != 0:
+        raise ValueError("alink_oracle_roc_counts rc=%d" % rc)
+    return tp, fp, int(ng.value), int(ni.value)

@@ -203,3 +203,17 @@ def disparity_select(p2, p1, ratio=0.25, eps=0.05, blind=False, y=None):
             if y is None or ((ep >= 0.5) == (y[j] >= 0.5)):                          # ALINK.py:196-200
                 query.append(j)
     return np.array(query, dtype=np.int64), active
+
+
+def roc_precompute(score_matrix, masked_matrix, thresholds, roc_case):
+    """utilities/ROC_precompute.py:19-63 with the Python loops replaced by their numpy meaning (float64 matrix, as
+    np.loadtxt gives): returns (true_positive_rate, false_positive_rate), one value per threshold."""
+    s = np.asarray(score_matrix, dtype=np.float64)
+    m = np.asarray(masked_matrix)
+    iu = np.triu_indices(s.shape[0], k=1, m=s.shape[1])
+    sv, mv = s[iu], m[iu]
+    gen_codes, imp_codes = {1: ((1,), (3,)), 2: ((2,), (4,)), 3: ((1, 2), (3, 4))}[roc_case]
+    gen, imp = sv[np.isin(mv, gen_codes)], sv[np.isin(mv, imp_codes)]
+    tpr = [float(np.sum(gen >= t)) / len(gen) for t in thresholds]
+    fpr = [float(np.sum(imp >= t)) / len(imp) for t in thresholds]
+    return np.array(tpr), np.array(fpr)
