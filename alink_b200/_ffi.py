@@ -39,6 +39,7 @@ SYMBOLS = (
     "alink_select_topk", "alink_topk_values", "alink_topk_keys", "alink_query", "alink_disparity_select",
     "alink_set_refine_eps", "alink_refine_stats", "alink_refine_detail", "alink_score_allpairs", "alink_query_allpairs",
     "alink_disparity_hist", "alink_disparity_select_sharded", "alink_roc_counts",
+    "alink_train_step", "alink_get_train_state", "alink_set_train_state",
 )
 
 
@@ -119,6 +120,13 @@ def load():
     L.alink_set_refine_eps.argtypes = [vp, dbl]
     L.alink_refine_stats.restype = i32
     L.alink_refine_stats.argtypes = [vp, C.POINTER(i64), C.POINTER(C.c_float)]
+    L.alink_train_step.restype = i32
+    L.alink_train_step.argtypes = [vp, i32, i32, i32, i32, vp, vp, vp, i32, i32, dbl, dbl, dbl, i32,
+                                   C.POINTER(C.c_float), C.POINTER(C.c_float), vp]
+    L.alink_get_train_state.restype = i32
+    L.alink_get_train_state.argtypes = [vp, i32, i32, i32, C.POINTER(vp)]
+    L.alink_set_train_state.restype = i32
+    L.alink_set_train_state.argtypes = [vp, i32, i32, i32, C.POINTER(vp)]
     L.alink_roc_counts.restype = i32
     L.alink_roc_counts.argtypes = [vp, vp, vp, i64, i64, i64, i32, vp, i32, i32, vp, vp, C.POINTER(u64), C.POINTER(u64)]
     L.alink_watchdog_record.restype = i32
@@ -373,6 +381,31 @@ class Context:
                                                            float(eps), int(bool(blind)), py, s2, idx.ctypes.data, HOST,
                                                            C.byref(n_out), C.byref(active)))
         return idx[:n_out.value].copy(), int(active.value)
+
+    def train_step(self, group, learner, slot_a, slot_b, ia, ib, y, lr=1.0, rho=0.95, eps=1e-7, apply=True,
+                   want_probs=False, C_out=2):
+        """One Adadelta minibatch step (or, apply=False, an evaluation) -> (loss, accuracy[, probs])."""
+        nb = int(len(y))
+        yy = y if _is_torch(y) else _f32(y).reshape(-1)
+        sp = _space_of(ia, ib, yy)
+        loss, acc = C.c_float(0), C.c_float(0)
+        probs = np.empty((nb, C_out), np.float32) if want_probs else None
+        self._check(self._L.alink_train_step(self._h, group, learner, slot_a, slot_b, _ptr_space(ia)[0], _ptr_space(ib)[0],
+                                             _ptr_space(yy)[0], nb, sp, float(lr), float(rho), float(eps), int(bool(apply)),
+                                             C.byref(loss), C.byref(acc), _ptr_space(probs)[0]))
+        return (float(loss.value), float(acc.value), probs) if want_probs else (float(loss.value), float(acc.value))
+
+    def get_train_state(self, group, learner, which, shapes):
+        """Six arrays (Keras order) of learner `learner`: which = 0 parameters, 1 Adadelta E[g^2], 2 E[dx^2]."""
+        arrs = [np.empty(shp, np.float32) for shp in shapes]
+        pp, keep = _pp(arrs)
+        self._check(self._L.alink_get_train_state(self._h, group, learner, which, pp))
+        return arrs
+
+    def set_train_state(self, group, learner, which, arrs):
+        arrs = [_f32(a) for a in arrs]
+        pp, keep = _pp(arrs)
+        self._check(self._L.alink_set_train_state(self._h, group, learner, which, pp))
 
     def roc_counts(self, scores, mask, thresholds, roc_case, row0=0):
         """(tp[nthr], fp[nthr], n_genuine, n_impostor) over the strict upper triangle of a score-matrix block."""

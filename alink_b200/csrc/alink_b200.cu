@@ -10,6 +10,7 @@
 #include "disparity.cuh"
 #include "refine.cuh"
 #include "roc.cuh"
+#include "train.cuh"
 
 #include <math.h>
 #include <new>
@@ -56,6 +57,10 @@ static void free_group(HeadGroup &g) {
   void *ptrs[] = {g.W1, g.b1, g.W2, g.b2, g.W3, g.b3, (void *)g.pW1, g.W1t, g.W2t, g.W1h, g.W2h};
   for (void *p : ptrs)
     if (p) cudaFree(p);
+  for (int t = 0; t < 6; ++t) {
+    if (g.opt_a[t]) cudaFree(g.opt_a[t]);
+    if (g.opt_d[t]) cudaFree(g.opt_d[t]);
+  }
   g = HeadGroup();
 }
 
@@ -67,7 +72,8 @@ int alink_destroy(alink_ctx *ctx) {
   for (auto &t : ctx->tables) dev_release(t.own);
   DevBuf *bufs[] = {&ctx->idx_a, &ctx->idx_b, &ctx->h1ws, &ctx->probs, &ctx->cons, &ctx->util, &ctx->sel_state,
                     &ctx->sel_keys, &ctx->sel_idx, &ctx->sel_util, &ctx->sel_in, &ctx->misc0, &ctx->misc1,
-                    &ctx->misc2, &ctx->misc3, &ctx->cand, &ctx->cia, &ctx->cib, &ctx->util_c, &ctx->rstat, &ctx->xscratch};
+                    &ctx->misc2, &ctx->misc3, &ctx->cand, &ctx->cia, &ctx->cib, &ctx->util_c, &ctx->rstat, &ctx->xscratch,
+                    &ctx->train_ws, &ctx->train_y, &ctx->train_out};
   for (DevBuf *b : bufs) dev_release(*b);
   for (int i = 0; i < 8; ++i)
     if (ctx->ev[i]) cudaEventDestroy(ctx->ev[i]);
@@ -452,7 +458,7 @@ static int refine_query(alink_ctx *ctx, const HeadGroup &g, Table &A, Table &Bt,
   ctx->N = N; ctx->sK = g.K; ctx->sC = g.C; ctx->util_valid = false; ctx->probs_full = false;
   // operand format of the filter: half unless a feature or hidden activation could exceed its range
   static const int fmt_env = [] { const char *e = getenv("ALINK_REFINE_FMT"); return e ? atoi(e) : 0; }();  // 1 = force bf16
-  bool f16 = g.W1h && g.W2h && fmt_env != 1;
+  bool f16 = g.W1h && g.W2h && fmt_env != 1 && !g.bounds_stale;
   if (f16) {
     double ma, mb;
     ALINK_TRY(table_absmax(ctx, A, &ma));
@@ -680,6 +686,143 @@ int alink_query_allpairs(alink_ctx *ctx, int group, int slot_probe, int slot_gal
   ctx->ap_G = 0;
   ctx->ap_pair0 = 0;
   return rc;
+}
+
+// ------------------------------------------------------------------------------------------ finetune step
+static void group_tensor_sizes(const HeadGroup &g, size_t each[6]) {
+  each[0] = (size_t)g.D_in * g.H1; each[1] = (size_t)g.H1; each[2] = (size_t)g.H1 * g.H2;
+  each[3] = (size_t)g.H2; each[4] = (size_t)g.H2 * g.C; each[5] = (size_t)g.C;
+}
+
+static int ensure_opt_state(alink_ctx *ctx, HeadGroup &g) {
+  size_t each[6];
+  group_tensor_sizes(g, each);
+  for (int t = 0; t < 6; ++t) {
+    if (g.opt_a[t]) continue;
+    ALINK_CUDA(ctx, cudaMalloc((void **)&g.opt_a[t], sizeof(float) * each[t] * g.K));
+    ALINK_CUDA(ctx, cudaMalloc((void **)&g.opt_d[t], sizeof(float) * each[t] * g.K));
+    ALINK_CUDA(ctx, cudaMemsetAsync(g.opt_a[t], 0, sizeof(float) * each[t] * g.K, ctx->stream));
+    ALINK_CUDA(ctx, cudaMemsetAsync(g.opt_d[t], 0, sizeof(float) * each[t] * g.K, ctx->stream));
+  }
+  return ALINK_OK;
+}
+
+int alink_train_step(alink_ctx *ctx, int group, int learner, int slot_a, int slot_b, const int32_t *ia, const int32_t *ib,
+                     const float *y, int nb, int in_space, double lr, double rho, double eps, int apply, float *loss_out,
+                     float *acc_out, float *probs_out) {
+  if (!ctx) return ALINK_E_INVALID;
+  if (group < 0 || group >= ALINK_MAX_GROUPS || !ctx->groups[group].set)
+    return alink_fail(ctx, ALINK_E_STATE, "head group %d not set (alink_set_heads)", group);
+  HeadGroup &g = ctx->groups[group];
+  if (learner < 0 || learner >= g.K) return alink_fail(ctx, ALINK_E_INVALID, "learner %d outside [0, %d)", learner, g.K);
+  if (slot_a < 0 || slot_a >= ALINK_MAX_SLOTS || slot_b < 0 || slot_b >= ALINK_MAX_SLOTS) return alink_fail(ctx, ALINK_E_INVALID, "bad slot");
+  if (nb < 1 || nb > 65536 || !y) return alink_fail(ctx, ALINK_E_INVALID, "bad batch (nb=%d)", nb);
+  if ((ia == nullptr) != (ib == nullptr)) return alink_fail(ctx, ALINK_E_INVALID, "ia and ib must both be given or both NULL");
+  const Table &A = ctx->tables[slot_a], &Bt = ctx->tables[slot_b];
+  if (!A.p || !Bt.p) return alink_fail(ctx, ALINK_E_STATE, "embedding table slot not set (alink_set_table)");
+  if (A.dtype != ALINK_F32 || Bt.dtype != ALINK_F32 || A.D != Bt.D || (g.feat_mode ? 2 * A.D : A.D) != g.D_in)
+    return alink_fail(ctx, ALINK_E_INVALID, "the finetune step needs fp32 tables matching the heads' fan-in");
+  if (!ia && (nb > A.M || nb > Bt.M)) return alink_fail(ctx, ALINK_E_INVALID, "identity pairs exceed table rows");
+  ALINK_CUDA(ctx, cudaSetDevice(ctx->device));
+  ALINK_TRY(ensure_opt_state(ctx, g));
+  const void *dia, *dib, *dy;
+  ALINK_TRY(stage_in(ctx, ia, sizeof(int32_t) * (size_t)nb, in_space, ctx->idx_a, &dia));
+  ALINK_TRY(stage_in(ctx, ib, sizeof(int32_t) * (size_t)nb, in_space, ctx->idx_b, &dib));
+  ALINK_TRY(stage_in(ctx, y, sizeof(float) * (size_t)nb, in_space, ctx->train_y, &dy));
+  // workspace: X | h1 | h2 | dz1 | dz2 | dz3 | loss | acc | probs
+  const size_t nX = (size_t)nb * g.D_in, n1 = (size_t)nb * g.H1, n2 = (size_t)nb * g.H2, n3 = (size_t)nb * 2;
+  ALINK_TRY(dev_reserve(ctx, ctx->train_ws, sizeof(float) * (nX + 2 * n1 + 2 * n2 + 2 * n3 + 2 * (size_t)nb)));
+  ALINK_TRY(dev_reserve(ctx, ctx->train_out, 16));
+  float *X = (float *)ctx->train_ws.p, *h1 = X + nX, *h2 = h1 + n1, *dz1 = h2 + n2, *dz2 = dz1 + n1, *dz3 = dz2 + n2;
+  float *lossv = dz3 + n3, *accv = lossv + nb, *probs = accv + nb;
+  size_t each[6];
+  group_tensor_sizes(g, each);
+  float *W1 = g.W1 + each[0] * learner, *b1 = g.b1 + each[1] * learner, *W2 = g.W2 + each[2] * learner;
+  float *b2 = g.b2 + each[3] * learner, *W3 = g.W3 + each[4] * learner, *b3 = g.b3 + each[5] * learner;
+  auto grid = [&](size_t n) { size_t b = (n + 255) / 256; return (unsigned)(b < 1 ? 1 : (b > 4096 ? 4096 : b)); };
+  cudaStream_t st = ctx->stream;
+  train_feat_kernel<<<grid(nX), 256, 0, st>>>((const float *)A.p, (const float *)Bt.p, (const int32_t *)dia, (const int32_t *)dib, A.D,
+                                              g.feat_mode == ALINK_FEAT_ABSDIFF_HADAMARD, nb, X);
+  ALINK_LAUNCHED(ctx);
+  train_dense_fwd_kernel<<<grid(n1), 256, 0, st>>>(X, g.D_in, W1, b1, g.H1, nb, h1);
+  ALINK_LAUNCHED(ctx);
+  train_dense_fwd_kernel<<<grid(n2), 256, 0, st>>>(h1, g.H1, W2, b2, g.H2, nb, h2);
+  ALINK_LAUNCHED(ctx);
+  train_head_kernel<<<grid(nb), 256, 0, st>>>(h2, W3, b3, g.H2, g.C, (const float *)dy, nb, lossv, accv, dz3, probs);
+  ALINK_LAUNCHED(ctx);
+  train_mean_kernel<<<1, 32, 0, st>>>(lossv, accv, nb, (float *)ctx->train_out.p);
+  ALINK_LAUNCHED(ctx);
+  if (apply) {
+    const float flr = (float)lr, frho = (float)rho, feps = (float)eps;
+    train_grad_in_kernel<<<grid(n2), 256, 0, st>>>(dz3, g.C, W3, g.H2, h2, nb, dz2);
+    ALINK_LAUNCHED(ctx);
+    train_grad_in_kernel<<<grid(n1), 256, 0, st>>>(dz2, g.H2, W2, g.H1, h1, nb, dz1);
+    ALINK_LAUNCHED(ctx);
+    float *oa[6], *od[6];
+    for (int t = 0; t < 6; ++t) {
+      oa[t] = g.opt_a[t] + each[t] * learner;
+      od[t] = g.opt_d[t] + each[t] * learner;
+    }
+    train_update_w_kernel<<<grid(each[4]), 256, 0, st>>>(h2, g.H2, dz3, g.C, nb, W3, oa[4], od[4], flr, frho, feps);
+    ALINK_LAUNCHED(ctx);
+    train_update_b_kernel<<<grid(each[5]), 256, 0, st>>>(dz3, g.C, nb, b3, oa[5], od[5], flr, frho, feps);
+    ALINK_LAUNCHED(ctx);
+    train_update_w_kernel<<<grid(each[2]), 256, 0, st>>>(h1, g.H1, dz2, g.H2, nb, W2, oa[2], od[2], flr, frho, feps);
+    ALINK_LAUNCHED(ctx);
+    train_update_b_kernel<<<grid(each[3]), 256, 0, st>>>(dz2, g.H2, nb, b2, oa[3], od[3], flr, frho, feps);
+    ALINK_LAUNCHED(ctx);
+    train_update_w_kernel<<<grid(each[0]), 256, 0, st>>>(X, g.D_in, dz1, g.H1, nb, W1, oa[0], od[0], flr, frho, feps);
+    ALINK_LAUNCHED(ctx);
+    train_update_b_kernel<<<grid(each[1]), 256, 0, st>>>(dz1, g.H1, nb, b1, oa[1], od[1], flr, frho, feps);
+    ALINK_LAUNCHED(ctx);
+    // the tensor-core operand images follow the fp32 masters; the half-overflow bound is recomputed by the next
+    // alink_set_heads (until then FP32_REFINE filters with bf16)
+    if (g.W1t) {
+      tc::prep_w1_kernel<false><<<ctx->sm_count * 4, 256, 0, st>>>(g.W1, (uint8_t *)g.W1t, g.K, g.D_in, g.H1);
+      ALINK_LAUNCHED(ctx);
+      tc::prep_w2_kernel<false><<<ctx->sm_count, 256, 0, st>>>(g.W2, (uint8_t *)g.W2t, g.K, g.H1, g.H2);
+      ALINK_LAUNCHED(ctx);
+    }
+    g.bounds_stale = true;
+  }
+  float hout[2] = {0, 0};
+  ALINK_CUDA(ctx, cudaMemcpyAsync(hout, ctx->train_out.p, 8, cudaMemcpyDeviceToHost, st));
+  if (probs_out) ALINK_CUDA(ctx, cudaMemcpyAsync(probs_out, probs, sizeof(float) * (size_t)nb * g.C, cudaMemcpyDeviceToHost, st));
+  ALINK_CUDA(ctx, cudaStreamSynchronize(st));
+  if (loss_out) *loss_out = hout[0];
+  if (acc_out) *acc_out = hout[1];
+  return ALINK_OK;
+}
+
+// which: 0 = parameters, 1 = Adadelta E[g^2], 2 = Adadelta E[dx^2]; six host arrays in Keras order (W1,b1,W2,b2,W3,b3)
+static int train_state_xfer(alink_ctx *ctx, int group, int learner, int which, float *const *host, bool to_host) {
+  if (!ctx) return ALINK_E_INVALID;
+  if (group < 0 || group >= ALINK_MAX_GROUPS || !ctx->groups[group].set)
+    return alink_fail(ctx, ALINK_E_STATE, "head group %d not set (alink_set_heads)", group);
+  HeadGroup &g = ctx->groups[group];
+  if (learner < 0 || learner >= g.K || which < 0 || which > 2 || !host) return alink_fail(ctx, ALINK_E_INVALID, "bad arguments");
+  ALINK_CUDA(ctx, cudaSetDevice(ctx->device));
+  if (which) ALINK_TRY(ensure_opt_state(ctx, g));
+  size_t each[6];
+  group_tensor_sizes(g, each);
+  float *base[6] = {g.W1, g.b1, g.W2, g.b2, g.W3, g.b3};
+  for (int t = 0; t < 6; ++t) {
+    if (!host[t]) continue;
+    float *dev = (which == 0 ? base[t] : (which == 1 ? g.opt_a[t] : g.opt_d[t])) + each[t] * learner;
+    if (to_host) ALINK_CUDA(ctx, cudaMemcpyAsync(host[t], dev, sizeof(float) * each[t], cudaMemcpyDeviceToHost, ctx->stream));
+    else ALINK_CUDA(ctx, cudaMemcpyAsync(dev, host[t], sizeof(float) * each[t], cudaMemcpyHostToDevice, ctx->stream));
+  }
+  ALINK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return ALINK_OK;
+}
+
+int alink_get_train_state(alink_ctx *ctx, int group, int learner, int which, float *const *host_out) {
+  return train_state_xfer(ctx, group, learner, which, host_out, true);
+}
+
+int alink_set_train_state(alink_ctx *ctx, int group, int learner, int which, const float *const *host_in) {
+  if (which == 0) return ctx ? alink_fail(ctx, ALINK_E_INVALID, "parameters are set with alink_set_heads") : ALINK_E_INVALID;
+  return train_state_xfer(ctx, group, learner, which, (float *const *)host_in, false);
 }
 
 // ------------------------------------------------------------------------------------------ ROC counts

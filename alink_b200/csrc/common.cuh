@@ -30,6 +30,10 @@ struct HeadGroup {
   bool tc_ok = false;  // the tensor-core images exist (shape supported by head_tc.cuh)
   // bound for "no half overflow": max_j sum_k |W1[k][j]| over learners, max |b1| (host, at alink_set_heads)
   double w1_col_l1 = 0.0, b1_absmax = 0.0, w_absmax = 0.0;
+  bool bounds_stale = false;  // weights changed on the device (train.cuh) since those bounds were computed
+  // Adadelta accumulators of the finetune step (train.cuh), same [K][...] layout as the six tensors; lazy, zeroed
+  float *opt_a[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+  float *opt_d[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
 };
 
 struct Table {
@@ -82,6 +86,7 @@ struct alink_ctx {
   uint32_t ap_G = 0;
   int64_t ap_pair0 = 0;
   DevBuf xscratch;  // head_tc_ko.cuh: per-CTA bf16 feature-tile images
+  DevBuf train_ws, train_y, train_out;  // train.cuh: activations / gradients of one minibatch
   unsigned long long *wd_host = nullptr;  // host-mapped watchdog record (ptx.cuh: mbar_timeout)
 };
 

@@ -72,11 +72,105 @@ class SiameseNetwork:
     def _alink_specs(self):
         return [self._spec]
 
-    # ---- out of scope
-    def _no_training(self, *a, **k):
-        raise NotImplementedError("training is outside the query-selection path (SURVEY.md §8f item 2)")
+    # ---- the finetune ("teach") step on the selected pairs
+    def finetune(self, X, Y, epochs, batch_size, verbose=1, validation_split=0.2):
+        """code/siamese.py:52-58: Keras `fit(X, to_categorical(Y), batch_size, epochs, validation_split=0.2,
+        callbacks=[EarlyStopping('val_loss', min_delta=0.1, patience=5), ReduceLROnPlateau('val_loss', factor=0.2,
+        patience=5, min_lr=0.01)])` with Adadelta(self.learningRate) and binary cross-entropy. [external: Keras 2.1.2
+        fit semantics] the LAST `validation_split` of the samples is held out, the rest is reshuffled every epoch
+        with np.random.shuffle (seeded by the driver, code/ALINK.py:19) and cut into batches of `batch_size`.
+        Every batch is one `alink_train_step` on device-resident weights; returns a Keras-History-like dict."""
+        from . import _ffi
+        XL, XR = engine._as_pair(self.preprocess(X))
+        y = np.asarray(Y, dtype=np.float32).reshape(-1)
+        n = len(y)
+        if n != len(XL):
+            raise ValueError("X and Y disagree on the number of pairs")
+        ctx = _ffi.default_context()
+        sa, sb = _ffi.MAX_SLOTS - 2, _ffi.MAX_SLOTS - 1
+        ctx.set_table(sa, XL)
+        ctx.set_table(sb, XR)
+        g = engine._GroupCache.group_for(ctx, [self._spec])
+        spec = self._spec
+        shapes = [(spec.D_in, spec.H1), (spec.H1,), (spec.H1, spec.H2), (spec.H2,), (spec.H2, spec.C), (spec.C,)]
+        if getattr(self, "_opt", None) is not None:  # Adadelta accumulators live as long as the model (Keras optimizer)
+            ctx.set_train_state(g, 0, 1, self._opt[0])
+            ctx.set_train_state(g, 0, 2, self._opt[1])
+        split = int(n * (1.0 - validation_split)) if validation_split else n
+        tr_idx, va_idx = np.arange(split, dtype=np.int32), np.arange(split, n, dtype=np.int32)
+        lr = float(self.learningRate)
+        hist = {"loss": [], "acc": [], "val_loss": [], "val_acc": [], "lr": []}
+        es_best, es_wait = np.inf, 0
+        rl_best, rl_wait = np.inf, 0
 
-    trainModel = finetune = customTrainModel = testAccuracy = getDenseBarebones = _no_training
+        def run(idx, apply):
+            tot_l = tot_a = 0.0
+            for lo in range(0, len(idx), batch_size):
+                b = np.ascontiguousarray(idx[lo:lo + batch_size])
+                l, a = ctx.train_step(g, 0, sa, sb, b, b, y[b], lr=lr, apply=apply)
+                tot_l += l * len(b)
+                tot_a += a * len(b)
+            return (tot_l / len(idx), tot_a / len(idx)) if len(idx) else (float("nan"), float("nan"))
+
+        for epoch in range(int(epochs)):
+            order = tr_idx.copy()
+            np.random.shuffle(order)
+            tl, ta = run(order, True)
+            vl, va = run(va_idx, False)
+            for k, v in zip(("loss", "acc", "val_loss", "val_acc", "lr"), (tl, ta, vl, va, lr)):
+                hist[k].append(v)
+            if verbose:
+                print("Epoch %d/%d - loss: %.4f - acc: %.4f - val_loss: %.4f - val_acc: %.4f" % (epoch + 1, epochs, tl, ta, vl, va))
+            if len(va_idx):
+                # EarlyStopping(monitor='val_loss', min_delta=0.1, patience=5)
+                if vl + 0.1 < es_best:
+                    es_best, es_wait = vl, 0
+                else:
+                    es_wait += 1
+                    if es_wait >= 5:
+                        break
+                # ReduceLROnPlateau(monitor='val_loss', factor=0.2, patience=5, min_lr=0.01, epsilon=1e-4)
+                if vl < rl_best - 1e-4:
+                    rl_best, rl_wait = vl, 0
+                else:
+                    if rl_wait >= 5:
+                        if lr > 0.01:
+                            lr = max(lr * 0.2, 0.01)
+                        rl_wait = 0
+                    rl_wait += 1
+        new = ctx.get_train_state(g, 0, 0, shapes)
+        self._opt = (ctx.get_train_state(g, 0, 1, shapes), ctx.get_train_state(g, 0, 2, shapes))
+        self._spec.set(*new)  # version bump: the next scoring call re-uploads heads, operand images and bounds
+        self.learningRate = lr
+        return hist
+
+    def testAccuracy(self, X, Y, batch_size=512):
+        """code/siamese.py:60-79: accuracy of argmax(predict) against 1*(Y[i] == Y[j]) over ALL ordered pairs
+        (i, j) of X — one all-pairs scoring call instead of n^2 / batch_size predict calls."""
+        from . import _ffi
+        feats = np.ascontiguousarray(self.preprocess(X), dtype=np.float32)
+        lab = np.asarray(Y).reshape(-1)
+        n = len(feats)
+        ctx = _ffi.default_context()
+        g = engine._GroupCache.group_for(ctx, [self._spec])
+        slot = _ffi.MAX_SLOTS - 3
+        ctx.set_table(slot, feats)
+        rows = max(1, min(n, (1 << 23) // max(n, 1)))
+        n_correct = 0
+        for r0 in range(0, n, rows):
+            nr = min(rows, n - r0)
+            _, cons = ctx.score_allpairs(g, slot, slot, r0, nr, n, 1, self._C, want_per=False, want_cons=True)
+            p = cons.reshape(nr, n, self._C)
+            pred = np.argmax(p, axis=2) if self._C == 2 else (p[:, :, 0] > 0.5).astype(np.int64)
+            n_correct += int(np.sum(pred == (lab[r0:r0 + nr, None] == lab[None, :]).astype(np.int64)))
+        return n_correct / float(n * n)
+
+    # ---- out of scope: generator-driven pre-training (data loaders, class weights: code/siamese.py:44-50, 81-112)
+    def _no_training(self, *a, **k):
+        raise NotImplementedError("generator-driven pre-training is outside the query-selection path; "
+                                  "finetune() / testAccuracy() are implemented (SURVEY.md §8f item 2)")
+
+    trainModel = customTrainModel = getDenseBarebones = _no_training
 
 
 class SmallRes(SiameseNetwork):

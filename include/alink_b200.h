@@ -194,6 +194,21 @@ int alink_disparity_select_sharded(alink_ctx *ctx, const float *p2, const float 
                                    const uint64_t *thr_keys, double eps, int blind, const float *y, int in_space,
                                    int64_t *idx_out, int out_space, int64_t *n_out, int64_t *active_count);
 
+/* One finetune ("teach") minibatch step of learner `learner` of a head group on the pairs (ia[n], ib[n]), labels
+ * y[n] in {0, 1}. Replaces what Keras runs per batch in code/siamese.py:52-58 (finetune ->
+ * fit(batch_size=16), called from code/ALINK.py:250) and :86-112 (train_on_batch / test_on_batch): forward,
+ * binary cross-entropy + binary accuracy, backward, Adadelta(lr, rho = 0.95, eps = 1e-7) on the group's fp32
+ * master weights, which stay on the device (apply = 0: evaluate only, like test_on_batch). loss_out / acc_out:
+ * host scalars (batch means, before the update); probs_out: host [nb][C] or NULL. ia, ib, y follow in_space.
+ * alink_get_train_state / alink_set_train_state move one learner's six tensors (Keras order W1,b1,W2,b2,W3,b3;
+ * NULL entries are skipped) between host and device: which = 0 parameters (get only), 1 = Adadelta E[g^2],
+ * 2 = Adadelta E[dx^2]. Accumulators start at zero when a group is (re)set. */
+int alink_train_step(alink_ctx *ctx, int group, int learner, int slot_a, int slot_b, const int32_t *ia,
+                     const int32_t *ib, const float *y, int nb, int in_space, double lr, double rho, double eps,
+                     int apply, float *loss_out, float *acc_out, float *probs_out);
+int alink_get_train_state(alink_ctx *ctx, int group, int learner, int which, float *const *host_out);
+int alink_set_train_state(alink_ctx *ctx, int group, int learner, int which, const float *const *host_in);
+
 /* Verification-curve counts on a block of the all-pairs score matrix. Replaces the loops of
  * utilities/ROC_precompute.py:19-63: over the strict upper triangle (j > row0 + r) of scores[P][G], mask codes
  * pick the genuine / impostor pairs of a protocol (roc_case 1: code 1 vs 3; 2: 2 vs 4; 3: {1,2} vs {3,4});

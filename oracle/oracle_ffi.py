@@ -190,3 +190,32 @@ def roc_counts(scores, mask, thresholds, roc_case, row0=0):
     if rc != 0:
         raise ValueError("alink_oracle_roc_counts rc=%d" % rc)
     return tp, fp, int(ng.value), int(ni.value)
+
+
+def train_step(table_a, table_b, ia, ib, y, params, acc_g, acc_d, D, H1, H2, Cc, feat_mode=0, lr=1.0, rho=0.95,
+               eps=1e-7, apply=True, want_probs=False):
+    """One finetune minibatch step of ONE learner (code/siamese.py:52-58 per batch). params / acc_g / acc_d: lists of
+    six float32 arrays (W1,b1,W2,b2,W3,b3), UPDATED IN PLACE when apply. Returns (loss, accuracy[, probs])."""
+    L = lib()
+    L.alink_oracle_train_step.restype = C.c_int
+    L.alink_oracle_train_step.argtypes = [C.c_void_p] * 5 + [C.c_int] * 6 + [C.POINTER(C.c_void_p)] * 3 + \
+        [C.c_float] * 3 + [C.c_int, C.POINTER(C.c_float), C.POINTER(C.c_float), C.c_void_p]
+    ta, tb = _f32(table_a), _f32(table_b)
+    yy = _f32(y).reshape(-1)
+    nb = len(yy)
+    ia_ = None if ia is None else np.ascontiguousarray(ia, dtype=np.int32)
+    ib_ = None if ib is None else np.ascontiguousarray(ib, dtype=np.int32)
+    for lst in (params, acc_g, acc_d):
+        for a in lst:
+            assert a.dtype == np.float32 and a.flags["C_CONTIGUOUS"]
+
+    def pp(lst):
+        return (C.c_void_p * 6)(*[a.ctypes.data for a in lst])
+    loss, acc = C.c_float(0), C.c_float(0)
+    probs = np.empty((nb, Cc), np.float32) if want_probs else None
+    rc = L.alink_oracle_train_step(_ptr(ta), _ptr(tb), _ptr(ia_), _ptr(ib_), _ptr(yy), nb, D, feat_mode, H1, H2, Cc,
+                                   pp(params), pp(acc_g), pp(acc_d), lr, rho, eps, int(bool(apply)),
+                                   C.byref(loss), C.byref(acc), _ptr(probs))
+    if rc != 0:
+        raise ValueError("alink_oracle_train_step rc=%d" % rc)
+    return (loss.value, acc.value, probs) if want_probs else (loss.value, acc.value)

@@ -217,3 +217,45 @@ def roc_precompute(score_matrix, masked_matrix, thresholds, roc_case):
     tpr = [float(np.sum(gen >= t)) / len(gen) for t in thresholds]
     fpr = [float(np.sum(imp >= t)) / len(imp) for t in thresholds]
     return np.array(tpr), np.array(fpr)
+
+
+def train_step(XL, XR, y, params, acc_g, acc_d, lr=1.0, rho=0.95, eps=1e-7, act="softmax"):
+    """Independent float64 restatement of one Keras batch of code/siamese.py:52-58 (finetune -> fit): forward of
+    the head (:24-33), K.binary_crossentropy on the clipped activation output averaged over outputs and batch,
+    binary accuracy, backprop, Adadelta (:35; Keras 2.1.2 formulas). params / acc_g / acc_d: lists of six float64
+    arrays (W1,b1,W2,b2,W3,b3). Returns (loss, accuracy, new_params, new_acc_g, new_acc_d, probs)."""
+    W1, b1, W2, b2, W3, b3 = [np.asarray(p, np.float64) for p in params]
+    x = np.abs(np.asarray(XL, np.float64) - np.asarray(XR, np.float64))
+    z1 = x @ W1 + b1
+    h1 = np.maximum(z1, 0)
+    z2 = h1 @ W2 + b2
+    h2 = np.maximum(z2, 0)
+    z3 = h2 @ W3 + b3
+    y = np.asarray(y, np.float64).reshape(-1)
+    nb = len(y)
+    if act == "softmax":
+        e = np.exp(z3 - z3.max(axis=1, keepdims=True))
+        p = e / e.sum(axis=1, keepdims=True)
+        t = np.stack([1 - y, y], axis=1)  # to_categorical
+    else:
+        p = 1 / (1 + np.exp(-z3))
+        t = y[:, None]
+    pc = np.clip(p, 1e-7, 1 - 1e-7)
+    loss = float(np.mean(np.mean(-(t * np.log(pc) + (1 - t) * np.log(1 - pc)), axis=1)))
+    acc = float(np.mean(np.mean((p > 0.5).astype(np.float64) == t, axis=1)))
+    dldp = np.where((p >= 1e-7) & (p <= 1 - 1e-7), (1 - t) / (1 - pc) - t / pc, 0.0) / p.shape[1] / nb
+    if act == "softmax":
+        dz3 = p * (dldp - np.sum(p * dldp, axis=1, keepdims=True))
+    else:
+        dz3 = dldp * p * (1 - p)
+    dz2 = (dz3 @ W3.T) * (h2 > 0)
+    dz1 = (dz2 @ W2.T) * (h1 > 0)
+    grads = [x.T @ dz1, dz1.sum(0), h1.T @ dz2, dz2.sum(0), h2.T @ dz3, dz3.sum(0)]
+    new_p, new_a, new_d = [], [], []
+    for P, g, a, d in zip([W1, b1, W2, b2, W3, b3], grads, acc_g, acc_d):
+        a = rho * np.asarray(a, np.float64) + (1 - rho) * g * g
+        u = g * np.sqrt(np.asarray(d, np.float64) + eps) / np.sqrt(a + eps)
+        new_p.append(P - lr * u)
+        new_a.append(a)
+        new_d.append(rho * np.asarray(d, np.float64) + (1 - rho) * u * u)
+    return loss, acc, new_p, new_a, new_d, p

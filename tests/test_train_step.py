@@ -1,0 +1,129 @@
+"""the finetune ("teach") minibatch step (code/siamese.py:52-58 per batch; ALINK.py:250).
+CPU: the C oracle (fp32, fixed reduction orders) against an independent float64 numpy restatement of the Keras
+math. GPU: csrc/train.cuh against the oracle, bit for bit, over several consecutive Adadelta steps."""
+import numpy as np
+import pytest
+
+from alink_b200 import synth
+
+
+def _setup(act, nb, seed=0, D=512, H1=512, H2=64):
+    pool = synth.make_pool(1, N=max(nb, 64), M=400, K=1, act=act, D=D, H1=H1, H2=H2)
+    rng = np.random.default_rng(seed)
+    y = (rng.random(nb) < 0.5).astype(np.float32)
+    params = [np.ascontiguousarray(a, np.float32).copy() for a in pool.heads.learner(0)]
+    return pool, y, params
+
+
+def _zeros_like(params):
+    return [np.zeros_like(p) for p in params]
+
+
+@pytest.mark.parametrize("act", ["softmax", "sigmoid"])
+def test_oracle_train_step_matches_float64_keras_math(oracle, act):
+    from oracle import ref_numpy
+    nb = 16
+    pool, y, params = _setup(act, nb)
+    Cc = pool.heads.C
+    ia, ib = pool.ia[:nb].copy(), pool.ib[:nb].copy()
+    ag, ad = _zeros_like(params), _zeros_like(params)
+    p64 = [p.astype(np.float64) for p in params]
+    a64, d64 = [np.zeros_like(p) for p in p64], [np.zeros_like(p) for p in p64]
+    for step in range(3):
+        loss, acc, probs = oracle.train_step(pool.table, pool.table, ia, ib, y, params, ag, ad, 512, 512, 64, Cc,
+                                             lr=0.1, want_probs=True)
+        rl, ra, p64, a64, d64, rp = ref_numpy.train_step(pool.table[ia], pool.table[ib], y, p64, a64, d64, lr=0.1, act=act)
+        assert abs(loss - rl) <= 1e-5 * max(1.0, abs(rl)), (step, loss, rl)
+        assert acc == pytest.approx(ra, abs=1e-6)
+        assert np.abs(probs - (rp if Cc == 2 else rp)).max() <= 2e-6
+        for got, want in zip(params, p64):
+            assert np.abs(got - want).max() <= 2e-5, step
+    # the loss went down on the batch it was trained on
+    l_after, _ = oracle.train_step(pool.table, pool.table, ia, ib, y, params, ag, ad, 512, 512, 64, Cc, apply=False)
+    l_first, _ = oracle.train_step(pool.table, pool.table, ia, ib, y,
+                                   [np.ascontiguousarray(a, np.float32).copy() for a in pool.heads.learner(0)],
+                                   _zeros_like(params), _zeros_like(params), 512, 512, 64, Cc, apply=False)
+    assert l_after < l_first
+
+
+def test_oracle_evaluate_only_changes_nothing(oracle):
+    pool, y, params = _setup("softmax", 8)
+    before = [p.copy() for p in params]
+    ag, ad = _zeros_like(params), _zeros_like(params)
+    oracle.train_step(pool.table, pool.table, pool.ia[:8].copy(), pool.ib[:8].copy(), y, params, ag, ad, 512, 512, 64, 2,
+                      apply=False)
+    for a, b in zip(params, before):
+        np.testing.assert_array_equal(a, b)
+    assert all(not a.any() for a in ag + ad)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("act,nb,H1,H2", [("softmax", 16, 512, 64), ("sigmoid", 16, 512, 64), ("softmax", 1, 512, 64),
+                                           ("softmax", 37, 128, 32)])
+def test_gpu_train_steps_bit_identical_to_oracle(ctx, oracle, act, nb, H1, H2):
+    from alink_b200 import _ffi
+    pool, y, params = _setup(act, nb, H1=H1, H2=H2)
+    Cc = pool.heads.C
+    ctx.set_table(0, pool.table)
+    ctx.set_heads(3, pool.heads, compute=_ffi.FP32_EXACT)
+    ag, ad = _zeros_like(params), _zeros_like(params)
+    shapes = [p.shape for p in params]
+    for step in range(4):
+        ia = pool.ia[step:step + nb].copy()
+        ib = pool.ib[step:step + nb].copy()
+        rl, ra, rp = oracle.train_step(pool.table, pool.table, ia, ib, y, params, ag, ad, 512, H1, H2, Cc, lr=0.1,
+                                       want_probs=True)
+        gl, ga, gp = ctx.train_step(3, 0, 0, 0, ia, ib, y, lr=0.1, want_probs=True, C_out=Cc)
+        assert np.float32(gl).view(np.uint32) == np.float32(rl).view(np.uint32), (step, gl, rl)
+        assert ga == ra
+        np.testing.assert_array_equal(gp.view(np.uint32), rp.view(np.uint32))
+        for which, ref in ((0, params), (1, ag), (2, ad)):
+            got = ctx.get_train_state(3, 0, which, shapes)
+            for a, b in zip(got, ref):
+                np.testing.assert_array_equal(a.view(np.uint32), b.view(np.uint32))
+    # scoring after training uses the updated device weights (exact head)
+    per, _ = ctx.score_indexed(3, 0, 0, pool.ia[:64].copy(), pool.ib[:64].copy(), 64, 1, Cc)
+    import copy
+    heads = copy.deepcopy(pool.heads)
+    heads.W1, heads.b1, heads.W2, heads.b2, heads.W3, heads.b3 = [[p] for p in params]
+    ref = oracle.score(pool.table, pool.table, pool.ia[:64].copy(), pool.ib[:64].copy(), heads)
+    np.testing.assert_array_equal(per.view(np.uint32), ref["per_learner"].view(np.uint32))
+
+
+@pytest.mark.gpu
+def test_finetune_like_alink_driver(ctx, oracle):
+    """code/ALINK.py:250 `disguisedFacesModel.finetune([XL, XR], y, ft_epochs, 16, 1)`: every batch equals the
+    oracle's step (same shuffles via np.random.seed), the loss goes down, the optimizer state persists, and the
+    model then scores with the new weights."""
+    from alink_b200 import siamese
+    n = 200
+    pool, _, params = _setup("softmax", n)
+    ia, ib = pool.ia[:n], pool.ib[:n]
+    XL, XR = pool.table[ia], pool.table[ib]
+    y = np.asarray(pool.genuine[:n], dtype=np.float32)  # genuine / impostor labels of the synthetic pairs
+    model = siamese.SiameseNetwork((512,), "unused", 0.1)
+    model.set_weights(*params)
+    np.random.seed(42)
+    hist = model.finetune([XL, XR], y, 3, 16, 0)
+    assert len(hist["loss"]) == 3 and hist["loss"][-1] < hist["loss"][0]
+    # replay with the oracle: same split, same shuffles, same batches
+    ag, ad = _zeros_like(params), _zeros_like(params)
+    np.random.seed(42)
+    split = int(n * 0.8)
+    for epoch in range(3):
+        order = np.arange(split, dtype=np.int32)
+        np.random.shuffle(order)
+        tot = 0.0
+        for lo in range(0, split, 16):
+            b = order[lo:lo + 16]
+            l, _ = oracle.train_step(XL, XR, b, b, y[b], params, ag, ad, 512, 512, 64, 2, lr=0.1)
+            tot += l * len(b)
+        assert hist["loss"][epoch] == pytest.approx(tot / split, rel=1e-6)
+    for got, want in zip(model.get_weights(), params):
+        np.testing.assert_array_equal(got.view(np.uint32), want.view(np.uint32))
+    for got, want in zip(model._opt[0], ag):
+        np.testing.assert_array_equal(got, want)
+    out = model.predict([XL[:32], XR[:32]])
+    assert out.shape == (32, 2) and np.allclose(out.sum(1), 1, atol=1e-6)
+    acc = model.testAccuracy(pool.table[:40], np.arange(40) // 4)
+    assert 0.0 <= acc <= 1.0
