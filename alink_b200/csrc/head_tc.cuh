@@ -54,7 +54,7 @@ constexpr uint32_t P_W3 = P_B2 + 2 * 64 * 4;                  // float [2][128]
 constexpr uint32_t P_B3 = P_W3 + 2 * 128 * 4;                 // float [2][2]
 constexpr uint32_t BOFF = P_B3 + 16;                          // mbarriers
 enum { W_FULL = 0, W_EMPTY = 4, X_FULL = 8, X_EMPTY = 16, A1_FULL = 24, A1_EMPTY = 26, H1_FULL = 28, H1_EMPTY = 29,
-       A2_FULL = 30, A2_EMPTY = 31, NBARS = 32 };
+       A2_FULL = 30, A2_EMPTY = 31, S_FULL = 32, S_EMPTY = 34, NBARS = 36 };  // S_*: staged feature tiles (2 buffers)
 constexpr uint32_t TOFF = BOFF + NBARS * 8;                   // TMEM base address
 constexpr uint32_t SMEM_BYTES = TOFF + 16;
 static_assert(SMEM_BYTES <= 232448, "exceeds the 227 KB per-CTA shared memory limit");
@@ -77,6 +77,7 @@ struct Args {
   float *probs;              // [N][K][C] or nullptr
   float *util;               // [N] or nullptr
   int ntiles;
+  uint8_t *xscratch;         // STAGED: [gridDim.x][2][MAX_KB] feature-tile images of 16 KB (L2-resident scratch)
   // debug build only (-DALINK_TC_DEBUG): bits 0-5 slow down one role per loop iteration by (dbg >> 8) ns —
   // 1 weight producer, 2 MMA issuer, 8 epilogue, 16 gather producers, 32 peer relay, 128 L2 prefetcher;
   // bit 6 publishes per-role progress counters in the watchdog buffer (ptx.cuh)
@@ -111,6 +112,14 @@ template <bool F16>
 __device__ __forceinline__ uint32_t pack16(float lo, float hi) {
   return F16 ? pack_f16(lo, hi) : pack_bf16(lo, hi);
 }
+// relu, round to the operand format and pack two values in one instruction
+template <bool F16>
+__device__ __forceinline__ uint32_t pack16_relu(float lo, float hi) {
+  uint32_t d;
+  if (F16) asm("cvt.rn.relu.f16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(hi), "f"(lo));
+  else asm("cvt.rn.relu.bf16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(hi), "f"(lo));
+  return d;
+}
 __device__ __forceinline__ void sts128(uint32_t addr, uint32_t x, uint32_t y, uint32_t z, uint32_t w) {
   asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(x), "r"(y), "r"(z), "r"(w) : "memory");
 }
@@ -139,7 +148,13 @@ __device__ __forceinline__ float4 ldg_bf4(const __nv_bfloat16 *p) {  // 4 bf16 -
 // NCTA = 2: CTA pairs (cluster of 2, tcgen05 cta_group::2, M = 256): each CTA keeps its own 128-pair tile,
 //           loads HALF of every weight block, and the leader's MMAs read both halves — half the TMA
 //           traffic and half the B-operand shared-memory reads per CTA.
-template <bool TAB_BF16, int NCTA, bool F16>
+// STAGED: the gather producers run up to two tiles AHEAD of the MMAs: they write the converted feature tile
+//           (the exact swizzled shared-memory image) to a per-CTA scratch buffer in global memory, which stays in
+//           L2, and warp 3 refills the shared-memory tile from it with one 16 KB bulk copy per k-block as soon as
+//           the last MMA of the previous tile has read that block. Without it the refill at a tile boundary is
+//           four dependent rounds of table loads (only two k-blocks of fp32 rows fit in the producers' registers)
+//           during which the tensor pipe idles — 22 % of the kernel in the profile of the unstaged version.
+template <bool TAB_BF16, int NCTA, bool F16, bool STAGED = false>
 __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
   constexpr uint32_t KPS = NCTA;                // k-blocks per ring slot (a pair CTA holds half of each block)
   constexpr uint32_t HB = STAGE_BYTES / NCTA;   // bytes of this CTA's part of one [128 n x 64 k] weight block
@@ -176,7 +191,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
       ptx::mbar_init(bar(W_EMPTY + s), 1);
     }
     for (int k = 0; k < MAX_KB; ++k) {
-      ptx::mbar_init(bar(X_FULL + k), 256 + fwd);
+      ptx::mbar_init(bar(X_FULL + k), (STAGED ? 1 : 256) + fwd);
       ptx::mbar_init(bar(X_EMPTY + k), 1);
     }
     for (int b = 0; b < 2; ++b) {
@@ -187,6 +202,10 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
     ptx::mbar_init(bar(H1_EMPTY), 1);
     ptx::mbar_init(bar(A2_FULL), 1);
     ptx::mbar_init(bar(A2_EMPTY), 128 + fwd);
+    for (int b = 0; b < 2; ++b) {
+      ptx::mbar_init(bar(S_FULL + b), 256);
+      ptx::mbar_init(bar(S_EMPTY + b), 1);
+    }
     ptx::fence_barrier_init();
   }
   if (warp == 2) {
@@ -379,6 +398,30 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
     }
   } else if (warp == 2) {
     ptx::setmaxnreg_dec<56>();
+  } else if (STAGED && warp == 3) {
+    // ------------------------------------------------------------------ staged mode: feature-tile loader
+    ptx::setmaxnreg_dec<56>();
+    const uint32_t leader = ptx::elect_one();
+    const uint8_t *scr = a.xscratch + (size_t)blockIdx.x * (2u * MAX_KB * STAGE_BYTES);
+    for (uint32_t i = 0; i < T; ++i) {
+      ALINK_DBG_ROLE(128u, 3, i);
+      const uint32_t buf = i & 1u;
+      ptx::mbar_wait(bar(S_FULL + buf), (i >> 1) & 1u);  // the producers have written tile i to the scratch buffer
+      for (uint32_t kb = 0; kb < nkb; ++kb) {
+        ptx::mbar_wait(bar(X_EMPTY + kb), (i & 1u) ^ 1u);  // the previous tile's MMAs have read this block
+        if (leader) {
+          ptx::mbar_expect_tx(bar(X_FULL + kb), STAGE_BYTES);
+          ptx::bulk_g2s(sbase + XOFF + kb * STAGE_BYTES, scr + (size_t)(buf * MAX_KB + kb) * STAGE_BYTES, STAGE_BYTES,
+                        bar(X_FULL + kb));
+        }
+        __syncwarp();
+      }
+      // the copies have landed (this warp arms every phase of X_FULL, so it sees every phase): the scratch
+      // buffer may be overwritten with tile i + 2
+      for (uint32_t kb = 0; kb < nkb; ++kb) ptx::mbar_wait(bar(X_FULL + kb), i & 1u);
+      if (leader) ptx::mbar_arrive(bar(S_EMPTY + buf));
+      __syncwarp();
+    }
   } else if (warp == 3) {
     ptx::setmaxnreg_dec<56>();
     // ------------------------------------------------------------------ L2 prefetch of the next tile's rows
@@ -401,6 +444,11 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
     }
   } else if (warp >= 4 && warp < 8) {
     // ------------------------------------------------------------------ epilogue
+    // One thread per tile row (= TMEM lane). This role is the critical path of the kernel (layer 2 of an item
+    // cannot start before the item's hidden chunk is in shared memory), so it is written for latency: the
+    // accumulator is read 16 columns at a time with the next read in flight, the bias loads sit before the
+    // TMEM wait, relu + rounding + packing is one cvt per two values, the per-item staging (bias, and the next
+    // learner's layer-2 bias / last layer) is fetched one item ahead, and there is no integer division.
     ptx::setmaxnreg_dec<112>();
     const int et = tid - 128;             // 0..127 = row of the tile = TMEM lane
     const uint32_t quad = (uint32_t)(warp & 3);
@@ -410,67 +458,115 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
     float *w3s = reinterpret_cast<float *>(smem + P_W3);
     float *b3s = reinterpret_cast<float *>(smem + P_B3);
     float rows[2 * ALINK_MAX_K];
+    const uint32_t nc = (uint32_t)a.nc;
+    const uint32_t hrow = sbase + HOFF + ((uint32_t)et >> 3) * 1024u + ((uint32_t)et & 7u) * 128u, hx = (uint32_t)et & 7u;
+    if (Q > 0) {  // staging of item 0 / learner 0
+      b1s[et] = __ldg(a.b1 + et);
+      if (et < a.H2) b2s[et] = __ldg(a.b2 + et);
+      if (et < a.H2 * a.C) w3s[et] = __ldg(a.W3 + et);
+      if (et < a.C) b3s[et] = __ldg(a.b3 + et);
+    }
+    asm volatile("bar.sync 1, 128;" ::: "memory");
+    uint32_t i = 0, l = 0, c = 0, vp = 0;  // tile, learner, chunk of item q; parity of the learners done so far
     for (uint32_t q = 0; q < Q; ++q) {
       ALINK_DBG_ROLE(8u, 4 + (warp & 3), q);
-      const uint32_t i = q / G, g = q % G, l = g / (uint32_t)a.nc, c = g % (uint32_t)a.nc, b = q & 1u, u = q >> 1;
-      // stage this chunk's bias (and, at a learner's first chunk, its layer-2 bias and last layer)
-      b1s[b * 128 + et] = __ldg(a.b1 + (size_t)l * a.H1 + c * CHUNK_N + et);
-      if (c == 0) {
-        const uint32_t lb = l & 1u;
-        if (et < a.H2) b2s[lb * 64 + et] = __ldg(a.b2 + (size_t)l * a.H2 + et);
-        if (et < a.H2 * a.C) w3s[lb * 128 + et] = __ldg(a.W3 + (size_t)l * a.H2 * a.C + et);
-        if (et < a.C) b3s[lb * 2 + et] = __ldg(a.b3 + (size_t)l * a.C + et);
+      const uint32_t b = q & 1u, u = q >> 1;
+      // item q + 1: fetch what it needs now, store it at the end of this item
+      uint32_t c1 = c + 1, l1 = l, i1 = i;
+      if (c1 == nc) {
+        c1 = 0;
+        if (++l1 == (uint32_t)a.K) { l1 = 0; ++i1; }
       }
-      asm volatile("bar.sync 1, 128;" ::: "memory");
+      const bool more = q + 1 < Q;
+      float nb1 = 0.0f, nb2 = 0.0f, nw3 = 0.0f, nb3 = 0.0f;
+      if (more) {
+        nb1 = __ldg(a.b1 + (size_t)l1 * a.H1 + c1 * CHUNK_N + et);
+        if (c1 == 0) {
+          if (et < a.H2) nb2 = __ldg(a.b2 + (size_t)l1 * a.H2 + et);
+          if (et < a.H2 * a.C) nw3 = __ldg(a.W3 + (size_t)l1 * a.H2 * a.C + et);
+          if (et < a.C) nb3 = __ldg(a.b3 + (size_t)l1 * a.C + et);
+        }
+      }
       ptx::mbar_wait(bar(A1_FULL + b), u & 1u);
       ptx::tc_fence_after();
-      ptx::mbar_wait(bar(H1_EMPTY), (q & 1u) ^ 1u);  // layer 2 of the previous item has read the h1 buffer
-#pragma unroll 1
-      for (uint32_t jj = 0; jj < 4; ++jj) {
-        uint32_t v[32];
-        ptx::tmem_ld32(trow + b * CHUNK_N + jj * 32, v);
-        ptx::tc_wait_ld();
-        const float4 *bias = reinterpret_cast<const float4 *>(b1s + b * 128 + jj * 32);  // 128-bit broadcast loads
-        const uint32_t hbase = sbase + HOFF + (jj >> 1) * STAGE_BYTES;
+      const uint32_t tacc = trow + b * CHUNK_N;
+      const float *bias_q = b1s + b * 128;
+      // 16 columns: + bias, relu, round, pack -> two 16-byte chunks of the swizzled hidden tile
+      auto convert = [&](const uint32_t(&v)[16], uint32_t k) __attribute__((always_inline)) {
+        const float4 *bias = reinterpret_cast<const float4 *>(bias_q + k * 16);  // 128-bit broadcast loads
+        const float4 ba = bias[0], bb = bias[1], bc = bias[2], bd = bias[3];
+        const uint32_t w0 = pack16_relu<F16>(__fadd_rn(__uint_as_float(v[0]), ba.x), __fadd_rn(__uint_as_float(v[1]), ba.y));
+        const uint32_t w1 = pack16_relu<F16>(__fadd_rn(__uint_as_float(v[2]), ba.z), __fadd_rn(__uint_as_float(v[3]), ba.w));
+        const uint32_t w2 = pack16_relu<F16>(__fadd_rn(__uint_as_float(v[4]), bb.x), __fadd_rn(__uint_as_float(v[5]), bb.y));
+        const uint32_t w3 = pack16_relu<F16>(__fadd_rn(__uint_as_float(v[6]), bb.z), __fadd_rn(__uint_as_float(v[7]), bb.w));
+        const uint32_t w4 = pack16_relu<F16>(__fadd_rn(__uint_as_float(v[8]), bc.x), __fadd_rn(__uint_as_float(v[9]), bc.y));
+        const uint32_t w5 = pack16_relu<F16>(__fadd_rn(__uint_as_float(v[10]), bc.z), __fadd_rn(__uint_as_float(v[11]), bc.w));
+        const uint32_t w6 = pack16_relu<F16>(__fadd_rn(__uint_as_float(v[12]), bd.x), __fadd_rn(__uint_as_float(v[13]), bd.y));
+        const uint32_t w7 = pack16_relu<F16>(__fadd_rn(__uint_as_float(v[14]), bd.z), __fadd_rn(__uint_as_float(v[15]), bd.w));
+        if (k == 0) ptx::mbar_wait(bar(H1_EMPTY), (q & 1u) ^ 1u);  // layer 2 of the previous item has read the h1 buffer
+        const uint32_t hb = hrow + (k >> 2) * STAGE_BYTES, ch = (k & 3u) * 2u;
+        sts128(hb + ((ch ^ hx) << 4), w0, w1, w2, w3);
+        sts128(hb + (((ch + 1u) ^ hx) << 4), w4, w5, w6, w7);
+      };
+      uint32_t va[16], vb[16];
+      ptx::tmem_ld16(tacc, va);
+      ptx::tc_wait_ld();
 #pragma unroll
-        for (uint32_t e = 0; e < 4; ++e) {
-          const float4 ba = bias[2 * e], bb = bias[2 * e + 1];
-          const float x0 = fmaxf(__fadd_rn(__uint_as_float(v[e * 8 + 0]), ba.x), 0.0f);
-          const float x1 = fmaxf(__fadd_rn(__uint_as_float(v[e * 8 + 1]), ba.y), 0.0f);
-          const float x2 = fmaxf(__fadd_rn(__uint_as_float(v[e * 8 + 2]), ba.z), 0.0f);
-          const float x3 = fmaxf(__fadd_rn(__uint_as_float(v[e * 8 + 3]), ba.w), 0.0f);
-          const float x4 = fmaxf(__fadd_rn(__uint_as_float(v[e * 8 + 4]), bb.x), 0.0f);
-          const float x5 = fmaxf(__fadd_rn(__uint_as_float(v[e * 8 + 5]), bb.y), 0.0f);
-          const float x6 = fmaxf(__fadd_rn(__uint_as_float(v[e * 8 + 6]), bb.z), 0.0f);
-          const float x7 = fmaxf(__fadd_rn(__uint_as_float(v[e * 8 + 7]), bb.w), 0.0f);
-          sts128(hbase + ptx::sw128_offset((uint32_t)et, (jj & 1u) * 4 + e), pack16<F16>(x0, x1), pack16<F16>(x2, x3),
-                 pack16<F16>(x4, x5), pack16<F16>(x6, x7));
-        }
+      for (uint32_t kk = 0; kk < 4; ++kk) {
+        ptx::tmem_ld16(tacc + (2 * kk + 1) * 16, vb);  // in flight while va is converted
+        convert(va, 2 * kk);
+        ptx::tc_wait_ld();
+        if (kk < 3) ptx::tmem_ld16(tacc + (2 * kk + 2) * 16, va);
+        convert(vb, 2 * kk + 1);
+        if (kk < 3) ptx::tc_wait_ld();
       }
       ptx::fence_proxy_async_smem();
       ptx::tc_fence_before();
       ptx::mbar_arrive(bar(A1_EMPTY + b));
       ptx::mbar_arrive(bar(H1_FULL));
+      // staging of item q + 1 (the other bias buffer; the other learner buffer: consecutive learners alternate)
+      if (more) {
+        b1s[(b ^ 1u) * 128 + et] = nb1;
+        if (c1 == 0) {
+          const uint32_t lb1 = vp ^ 1u;
+          if (et < a.H2) b2s[lb1 * 64 + et] = nb2;
+          if (et < a.H2 * a.C) w3s[lb1 * 128 + et] = nw3;
+          if (et < a.C) b3s[lb1 * 2 + et] = nb3;
+        }
+      }
+      asm volatile("bar.sync 1, 128;" ::: "memory");
 
-      if (c == (uint32_t)a.nc - 1) {
+      if (c == nc - 1) {
         // ---- learner l is complete for this tile: layer-2 accumulator -> Dense(H2, C) -> activation
-        const uint32_t lb = l & 1u;
-        ptx::mbar_wait(bar(A2_FULL), (i * (uint32_t)a.K + l) & 1u);
+        const uint32_t lb = vp;
+        ptx::mbar_wait(bar(A2_FULL), vp);
         ptx::tc_fence_after();
         float z0 = 0.0f, z1 = 0.0f;
         for (int jj = 0; jj < a.H2 / 32; ++jj) {
           uint32_t v[32];
           ptx::tmem_ld32(trow + ACC2_COL + jj * 32, v);
+          const float4 *b2v = reinterpret_cast<const float4 *>(b2s + lb * 64 + jj * 32);
           ptx::tc_wait_ld();
 #pragma unroll
-          for (int e = 0; e < 32; ++e) {
-            const int jn = jj * 32 + e;
-            const float h = fmaxf(__fadd_rn(__uint_as_float(v[e]), b2s[lb * 64 + jn]), 0.0f);
+          for (int e = 0; e < 32; e += 4) {
+            const float4 bq = b2v[e >> 2];
+            const float h0 = fmaxf(__fadd_rn(__uint_as_float(v[e + 0]), bq.x), 0.0f);
+            const float h1 = fmaxf(__fadd_rn(__uint_as_float(v[e + 1]), bq.y), 0.0f);
+            const float h2 = fmaxf(__fadd_rn(__uint_as_float(v[e + 2]), bq.z), 0.0f);
+            const float h3 = fmaxf(__fadd_rn(__uint_as_float(v[e + 3]), bq.w), 0.0f);
             if (a.C == 2) {
-              z0 = __fmaf_rn(h, w3s[lb * 128 + 2 * jn], z0);
-              z1 = __fmaf_rn(h, w3s[lb * 128 + 2 * jn + 1], z1);
+              const float4 *wv = reinterpret_cast<const float4 *>(w3s + lb * 128 + 2 * (jj * 32 + e));
+              const float4 wa = wv[0], wb = wv[1];
+              z0 = __fmaf_rn(h0, wa.x, z0); z1 = __fmaf_rn(h0, wa.y, z1);
+              z0 = __fmaf_rn(h1, wa.z, z0); z1 = __fmaf_rn(h1, wa.w, z1);
+              z0 = __fmaf_rn(h2, wb.x, z0); z1 = __fmaf_rn(h2, wb.y, z1);
+              z0 = __fmaf_rn(h3, wb.z, z0); z1 = __fmaf_rn(h3, wb.w, z1);
             } else {
-              z0 = __fmaf_rn(h, w3s[lb * 128 + jn], z0);
+              const float4 wa = *reinterpret_cast<const float4 *>(w3s + lb * 128 + jj * 32 + e);
+              z0 = __fmaf_rn(h0, wa.x, z0);
+              z0 = __fmaf_rn(h1, wa.y, z0);
+              z0 = __fmaf_rn(h2, wa.z, z0);
+              z0 = __fmaf_rn(h3, wa.w, z0);
             }
           }
         }
@@ -490,11 +586,13 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
         rows[2 * l] = p0;
         rows[2 * l + 1] = p1;
         if (l == (uint32_t)a.K - 1 && a.util && n < a.N) {
-          float c0, c1;
-          alink_consensus2(rows, a.K, &c0, &c1);
-          a.util[n] = alink_utility2(a.measure, rows, a.K, c0, c1);
+          float c0, c1u;
+          alink_consensus2(rows, a.K, &c0, &c1u);
+          a.util[n] = alink_utility2(a.measure, rows, a.K, c0, c1u);
         }
+        vp ^= 1u;
       }
+      c = c1; l = l1; i = i1;
     }
   } else if (warp >= 8) {
     // ------------------------------------------------------------------ gather producers
@@ -533,7 +631,13 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
     };
     auto finish = [&](const float4(&va)[8], const float4(&vb)[8], uint32_t i, uint32_t kb) __attribute__((always_inline)) {
       const bool had = kb >= nkb_feat;
-      ptx::mbar_wait(bar(X_EMPTY + kb), (i & 1u) ^ 1u);  // the previous tile's MMAs have read this block
+      uint8_t *xg = nullptr;
+      if (STAGED) {
+        if (kb == 0) ptx::mbar_wait(bar(S_EMPTY + (i & 1u)), ((i >> 1) & 1u) ^ 1u);  // tile i - 2 has left the buffer
+        xg = a.xscratch + ((size_t)blockIdx.x * 2u + (i & 1u)) * (MAX_KB * STAGE_BYTES) + (size_t)kb * STAGE_BYTES;
+      } else {
+        ptx::mbar_wait(bar(X_EMPTY + kb), (i & 1u) ^ 1u);  // the previous tile's MMAs have read this block
+      }
       const uint32_t xb = sbase + XOFF + kb * STAGE_BYTES;
 #pragma unroll
       for (int ii = 0; ii < 8; ++ii) {
@@ -546,11 +650,19 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
           x2 = fabsf(__fsub_rn(va[ii].z, vb[ii].z)); x3 = fabsf(__fsub_rn(va[ii].w, vb[ii].w));
         }
         const uint32_t r = (uint32_t)(rbase + 16 * ii);
-        sts64(xb + ptx::sw128_offset(r, (uint32_t)sub >> 1) + ((uint32_t)sub & 1u) * 8u, pack16<F16>(x0, x1),
-              pack16<F16>(x2, x3));
+        const uint32_t off = ptx::sw128_offset(r, (uint32_t)sub >> 1) + ((uint32_t)sub & 1u) * 8u;
+        if (STAGED) *reinterpret_cast<uint2 *>(xg + off) = make_uint2(pack16<F16>(x0, x1), pack16<F16>(x2, x3));
+        else sts64(xb + off, pack16<F16>(x0, x1), pack16<F16>(x2, x3));
       }
-      ptx::fence_proxy_async_smem();
-      ptx::mbar_arrive(bar(X_FULL + kb));
+      if (STAGED) {
+        if (kb + 1 == nkb) {  // tile complete: publish the buffer to the loader's bulk copies (async proxy)
+          ptx::fence_proxy_async_global();
+          ptx::mbar_arrive(bar(S_FULL + (i & 1u)));
+        }
+      } else {
+        ptx::fence_proxy_async_smem();
+        ptx::mbar_arrive(bar(X_FULL + kb));
+      }
     };
     float4 va0[8], vb0[8], va1[8], vb1[8];
     if (T > 0) {
@@ -681,6 +793,14 @@ static int tc_score(alink_ctx *ctx, const HeadGroup &g, const Table &A, const Ta
   static const int ncta_env = [] { const char *e = getenv("ALINK_TC_NCTA"); return e ? atoi(e) : 2; }();
   const int ncta = (ncta_env == 1 || ctx->sm_count < 2 || (a.nkb & 1)) ? 1 : 2;  // a pair slot holds 2 k-blocks
   const bool tb16 = A.dtype == ALINK_BF16;
+  // Staged feature tiles (see the kernel) unless ALINK_TC_STAGED=0; the scratch buffer is allocated once per context.
+  static const int staged_env = [] { const char *e = getenv("ALINK_TC_STAGED"); return e ? atoi(e) : 1; }();
+  const bool staged = staged_env != 0;
+  if (staged) {
+    const size_t need = (size_t)ctx->sm_count * 2u * tc::MAX_KB * tc::STAGE_BYTES;
+    ALINK_TRY(dev_reserve(ctx, ctx->xscratch, need));  // shared with the k-outer kernel (same stream)
+    a.xscratch = (uint8_t *)ctx->xscratch.p;
+  }
   cudaLaunchConfig_t cfg;
   memset(&cfg, 0, sizeof(cfg));
   cfg.blockDim = dim3(tc::NTHREADS);
@@ -697,10 +817,18 @@ static int tc_score(alink_ctx *ctx, const HeadGroup &g, const Table &A, const Ta
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    kern = f16 ? tc::head_kernel<false, 2, true> : tb16 ? tc::head_kernel<true, 2, false> : tc::head_kernel<false, 2, false>;
+    if (staged)
+      kern = f16 ? tc::head_kernel<false, 2, true, true>
+                 : tb16 ? tc::head_kernel<true, 2, false, true> : tc::head_kernel<false, 2, false, true>;
+    else
+      kern = f16 ? tc::head_kernel<false, 2, true> : tb16 ? tc::head_kernel<true, 2, false> : tc::head_kernel<false, 2, false>;
   } else {
     cfg.gridDim = dim3((unsigned)(a.ntiles < ctx->sm_count ? a.ntiles : ctx->sm_count));
-    kern = f16 ? tc::head_kernel<false, 1, true> : tb16 ? tc::head_kernel<true, 1, false> : tc::head_kernel<false, 1, false>;
+    if (staged)
+      kern = f16 ? tc::head_kernel<false, 1, true, true>
+                 : tb16 ? tc::head_kernel<true, 1, false, true> : tc::head_kernel<false, 1, false, true>;
+    else
+      kern = f16 ? tc::head_kernel<false, 1, true> : tb16 ? tc::head_kernel<true, 1, false> : tc::head_kernel<false, 1, false>;
   }
   ALINK_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tc::SMEM_BYTES));
   ALINK_CUDA(ctx, cudaLaunchKernelEx(&cfg, kern, a));
