@@ -54,14 +54,14 @@ constexpr uint32_t P_W3 = P_B2 + 2 * 64 * 4;                  // float [2][128]
 constexpr uint32_t P_B3 = P_W3 + 2 * 128 * 4;                 // float [2][2]
 constexpr uint32_t BOFF = P_B3 + 16;                          // mbarriers
 enum { W_FULL = 0, W_EMPTY = 4, X_FULL = 8, X_EMPTY = 16, A1_FULL = 24, A1_EMPTY = 26, H1_FULL = 28, H1_EMPTY = 29,
-       A2_FULL = 30, A2_EMPTY = 31, S_FULL = 32, S_EMPTY = 34, NBARS = 36 };  // S_*: staged feature tiles (2 buffers)
+       A2_FULL = 30, A2_EMPTY = 32, S_FULL = 34, S_EMPTY = 36, NBARS = 38 };  // A2_*: one per layer-2 accumulator; S_*: staged feature tiles (2 buffers)
 constexpr uint32_t TOFF = BOFF + NBARS * 8;                   // TMEM base address
 constexpr uint32_t SMEM_BYTES = TOFF + 16;
 static_assert(SMEM_BYTES <= 232448, "exceeds the 227 KB per-CTA shared memory limit");
 static_assert(BOFF % 8 == 0, "mbarriers need 8-byte alignment");
 
 constexpr uint32_t TMEM_COLS = 512;
-constexpr uint32_t ACC2_COL = 256;
+constexpr uint32_t ACC2_COL = 256;  // two layer-2 accumulators of 64 columns (consecutive learners alternate)
 
 struct Args {
   const void *ta, *tb;       // embedding tables (fp32 or bf16), D columns
@@ -201,7 +201,9 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
     ptx::mbar_init(bar(H1_FULL), 128 + fwd);
     ptx::mbar_init(bar(H1_EMPTY), 1);
     ptx::mbar_init(bar(A2_FULL), 1);
+    ptx::mbar_init(bar(A2_FULL + 1), 1);
     ptx::mbar_init(bar(A2_EMPTY), 128 + fwd);
+    ptx::mbar_init(bar(A2_EMPTY + 1), 128 + fwd);
     for (int b = 0; b < 2; ++b) {
       ptx::mbar_init(bar(S_FULL + b), 256);
       ptx::mbar_init(bar(S_EMPTY + b), 1);
@@ -285,7 +287,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
     const uint64_t xdesc0 = ptx::umma_desc_sw128(sbase + XOFF);
     const uint64_t hdesc0 = ptx::umma_desc_sw128(sbase + HOFF);
     const uint64_t rdesc0 = ptx::umma_desc_sw128(sbase + ROFF);
-    const uint32_t acc2 = tmem + ACC2_COL;
+    const uint32_t acc2_0 = tmem + ACC2_COL;
     auto mma = [&](uint32_t d, uint64_t ad, uint64_t bd, uint32_t idesc, uint32_t acc) {
       if (NCTA == 2) ptx::umma2_bf16(d, ad, bd, idesc, acc);
       else ptx::umma_bf16(d, ad, bd, idesc, acc);
@@ -297,8 +299,9 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
     uint32_t s = 0, ph = 0;
     // work-item coordinates as running counters (no integer division in the issue loop — this one warp's
     // instruction stream is the critical path of the kernel): g1 / xpar for layer 1 of item q,
-    // c2 / vpar (parity of tile * K + learner) for layer 2 of item q - 1
-    uint32_t g1 = 0, xpar = 0, c2 = 0, vpar = 0;
+    // c2 / v2 (= tile * K + learner, mod 4: accumulator v2 & 1, its use count parity (v2 >> 1) & 1) for layer 2
+    // of item q - 1
+    uint32_t g1 = 0, xpar = 0, c2 = 0, v2 = 0;
     for (uint32_t q = 0; q <= Q; ++q) {
       ALINK_DBG_ROLE(2u, 1, q);
       if (q < Q) {
@@ -337,7 +340,9 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
       if (q >= 1) {
         const uint32_t p = q - 1, c = c2;
         ptx::mbar_wait(bar(H1_FULL), p & 1u);
-        if (c == 0) ptx::mbar_wait(bar(A2_EMPTY), vpar ^ 1u);
+        const uint32_t acc2 = acc2_0 + (v2 & 1u) * 64u;
+        // the epilogue has read what the learner before last left in this accumulator
+        if (c == 0) ptx::mbar_wait(bar(A2_EMPTY + (v2 & 1u)), ((v2 >> 1) & 1u) ^ 1u);
         ptx::mbar_wait(bar(W_FULL + s), ph);
         ptx::tc_fence_after();
         if (leader) {
@@ -351,11 +356,11 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
           }
           commit(W_EMPTY + s);
           commit(H1_EMPTY);
-          if (c == (uint32_t)a.nc - 1) commit(A2_FULL);
+          if (c == (uint32_t)a.nc - 1) commit(A2_FULL + (v2 & 1u));
         }
         __syncwarp();
         if (++s == NS) { s = 0; ph ^= 1u; }
-        if (++c2 == (uint32_t)a.nc) { c2 = 0; vpar ^= 1u; }
+        if (++c2 == (uint32_t)a.nc) { c2 = 0; v2 = (v2 + 1u) & 3u; }
       }
     }
   } else if (warp == 1) {
@@ -390,7 +395,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
       if (q >= 1) {
         const uint32_t p = q - 1;
         relay(H1_FULL, p & 1u);
-        if (c2 == 0 && v2 > 0) relay(A2_EMPTY, (v2 & 1u) ^ 1u);
+        if (c2 == 0 && v2 > 1) relay(A2_EMPTY + (v2 & 1u), ((v2 >> 1) & 1u) ^ 1u);
         relay(W_FULL + s, ph);
         if (++s == NS) { s = 0; ph ^= 1u; }
         if (++c2 == (uint32_t)a.nc) { c2 = 0; ++v2; }
@@ -467,18 +472,26 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
       if (et < a.C) b3s[et] = __ldg(a.b3 + et);
     }
     asm volatile("bar.sync 1, 128;" ::: "memory");
-    uint32_t i = 0, l = 0, c = 0, vp = 0;  // tile, learner, chunk of item q; parity of the learners done so far
-    for (uint32_t q = 0; q < Q; ++q) {
+    uint32_t i = 0, l = 0, c = 0, vp = 0;  // tile, learner, chunk of item q; learners done so far, mod 4
+    // A finished learner's layer-2 accumulator is read one item LATER (after that item's hidden chunk has been
+    // handed to the tensor pipe), so that this work overlaps the MMAs instead of extending the
+    // epilogue -> layer 2 -> epilogue chain; consecutive learners use alternate accumulators.
+    bool pend = false;
+    uint32_t pl = 0, pi = 0, pvp = 0;  // the pending learner, its tile, its running index mod 4
+    for (uint32_t q = 0; q <= Q; ++q) {
       ALINK_DBG_ROLE(8u, 4 + (warp & 3), q);
       const uint32_t b = q & 1u, u = q >> 1;
+      uint32_t c1 = 0, l1 = 0, i1 = 0;
+      bool more = false;
+      float nb1 = 0.0f, nb2 = 0.0f, nw3 = 0.0f, nb3 = 0.0f;
+      if (q < Q) {
       // item q + 1: fetch what it needs now, store it at the end of this item
-      uint32_t c1 = c + 1, l1 = l, i1 = i;
+      c1 = c + 1, l1 = l, i1 = i;
       if (c1 == nc) {
         c1 = 0;
         if (++l1 == (uint32_t)a.K) { l1 = 0; ++i1; }
       }
-      const bool more = q + 1 < Q;
-      float nb1 = 0.0f, nb2 = 0.0f, nw3 = 0.0f, nb3 = 0.0f;
+      more = q + 1 < Q;
       if (more) {
         nb1 = __ldg(a.b1 + (size_t)l1 * a.H1 + c1 * CHUNK_N + et);
         if (c1 == 0) {
@@ -487,14 +500,17 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
           if (et < a.C) nb3 = __ldg(a.b3 + (size_t)l1 * a.C + et);
         }
       }
-      ptx::mbar_wait(bar(A1_FULL + b), u & 1u);
-      ptx::tc_fence_after();
       const uint32_t tacc = trow + b * CHUNK_N;
       const float *bias_q = b1s + b * 128;
       // 16 columns: + bias, relu, round, pack -> two 16-byte chunks of the swizzled hidden tile
-      auto convert = [&](const uint32_t(&v)[16], uint32_t k) __attribute__((always_inline)) {
+      // (shared memory is busy feeding the tensor pipe, so its loads are slow: the bias of a stage is loaded
+      // one stage ahead, the first one before the accumulator is even ready)
+      auto load_bias = [&](float4(&bz)[4], uint32_t k) __attribute__((always_inline)) {
         const float4 *bias = reinterpret_cast<const float4 *>(bias_q + k * 16);  // 128-bit broadcast loads
-        const float4 ba = bias[0], bb = bias[1], bc = bias[2], bd = bias[3];
+        bz[0] = bias[0]; bz[1] = bias[1]; bz[2] = bias[2]; bz[3] = bias[3];
+      };
+      auto convert = [&](const uint32_t(&v)[16], uint32_t k, const float4(&bz)[4]) __attribute__((always_inline)) {
+        const float4 ba = bz[0], bb = bz[1], bc = bz[2], bd = bz[3];
         const uint32_t w0 = pack16_relu<F16>(__fadd_rn(__uint_as_float(v[0]), ba.x), __fadd_rn(__uint_as_float(v[1]), ba.y));
         const uint32_t w1 = pack16_relu<F16>(__fadd_rn(__uint_as_float(v[2]), ba.z), __fadd_rn(__uint_as_float(v[3]), ba.w));
         const uint32_t w2 = pack16_relu<F16>(__fadd_rn(__uint_as_float(v[4]), bb.x), __fadd_rn(__uint_as_float(v[5]), bb.y));
@@ -509,26 +525,136 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
         sts128(hb + (((ch + 1u) ^ hx) << 4), w4, w5, w6, w7);
       };
       uint32_t va[16], vb[16];
+      float4 ba4[4], bb4[4];
+      load_bias(ba4, 0);
+      ptx::mbar_wait(bar(A1_FULL + b), u & 1u);
+      ptx::tc_fence_after();
       ptx::tmem_ld16(tacc, va);
       ptx::tc_wait_ld();
 #pragma unroll
       for (uint32_t kk = 0; kk < 4; ++kk) {
         ptx::tmem_ld16(tacc + (2 * kk + 1) * 16, vb);  // in flight while va is converted
-        convert(va, 2 * kk);
+        load_bias(bb4, 2 * kk + 1);
+        convert(va, 2 * kk, ba4);
         ptx::tc_wait_ld();
-        if (kk < 3) ptx::tmem_ld16(tacc + (2 * kk + 2) * 16, va);
-        convert(vb, 2 * kk + 1);
+        if (kk < 3) {
+          ptx::tmem_ld16(tacc + (2 * kk + 2) * 16, va);
+          load_bias(ba4, 2 * kk + 2);
+        }
+        convert(vb, 2 * kk + 1, bb4);
         if (kk < 3) ptx::tc_wait_ld();
       }
       ptx::fence_proxy_async_smem();
       ptx::tc_fence_before();
       ptx::mbar_arrive(bar(A1_EMPTY + b));
       ptx::mbar_arrive(bar(H1_FULL));
+      }  // q < Q
+      if (pend) {
+        // ---- learner pl is complete for tile pi: layer-2 accumulator -> Dense(H2, C) -> activation
+        pend = false;
+        const uint32_t lb = pvp & 1u;  // accumulator and parameter buffer of this learner
+        ptx::mbar_wait(bar(A2_FULL + lb), (pvp >> 1) & 1u);
+        ptx::tc_fence_after();
+        float z0 = 0.0f, z1 = 0.0f;
+        // (shared memory is busy feeding the tensor pipe: its loads are slow, so they are issued in batches
+        // well ahead of their use, and the C == 2 / C == 1 variants are separate loops without inner branches)
+        const float *b2p = b2s + lb * 64, *w3p = w3s + lb * 128;
+        const uint32_t tacc2 = trow + ACC2_COL + lb * 64;
+        if (a.C == 2) {
+          for (int jj = 0; jj < a.H2 / 32; ++jj) {
+            uint32_t v[32];
+            ptx::tmem_ld32(tacc2 + jj * 32, v);
+            const float4 *b2v = reinterpret_cast<const float4 *>(b2p + jj * 32);
+            const float4 *wv = reinterpret_cast<const float4 *>(w3p + 2 * jj * 32);
+            float4 bq[4], wq[8];
+#pragma unroll
+            for (int t = 0; t < 4; ++t) bq[t] = b2v[t];
+#pragma unroll
+            for (int t = 0; t < 8; ++t) wq[t] = wv[t];
+            ptx::tc_wait_ld();
+#pragma unroll
+            for (int hf = 0; hf < 2; ++hf) {
+              float4 bn[4], wn[8];
+              if (hf == 0) {  // second half's operands, in flight while the first half is consumed
+#pragma unroll
+                for (int t = 0; t < 4; ++t) bn[t] = b2v[4 + t];
+#pragma unroll
+                for (int t = 0; t < 8; ++t) wn[t] = wv[8 + t];
+              }
+#pragma unroll
+              for (int t = 0; t < 4; ++t) {
+                const int e = hf * 16 + t * 4;
+                const float h0 = fmaxf(__fadd_rn(__uint_as_float(v[e + 0]), bq[t].x), 0.0f);
+                const float h1 = fmaxf(__fadd_rn(__uint_as_float(v[e + 1]), bq[t].y), 0.0f);
+                const float h2 = fmaxf(__fadd_rn(__uint_as_float(v[e + 2]), bq[t].z), 0.0f);
+                const float h3 = fmaxf(__fadd_rn(__uint_as_float(v[e + 3]), bq[t].w), 0.0f);
+                const float4 wa = wq[2 * t], wb = wq[2 * t + 1];
+                z0 = __fmaf_rn(h0, wa.x, z0); z1 = __fmaf_rn(h0, wa.y, z1);
+                z0 = __fmaf_rn(h1, wa.z, z0); z1 = __fmaf_rn(h1, wa.w, z1);
+                z0 = __fmaf_rn(h2, wb.x, z0); z1 = __fmaf_rn(h2, wb.y, z1);
+                z0 = __fmaf_rn(h3, wb.z, z0); z1 = __fmaf_rn(h3, wb.w, z1);
+              }
+              if (hf == 0) {
+#pragma unroll
+                for (int t = 0; t < 4; ++t) bq[t] = bn[t];
+#pragma unroll
+                for (int t = 0; t < 8; ++t) wq[t] = wn[t];
+              }
+            }
+          }
+        } else {
+          for (int jj = 0; jj < a.H2 / 32; ++jj) {
+            uint32_t v[32];
+            ptx::tmem_ld32(tacc2 + jj * 32, v);
+            const float4 *b2v = reinterpret_cast<const float4 *>(b2p + jj * 32);
+            const float4 *wv = reinterpret_cast<const float4 *>(w3p + jj * 32);
+            float4 bq[8], wq[8];
+#pragma unroll
+            for (int t = 0; t < 8; ++t) { bq[t] = b2v[t]; wq[t] = wv[t]; }
+            ptx::tc_wait_ld();
+#pragma unroll
+            for (int t = 0; t < 8; ++t) {
+              const int e = t * 4;
+              const float h0 = fmaxf(__fadd_rn(__uint_as_float(v[e + 0]), bq[t].x), 0.0f);
+              const float h1 = fmaxf(__fadd_rn(__uint_as_float(v[e + 1]), bq[t].y), 0.0f);
+              const float h2 = fmaxf(__fadd_rn(__uint_as_float(v[e + 2]), bq[t].z), 0.0f);
+              const float h3 = fmaxf(__fadd_rn(__uint_as_float(v[e + 3]), bq[t].w), 0.0f);
+              z0 = __fmaf_rn(h0, wq[t].x, z0);
+              z0 = __fmaf_rn(h1, wq[t].y, z0);
+              z0 = __fmaf_rn(h2, wq[t].z, z0);
+              z0 = __fmaf_rn(h3, wq[t].w, z0);
+            }
+          }
+        }
+        ptx::tc_fence_before();
+        ptx::mbar_arrive(bar(A2_EMPTY + lb));
+        const int64_t n = tile_of(pi) * TILE_M + et;
+        float p0, p1;
+        if (a.C == 2) {
+          alink_softmax2(__fadd_rn(z0, b3s[lb * 2 + 0]), __fadd_rn(z1, b3s[lb * 2 + 1]), &p0, &p1);
+          if (a.probs && n < a.N)
+            *reinterpret_cast<float2 *>(a.probs + ((size_t)n * a.K + pl) * 2) = make_float2(p0, p1);
+        } else {
+          p1 = alink_sigmoid(__fadd_rn(z0, b3s[lb * 2 + 0]));
+          p0 = __fsub_rn(1.0f, p1);  // code/keras_wrapper.py:268
+          if (a.probs && n < a.N) a.probs[(size_t)n * a.K + pl] = p1;
+        }
+        rows[2 * pl] = p0;
+        rows[2 * pl + 1] = p1;
+        if (pl == (uint32_t)a.K - 1 && a.util && n < a.N) {
+          float c0, c1u;
+          alink_consensus2(rows, a.K, &c0, &c1u);
+          a.util[n] = alink_utility2(a.measure, rows, a.K, c0, c1u);
+        }
+      }
+      if (q == Q) break;
+      // one-chunk learners: the parameters staged below replace those of the learner just finished above
+      if (nc == 1) asm volatile("bar.sync 1, 128;" ::: "memory");
       // staging of item q + 1 (the other bias buffer; the other learner buffer: consecutive learners alternate)
       if (more) {
         b1s[(b ^ 1u) * 128 + et] = nb1;
         if (c1 == 0) {
-          const uint32_t lb1 = vp ^ 1u;
+          const uint32_t lb1 = (vp & 1u) ^ 1u;
           if (et < a.H2) b2s[lb1 * 64 + et] = nb2;
           if (et < a.H2 * a.C) w3s[lb1 * 128 + et] = nw3;
           if (et < a.C) b3s[lb1 * 2 + et] = nb3;
@@ -536,61 +662,10 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
       }
       asm volatile("bar.sync 1, 128;" ::: "memory");
 
-      if (c == nc - 1) {
-        // ---- learner l is complete for this tile: layer-2 accumulator -> Dense(H2, C) -> activation
-        const uint32_t lb = vp;
-        ptx::mbar_wait(bar(A2_FULL), vp);
-        ptx::tc_fence_after();
-        float z0 = 0.0f, z1 = 0.0f;
-        for (int jj = 0; jj < a.H2 / 32; ++jj) {
-          uint32_t v[32];
-          ptx::tmem_ld32(trow + ACC2_COL + jj * 32, v);
-          const float4 *b2v = reinterpret_cast<const float4 *>(b2s + lb * 64 + jj * 32);
-          ptx::tc_wait_ld();
-#pragma unroll
-          for (int e = 0; e < 32; e += 4) {
-            const float4 bq = b2v[e >> 2];
-            const float h0 = fmaxf(__fadd_rn(__uint_as_float(v[e + 0]), bq.x), 0.0f);
-            const float h1 = fmaxf(__fadd_rn(__uint_as_float(v[e + 1]), bq.y), 0.0f);
-            const float h2 = fmaxf(__fadd_rn(__uint_as_float(v[e + 2]), bq.z), 0.0f);
-            const float h3 = fmaxf(__fadd_rn(__uint_as_float(v[e + 3]), bq.w), 0.0f);
-            if (a.C == 2) {
-              const float4 *wv = reinterpret_cast<const float4 *>(w3s + lb * 128 + 2 * (jj * 32 + e));
-              const float4 wa = wv[0], wb = wv[1];
-              z0 = __fmaf_rn(h0, wa.x, z0); z1 = __fmaf_rn(h0, wa.y, z1);
-              z0 = __fmaf_rn(h1, wa.z, z0); z1 = __fmaf_rn(h1, wa.w, z1);
-              z0 = __fmaf_rn(h2, wb.x, z0); z1 = __fmaf_rn(h2, wb.y, z1);
-              z0 = __fmaf_rn(h3, wb.z, z0); z1 = __fmaf_rn(h3, wb.w, z1);
-            } else {
-              const float4 wa = *reinterpret_cast<const float4 *>(w3s + lb * 128 + jj * 32 + e);
-              z0 = __fmaf_rn(h0, wa.x, z0);
-              z0 = __fmaf_rn(h1, wa.y, z0);
-              z0 = __fmaf_rn(h2, wa.z, z0);
-              z0 = __fmaf_rn(h3, wa.w, z0);
-            }
-          }
-        }
-        ptx::tc_fence_before();
-        ptx::mbar_arrive(bar(A2_EMPTY));
-        const int64_t n = tile_of(i) * TILE_M + et;
-        float p0, p1;
-        if (a.C == 2) {
-          alink_softmax2(__fadd_rn(z0, b3s[lb * 2 + 0]), __fadd_rn(z1, b3s[lb * 2 + 1]), &p0, &p1);
-          if (a.probs && n < a.N)
-            *reinterpret_cast<float2 *>(a.probs + ((size_t)n * a.K + l) * 2) = make_float2(p0, p1);
-        } else {
-          p1 = alink_sigmoid(__fadd_rn(z0, b3s[lb * 2 + 0]));
-          p0 = __fsub_rn(1.0f, p1);  // code/keras_wrapper.py:268
-          if (a.probs && n < a.N) a.probs[(size_t)n * a.K + l] = p1;
-        }
-        rows[2 * l] = p0;
-        rows[2 * l + 1] = p1;
-        if (l == (uint32_t)a.K - 1 && a.util && n < a.N) {
-          float c0, c1u;
-          alink_consensus2(rows, a.K, &c0, &c1u);
-          a.util[n] = alink_utility2(a.measure, rows, a.K, c0, c1u);
-        }
-        vp ^= 1u;
+      if (c == nc - 1) {  // learner l is complete once layer 2 of this item has run: read it during the next item
+        pend = true;
+        pl = l; pi = i; pvp = vp;
+        vp = (vp + 1u) & 3u;
       }
       c = c1; l = l1; i = i1;
     }
