@@ -782,6 +782,8 @@ int alink_train_step(alink_ctx *ctx, int group, int learner, int slot_a, int slo
       ALINK_LAUNCHED(ctx);
       tc::prep_w2_kernel<false><<<ctx->sm_count, 256, 0, st>>>(g.W2, (uint8_t *)g.W2t, g.K, g.H1, g.H2);
       ALINK_LAUNCHED(ctx);
+      tc::prep_b1_kernel<false><<<ctx->sm_count, 256, 0, st>>>(g.b1, (uint8_t *)g.W2t + (size_t)g.K * g.H1 * g.H2 * 2, g.K, g.H1);
+      ALINK_LAUNCHED(ctx);
     }
     g.bounds_stale = true;
   }

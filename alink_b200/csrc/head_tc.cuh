@@ -60,6 +60,14 @@ constexpr uint32_t SMEM_BYTES = TOFF + 16;
 static_assert(SMEM_BYTES <= 232448, "exceeds the 227 KB per-CTA shared memory limit");
 static_assert(BOFF % 8 == 0, "mbarriers need 8-byte alignment");
 
+// Pair mode adds the layer-1 bias ON THE TENSOR PIPE: one extra K = 16 MMA per item, A = a constant tile whose
+// first three k-columns are 1 (256 bytes of shared memory: every 8-row group aliases the same rows), B = the
+// bias split into three operand-format parts (hi + mid + lo = the fp32 value). The epilogue — the critical
+// path of the kernel — then only clamps, rounds and packs. The B tile (64 n x 16 k per CTA, no swizzle:
+// core matrices 128 B apart along k, 256 B apart along n) travels in the ring slot of the layer-2 slice.
+constexpr uint32_t BIAS_TILE = 2048, BIAS_OFF = 8192, BIAS_LBO = 128, BIAS_SBO = 256;
+constexpr uint32_t P_ONES = P_B1;  // the constant A tile replaces the staged bias in shared memory
+
 constexpr uint32_t TMEM_COLS = 512;
 constexpr uint32_t ACC2_COL = 256;  // two layer-2 accumulators of 64 columns (consecutive learners alternate)
 
@@ -77,6 +85,7 @@ struct Args {
   float *probs;              // [N][K][C] or nullptr
   float *util;               // [N] or nullptr
   int ntiles;
+  const uint8_t *bimg;       // pair mode: [K][nc][2 ranks] layer-1 bias tiles of 2 KB (BIAS_TILE below)
   uint8_t *xscratch;         // STAGED: [gridDim.x][2][MAX_KB] feature-tile images of 16 KB (L2-resident scratch)
   // debug build only (-DALINK_TC_DEBUG): bits 0-5 slow down one role per loop iteration by (dbg >> 8) ns —
   // 1 weight producer, 2 MMA issuer, 8 epilogue, 16 gather producers, 32 peer relay, 128 L2 prefetcher;
@@ -159,6 +168,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
   constexpr uint32_t KPS = NCTA;                // k-blocks per ring slot (a pair CTA holds half of each block)
   constexpr uint32_t HB = STAGE_BYTES / NCTA;   // bytes of this CTA's part of one [128 n x 64 k] weight block
   constexpr uint32_t NS = NSTAGE;               // ring slots of STAGE_BYTES
+  constexpr bool BMMA = NCTA == 2;              // layer-1 bias added by an MMA (see BIAS_TILE)
   const uint32_t rank = NCTA == 2 ? ptx::cluster_ctarank() : 0u;
   const uint32_t unit0 = blockIdx.x / NCTA, nunit = gridDim.x / NCTA;  // tile (pair) scheduling units
   extern __shared__ __align__(1024) uint8_t smem[];
@@ -210,6 +220,13 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
     }
     ptx::fence_barrier_init();
   }
+  if (BMMA && warp == 3 && lane < 16) {
+    // constant A tile: 8 rows x 16 B with k = 0, 1, 2 set to 1.0, then 8 rows x 16 B of zeros (k = 8..15)
+    const uint32_t one = F16 ? 0x3C00u : 0x3F80u;
+    if (lane < 8) sts128(sbase + P_ONES + lane * 16u, one | (one << 16), one, 0u, 0u);
+    else sts128(sbase + P_ONES + lane * 16u, 0u, 0u, 0u, 0u);
+    ptx::fence_proxy_async_smem();
+  }
   if (warp == 2) {
     if (NCTA == 2) ptx::tmem_alloc2(sbase + TOFF, TMEM_COLS);
     else ptx::tmem_alloc(sbase + TOFF, TMEM_COLS);
@@ -256,18 +273,25 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
           if (++s == NS) { s = 0; ph ^= 1u; }
         }
       }
-      if (q >= 1) {
-        // layer-2 slice: 2 k-blocks of [H2 n x 64 k]; a pair CTA takes rows [H2/2 * rank, +H2/2) of each
-        const uint8_t *src = a.w2img + (size_t)((q - 1) % G) * l2bytes;
+      if (BMMA || q >= 1) {
+        // layer-2 slice of item q - 1: 2 k-blocks of [H2 n x 64 k]; a pair CTA takes rows [H2/2 * rank, +H2/2)
+        // of each. In pair mode the slot also carries the layer-1 bias tile of item q.
+        const uint8_t *src = a.w2img + (size_t)((q ? q - 1 : 0u) % G) * l2bytes;
         ptx::mbar_wait(bar(W_EMPTY + s), ph ^ 1u);
         if (leader) {
-          ptx::mbar_expect_tx(bar(W_FULL + s), l2bytes / NCTA);
           if (NCTA == 1) {
+            ptx::mbar_expect_tx(bar(W_FULL + s), l2bytes);
             ptx::bulk_g2s(ring + s * STAGE_BYTES, src, l2bytes, bar(W_FULL + s));
           } else {
             const uint32_t piece = l2bytes / 4;  // H2/2 rows x 128 B
-            ptx::bulk_g2s(ring + s * STAGE_BYTES, src + rank * piece, piece, bar(W_FULL + s));
-            ptx::bulk_g2s(ring + s * STAGE_BYTES + piece, src + 2 * piece + rank * piece, piece, bar(W_FULL + s));
+            ptx::mbar_expect_tx(bar(W_FULL + s), (q >= 1 ? 2u * piece : 0u) + (q < Q ? BIAS_TILE : 0u));
+            if (q >= 1) {
+              ptx::bulk_g2s(ring + s * STAGE_BYTES, src + rank * piece, piece, bar(W_FULL + s));
+              ptx::bulk_g2s(ring + s * STAGE_BYTES + piece, src + 2 * piece + rank * piece, piece, bar(W_FULL + s));
+            }
+            if (q < Q)
+              ptx::bulk_g2s(ring + s * STAGE_BYTES + BIAS_OFF, a.bimg + ((size_t)(q % G) * 2u + rank) * BIAS_TILE,
+                            BIAS_TILE, bar(W_FULL + s));
           }
         }
         __syncwarp();
@@ -288,6 +312,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
     const uint64_t hdesc0 = ptx::umma_desc_sw128(sbase + HOFF);
     const uint64_t rdesc0 = ptx::umma_desc_sw128(sbase + ROFF);
     const uint32_t acc2_0 = tmem + ACC2_COL;
+    const uint64_t onesdesc = ptx::umma_desc_nosw(sbase + P_ONES, 128u, 0u);
     auto mma = [&](uint32_t d, uint64_t ad, uint64_t bd, uint32_t idesc, uint32_t acc) {
       if (NCTA == 2) ptx::umma2_bf16(d, ad, bd, idesc, acc);
       else ptx::umma_bf16(d, ad, bd, idesc, acc);
@@ -333,9 +358,21 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
           __syncwarp();
           if (++s == NS) { s = 0; ph ^= 1u; }
         }
+        if (BMMA) {
+          // + bias: the tile rides in the next ring slot (the one of the layer-2 slice below)
+          ptx::mbar_wait(bar(W_FULL + s), ph);
+          ptx::tc_fence_after();
+          if (leader)
+            mma(d_tmem, onesdesc, ptx::umma_desc_nosw(sbase + ROFF + s * STAGE_BYTES + BIAS_OFF, BIAS_LBO, BIAS_SBO), idesc1, 1u);
+        }
         if (leader) commit(A1_FULL + b);
         __syncwarp();
         if (++g1 == G) { g1 = 0; xpar ^= 1u; }
+      }
+      if (BMMA && q == 0) {  // the first slot of this kind carries a bias tile only
+        if (leader) commit(W_EMPTY + s);
+        __syncwarp();
+        if (++s == NS) { s = 0; ph ^= 1u; }
       }
       if (q >= 1) {
         const uint32_t p = q - 1, c = c2;
@@ -343,7 +380,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
         const uint32_t acc2 = acc2_0 + (v2 & 1u) * 64u;
         // the epilogue has read what the learner before last left in this accumulator
         if (c == 0) ptx::mbar_wait(bar(A2_EMPTY + (v2 & 1u)), ((v2 >> 1) & 1u) ^ 1u);
-        ptx::mbar_wait(bar(W_FULL + s), ph);
+        if (!BMMA || q == Q) ptx::mbar_wait(bar(W_FULL + s), ph);
         ptx::tc_fence_after();
         if (leader) {
           const uint64_t bd = rdesc0 + s * STAGE_STEP;
@@ -392,12 +429,14 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
         }
         if (++g1 == G) { g1 = 0; xpar ^= 1u; }
       }
+      // (pair mode: the slot of the layer-2 slice exists for every q — it carries the bias tile of item q — and
+      // the leader needs it BEFORE the hidden chunk of item q - 1)
+      relay(W_FULL + s, ph);
+      if (++s == NS) { s = 0; ph ^= 1u; }
       if (q >= 1) {
         const uint32_t p = q - 1;
         relay(H1_FULL, p & 1u);
         if (c2 == 0 && v2 > 1) relay(A2_EMPTY + (v2 & 1u), ((v2 >> 1) & 1u) ^ 1u);
-        relay(W_FULL + s, ph);
-        if (++s == NS) { s = 0; ph ^= 1u; }
         if (++c2 == (uint32_t)a.nc) { c2 = 0; ++v2; }
       }
     }
@@ -466,7 +505,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
     const uint32_t nc = (uint32_t)a.nc;
     const uint32_t hrow = sbase + HOFF + ((uint32_t)et >> 3) * 1024u + ((uint32_t)et & 7u) * 128u, hx = (uint32_t)et & 7u;
     if (Q > 0) {  // staging of item 0 / learner 0
-      b1s[et] = __ldg(a.b1 + et);
+      if (!BMMA) b1s[et] = __ldg(a.b1 + et);
       if (et < a.H2) b2s[et] = __ldg(a.b2 + et);
       if (et < a.H2 * a.C) w3s[et] = __ldg(a.W3 + et);
       if (et < a.C) b3s[et] = __ldg(a.b3 + et);
@@ -493,7 +532,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
       }
       more = q + 1 < Q;
       if (more) {
-        nb1 = __ldg(a.b1 + (size_t)l1 * a.H1 + c1 * CHUNK_N + et);
+        if (!BMMA) nb1 = __ldg(a.b1 + (size_t)l1 * a.H1 + c1 * CHUNK_N + et);
         if (c1 == 0) {
           if (et < a.H2) nb2 = __ldg(a.b2 + (size_t)l1 * a.H2 + et);
           if (et < a.H2 * a.C) nw3 = __ldg(a.W3 + (size_t)l1 * a.H2 * a.C + et);
@@ -506,26 +545,30 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
       // (shared memory is busy feeding the tensor pipe, so its loads are slow: the bias of a stage is loaded
       // one stage ahead, the first one before the accumulator is even ready)
       auto load_bias = [&](float4(&bz)[4], uint32_t k) __attribute__((always_inline)) {
+        if (BMMA) return;  // the accumulator already holds x W1 + b1
         const float4 *bias = reinterpret_cast<const float4 *>(bias_q + k * 16);  // 128-bit broadcast loads
         bz[0] = bias[0]; bz[1] = bias[1]; bz[2] = bias[2]; bz[3] = bias[3];
       };
+      auto addb = [&](uint32_t v, float bv) __attribute__((always_inline)) -> float {
+        return BMMA ? __uint_as_float(v) : __fadd_rn(__uint_as_float(v), bv);
+      };
       auto convert = [&](const uint32_t(&v)[16], uint32_t k, const float4(&bz)[4]) __attribute__((always_inline)) {
         const float4 ba = bz[0], bb = bz[1], bc = bz[2], bd = bz[3];
-        const uint32_t w0 = pack16_relu<F16>(__fadd_rn(__uint_as_float(v[0]), ba.x), __fadd_rn(__uint_as_float(v[1]), ba.y));
-        const uint32_t w1 = pack16_relu<F16>(__fadd_rn(__uint_as_float(v[2]), ba.z), __fadd_rn(__uint_as_float(v[3]), ba.w));
-        const uint32_t w2 = pack16_relu<F16>(__fadd_rn(__uint_as_float(v[4]), bb.x), __fadd_rn(__uint_as_float(v[5]), bb.y));
-        const uint32_t w3 = pack16_relu<F16>(__fadd_rn(__uint_as_float(v[6]), bb.z), __fadd_rn(__uint_as_float(v[7]), bb.w));
-        const uint32_t w4 = pack16_relu<F16>(__fadd_rn(__uint_as_float(v[8]), bc.x), __fadd_rn(__uint_as_float(v[9]), bc.y));
-        const uint32_t w5 = pack16_relu<F16>(__fadd_rn(__uint_as_float(v[10]), bc.z), __fadd_rn(__uint_as_float(v[11]), bc.w));
-        const uint32_t w6 = pack16_relu<F16>(__fadd_rn(__uint_as_float(v[12]), bd.x), __fadd_rn(__uint_as_float(v[13]), bd.y));
-        const uint32_t w7 = pack16_relu<F16>(__fadd_rn(__uint_as_float(v[14]), bd.z), __fadd_rn(__uint_as_float(v[15]), bd.w));
+        const uint32_t w0 = pack16_relu<F16>(addb(v[0], ba.x), addb(v[1], ba.y));
+        const uint32_t w1 = pack16_relu<F16>(addb(v[2], ba.z), addb(v[3], ba.w));
+        const uint32_t w2 = pack16_relu<F16>(addb(v[4], bb.x), addb(v[5], bb.y));
+        const uint32_t w3 = pack16_relu<F16>(addb(v[6], bb.z), addb(v[7], bb.w));
+        const uint32_t w4 = pack16_relu<F16>(addb(v[8], bc.x), addb(v[9], bc.y));
+        const uint32_t w5 = pack16_relu<F16>(addb(v[10], bc.z), addb(v[11], bc.w));
+        const uint32_t w6 = pack16_relu<F16>(addb(v[12], bd.x), addb(v[13], bd.y));
+        const uint32_t w7 = pack16_relu<F16>(addb(v[14], bd.z), addb(v[15], bd.w));
         if (k == 0) ptx::mbar_wait(bar(H1_EMPTY), (q & 1u) ^ 1u);  // layer 2 of the previous item has read the h1 buffer
         const uint32_t hb = hrow + (k >> 2) * STAGE_BYTES, ch = (k & 3u) * 2u;
         sts128(hb + ((ch ^ hx) << 4), w0, w1, w2, w3);
         sts128(hb + (((ch + 1u) ^ hx) << 4), w4, w5, w6, w7);
       };
       uint32_t va[16], vb[16];
-      float4 ba4[4], bb4[4];
+      float4 ba4[4] = {}, bb4[4] = {};
       load_bias(ba4, 0);
       ptx::mbar_wait(bar(A1_FULL + b), u & 1u);
       ptx::tc_fence_after();
@@ -652,7 +695,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
       if (nc == 1) asm volatile("bar.sync 1, 128;" ::: "memory");
       // staging of item q + 1 (the other bias buffer; the other learner buffer: consecutive learners alternate)
       if (more) {
-        b1s[(b ^ 1u) * 128 + et] = nb1;
+        if (!BMMA) b1s[(b ^ 1u) * 128 + et] = nb1;
         if (c1 == 0) {
           const uint32_t lb1 = (vp & 1u) ^ 1u;
           if (et < a.H2) b2s[lb1 * 64 + et] = nb2;
@@ -660,7 +703,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
           if (et < a.C) b3s[lb1 * 2 + et] = nb3;
         }
       }
-      asm volatile("bar.sync 1, 128;" ::: "memory");
+      if (!BMMA || (more && c1 == 0)) asm volatile("bar.sync 1, 128;" ::: "memory");
 
       if (c == nc - 1) {  // learner l is complete once layer 2 of this item has run: read it during the next item
         pend = true;
@@ -806,6 +849,38 @@ __global__ void prep_w2_kernel(const float *__restrict__ W2, uint8_t *__restrict
   }
 }
 
+// layer-1 bias tiles for the bias MMA of pair mode: [K][nc][2 ranks][BIAS_TILE]; element (n, k) of a tile at
+// (n / 8) * BIAS_SBO + (k / 8) * BIAS_LBO + (n % 8) * 16 + (k % 8) * 2; k = 0, 1, 2 hold hi, mid, lo with
+// hi + mid + lo = b1 (each part rounded to the operand format), the other k are zero
+template <bool F16>
+__global__ void prep_b1_kernel(const float *__restrict__ b1, uint8_t *__restrict__ img, int K, int H1) {
+  const int nc = H1 / CHUNK_N;
+  const int total = K * nc * 2 * 64;
+  for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < total; e += gridDim.x * blockDim.x) {
+    const int n = e & 63, r = (e >> 6) & 1, lc = e >> 7;  // lc = l * nc + c
+    const float b = b1[(size_t)(lc / nc) * H1 + (lc % nc) * CHUNK_N + r * 64 + n];
+    uint16_t part[3];
+    float rest = b;
+#pragma unroll
+    for (int t = 0; t < 3; ++t) {
+      float back;
+      if (F16) {
+        const __half h = __float2half_rn(rest);
+        part[t] = __half_as_ushort(h);
+        back = __half2float(h);
+      } else {
+        const __nv_bfloat16 h = __float2bfloat16_rn(rest);
+        part[t] = __bfloat16_as_ushort(h);
+        back = __bfloat162float(h);
+      }
+      rest = __fsub_rn(rest, back);
+    }
+    uint8_t *tile = img + ((size_t)lc * 2 + r) * BIAS_TILE + (n >> 3) * BIAS_SBO + (n & 7) * 16;
+    *reinterpret_cast<uint4 *>(tile) = make_uint4((uint32_t)part[0] | ((uint32_t)part[1] << 16), (uint32_t)part[2], 0u, 0u);
+    *reinterpret_cast<uint4 *>(tile + BIAS_LBO) = make_uint4(0u, 0u, 0u, 0u);
+  }
+}
+
 }  // namespace tc
 
 // formats: bit 0 = bf16 images, bit 1 = half images
@@ -817,21 +892,27 @@ static int tc_prepare_heads(alink_ctx *ctx, HeadGroup &g, int formats = 1) {
   if (g.H1 % tc::CHUNK_N || g.H1 > 4096)
     return alink_fail(ctx, ALINK_E_UNSUPPORTED, "BF16_TC head needs H1 %% 128 == 0 (got %d)", g.H1);
   if (g.H2 != 32 && g.H2 != 64) return alink_fail(ctx, ALINK_E_UNSUPPORTED, "BF16_TC head needs H2 in {32, 64}");
+  // the layer-1 bias tiles of pair mode (tc::BIAS_TILE) live behind the layer-2 image
   const size_t w1b = (size_t)g.K * g.D_in * g.H1 * 2, w2b = (size_t)g.K * g.H1 * g.H2 * 2;
+  const size_t bb = (size_t)g.K * (g.H1 / tc::CHUNK_N) * 2 * tc::BIAS_TILE;
   if (formats & 1) {
     ALINK_CUDA(ctx, cudaMalloc((void **)&g.W1t, w1b));
-    ALINK_CUDA(ctx, cudaMalloc((void **)&g.W2t, w2b));
+    ALINK_CUDA(ctx, cudaMalloc((void **)&g.W2t, w2b + bb));
     tc::prep_w1_kernel<false><<<ctx->sm_count * 4, 256, 0, ctx->stream>>>(g.W1, (uint8_t *)g.W1t, g.K, g.D_in, g.H1);
     ALINK_LAUNCHED(ctx);
     tc::prep_w2_kernel<false><<<ctx->sm_count, 256, 0, ctx->stream>>>(g.W2, (uint8_t *)g.W2t, g.K, g.H1, g.H2);
     ALINK_LAUNCHED(ctx);
+    tc::prep_b1_kernel<false><<<ctx->sm_count, 256, 0, ctx->stream>>>(g.b1, (uint8_t *)g.W2t + w2b, g.K, g.H1);
+    ALINK_LAUNCHED(ctx);
   }
   if (formats & 2) {
     ALINK_CUDA(ctx, cudaMalloc((void **)&g.W1h, w1b));
-    ALINK_CUDA(ctx, cudaMalloc((void **)&g.W2h, w2b));
+    ALINK_CUDA(ctx, cudaMalloc((void **)&g.W2h, w2b + bb));
     tc::prep_w1_kernel<true><<<ctx->sm_count * 4, 256, 0, ctx->stream>>>(g.W1, (uint8_t *)g.W1h, g.K, g.D_in, g.H1);
     ALINK_LAUNCHED(ctx);
     tc::prep_w2_kernel<true><<<ctx->sm_count, 256, 0, ctx->stream>>>(g.W2, (uint8_t *)g.W2h, g.K, g.H1, g.H2);
+    ALINK_LAUNCHED(ctx);
+    tc::prep_b1_kernel<true><<<ctx->sm_count, 256, 0, ctx->stream>>>(g.b1, (uint8_t *)g.W2h + w2b, g.K, g.H1);
     ALINK_LAUNCHED(ctx);
   }
   return ALINK_OK;
@@ -853,6 +934,7 @@ static int tc_score(alink_ctx *ctx, const HeadGroup &g, const Table &A, const Ta
   a.K = g.K; a.nc = g.H1 / tc::CHUNK_N; a.H1 = g.H1; a.H2 = g.H2; a.C = g.C; a.act = g.act; a.measure = measure;
   a.w1img = (const uint8_t *)(f16 ? (void *)g.W1h : (void *)g.W1t);
   a.w2img = (const uint8_t *)(f16 ? (void *)g.W2h : (void *)g.W2t);
+  a.bimg = a.w2img + (size_t)g.K * g.H1 * g.H2 * 2;
   a.b1 = g.b1; a.b2 = g.b2; a.W3 = g.W3; a.b3 = g.b3;
   a.probs = probs; a.util = util;
   a.ntiles = (int)((N + tc::TILE_M - 1) / tc::TILE_M);

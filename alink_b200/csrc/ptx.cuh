@@ -246,6 +246,16 @@ __device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t smem_addr) {
   d |= (uint64_t)2 << 61;                      // [61,64) SWIZZLE_128B
   return d;
 }
+// K-major operand WITHOUT swizzle: core matrices of 8 rows x 16 bytes; lbo = byte stride between the core
+// matrices along K, sbo = between those along M/N (sbo = 0 makes every 8-row group read the same rows)
+__device__ __forceinline__ uint64_t umma_desc_nosw(uint32_t smem_addr, uint32_t lbo, uint32_t sbo) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr >> 4) & 0x3FFF);
+  d |= (uint64_t)((lbo >> 4) & 0x3FFF) << 16;
+  d |= (uint64_t)((sbo >> 4) & 0x3FFF) << 32;
+  d |= (uint64_t)1 << 46;
+  return d;
+}
 // kind::f16 instruction descriptor: bf16 x bf16 -> fp32, both operands K-major, dense.
 __host__ __device__ constexpr uint32_t umma_idesc_bf16(int M, int N) {
   return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
