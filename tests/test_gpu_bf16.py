@@ -73,6 +73,21 @@ def test_bf16_smallres_widths(ctx, oracle):
     assert np.abs(per - ref["per_learner"]).max() <= TOL
 
 
+@pytest.mark.parametrize("act", ["softmax", "sigmoid"])
+@pytest.mark.parametrize("K,H1,H2", [(1, 128, 32), (3, 128, 64), (1, 512, 64), (3, 512, 32), (5, 256, 64)])
+def test_bf16_item_loop_shapes(ctx, oracle, K, H1, H2, act):
+    """Odd committee sizes, one-chunk learners (H1 = 128: every item ends a learner) and several tiles per CTA: the
+    layer-2 accumulator and the learner parameters alternate between two buffers by RUNNING learner count, and
+    a learner is finished one item late (csrc/head_tc.cuh epilogue) — every (tile, learner) must still land in
+    its own row of the output."""
+    pool = synth.make_pool(1, N=60000, K=K, H1=H1, H2=H2, act=act, M=3000)
+    _install(ctx, pool)
+    per, cons = ctx.score_indexed(1, 0, 0, pool.ia, pool.ib, pool.N, pool.heads.K, pool.heads.C)
+    ref = oracle.score(pool.table, pool.table, pool.ia, pool.ib, pool.heads)
+    assert np.abs(per - ref["per_learner"]).max() <= TOL
+    assert np.abs(cons - ref["consensus"]).max() <= TOL
+
+
 def test_bf16_hadamard_d256(ctx, oracle):
     pool = synth.make_pool(1, N=500, D=256, feat_mode=1)
     _install(ctx, pool, feat_mode=1)
