@@ -489,24 +489,26 @@ static int refine_query(alink_ctx *ctx, const HeadGroup &g, Table &A, Table &Bt,
   static const double scale[ALINK_UTIL_COUNT] = {1.0, 2.0, 1.25, 1.0, 1.25, 5.0};
   double eps = ctx->refine_eps > 0.0 ? ctx->refine_eps : (f16 ? REFINE_EPS_F16 : REFINE_EPS_BF16);
   ctx->refine_f16 = f16 ? 1 : 0;
-  for (int round = 1;; ++round) {
-    // (3) candidates within 2 eps of the threshold
-    ALINK_CUDA(ctx, cudaMemsetAsync(rstat, 0, 32, ctx->stream));
-    refine_mark_kernel<<<(unsigned)blocks, 256, 0, ctx->stream>>>(util_a, N, st, (float)(2.0 * eps * scale[measure]),
-                                                                  (uint32_t *)ctx->cand.p, rstat);
+  // marks the candidates (ctx->cand, count -> *M_out) and scores them exactly (ctx->probs, ctx->util_c)
+  auto mark_and_rescore = [&](const unsigned int *pilot_min, float margin, int64_t *M_out, int64_t *cb_out) -> int {
+    ALINK_CUDA(ctx, cudaMemsetAsync(rstat, 0, 16, ctx->stream));
+    refine_mark_kernel<<<(unsigned)blocks, 256, 0, ctx->stream>>>(util_a, N, st, pilot_min, margin, (uint32_t *)ctx->cand.p,
+                                                                  rstat);
     ALINK_LAUNCHED(ctx);
     unsigned int hM = 0;
     ALINK_CUDA(ctx, cudaMemcpyAsync(&hM, rstat, 4, cudaMemcpyDeviceToHost, ctx->stream));
     ALINK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     const int64_t M = (int64_t)hM;
+    *M_out = M;
     if (M < B) return alink_fail(ctx, ALINK_E_STATE, "refine: %lld candidates < B=%lld", (long long)M, (long long)B);
-    // (4) exact re-score of the candidates (oracle summation order, CUDA cores)
+    // exact re-score of the candidates (oracle summation order, CUDA cores)
     ALINK_TRY(dev_reserve(ctx, ctx->cia, sizeof(int32_t) * (size_t)M));
     ALINK_TRY(dev_reserve(ctx, ctx->cib, sizeof(int32_t) * (size_t)M));
     ALINK_TRY(dev_reserve(ctx, ctx->util_c, sizeof(float) * (size_t)M));
     ALINK_TRY(dev_reserve(ctx, ctx->probs, sizeof(float) * (size_t)M * g.K * g.C));
     int64_t cb = (M + 255) / 256;
     if (cb > cap) cb = cap;
+    *cb_out = cb;
     refine_compose_kernel<<<(unsigned)cb, 256, 0, ctx->stream>>>((const uint32_t *)ctx->cand.p, (unsigned)M, ia, ib,
                                                                  ia ? 0u : ctx->ap_G, ctx->ap_pair0,
                                                                  (int32_t *)ctx->cia.p, (int32_t *)ctx->cib.p);
@@ -521,7 +523,24 @@ static int refine_query(alink_ctx *ctx, const HeadGroup &g, Table &A, Table &Bt,
                                 (const int32_t *)ctx->cib.p, row0, Mc, (float *)ctx->h1ws.p, lstride,
                                 (float *)ctx->probs.p));
     }
-    ALINK_TRY(launch_utility(ctx, (const float *)ctx->probs.p, M, g.K, g.C, measure, (float *)ctx->util_c.p, nullptr));
+    return launch_utility(ctx, (const float *)ctx->probs.p, M, g.K, g.C, measure, (float *)ctx->util_c.p, nullptr);
+  };
+  // (2b) pilot: the pairs with u~ >= tau, scored exactly; the smallest of their exact utilities bounds the exact
+  // B-th largest value from below (refine.cuh). ALINK_REFINE_PILOT=0 keeps the plain 2 eps band.
+  static const int pilot_env = [] { const char *e = getenv("ALINK_REFINE_PILOT"); return e ? atoi(e) : 1; }();
+  unsigned int *pilot_min = nullptr;
+  if (pilot_env) {
+    int64_t M0 = 0, cb0 = 1;
+    ALINK_TRY(mark_and_rescore(nullptr, 0.0f, &M0, &cb0));
+    pilot_min = rstat + 4;
+    ALINK_CUDA(ctx, cudaMemsetAsync(pilot_min, 0xFF, 4, ctx->stream));
+    refine_min_kernel<<<(unsigned)cb0, 256, 0, ctx->stream>>>((const float *)ctx->util_c.p, (unsigned)M0, pilot_min);
+    ALINK_LAUNCHED(ctx);
+  }
+  for (int round = 1;; ++round) {
+    // (3) candidates: within eps of the pilot's bound, or within 2 eps of tau; (4) their exact re-score
+    int64_t M = 0, cb = 1;
+    ALINK_TRY(mark_and_rescore(pilot_min, (float)((pilot_min ? 1.0 : 2.0) * eps * scale[measure]), &M, &cb));
     refine_maxerr_kernel<<<(unsigned)cb, 256, 0, ctx->stream>>>((const float *)ctx->util_c.p, util_a,
                                                                 (const uint32_t *)ctx->cand.p, (unsigned)M, rstat);
     ALINK_LAUNCHED(ctx);

@@ -7,7 +7,11 @@
 // is >= tau - eps and a pair outside has u < tau - 2 eps + eps; (4) re-score only the candidates with the
 // bit-exact FFMA head (head_ffma.cuh, the oracle's summation order) and (5) select the top-B of the exact
 // utilities with the pairs' ORIGINAL indices in the keys. The result is identical to FP32_EXACT whenever
-// the error bound holds. The bound is checked on every query: the observed max |u~ - u| over the
+// the error bound holds. A PILOT narrows the band first: the pairs with u~ >= tau (at least B of them) are
+// re-scored exactly; the smallest of their exact utilities, L, is a lower bound of the exact B-th largest value
+// (B pairs reach it), so a pair of the exact top-B has u >= L and u~ >= L - eps — the candidates are
+// {u~ >= L - eps}, a band of about eps + |error| below tau instead of 2 eps (a third fewer re-scored pairs).
+// The bound is checked on every query: the observed max |u~ - u| over the
 // candidates must stay below it, otherwise it is widened and steps (3)-(5) are repeated (alink_refine_stats
 // / alink_refine_detail report survivors, max and rms error, the bound used and the number of rounds).
 //
@@ -19,11 +23,15 @@
 #include "common.cuh"
 #include "topk.cuh"
 
-// candidates = pairs whose approximate utility is within `margin` of the B-th largest (st->prefix = its key)
+// candidates = pairs whose approximate utility is within `margin` of a reference value: the B-th largest
+// approximate utility (st->prefix = its key) or, when `pilot_min` is given, the smallest EXACT utility of the
+// pilot set (an order-preserving uint, refine_min_kernel)
 __global__ void __launch_bounds__(256) refine_mark_kernel(const float *__restrict__ util, int64_t N, const SelectState *st,
-                                                          float margin, uint32_t *__restrict__ cand,
-                                                          unsigned int *__restrict__ count) {
-  const float thr = __fsub_rn(alink_key_utility(st->prefix), margin);
+                                                          const unsigned int *__restrict__ pilot_min, float margin,
+                                                          uint32_t *__restrict__ cand, unsigned int *__restrict__ count) {
+  const float tau = alink_key_utility(st->prefix);
+  // never above tau: the pilot set itself always stays in (it matters when the caller's bound is too tight)
+  const float thr = pilot_min ? fminf(__fsub_rn(alink_unorderable(*pilot_min), margin), tau) : __fsub_rn(tau, margin);
   const int lane = threadIdx.x & 31;
   // warp-uniform loop bound: every lane takes part in the ballot
   for (int64_t n0 = (int64_t)blockIdx.x * 256 + (threadIdx.x & ~31); n0 < N; n0 += (int64_t)gridDim.x * 256) {
@@ -80,6 +88,15 @@ __global__ void __launch_bounds__(256) refine_maxerr_kernel(const float *__restr
     atomicMax(stat + 1, __float_as_uint(m));
     atomicAdd(reinterpret_cast<double *>(stat + 2), (double)ss);
   }
+}
+
+// smallest exact utility of the pilot set, as an order-preserving uint (out starts at 0xFFFFFFFF)
+__global__ void __launch_bounds__(256) refine_min_kernel(const float *__restrict__ exact, unsigned int M,
+                                                         unsigned int *__restrict__ out) {
+  unsigned int m = 0xFFFFFFFFu;
+  for (unsigned int j = blockIdx.x * 256 + threadIdx.x; j < M; j += gridDim.x * 256) m = min(m, alink_orderable(exact[j]));
+  for (int o = 16; o > 0; o >>= 1) m = min(m, __shfl_xor_sync(0xffffffffu, m, o));
+  if ((threadIdx.x & 31) == 0) atomicMin(out, m);
 }
 
 // max |element| of a table (fp32): decides whether the half-precision filter can overflow (65504)
