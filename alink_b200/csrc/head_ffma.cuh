@@ -7,8 +7,9 @@
 // then acc + b[j], then relu — the order the oracle defines. The tiling below parallelises over pairs
 // (rows) and output neurons (columns) only, never over k, so the result is bit-exact by construction.
 //
-// Kernel: 128 x BN output tile per CTA, BK = 8, 256 threads, 8 x (BN/16) accumulators per thread,
-// double-buffered shared memory, one __syncthreads per k-chunk.
+// Kernel: 128 x BN output tile per CTA, BK = 16 (layer 1) or 8 (layer 2: its epilogue tile needs the shared
+// memory), 256 threads, 8 x (BN/16) accumulators per thread, double-buffered shared memory, one __syncthreads
+// per k-chunk.
 //   A operand: AMODE 0 dense fp32 rows; AMODE 1 index-driven gather of two table rows -> |a-b|;
 //              AMODE 2 gather -> [|a-b| ; a*b] (fan-in 2D, north_star's opt-in Hadamard feature).
 //   epilogue : EPI 0 bias + relu -> hidden activations (fp32, global);
@@ -44,9 +45,11 @@ struct FfmaArgs {
   float *probs;                // [(row0 + row) * K + learner] * C + c
 };
 
-template <int BN, int AMODE, int EPI>
+template <int BN, int AMODE, int EPI, int BK = (EPI == 0 ? 16 : 8)>
 __global__ void __launch_bounds__(256, 2) ffma_layer_kernel(const FfmaArgs a) {
-  constexpr int BM = 128, BK = 8, TM = 8, TN = BN / 16;
+  constexpr int BM = 128, TM = 8, TN = BN / 16;
+  constexpr int NA = BK / 8;                                   // float4 of A per thread and chunk
+  constexpr int NB = (BK * BN / 4 + 255) / 256;                // float4 of B per thread and chunk
   __shared__ __align__(16) float As[2][BK][BM];
   __shared__ __align__(16) float Bs[2][BK][BN];
 
@@ -57,8 +60,8 @@ __global__ void __launch_bounds__(256, 2) ffma_layer_kernel(const FfmaArgs a) {
   const int mtile = blockIdx.y;
   const int n0 = ntile * BN;
 
-  // ---- A loader state: this thread owns row (tid>>1), k-quad (tid&1)*4 of every chunk
-  const int lrow = tid >> 1, kq = (tid & 1) * 4;
+  // ---- A loader state: this thread owns row (tid>>1), k-quads (tid&1)*4*NA + 4*i of every chunk
+  const int lrow = tid >> 1, kq = (tid & 1) * 4 * NA;
   int grow = mtile * BM + lrow;
   if (grow >= a.M) grow = a.M - 1;
   const float *pa, *pb = nullptr;
@@ -80,13 +83,10 @@ __global__ void __launch_bounds__(256, 2) ffma_layer_kernel(const FfmaArgs a) {
     pa = a.ta + (size_t)ra * a.D;
     pb = a.tb + (size_t)rb * a.D;
   }
-  // ---- B loader state
-  constexpr int BTHREADS = BK * BN / 4;
+  // ---- B loader state: float4 number tid + 256 * i of the [BK][BN] chunk
+  constexpr int BTOTAL = BK * BN / 4;
   constexpr int BROW = BN / 4;  // float4 per k-row
-  const int kb = tid / BROW, n4 = (tid % BROW) * 4;
-  const bool b_active = tid < BTHREADS;
-  const bool b_valid = b_active && (n0 + n4 < a.Ncols);
-  const float *pw = a.W[learner] + (size_t)kb * a.Ncols + n0 + n4;
+  const float *pwl = a.W[learner] + n0;
 
   float acc[TM][TN];
 #pragma unroll
@@ -94,42 +94,56 @@ __global__ void __launch_bounds__(256, 2) ffma_layer_kernel(const FfmaArgs a) {
 #pragma unroll
     for (int j = 0; j < TN; ++j) acc[i][j] = 0.0f;
 
-  float4 ra4, rb4;
+  float4 ra4[NA], rb4[NB];
   auto load_chunk = [&](int k0) {
-    if constexpr (AMODE == 0) {
-      ra4 = __ldg(reinterpret_cast<const float4 *>(pa + k0 + kq));
-    } else {
-      int kk = k0;
-      bool had = false;
-      if (AMODE == 2 && k0 >= a.D) {
-        kk = k0 - a.D;
-        had = true;
-      }
-      const float4 va = __ldg(reinterpret_cast<const float4 *>(pa + kk + kq));
-      const float4 vb = __ldg(reinterpret_cast<const float4 *>(pb + kk + kq));
-      if (had) {
-        ra4.x = __fmul_rn(va.x, vb.x);
-        ra4.y = __fmul_rn(va.y, vb.y);
-        ra4.z = __fmul_rn(va.z, vb.z);
-        ra4.w = __fmul_rn(va.w, vb.w);
+#pragma unroll
+    for (int i = 0; i < NA; ++i) {
+      if constexpr (AMODE == 0) {
+        ra4[i] = __ldg(reinterpret_cast<const float4 *>(pa + k0 + kq + 4 * i));
       } else {
-        ra4.x = fabsf(__fsub_rn(va.x, vb.x));  // K.abs(l - r), code/siamese.py:27
-        ra4.y = fabsf(__fsub_rn(va.y, vb.y));
-        ra4.z = fabsf(__fsub_rn(va.z, vb.z));
-        ra4.w = fabsf(__fsub_rn(va.w, vb.w));
+        int kk = k0;
+        bool had = false;
+        if (AMODE == 2 && k0 >= a.D) {
+          kk = k0 - a.D;
+          had = true;
+        }
+        const float4 va = __ldg(reinterpret_cast<const float4 *>(pa + kk + kq + 4 * i));
+        const float4 vb = __ldg(reinterpret_cast<const float4 *>(pb + kk + kq + 4 * i));
+        if (had) {
+          ra4[i].x = __fmul_rn(va.x, vb.x);
+          ra4[i].y = __fmul_rn(va.y, vb.y);
+          ra4[i].z = __fmul_rn(va.z, vb.z);
+          ra4[i].w = __fmul_rn(va.w, vb.w);
+        } else {
+          ra4[i].x = fabsf(__fsub_rn(va.x, vb.x));  // K.abs(l - r), code/siamese.py:27
+          ra4[i].y = fabsf(__fsub_rn(va.y, vb.y));
+          ra4[i].z = fabsf(__fsub_rn(va.z, vb.z));
+          ra4[i].w = fabsf(__fsub_rn(va.w, vb.w));
+        }
       }
     }
-    if (b_valid)
-      rb4 = __ldg(reinterpret_cast<const float4 *>(pw + (size_t)k0 * a.Ncols));
-    else
-      rb4 = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+    for (int i = 0; i < NB; ++i) {
+      const int f = tid + 256 * i, kb = f / BROW, n4 = (f % BROW) * 4;
+      if (f < BTOTAL && n0 + n4 < a.Ncols)
+        rb4[i] = __ldg(reinterpret_cast<const float4 *>(pwl + (size_t)(k0 + kb) * a.Ncols + n4));
+      else
+        rb4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
   };
   auto store_chunk = [&](int buf) {
-    As[buf][kq + 0][lrow] = ra4.x;
-    As[buf][kq + 1][lrow] = ra4.y;
-    As[buf][kq + 2][lrow] = ra4.z;
-    As[buf][kq + 3][lrow] = ra4.w;
-    if (b_active) *reinterpret_cast<float4 *>(&Bs[buf][kb][n4]) = rb4;
+#pragma unroll
+    for (int i = 0; i < NA; ++i) {
+      As[buf][kq + 4 * i + 0][lrow] = ra4[i].x;
+      As[buf][kq + 4 * i + 1][lrow] = ra4[i].y;
+      As[buf][kq + 4 * i + 2][lrow] = ra4[i].z;
+      As[buf][kq + 4 * i + 3][lrow] = ra4[i].w;
+    }
+#pragma unroll
+    for (int i = 0; i < NB; ++i) {
+      const int f = tid + 256 * i, kb = f / BROW, n4 = (f % BROW) * 4;
+      if (f < BTOTAL) *reinterpret_cast<float4 *>(&Bs[buf][kb][n4]) = rb4[i];
+    }
   };
 
   const int nk = a.Kdim / BK;
