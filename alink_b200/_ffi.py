@@ -34,7 +34,7 @@ MAX_SLOTS = 8
 # every symbol include/alink_b200.h declares (tests/test_abi.py checks the .so exports them all)
 SYMBOLS = (
     "alink_abi_version", "alink_create", "alink_destroy", "alink_last_error", "alink_sync",
-    "alink_set_stream", "alink_launch_count", "alink_watchdog_record", "alink_host_alloc", "alink_host_free", "alink_set_heads", "alink_set_table",
+    "alink_set_stream", "alink_launch_count", "alink_watchdog_record", "alink_host_alloc", "alink_host_free", "alink_set_heads", "alink_set_table", "alink_set_table_async",
     "alink_score_indexed", "alink_score_dense", "alink_utility", "alink_utility_from_proba",
     "alink_select_topk", "alink_topk_values", "alink_topk_keys", "alink_query", "alink_disparity_select",
     "alink_set_refine_eps", "alink_refine_stats", "alink_refine_detail", "alink_score_allpairs", "alink_query_allpairs",
@@ -92,6 +92,8 @@ def load():
     L.alink_set_heads.argtypes = [vp, i32, i32, i32, i32, i32, i32, i32, i32, pp, pp, pp, pp, pp, pp, i32]
     L.alink_set_table.restype = i32
     L.alink_set_table.argtypes = [vp, i32, vp, i64, i32, i32, i32]
+    L.alink_set_table_async.restype = i32
+    L.alink_set_table_async.argtypes = [vp, i32, vp, i64, i32, i32]
     L.alink_score_indexed.restype = i32
     L.alink_score_indexed.argtypes = [vp, i32, i32, i32, vp, vp, i64, i32, vp, vp, i32]
     L.alink_score_dense.restype = i32
@@ -248,6 +250,23 @@ class Context:
         self._check(self._L.alink_set_table(self._h, slot, p, M, D, dtype, space))
         if space == DEVICE:
             self._keep[("table", slot)] = emb  # borrowed: keep alive
+
+    def set_table_async(self, slot, emb):
+        """Upload a HOST table (numpy or pinned CPU torch tensor, float32) on the copy stream and return at once; the
+        next call that reads the slot waits for it on the device. The buffer is kept alive until the slot is set again."""
+        p, space = _ptr_space(emb)
+        if space != HOST:
+            raise AlinkError("set_table_async takes a host table")
+        if _is_torch(emb):
+            import torch
+            dtype = {torch.float32: F32, torch.bfloat16: BF16}[emb.dtype]
+        else:
+            if emb.dtype != np.float32:
+                raise AlinkError("host tables must be float32")
+            dtype = F32
+        M, D = emb.shape
+        self._check(self._L.alink_set_table_async(self._h, slot, p, M, D, dtype))
+        self._keep[("table", slot)] = emb
 
     # ---- scoring
     def _outs(self, N, K, Cc, want_per, want_cons, out_device):

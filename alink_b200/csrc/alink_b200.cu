@@ -77,6 +77,14 @@ int alink_destroy(alink_ctx *ctx) {
   for (DevBuf *b : bufs) dev_release(*b);
   for (int i = 0; i < 8; ++i)
     if (ctx->ev[i]) cudaEventDestroy(ctx->ev[i]);
+  if (ctx->copy_stream) {
+    cudaStreamSynchronize(ctx->copy_stream);
+    cudaStreamDestroy(ctx->copy_stream);
+    cudaEventDestroy(ctx->copy_gate);
+    cudaEventDestroy(ctx->copy_done);
+  }
+  for (auto &t : ctx->tables)
+    if (t.ready) cudaEventDestroy(t.ready);
   cudaStreamDestroy(ctx->own_stream);
   delete ctx;
   return ALINK_OK;
@@ -202,6 +210,10 @@ int alink_set_table(alink_ctx *ctx, int slot, const void *emb, int64_t M, int D,
   if (dtype != ALINK_F32 && dtype != ALINK_BF16) return alink_fail(ctx, ALINK_E_INVALID, "bad dtype %d", dtype);
   ALINK_CUDA(ctx, cudaSetDevice(ctx->device));
   Table &t = ctx->tables[slot];
+  if (t.pending) {  // an asynchronous upload into this slot is still in flight: let it land first
+    ALINK_CUDA(ctx, cudaEventSynchronize(t.ready));
+    t.pending = false;
+  }
   const size_t bytes = (size_t)M * D * (dtype == ALINK_F32 ? 4 : 2);
   if (space == ALINK_DEVICE) {
     t.p = emb;
@@ -213,6 +225,49 @@ int alink_set_table(alink_ctx *ctx, int slot, const void *emb, int64_t M, int D,
   }
   t.M = M; t.D = D; t.dtype = dtype;
   t.absmax = -1.0;
+  return ALINK_OK;
+}
+
+// Upload a HOST table into a slot on the context's copy stream and return at once; the next call that reads the
+// slot makes the compute stream wait for the upload. With two slots the upload of the next pool overlaps the query
+// on the current one (bench.py e2e). The host buffer must stay valid (and should be pinned) until that next call.
+int alink_set_table_async(alink_ctx *ctx, int slot, const void *emb, int64_t M, int D, int dtype) {
+  if (!ctx) return ALINK_E_INVALID;
+  if (slot < 0 || slot >= ALINK_MAX_SLOTS) return alink_fail(ctx, ALINK_E_INVALID, "bad slot %d", slot);
+  if (!emb || M < 1 || D < 8 || D % 8) return alink_fail(ctx, ALINK_E_INVALID, "bad table (M=%lld, D=%d)", (long long)M, D);
+  if (dtype != ALINK_F32 && dtype != ALINK_BF16) return alink_fail(ctx, ALINK_E_INVALID, "bad dtype %d", dtype);
+  ALINK_CUDA(ctx, cudaSetDevice(ctx->device));
+  if (!ctx->copy_stream) {
+    ALINK_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
+    ALINK_CUDA(ctx, cudaEventCreateWithFlags(&ctx->copy_gate, cudaEventDisableTiming));
+    ALINK_CUDA(ctx, cudaEventCreateWithFlags(&ctx->copy_done, cudaEventDisableTiming));
+  }
+  Table &t = ctx->tables[slot];
+  if (!t.ready) ALINK_CUDA(ctx, cudaEventCreateWithFlags(&t.ready, cudaEventDisableTiming));
+  const size_t bytes = (size_t)M * D * (dtype == ALINK_F32 ? 4 : 2);
+  ALINK_TRY(dev_reserve(ctx, t.own, bytes));  // (a reallocation synchronises the compute stream)
+  // kernels already queued on the compute stream may still read this slot: the copy starts behind them
+  ALINK_CUDA(ctx, cudaEventRecord(ctx->copy_gate, ctx->stream));
+  ALINK_CUDA(ctx, cudaStreamWaitEvent(ctx->copy_stream, ctx->copy_gate, 0));
+  ALINK_CUDA(ctx, cudaMemcpyAsync(t.own.p, emb, bytes, cudaMemcpyHostToDevice, ctx->copy_stream));
+  ALINK_CUDA(ctx, cudaEventRecord(t.ready, ctx->copy_stream));
+  ALINK_CUDA(ctx, cudaEventRecord(ctx->copy_done, ctx->copy_stream));
+  ctx->copy_busy = true;
+  t.p = t.own.p;
+  t.M = M; t.D = D; t.dtype = dtype;
+  t.absmax = -1.0;
+  t.pending = true;
+  return ALINK_OK;
+}
+
+// the compute stream waits for an upload in flight into this slot (no host synchronisation)
+static int table_wait(alink_ctx *ctx, int slot) {
+  if (slot < 0 || slot >= ALINK_MAX_SLOTS) return ALINK_OK;  // the caller reports the bad slot
+  Table &t = ctx->tables[slot];
+  if (t.pending) {
+    ALINK_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, t.ready, 0));
+    t.pending = false;
+  }
   return ALINK_OK;
 }
 
@@ -293,6 +348,8 @@ int alink_score_indexed(alink_ctx *ctx, int group, int slot_a, int slot_b, const
   const void *dia, *dib;
   ALINK_TRY(stage_in(ctx, ia, sizeof(int32_t) * (size_t)N, in_space, ctx->idx_a, &dia));
   ALINK_TRY(stage_in(ctx, ib, sizeof(int32_t) * (size_t)N, in_space, ctx->idx_b, &dib));
+  ALINK_TRY(table_wait(ctx, slot_a));
+  ALINK_TRY(table_wait(ctx, slot_b));
   ALINK_TRY(score_impl(ctx, group, ctx->tables[slot_a], ctx->tables[slot_b], (const int32_t *)dia,
                        (const int32_t *)dib, N));
   return emit_scores(ctx, per_learner, consensus, out_space);
@@ -604,9 +661,12 @@ int alink_query(alink_ctx *ctx, int group, int slot_a, int slot_b, const int32_t
   cudaEvent_t *e = ctx->ev;
   if (timing) ALINK_CUDA(ctx, cudaEventRecord(e[0], ctx->stream));
   const void *dia, *dib;
+  if (ctx->copy_busy && cudaEventQuery(ctx->copy_done) == cudaSuccess) ctx->copy_busy = false;
   ALINK_TRY(stage_in(ctx, ia, sizeof(int32_t) * (size_t)N, in_space, ctx->idx_a, &dia));
   ALINK_TRY(stage_in(ctx, ib, sizeof(int32_t) * (size_t)N, in_space, ctx->idx_b, &dib));
   if (timing) ALINK_CUDA(ctx, cudaEventRecord(e[1], ctx->stream));
+  ALINK_TRY(table_wait(ctx, slot_a));
+  ALINK_TRY(table_wait(ctx, slot_b));
   ctx->refine_survivors = 0;
   ctx->refine_max_err = 0.0f;
   if (group >= 0 && group < ALINK_MAX_GROUPS && ctx->groups[group].set &&
@@ -668,6 +728,8 @@ static int allpairs_begin(alink_ctx *ctx, int slot_probe, int slot_gallery, int6
                           int64_t *base) {
   if (slot_probe < 0 || slot_probe >= ALINK_MAX_SLOTS || slot_gallery < 0 || slot_gallery >= ALINK_MAX_SLOTS)
     return alink_fail(ctx, ALINK_E_INVALID, "bad slot");
+  ALINK_TRY(table_wait(ctx, slot_probe));
+  ALINK_TRY(table_wait(ctx, slot_gallery));
   const Table &P = ctx->tables[slot_probe], &G = ctx->tables[slot_gallery];
   if (!P.p || !G.p) return alink_fail(ctx, ALINK_E_STATE, "embedding table slot not set (alink_set_table)");
   if (row0 < 0 || nrows < 0 || row0 + nrows > P.M) return alink_fail(ctx, ALINK_E_INVALID, "probe rows outside the table");
@@ -737,6 +799,8 @@ int alink_train_step(alink_ctx *ctx, int group, int learner, int slot_a, int slo
   if (slot_a < 0 || slot_a >= ALINK_MAX_SLOTS || slot_b < 0 || slot_b >= ALINK_MAX_SLOTS) return alink_fail(ctx, ALINK_E_INVALID, "bad slot");
   if (nb < 1 || nb > 65536 || !y) return alink_fail(ctx, ALINK_E_INVALID, "bad batch (nb=%d)", nb);
   if ((ia == nullptr) != (ib == nullptr)) return alink_fail(ctx, ALINK_E_INVALID, "ia and ib must both be given or both NULL");
+  ALINK_TRY(table_wait(ctx, slot_a));
+  ALINK_TRY(table_wait(ctx, slot_b));
   const Table &A = ctx->tables[slot_a], &Bt = ctx->tables[slot_b];
   if (!A.p || !Bt.p) return alink_fail(ctx, ALINK_E_STATE, "embedding table slot not set (alink_set_table)");
   if (A.dtype != ALINK_F32 || Bt.dtype != ALINK_F32 || A.D != Bt.D || (g.feat_mode ? 2 * A.D : A.D) != g.D_in)

@@ -43,6 +43,8 @@ struct Table {
   int dtype = ALINK_F32;
   DevBuf own;
   double absmax = -1.0;  // max |element| (lazy, refine.cuh; reset by alink_set_table)
+  cudaEvent_t ready = nullptr;  // alink_set_table_async: recorded on the copy stream behind the upload
+  bool pending = false;         // the compute stream has not yet been made to wait for `ready`
 };
 
 struct SelectState;  // topk.cuh
@@ -52,6 +54,10 @@ struct alink_ctx {
   int sm_count = 148;
   cudaStream_t stream = nullptr;      // stream in use
   cudaStream_t own_stream = nullptr;  // private stream created by alink_create
+  cudaStream_t copy_stream = nullptr; // alink_set_table_async uploads (created on first use)
+  cudaEvent_t copy_gate = nullptr;    // compute-stream marker the copy stream waits for before overwriting a slot
+  cudaEvent_t copy_done = nullptr;    // behind the latest asynchronous upload
+  bool copy_busy = false;             // an asynchronous upload may still be in flight (cleared when copy_done has passed)
   cudaEvent_t ev[8] = {};
   char err[512] = {0};
   int64_t launches = 0;
@@ -150,6 +156,11 @@ static inline void dev_release(DevBuf &b) {
 
 // Bring a caller buffer onto the device: ALINK_DEVICE pointers pass through, ALINK_HOST ones are
 // copied into `stage` on the context stream.
+// reads page-locked HOST memory straight over PCIe (16 bytes per thread and step)
+__global__ void __launch_bounds__(256) zero_copy_in_kernel(const uint4 *__restrict__ src, uint4 *__restrict__ dst, size_t n16) {
+  for (size_t i = (size_t)blockIdx.x * 256 + threadIdx.x; i < n16; i += (size_t)gridDim.x * 256) dst[i] = src[i];
+}
+
 static inline int stage_in(alink_ctx *ctx, const void *src, size_t bytes, int space, DevBuf &stage,
                            const void **out) {
   if (!src) {
@@ -161,6 +172,23 @@ static inline int stage_in(alink_ctx *ctx, const void *src, size_t bytes, int sp
     return ALINK_OK;
   }
   ALINK_TRY(dev_reserve(ctx, stage, bytes));
+  // While an asynchronous table upload occupies the host-to-device copy engine (alink_set_table_async), a
+  // cudaMemcpyAsync of this call's small inputs would queue behind it; page-locked inputs are then read by a
+  // kernel instead, sharing the link with the upload.
+  if (ctx->copy_busy && bytes % 16 == 0 && ((uintptr_t)src & 15u) == 0) {
+    cudaPointerAttributes at;
+    if (cudaPointerGetAttributes(&at, src) == cudaSuccess && at.type == cudaMemoryTypeHost && at.devicePointer) {
+      const size_t n16 = bytes / 16;
+      size_t blocks = (n16 + 255) / 256;
+      if (blocks > (size_t)ctx->sm_count * 4) blocks = (size_t)ctx->sm_count * 4;
+      if (blocks < 1) blocks = 1;
+      zero_copy_in_kernel<<<(unsigned)blocks, 256, 0, ctx->stream>>>((const uint4 *)at.devicePointer, (uint4 *)stage.p, n16);
+      ALINK_LAUNCHED(ctx);
+      *out = stage.p;
+      return ALINK_OK;
+    }
+    cudaGetLastError();  // pageable memory: not an error, take the copy-engine path
+  }
   ALINK_CUDA(ctx, cudaMemcpyAsync(stage.p, src, bytes, cudaMemcpyHostToDevice, ctx->stream));
   *out = stage.p;
   return ALINK_OK;

@@ -105,6 +105,13 @@ int alink_set_heads(alink_ctx *ctx, int group, int K, int D_in, int H1, int H2, 
  * space = ALINK_HOST: copied to the GPU; ALINK_DEVICE: borrowed (caller keeps it alive). */
 int alink_set_table(alink_ctx *ctx, int slot, const void *emb, int64_t M, int D, int dtype, int space);
 
+/* Same for a HOST table, without waiting: the upload runs on the context's copy stream behind whatever the
+ * compute stream has queued, and the next call that reads the slot waits for it on the device. With two slots the
+ * table of the next pool crosses PCIe while the current pool is scored (the per-iteration feature arrays of
+ * code/ALINK.py:139-160 are host arrays in the reference). `emb` must stay valid — and should be page-locked
+ * (alink_host_alloc) — until that next call returns. */
+int alink_set_table_async(alink_ctx *ctx, int slot, const void *emb, int64_t M, int D, int dtype);
+
 /* Score N indexed pairs (row ia[n] of slot_a vs row ib[n] of slot_b) with every learner of `group`.
  * Replaces SiameseNetwork.predict (code/siamese.py:130-131) called per learner by Bagging.predict
  * (code/committee.py:13-20) / Committee.vote_proba (code/learners.py:383-416).

@@ -142,3 +142,31 @@ def test_errors_are_reported_not_fatal(ctx):
     # the context is still usable afterwards
     idx, _, _ = ctx.query(0, 0, 0, pool.ia, pool.ib, pool.N, "uncertainty", 8)
     assert len(idx) == 8
+
+
+def test_async_table_upload_matches_the_blocking_one(oracle):
+    """alink_set_table_async: the upload runs on the copy stream, the next reader waits on the device; alternating
+    two slots (the e2e pipeline of bench.py) must give the scores of the blocking upload, also when a slot is
+    overwritten right after it was read."""
+    import torch
+
+    ctx = _ffi.Context(0)
+    pool = synth.make_pool(1, N=3000, M=900)
+    t0 = torch.from_numpy(pool.table)
+    tabs = [t0.clone().pin_memory(), torch.roll(t0, 7, dims=0).contiguous().pin_memory()]
+    K, Cc = pool.heads.K, pool.heads.C
+    ctx.set_heads(0, pool.heads, compute=_ffi.FP32_EXACT)
+    ref = []
+    for t in tabs:
+        ctx.set_table(0, t)
+        ref.append(ctx.score_indexed(0, 0, 0, pool.ia, pool.ib, pool.N, K, Cc)[0].copy())
+    assert not np.array_equal(ref[0], ref[1])
+    cur = 1
+    ctx.set_table(cur, tabs[0])
+    for step in range(6):
+        nxt = 3 - cur
+        ctx.set_table_async(nxt, tabs[(step + 1) % 2])  # in flight while `cur` is scored
+        per, _ = ctx.score_indexed(0, cur, cur, pool.ia, pool.ib, pool.N, K, Cc)
+        assert np.array_equal(per.view(np.uint32), ref[step % 2].view(np.uint32)), f"step {step}"
+        cur = nxt
+    ctx.close()
