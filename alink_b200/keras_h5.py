@@ -313,11 +313,24 @@ class H5File:
 
     def _dataset(self, p, shape, t):
         ver, cls = self._u(p, 1), self._u(p + 1, 1)
-        if ver != 3:
-            raise H5FormatError(f"data layout message version {ver} not supported (3 expected)")
         if shape is None:
             return np.zeros((0,), t.dtype or object)
         n = int(np.prod(shape, dtype=np.int64)) if shape else 1
+        if ver in (1, 2):  # libhdf5 <= 1.6 (e.g. MATLAB 7.3 files): version, rank, class, 5 reserved bytes
+            ndim, cls = self._u(p + 1, 1), self._u(p + 2, 1)
+            if cls == 1:
+                addr = self._u(p + 8, self.O)
+                raw = bytes(n * t.size) if addr == UNDEF else self._bytes(addr + self.base, n * t.size)
+            elif cls == 0:
+                q = p + 8 + (self.O if ver == 1 else 0) + 4 * ndim
+                if self._u(q, 4) < n * t.size:
+                    raise H5FormatError("compact dataset shorter than its dataspace")
+                raw = self._bytes(q + 4, n * t.size)
+            else:
+                raise H5FormatError("chunked datasets not supported")
+            return self._decode(raw, shape, t)
+        if ver != 3:
+            raise H5FormatError(f"data layout message version {ver} not supported")
         if cls == 0:
             size = self._u(p + 2, 2)
             if size < n * t.size:

@@ -7,15 +7,18 @@ Same class name, constructor and `predict` contract as the reference
 (`trainModel`, `finetune`, `customTrainModel`, code/siamese.py:44-112) are outside the path this
 package replaces and raise NotImplementedError.
 
-Weights: Keras Dense layout, W (in, out) row-major fp32, b (out,). h5py is not available in this
-image, so checkpoints are `<modelName>.npz` with keys W1,b1,W2,b2,W3,b3 (Keras `.h5` import is a
-"next" item).
+Weights: Keras Dense layout, W (in, out) row-major fp32, b (out,). Checkpoints are the reference's
+`<modelName>.h5` Keras weight files, read and written by `keras_h5` (a self-contained HDF5-subset
+reader/writer: h5py is not in this image); `<modelName>.npz` with keys W1,b1,W2,b2,W3,b3 is read as a
+fallback when no `.h5` exists.
 """
 from __future__ import annotations
 
 import numpy as np
 
-from . import engine
+import os
+
+from . import engine, keras_h5
 
 
 def _glorot_uniform(rng, fan_in, fan_out):
@@ -51,15 +54,19 @@ class SiameseNetwork:
 
     def maybeLoadFromMemory(self):
         try:
-            z = np.load(self.modelName + ".npz")
-            self._spec.set(z["W1"], z["b1"], z["W2"], z["b2"], z["W3"], z["b3"])
+            s = self._spec
+            if os.path.exists(self.modelName + ".h5"):  # code/siamese.py:116
+                s.set(*keras_h5.load_head_weights(self.modelName + ".h5", s.D_in, s.H1, s.H2, s.C))
+            else:
+                z = np.load(self.modelName + ".npz")
+                s.set(z["W1"], z["b1"], z["W2"], z["b2"], z["W3"], z["b3"])
             return True
         except Exception:  # the reference swallows every failure (code/siamese.py:118-119)
             return False
 
     def save(self, customName=None):
-        s = self._spec
-        np.savez((customName or self.modelName) + ".npz", W1=s.W1, b1=s.b1, W2=s.W2, b2=s.b2, W3=s.W3, b3=s.b3)
+        s = self._spec  # code/siamese.py:121-125: save_weights(<name> + ".h5")
+        keras_h5.save_head_weights((customName or self.modelName) + ".h5", [s.W1, s.b1, s.W2, s.b2, s.W3, s.b3])
 
     # ---- inference (the path)
     def preprocess(self, X):

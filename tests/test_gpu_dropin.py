@@ -1,6 +1,8 @@
 """GPU tests of the drop-in Python interfaces, written the way the reference's drivers call them
 (/root/reference/code/ALINK.py:96-97,160,170; code/existing_al.py:95-110; code/learners.py:287-416;
 utilities/generateMatrixDFW.py:19-33) and checked against the CPU oracle."""
+import os
+
 import numpy as np
 import pytest
 
@@ -44,12 +46,13 @@ def test_siamese_predict_and_bagging(oracle):
     np.testing.assert_array_equal(ens, ref["consensus"])
 
 
-def test_weights_roundtrip_npz(tmp_path):
+def test_weights_roundtrip_h5(tmp_path):
     pool = synth.make_pool(1, N=64)
     net = siamese.SiameseNetwork((pool.D,), str(tmp_path / "m"), 0.1)
     assert net.maybeLoadFromMemory() is False  # the reference swallows the failure (code/siamese.py:114-119)
     net.set_weights(*pool.heads.learner(0))
-    net.save()
+    net.save()  # <modelName>.h5, a Keras weight file (code/siamese.py:121-125)
+    assert os.path.exists(str(tmp_path / "m") + ".h5")
     net2 = siamese.SiameseNetwork((pool.D,), str(tmp_path / "m"), 0.1)
     assert net2.maybeLoadFromMemory() is True
     X = _dense(pool)
