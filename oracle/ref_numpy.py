@@ -259,3 +259,36 @@ def train_step(XL, XR, y, params, acc_g, acc_d, lr=1.0, rho=0.95, eps=1e-7, act=
         new_a.append(a)
         new_d.append(rho * np.asarray(d, np.float64) + (1 - rho) * u * u)
     return loss, acc, new_p, new_a, new_d, p
+
+
+def create_mini_batch_dfw(X_plain, X_dig):
+    """code/readDFW.py:222-244, loop for loop (test infrastructure: O(N) Python)."""
+    X_left, X_right, Y = [], [], []
+    for i in range(len(X_plain)):
+        for j in range(len(X_dig)):
+            for x in X_plain[i]:
+                for y in X_dig[j]:
+                    X_left.append(x)
+                    X_right.append(y)
+                    Y.append([1] if i == j else [0])
+    for i in range(len(X_dig)):
+        for j in range(len(X_dig)):
+            for x in X_dig[i]:
+                for y in X_dig[j]:
+                    X_left.append(x)
+                    X_right.append(y)
+                    Y.append([1] if i == j else [0])
+    return [np.stack(X_left), np.stack(X_right)], np.stack(Y)
+
+
+def create_mini_batch_mtp(X_plain):
+    """code/readMTP.py:123-135."""
+    X_left, X_right, Y = [], [], []
+    for i in range(len(X_plain)):
+        for j in range(len(X_plain)):
+            for x in X_plain[i]:
+                for y in X_plain[j]:
+                    X_left.append(x)
+                    X_right.append(y)
+                    Y.append([1] if i == j else [0])
+    return [np.stack(X_left), np.stack(X_right)], np.stack(Y)
