@@ -526,18 +526,19 @@ static int refine_query(alink_ctx *ctx, const HeadGroup &g, Table &A, Table &Bt,
     f16 = xmax < 6.0e4 && h1max < 6.0e4 && g.w_absmax < 6.0e4;  // false for NaN / inf
   }
   ALINK_TRY(dev_reserve(ctx, ctx->util, sizeof(float) * (size_t)N));
-  ALINK_TRY(dev_reserve(ctx, ctx->sel_state, sizeof(SelectState)));
+  ALINK_TRY(dev_reserve(ctx, ctx->sel_state, 2 * sizeof(SelectState)));
   ALINK_TRY(dev_reserve(ctx, ctx->cand, sizeof(uint32_t) * (size_t)N));
   ALINK_TRY(dev_reserve(ctx, ctx->rstat, 32));
   float *util_a = (float *)ctx->util.p;
-  SelectState *st = (SelectState *)ctx->sel_state.p;
+  // second state slot: tau must survive the exact top-B of step (5), which runs in slot 0, for a widening round
+  SelectState *st = (SelectState *)ctx->sel_state.p + 1;
   unsigned int *rstat = (unsigned int *)ctx->rstat.p;  // [0] candidate count, [1] max error bits, [2..3] sum sq
   // (1) approximate utilities of every pair, fused K-learner reduction in the kernel's epilogue
   ALINK_TRY(tc_score(ctx, g, A, Bt, ia, ib, N, nullptr, util_a, measure, f16));
   if (ev) ALINK_CUDA(ctx, cudaEventRecord(ev[2], ctx->stream));
   // (2) B-th largest approximate utility
   KeySrc asrc{util_a, nullptr, 0, nullptr};
-  ALINK_TRY(select_threshold(ctx, asrc, N, B, st));
+  ALINK_TRY(select_threshold(ctx, asrc, N, B, st, 3));  // the utility bits only: tau, not a tie-broken key
   int64_t blocks = (N + 2047) / 2048;
   const int64_t cap = (int64_t)ctx->sm_count * 8;
   if (blocks > cap) blocks = cap;

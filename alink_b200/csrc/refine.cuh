@@ -24,12 +24,12 @@
 #include "topk.cuh"
 
 // candidates = pairs whose approximate utility is within `margin` of a reference value: the B-th largest
-// approximate utility (st->prefix = its key) or, when `pilot_min` is given, the smallest EXACT utility of the
+// approximate utility (st->prefix = the high 32 bits of its key: select_threshold(..., passes = 3)) or, when `pilot_min` is given, the smallest EXACT utility of the
 // pilot set (an order-preserving uint, refine_min_kernel)
 __global__ void __launch_bounds__(256) refine_mark_kernel(const float *__restrict__ util, int64_t N, const SelectState *st,
                                                           const unsigned int *__restrict__ pilot_min, float margin,
                                                           uint32_t *__restrict__ cand, unsigned int *__restrict__ count) {
-  const float tau = alink_key_utility(st->prefix);
+  const float tau = alink_key_utility(st->prefix << 32);
   // never above tau: the pilot set itself always stays in (it matters when the caller's bound is too tight)
   const float thr = pilot_min ? fminf(__fsub_rn(alink_unorderable(*pilot_min), margin), tau) : __fsub_rn(tau, margin);
   const int lane = threadIdx.x & 31;

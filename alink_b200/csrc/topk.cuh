@@ -104,6 +104,71 @@ __global__ void __launch_bounds__(256) radix_pass_kernel(KeySrc src, int64_t n, 
   if (threadIdx.x == 0) st->ticket = 0;
 }
 
+// Small sources (the exact re-score's candidates, the cross-shard merge of B keys per rank): the same passes
+// inside ONE CTA — no global histogram, no ticket, one launch instead of seven. Each multi-CTA pass costs
+// ~10 us of launch + tail-scan latency whatever n is, which is all a 10 k-key select consists of.
+__global__ void __launch_bounds__(1024) radix_select_small_kernel(KeySrc src, int n, unsigned long long B, int passes,
+                                                                  SelectState *st) {
+  __shared__ unsigned int sh[2048];
+  __shared__ unsigned int part[256];
+  __shared__ unsigned long long s_prefix, s_remaining;
+  const int tid = threadIdx.x;
+  if (tid == 0) {
+    s_prefix = 0;
+    s_remaining = B;
+  }
+  const int shifts[6] = {53, 42, 32, 21, 10, 0};
+  const int nbits[6] = {11, 11, 10, 11, 11, 10};
+  for (int p = 0; p < passes; ++p) {
+    const int shift = shifts[p], bits = nbits[p], nb = 1 << bits, hi = shift + bits;
+    const unsigned mask = (unsigned)nb - 1u;
+    for (int i = tid; i < nb; i += 1024) sh[i] = 0;
+    __syncthreads();
+    const unsigned long long prefix = s_prefix, remaining = s_remaining;
+    for (int i = tid; i < n; i += 1024) {
+      const uint64_t key = load_key(src, i);
+      if (p == 0 || (key >> hi) == prefix) atomicAdd(&sh[(unsigned)(key >> shift) & mask], 1u);
+    }
+    __syncthreads();
+    const int per = nb / 256;  // thread t < 256 owns bins [nb-1-per*t-(per-1), nb-1-per*t], descending
+    unsigned int mine = 0;
+    if (tid < 256) {
+      for (int j = 0; j < per; ++j) mine += sh[nb - 1 - per * tid - j];
+      part[tid] = mine;
+    }
+    __syncthreads();
+    for (int off = 1; off < 256; off <<= 1) {
+      unsigned int v = (tid < 256 && tid >= off) ? part[tid - off] : 0u;
+      __syncthreads();
+      if (tid < 256) part[tid] += v;
+      __syncthreads();
+    }
+    if (tid < 256) {
+      const unsigned long long incl = part[tid], before = incl - mine;
+      if (before < remaining && remaining <= incl) {
+        unsigned long long cum = before;
+        for (int j = 0; j < per; ++j) {
+          const int bin = nb - 1 - per * tid - j;
+          const unsigned int c = sh[bin];
+          if (cum + c >= remaining) {
+            s_prefix = p == 0 ? (unsigned long long)bin : ((prefix << bits) | (unsigned long long)bin);
+            s_remaining = remaining - cum;
+            break;
+          }
+          cum += c;
+        }
+      }
+    }
+    __syncthreads();
+  }
+  if (tid == 0) {
+    st->prefix = s_prefix;
+    st->remaining = s_remaining;
+    st->ticket = 0;
+    st->out_count = 0;
+  }
+}
+
 // keys >= threshold (st->prefix after the last pass) -> out (exactly B of them, unordered)
 __global__ void __launch_bounds__(256) compact_kernel(KeySrc src, int64_t n, SelectState *st, uint64_t *out,
                                                       unsigned int cap) {
@@ -177,8 +242,17 @@ static inline int64_t next_pow2(int64_t v) {
   return p;
 }
 
-// Radix-select the B-th largest key; on return st->prefix holds it (device).
-static int select_threshold(alink_ctx *ctx, const KeySrc &src, int64_t n, int64_t B, SelectState *st) {
+static const int64_t SELECT_SMALL_N = 32768;  // below this one CTA runs every pass (radix_select_small_kernel)
+
+// Radix-select the B-th largest key; on return st->prefix holds it (device). passes = 3 stops after the 32
+// utility bits: st->prefix is then key >> 32 of the B-th largest key (its utility, ties unresolved) — all the
+// refine filter needs (refine.cuh), at half the streaming passes.
+static int select_threshold(alink_ctx *ctx, const KeySrc &src, int64_t n, int64_t B, SelectState *st, int passes = 6) {
+  if (n <= SELECT_SMALL_N) {
+    radix_select_small_kernel<<<1, 1024, 0, ctx->stream>>>(src, (int)n, (unsigned long long)B, passes, st);
+    ALINK_LAUNCHED(ctx);
+    return ALINK_OK;
+  }
   select_init_kernel<<<1, 256, 0, ctx->stream>>>(st, (unsigned long long)B);
   ALINK_LAUNCHED(ctx);
   int64_t blocks = (n + 256 * 8 - 1) / (256 * 8);
@@ -187,7 +261,7 @@ static int select_threshold(alink_ctx *ctx, const KeySrc &src, int64_t n, int64_
   if (blocks < 1) blocks = 1;
   static const int shifts[6] = {53, 42, 32, 21, 10, 0};
   static const int nbits[6] = {11, 11, 10, 11, 11, 10};
-  for (int p = 0; p < 6; ++p) {
+  for (int p = 0; p < passes; ++p) {
     radix_pass_kernel<<<(unsigned)blocks, 256, 0, ctx->stream>>>(src, n, shifts[p], nbits[p], p == 0, st);
     ALINK_LAUNCHED(ctx);
   }
