@@ -175,13 +175,16 @@ def _f32(a):
     return np.ascontiguousarray(a, dtype=np.float32)
 
 
+FLAG_CHECK_INDICES = 1  # include/alink_b200.h ALINK_FLAG_CHECK_INDICES
+
+
 class Context:
     """One GPU, one stream, all scratch. Mirrors `alink_ctx`."""
 
-    def __init__(self, device: int = 0):
+    def __init__(self, device: int = 0, check_indices: bool = False):
         self._L = load()
         h = C.c_void_p()
-        rc = self._L.alink_create(C.byref(h), int(device), 0)
+        rc = self._L.alink_create(C.byref(h), int(device), FLAG_CHECK_INDICES if check_indices else 0)
         if rc != 0:
             raise AlinkError(f"alink_create(device={device}) failed with {rc}: no usable CUDA device "
                              "(this library has no CPU fallback)")

@@ -22,7 +22,6 @@ extern "C" {
 int alink_abi_version(void) { return ALINK_ABI_VERSION; }
 
 int alink_create(alink_ctx **out, int device, unsigned flags) {
-  (void)flags;
   if (!out) return ALINK_E_INVALID;
   *out = nullptr;
   int ndev = 0;
@@ -31,6 +30,7 @@ int alink_create(alink_ctx **out, int device, unsigned flags) {
   alink_ctx *ctx = new (std::nothrow) alink_ctx();
   if (!ctx) return ALINK_E_NOMEM;
   ctx->device = device;
+  ctx->flags = flags;
   if (cudaSetDevice(device) != cudaSuccess ||
       cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) {
     delete ctx;
@@ -338,6 +338,45 @@ static int emit_scores(alink_ctx *ctx, float *per_learner, float *consensus, int
   return ALINK_OK;
 }
 
+// ALINK_FLAG_CHECK_INDICES: largest index as an unsigned number (a negative one becomes huge) per side
+__global__ void __launch_bounds__(256) index_range_kernel(const int32_t *__restrict__ ia, const int32_t *__restrict__ ib,
+                                                          int64_t N, unsigned int *__restrict__ out) {
+  unsigned int ma = 0, mb = 0;
+  for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < N; i += (int64_t)gridDim.x * 256) {
+    ma = max(ma, (unsigned int)__ldg(ia + i));
+    mb = max(mb, (unsigned int)__ldg(ib + i));
+  }
+  for (int o = 16; o; o >>= 1) {
+    ma = max(ma, __shfl_xor_sync(0xffffffffu, ma, o));
+    mb = max(mb, __shfl_xor_sync(0xffffffffu, mb, o));
+  }
+  if ((threadIdx.x & 31) == 0) {
+    if (ma) atomicMax(out, ma);
+    if (mb) atomicMax(out + 1, mb);
+  }
+}
+
+static int check_indices(alink_ctx *ctx, const int32_t *dia, const int32_t *dib, int64_t N, int slot_a, int slot_b) {
+  if (!(ctx->flags & ALINK_FLAG_CHECK_INDICES) || !dia || N <= 0) return ALINK_OK;
+  ALINK_TRY(dev_reserve(ctx, ctx->rstat, 32));
+  unsigned int *d = (unsigned int *)ctx->rstat.p + 6;
+  ALINK_CUDA(ctx, cudaMemsetAsync(d, 0, 8, ctx->stream));
+  int64_t blocks = (N + 2047) / 2048;
+  if (blocks > (int64_t)ctx->sm_count * 8) blocks = (int64_t)ctx->sm_count * 8;
+  index_range_kernel<<<(unsigned)blocks, 256, 0, ctx->stream>>>(dia, dib, N, d);
+  ALINK_LAUNCHED(ctx);
+  unsigned int h[2] = {0, 0};
+  ALINK_CUDA(ctx, cudaMemcpyAsync(h, d, 8, cudaMemcpyDeviceToHost, ctx->stream));
+  ALINK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  if ((int64_t)h[0] >= ctx->tables[slot_a].M)
+    return alink_fail(ctx, ALINK_E_INVALID, "ia holds index %d, table slot %d has %lld rows", (int)h[0], slot_a,
+                      (long long)ctx->tables[slot_a].M);
+  if ((int64_t)h[1] >= ctx->tables[slot_b].M)
+    return alink_fail(ctx, ALINK_E_INVALID, "ib holds index %d, table slot %d has %lld rows", (int)h[1], slot_b,
+                      (long long)ctx->tables[slot_b].M);
+  return ALINK_OK;
+}
+
 int alink_score_indexed(alink_ctx *ctx, int group, int slot_a, int slot_b, const int32_t *ia, const int32_t *ib,
                         int64_t N, int in_space, float *per_learner, float *consensus, int out_space) {
   if (!ctx) return ALINK_E_INVALID;
@@ -348,6 +387,7 @@ int alink_score_indexed(alink_ctx *ctx, int group, int slot_a, int slot_b, const
   const void *dia, *dib;
   ALINK_TRY(stage_in(ctx, ia, sizeof(int32_t) * (size_t)N, in_space, ctx->idx_a, &dia));
   ALINK_TRY(stage_in(ctx, ib, sizeof(int32_t) * (size_t)N, in_space, ctx->idx_b, &dib));
+  ALINK_TRY(check_indices(ctx, (const int32_t *)dia, (const int32_t *)dib, N, slot_a, slot_b));
   ALINK_TRY(table_wait(ctx, slot_a));
   ALINK_TRY(table_wait(ctx, slot_b));
   ALINK_TRY(score_impl(ctx, group, ctx->tables[slot_a], ctx->tables[slot_b], (const int32_t *)dia,
@@ -666,6 +706,7 @@ int alink_query(alink_ctx *ctx, int group, int slot_a, int slot_b, const int32_t
   ALINK_TRY(stage_in(ctx, ia, sizeof(int32_t) * (size_t)N, in_space, ctx->idx_a, &dia));
   ALINK_TRY(stage_in(ctx, ib, sizeof(int32_t) * (size_t)N, in_space, ctx->idx_b, &dib));
   if (timing) ALINK_CUDA(ctx, cudaEventRecord(e[1], ctx->stream));
+  ALINK_TRY(check_indices(ctx, (const int32_t *)dia, (const int32_t *)dib, N, slot_a, slot_b));
   ALINK_TRY(table_wait(ctx, slot_a));
   ALINK_TRY(table_wait(ctx, slot_b));
   ctx->refine_survivors = 0;

@@ -61,6 +61,7 @@ struct alink_ctx {
   cudaEvent_t ev[8] = {};
   char err[512] = {0};
   int64_t launches = 0;
+  unsigned flags = 0;                 // ALINK_FLAG_* of alink_create
 
   HeadGroup groups[ALINK_MAX_GROUPS];
   Table tables[ALINK_MAX_SLOTS];

@@ -135,6 +135,11 @@ class PairPool:
             self.ctx.set_table(self.slot_b, table_b)
         self.table_a, self.table_b = table_a, (table_a if table_b is None else table_b)
         self.ia, self.ib = ia, ib
+        for name, idx, t in (("ia", ia, self.table_a), ("ib", ib, self.table_b)):
+            if isinstance(idx, np.ndarray) and idx.size:  # once per pool; device tensors: Context(check_indices=True)
+                lo, hi = int(idx.min()), int(idx.max())
+                if lo < 0 or hi >= int(t.shape[0]):
+                    raise IndexError(f"{name} holds index {lo if lo < 0 else hi}, the table has {int(t.shape[0])} rows")
         self.N = int(len(ia)) if ia is not None else int(table_a.shape[0])
         self.D = int(table_a.shape[1])
 

@@ -142,6 +142,10 @@ class Pool:
     def D(self):
         return self.table.shape[1]
 
+    @property
+    def M(self):
+        return self.table.shape[0]
+
 
 # BASELINE.json configs, 1-based ordinal as in SURVEY.md §8d
 CONFIGS = {

@@ -70,7 +70,13 @@ typedef struct alink_timing {
 int alink_abi_version(void);
 
 /* Context on CUDA device `device`. Replaces the reference's global TF session
- * (code/ALINK.py:22-25: ConfigProto(allow_growth) + K.set_session). */
+ * (code/ALINK.py:22-25: ConfigProto(allow_growth) + K.set_session).
+ * flags: ALINK_FLAG_CHECK_INDICES — every indexed call (alink_score_indexed, alink_query) first range-checks
+ * ia / ib against the row counts of the two table slots on the device (one 8 B/pair streaming pass + one
+ * 4-byte read-back) and returns ALINK_E_INVALID instead of letting a caller's bad index fault the context.
+ * The reference has no index arrays (it materialises rows, code/readDFW.py:222-244), hence no such failure;
+ * off by default because the hot path is otherwise free of host synchronisation before the head kernel. */
+#define ALINK_FLAG_CHECK_INDICES 1u
 int alink_create(alink_ctx **out, int device, unsigned flags);
 int alink_destroy(alink_ctx *ctx);
 const char *alink_last_error(const alink_ctx *ctx);

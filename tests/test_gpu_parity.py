@@ -170,3 +170,33 @@ def test_async_table_upload_matches_the_blocking_one(oracle):
         assert np.array_equal(per.view(np.uint32), ref[step % 2].view(np.uint32)), f"step {step}"
         cur = nxt
     ctx.close()
+
+
+def test_index_range_check_flag(oracle):
+    """ALINK_FLAG_CHECK_INDICES: an out-of-range pair index is an ALINK_E_INVALID error, not a device fault;
+    in-range pools are unaffected (bit-exact) and the context stays usable after the error."""
+    pool = synth.make_pool(1, N=3000)
+    c = _ffi.Context(0, check_indices=True)
+    try:
+        c.set_table(0, pool.table)
+        c.set_heads(0, pool.heads, compute=_ffi.FP32_EXACT)
+        good = c.query(0, 0, 0, pool.ia, pool.ib, pool.N, "uncertainty", 50)
+        for bad_value in (pool.M, -1, 2**31 - 1):
+            for side in (0, 1):
+                ia, ib = pool.ia.copy(), pool.ib.copy()
+                (ia, ib)[side][1234] = bad_value
+                with pytest.raises(_ffi.AlinkError, match="holds index"):
+                    c.query(0, 0, 0, ia, ib, pool.N, "uncertainty", 50)
+                with pytest.raises(_ffi.AlinkError, match="holds index"):
+                    c.score_indexed(0, 0, 0, ia, ib, pool.N, pool.heads.K, pool.heads.C)
+        again = c.query(0, 0, 0, pool.ia, pool.ib, pool.N, "uncertainty", 50)
+        np.testing.assert_array_equal(good[2], again[2])
+        ref = oracle.score(pool.table, pool.table, pool.ia, pool.ib, pool.heads, measure="uncertainty")
+        np.testing.assert_array_equal(good[0], oracle.topk(ref["util"], 50)[0])
+    finally:
+        c.close()
+    from alink_b200 import engine
+    bad = pool.ia.copy()
+    bad[7] = pool.M
+    with pytest.raises(IndexError, match="holds index"):
+        engine.PairPool(pool.table, bad, pool.ib)
