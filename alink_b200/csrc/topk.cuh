@@ -107,11 +107,9 @@ __global__ void __launch_bounds__(256) radix_pass_kernel(KeySrc src, int64_t n, 
 // Small sources (the exact re-score's candidates, the cross-shard merge of B keys per rank): the same passes
 // inside ONE CTA — no global histogram, no ticket, one launch instead of seven. Each multi-CTA pass costs
 // ~10 us of launch + tail-scan latency whatever n is, which is all a 10 k-key select consists of.
-__global__ void __launch_bounds__(1024) radix_select_small_kernel(KeySrc src, int n, unsigned long long B, int passes,
-                                                                  SelectState *st) {
-  __shared__ unsigned int sh[2048];
-  __shared__ unsigned int part[256];
-  __shared__ unsigned long long s_prefix, s_remaining;
+__device__ __forceinline__ void radix_select_cta(const KeySrc &src, int n, unsigned long long B, int passes,
+                                                 unsigned int *sh /*2048*/, unsigned int *part /*256*/,
+                                                 unsigned long long &s_prefix, unsigned long long &s_remaining) {
   const int tid = threadIdx.x;
   if (tid == 0) {
     s_prefix = 0;
@@ -161,12 +159,61 @@ __global__ void __launch_bounds__(1024) radix_select_small_kernel(KeySrc src, in
     }
     __syncthreads();
   }
-  if (tid == 0) {
+}
+
+__global__ void __launch_bounds__(1024) radix_select_small_kernel(KeySrc src, int n, unsigned long long B, int passes,
+                                                                  SelectState *st) {
+  __shared__ unsigned int sh[2048];
+  __shared__ unsigned int part[256];
+  __shared__ unsigned long long s_prefix, s_remaining;
+  radix_select_cta(src, n, B, passes, sh, part, s_prefix, s_remaining);
+  if (threadIdx.x == 0) {
     st->prefix = s_prefix;
     st->remaining = s_remaining;
     st->ticket = 0;
     st->out_count = 0;
   }
+}
+
+// Whole top-B of a small source in one launch: select the B-th key, gather the B keys >= it into shared
+// memory, bitonic-sort them descending, write them out (B <= npad <= 4096).
+__global__ void __launch_bounds__(1024) topk_small_kernel(KeySrc src, int n, int B, int npad, uint64_t *__restrict__ out) {
+  __shared__ unsigned int sh[2048];
+  __shared__ unsigned int part[256];
+  __shared__ unsigned long long s_prefix, s_remaining;
+  __shared__ unsigned int s_count;
+  __shared__ uint64_t sk[4096];
+  const int tid = threadIdx.x;
+  if (tid == 0) s_count = 0;
+  radix_select_cta(src, n, (unsigned long long)B, 6, sh, part, s_prefix, s_remaining);
+  const unsigned long long thr = s_prefix;
+  for (int i = tid; i < npad; i += 1024) sk[i] = 0ull;
+  __syncthreads();
+  for (int i = tid; i < n; i += 1024) {
+    const uint64_t key = load_key(src, i);
+    if (key >= thr) {
+      const unsigned int pos = atomicAdd(&s_count, 1u);
+      if (pos < (unsigned)B) sk[pos] = key;
+    }
+  }
+  __syncthreads();
+  for (int k = 2; k <= npad; k <<= 1) {
+    for (int j = k >> 1; j > 0; j >>= 1) {
+      for (int i = tid; i < npad; i += 1024) {
+        const int ixj = i ^ j;
+        if (ixj > i) {
+          const uint64_t a = sk[i], b = sk[ixj];
+          const bool desc = (i & k) == 0;
+          if (desc ? (a < b) : (a > b)) {
+            sk[i] = b;
+            sk[ixj] = a;
+          }
+        }
+      }
+      __syncthreads();
+    }
+  }
+  for (int i = tid; i < B; i += 1024) out[i] = sk[i];
 }
 
 // keys >= threshold (st->prefix after the last pass) -> out (exactly B of them, unordered)
@@ -275,6 +322,11 @@ static int topk_device(alink_ctx *ctx, const KeySrc &src, int64_t n, int64_t B) 
   ALINK_TRY(dev_reserve(ctx, ctx->sel_keys, sizeof(uint64_t) * (size_t)npad));
   SelectState *st = (SelectState *)ctx->sel_state.p;
   uint64_t *out = (uint64_t *)ctx->sel_keys.p;
+  if (n <= SELECT_SMALL_N && npad <= 4096) {
+    topk_small_kernel<<<1, 1024, 0, ctx->stream>>>(src, (int)n, (int)B, (int)(npad < 2 ? 2 : npad), out);
+    ALINK_LAUNCHED(ctx);
+    return ALINK_OK;
+  }
   ALINK_TRY(select_threshold(ctx, src, n, B, st));
   int64_t blocks = (n + 256 * 8 - 1) / (256 * 8);
   const int64_t cap = (int64_t)ctx->sm_count * 8;
