@@ -17,4 +17,4 @@ except Exception as e: print('$name FAILED', e)
 run scale_n8
 run target_bf16_n8 --mode bf16 --pairs 1250000
 run target_refine_n8 --pairs 1250000
-run cfg3_n8 --config 3 --mode bf16
+[ -n "$SKIP_CFG3" ] || run cfg3_n8 --config 3 --mode bf16
