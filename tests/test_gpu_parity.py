@@ -80,7 +80,11 @@ def test_smallres_widths_and_d2048(ctx, oracle):
     np.testing.assert_array_equal(per.view(np.uint32), ref["per_learner"].view(np.uint32))
 
 
-@pytest.mark.parametrize("n,B", [(1, 1), (5, 5), (1000, 1), (4097, 4096), (100000, 1000), (300000, 5000)])
+@pytest.mark.parametrize("n,B", [(1, 1), (5, 5), (1000, 1), (4097, 4096), (100000, 1000), (300000, 5000),
+                                 # the one-CTA paths (topk.cuh SELECT_SMALL_N = 32768, shared-memory sort up to 4096 keys)
+                                 # and their boundaries: fused top-B, small select + global sort, multi-CTA select
+                                 (2, 1), (3, 2), (10000, 1000), (32768, 4096), (32768, 32768), (20000, 5000),
+                                 (32769, 4096), (32769, 1)])
 def test_topk_values(ctx, oracle, n, B):
     rng = np.random.default_rng(n + B)
     v = rng.standard_normal(n).astype(np.float32)
@@ -95,8 +99,9 @@ def test_topk_values(ctx, oracle, n, B):
     np.testing.assert_array_equal(util, rutil)
 
 
-def test_topk_all_tied_picks_lowest_indices(ctx):
-    v = np.full(50000, 0.673012, np.float32)  # vote-entropy style plateau
+@pytest.mark.parametrize("n", [50000, 9000])  # multi-CTA passes / the one-CTA kernel
+def test_topk_all_tied_picks_lowest_indices(ctx, n):
+    v = np.full(n, 0.673012, np.float32)  # vote-entropy style plateau
     idx, _, _ = ctx.topk_values(v, 1000)
     np.testing.assert_array_equal(idx, np.arange(1000))
 
