@@ -41,6 +41,10 @@ class Committee(BaseCommittee):
         self.classes_ = np.unique(np.concatenate(known, axis=0), axis=0)
         self.n_classes_ = len(self.classes_)
 
+    def _add_training_data(self, X, y):  # code/learners.py:311-313
+        super()._add_training_data(X, y)
+        self._set_classes()
+
     def _widened(self, X):
         specs = self._alink_specs()
         if specs is None:

@@ -80,7 +80,17 @@ class SiameseNetwork:
         return [self._spec]
 
     # ---- the finetune ("teach") step on the selected pairs
-    def finetune(self, X, Y, epochs, batch_size, verbose=1, validation_split=0.2):
+    def fit(self, x, y, batch_size=32, epochs=1, verbose=1, validation_split=0.0, shuffle=True, **ignored):
+        """Keras `Model.fit` on the head, as `KerasClassifier.fit` / `ActiveLearner.teach` reach it
+        (code/keras_wrapper.py:139-165, code/base.py:107-128; e.g. `learner.teach(X=..., y=..., only_new=True,
+        verbose=1, epochs=2, validation_split=0.1)`, code/existing_al.py:111-117): Keras defaults (batch 32, one
+        epoch, no hold-out), no callbacks. `y`: class indices, an (N,1) column or one-hot rows."""
+        y = np.asarray(y)
+        if y.ndim == 2 and y.shape[1] > 1:
+            y = np.argmax(y, axis=1)
+        return self.finetune(x, y, epochs, batch_size, verbose, validation_split, _callbacks=False)
+
+    def finetune(self, X, Y, epochs, batch_size, verbose=1, validation_split=0.2, _callbacks=True):
         """code/siamese.py:52-58: Keras `fit(X, to_categorical(Y), batch_size, epochs, validation_split=0.2,
         callbacks=[EarlyStopping('val_loss', min_delta=0.1, patience=5), ReduceLROnPlateau('val_loss', factor=0.2,
         patience=5, min_lr=0.01)])` with Adadelta(self.learningRate) and binary cross-entropy. [external: Keras 2.1.2
@@ -128,7 +138,7 @@ class SiameseNetwork:
                 hist[k].append(v)
             if verbose:
                 print("Epoch %d/%d - loss: %.4f - acc: %.4f - val_loss: %.4f - val_acc: %.4f" % (epoch + 1, epochs, tl, ta, vl, va))
-            if len(va_idx):
+            if len(va_idx) and _callbacks:
                 # EarlyStopping(monitor='val_loss', min_delta=0.1, patience=5)
                 if vl + 0.1 < es_best:
                     es_best, es_wait = vl, 0

@@ -127,3 +127,53 @@ def test_finetune_like_alink_driver(ctx, oracle):
     assert out.shape == (32, 2) and np.allclose(out.sum(1), 1, atol=1e-6)
     acc = model.testAccuracy(pool.table[:40], np.arange(40) // 4)
     assert 0.0 <= acc <= 1.0
+
+
+@pytest.mark.gpu
+def test_teach_runs_the_finetune_step_like_existing_al():
+    """`learner.query(...)` then `learner.teach(X=..., y=..., only_new=True, verbose=1, epochs=2,
+    validation_split=0.1)` exactly as /root/reference/code/existing_al.py:95-117 calls them: teach ==
+    KerasClassifier.fit == Keras `Model.fit` (batch 32, no callbacks) on the head, bit-identical to driving
+    `finetune`'s step loop by hand with the same shuffles; the known-data bookkeeping follows code/base.py:62-84."""
+    from alink_b200 import engine, siamese, synth, uncertainty
+    from alink_b200.keras_wrapper import KerasClassifier
+    from alink_b200.learners import ActiveLearner, Committee
+    engine.set_compute_mode("fp32")
+    pool = synth.make_pool(1, N=400)
+    XL, XR = pool.table[pool.ia], pool.table[pool.ib]
+    Y = pool.genuine.astype(np.int64).reshape(-1, 1)
+
+    def build(seed_name):
+        net = siamese.SiameseNetwork((pool.D,), seed_name, 0.1)
+        net.set_weights(*pool.heads.learner(0))
+        return net
+
+    net, twin = build("a"), build("b")
+    learner = ActiveLearner(estimator=KerasClassifier(lambda: net), query_strategy=uncertainty.uncertainty_sampling, verbose=1)
+    idx, inst = learner.query([XL, XR], n_instances=100, verbose=0)
+    assert len(idx) == 100 and learner.X_training is None
+    np.random.seed(11)
+    learner.teach(X=[XL[idx], XR[idx]], y=Y[idx], only_new=True, verbose=0, epochs=2, validation_split=0.1)
+    assert learner.estimator.classes_.tolist() == [0, 1]
+    assert len(learner.X_training[0]) == 100 and len(learner.y_training) == 100
+    np.random.seed(11)
+    twin.finetune([XL[idx], XR[idx]], Y[idx], 2, 32, verbose=0, validation_split=0.1, _callbacks=False)
+    for a, b in zip(net.get_weights(), twin.get_weights()):
+        np.testing.assert_array_equal(a.view(np.uint32), b.view(np.uint32))
+    assert any(not np.array_equal(a, b) for a, b in zip(net.get_weights(), pool.heads.learner(0)))  # it did train
+    # a second batch of another size: each side is stacked with itself (base.py docstring)
+    learner.teach(X=[XL[:37], XR[:37]], y=Y[:37], only_new=True, verbose=0)
+    assert learner.X_training[0].shape == (137, pool.D) and learner.X_training[1].shape == (137, pool.D)
+    assert 0.0 <= learner.score([XL, XR], Y) <= 1.0
+    with pytest.raises(ValueError, match="inconsistent numbers of samples"):
+        learner.teach(X=[XL[:5], XR[:5]], y=Y[:4])
+    # committee: every learner is taught; rebag refits each on its own bootstrap of the known data
+    nets = [build("c"), build("d")]
+    com = Committee([ActiveLearner(KerasClassifier(lambda n=n: n)) for n in nets])
+    com.teach([XL[:64], XR[:64]], Y[:64], verbose=0)
+    assert com.classes_.tolist() == [0, 1]
+    np.random.seed(3)
+    com.rebag(verbose=0)
+    assert not np.array_equal(nets[0].get_weights()[0], nets[1].get_weights()[0])  # different bootstraps
+    p = com.predict_proba([XL, XR])
+    assert p.shape == (400, 2)
