@@ -20,9 +20,12 @@ this image, so this module is a small reader (and writer) of the subset of the H
     messages v1/v2/v3.
 
 Chunked or filtered datasets, v2 object headers and link-message groups (libver="latest") raise
-`H5FormatError` naming the feature. PARITY NOTE: no real Keras/h5py-written file exists in this image to pin
-the reader against; it is tested against files produced by `write_keras_weights` below (which follows the
-same specification, in several structural variants). Treat cross-library compatibility as unverified.
+`H5FormatError` naming the feature (data layout messages v1/v2 of libhdf5 <= 1.6 are read too). PARITY NOTE: the
+reader is pinned against ONE file written by a real libhdf5 (tests/golden/libhdf5_written_testdouble.mat, SciPy's
+MATLAB-7.3 fixture: user block, symbol-table group, v1 object header, float dataset, string attribute). No
+Keras/h5py-written file exists in this image: the Keras tree layout is restated from Keras 2.1.2 and round-trips
+only against `write_keras_weights` below (same specification, many structural variants), so cross-library
+compatibility of the WRITER is unverified.
 """
 from __future__ import annotations
 
@@ -514,7 +517,7 @@ class _Writer:
         return off
 
     def dataset(self, arr):
-        arr = np.ascontiguousarray(arr)
+        arr = np.asarray(arr, order="C")  # (ascontiguousarray would turn a 0-d array into shape (1,))
         raw = arr.astype(arr.dtype.newbyteorder("<")).tobytes()
         if self.compact:
             layout = struct.pack("<BBH", 3, 0, len(raw)) + raw

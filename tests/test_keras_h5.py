@@ -119,3 +119,36 @@ def test_shim_save_and_maybe_load(tmp_path, mod):
     np.testing.assert_array_equal(net3.get_weights()[4], W[4])
     net.save(customName=str(tmp_path / "other"))
     assert os.path.exists(str(tmp_path / "other.h5"))
+
+
+def test_property_random_trees_and_dtypes(tmp_path):
+    """hypothesis: random layer lists, weight shapes (rank 0-4, empty dims) and dtypes round-trip bit for bit
+    in every writer variant."""
+    from hypothesis import given, settings, strategies as st
+
+    dtypes = st.sampled_from([np.float32, np.float64, np.float16, np.int32, np.int64, np.uint8])
+    shape = st.lists(st.integers(0, 5), min_size=0, max_size=4).map(tuple)
+    weight = st.tuples(shape, dtypes)
+    layer = st.lists(weight, min_size=0, max_size=3)
+    p = str(tmp_path / "h.h5")
+
+    @settings(max_examples=40, deadline=None)
+    @given(layers=st.lists(layer, min_size=1, max_size=12), av=st.sampled_from([1, 2, 3]), sv=st.sampled_from([1, 2]),
+           cont=st.booleans(), comp=st.booleans(), vl=st.booleans(), sb=st.sampled_from([0, 1, 2]), seed=st.integers(0, 99))
+    def check(layers, av, sv, cont, comp, vl, sb, seed):
+        rng = np.random.default_rng(seed)
+        L = []
+        for i, ws in enumerate(layers):
+            name = f"layer_{i}"
+            L.append((name, [(f"{name}/w{j}:0", (rng.standard_normal(s) * 50).astype(dt)) for j, (s, dt) in enumerate(ws)]))
+        kh.write_keras_weights(p, L, attr_version=av, space_version=sv, continuation=cont, compact=comp,
+                               vlen_names=vl, superblock=sb)
+        got = kh.read_keras_weights(p)
+        assert [n for n, _ in got] == [n for n, _ in L]
+        for (_, w), (_, w2) in zip(L, got):
+            assert [n for n, _ in w] == [n for n, _ in w2]
+            for (_, a), (_, b) in zip(w, w2):
+                assert a.dtype == b.dtype and a.shape == b.shape
+                assert a.tobytes() == b.tobytes()
+
+    check()

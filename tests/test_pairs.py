@@ -75,3 +75,30 @@ def test_pool_scores_equal_materialised_scores():
     pool2, Y2 = pairs.createMiniBatch(P)
     X2, _ = ref_numpy.create_mini_batch_mtp(P)
     np.testing.assert_array_equal(nets[0].predict(pool2), nets[0].predict(X2))
+
+
+def test_property_random_ragged_groups():
+    """hypothesis: any ragged group sizes (zeros included) give the loops' order."""
+    from hypothesis import given, settings, strategies as st
+
+    sizes = st.lists(st.integers(0, 4), min_size=1, max_size=5)
+
+    @settings(max_examples=60, deadline=None)
+    @given(ps=sizes, ds=sizes)
+    def check(ps, ds):
+        rng = np.random.default_rng(1)
+        P, G = _groups(rng, ps, 3), _groups(rng, ds, 3)
+        total = sum(ps) * sum(ds) + sum(ds) ** 2
+        if total == 0:
+            with pytest.raises(ValueError):
+                pairs.pair_indices_dfw(ps, ds)
+            return
+        (XL, XR), Y = ref_numpy.create_mini_batch_dfw(P, G)
+        ia, ib, y = pairs.pair_indices_dfw(ps, ds)
+        L, R = pairs.materialise(np.concatenate(P + G), ia, ib)
+        assert len(ia) == total
+        np.testing.assert_array_equal(L, XL)
+        np.testing.assert_array_equal(R, XR)
+        np.testing.assert_array_equal(y, Y)
+
+    check()
