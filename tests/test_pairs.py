@@ -102,3 +102,18 @@ def test_property_random_ragged_groups():
         np.testing.assert_array_equal(y, Y)
 
     check()
+
+
+def test_split_disguise_data_like_reference():
+    """code/readDFW.py:212-219."""
+    from alink_b200 import readDFW
+    rng = np.random.default_rng(0)
+    G = _groups(rng, [5, 1, 4, 0])
+    pre, post = readDFW.splitDisguiseData(G, pre_ratio=0.5)
+    assert [len(g) for g in pre] == [2, 0, 2, 0] and [len(g) for g in post] == [3, 1, 2, 0]
+    for g, a, b in zip(G, pre, post):
+        np.testing.assert_array_equal(np.concatenate([a, b]), g)
+    import inspect
+    from alink_b200 import readMTP
+    assert list(inspect.signature(readDFW.createMiniBatch).parameters)[:2] == ["X_plain", "X_dig"]
+    assert list(inspect.signature(readMTP.createMiniBatch).parameters)[:1] == ["X_plain"]
