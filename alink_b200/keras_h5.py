@@ -16,10 +16,10 @@ this image, so this module is a small reader (and writer) of the subset of the H
 
     superblock v0/v1 (v2/v3 accepted), symbol-table groups (B-tree v1 + local heap + SNOD), version-1
     object headers with continuation blocks, dataspace v1/v2, datatypes: fixed-point, IEEE float, fixed-
-    length strings, variable-length strings (global heap), data layout v3 compact/contiguous, attribute
-    messages v1/v2/v3.
+    length strings, variable-length strings (global heap), data layout v3 compact / contiguous / chunked
+    without filters (v1 chunk B-tree), attribute messages v1/v2/v3.
 
-Chunked or filtered datasets, v2 object headers and link-message groups (libver="latest") raise
+Filtered (compressed) datasets, v2 object headers and link-message groups (libver="latest") raise
 `H5FormatError` naming the feature (data layout messages v1/v2 of libhdf5 <= 1.6 are read too). PARITY NOTE: the
 reader is pinned against ONE file written by a real libhdf5 (tests/golden/libhdf5_written_testdouble.mat, SciPy's
 MATLAB-7.3 fixture: user block, symbol-table group, v1 object header, float dataset, string attribute). No
@@ -347,9 +347,49 @@ class H5File:
                 if size < n * t.size:
                     raise H5FormatError("contiguous dataset shorter than its dataspace")
                 raw = self._bytes(addr + self.base, n * t.size)
+        elif cls == 2:
+            ndim = self._u(p + 2, 1)  # rank + 1: the last "dimension" is the element size
+            btree = self._u(p + 3, self.O)
+            cdims = tuple(self._u(p + 3 + self.O + 4 * i, 4) for i in range(ndim - 1))
+            if len(cdims) != len(shape):
+                raise H5FormatError("chunk rank differs from the dataspace rank")
+            raw = self._chunked(btree, shape, cdims, t)
         else:
-            raise H5FormatError("chunked datasets not supported")
+            raise H5FormatError(f"data layout class {cls} not supported")
         return self._decode(raw, shape, t)
+
+    def _chunked(self, btree, shape, cdims, t):
+        """Unfiltered chunked storage: walk the version-1 B-tree (node type 1) and paste every chunk (stored at
+        its full chunk size, cropped at the dataset's edges) into a zero-filled array."""
+        out = np.zeros(shape, dtype=np.dtype(f"V{t.size}"))
+        csize = int(np.prod(cdims, dtype=np.int64)) * t.size
+        rank = len(shape)
+
+        def node(addr):
+            a = addr + self.base
+            if self._bytes(a, 4) != b"TREE" or self._u(a + 4, 1) != 1:
+                raise H5FormatError(f"expected a chunk B-tree node at {addr}")
+            level, used = self._u(a + 5, 1), self._u(a + 6, 2)
+            q = a + 8 + 2 * self.O
+            klen = 8 + 8 * (rank + 1)
+            for i in range(used):
+                k = q + i * (klen + self.O)
+                nbytes, fmask = self._u(k, 4), self._u(k + 4, 4)
+                off = tuple(self._u(k + 8 + 8 * d, 8) for d in range(rank))
+                child = self._u(k + klen, self.O)
+                if level > 0:
+                    node(child)
+                    continue
+                if fmask or nbytes != csize:
+                    raise H5FormatError("filtered (compressed) chunks not supported")
+                chunk = np.frombuffer(self._bytes(child + self.base, csize), dtype=out.dtype).reshape(cdims)
+                sl_out = tuple(slice(o, min(o + c, s)) for o, c, s in zip(off, cdims, shape))
+                sl_in = tuple(slice(0, s.stop - s.start) for s in sl_out)
+                out[sl_out] = chunk[sl_in]
+
+        if btree != UNDEF and out.size:
+            node(btree)
+        return out.tobytes()
 
 
 def _names(attr):
@@ -407,10 +447,11 @@ class _Writer:
     LEAF_K, INTERNAL_K = 4, 16
 
     def __init__(self, attr_version=1, space_version=1, continuation=False, compact=False, vlen_names=False,
-                 superblock=0):
+                 superblock=0, chunks=None):
         self.buf = bytearray()
         self.av, self.sv, self.cont, self.compact, self.vlen, self.sb = (
             attr_version, space_version, continuation, compact, vlen_names, superblock)
+        self.chunks = chunks  # e.g. 3: every dataset of rank >= 1 is stored in chunks of (up to) 3 per dimension
         self.gheap = []  # variable-length string payloads, written as one global heap collection at the end
         self.gheap_fix = []
 
@@ -519,13 +560,40 @@ class _Writer:
     def dataset(self, arr):
         arr = np.asarray(arr, order="C")  # (ascontiguousarray would turn a 0-d array into shape (1,))
         raw = arr.astype(arr.dtype.newbyteorder("<")).tobytes()
-        if self.compact:
+        if self.chunks and arr.ndim >= 1 and arr.size:
+            layout = self.chunked_layout(arr)
+        elif self.compact:
             layout = struct.pack("<BBH", 3, 0, len(raw)) + raw
         else:
             layout = struct.pack("<BBQQ", 3, 1, self.alloc(raw) if raw else UNDEF, len(raw))
         fill = struct.pack("<BBBB", 2, 2, 2, 0)
         return self.place([(0x01, self.m_space(arr.shape)), (0x03, self.m_type(arr.dtype)), (0x05, fill),
                            (0x08, layout)])
+
+    def chunked_layout(self, arr):
+        import itertools
+        cd = tuple(min(self.chunks, d) for d in arr.shape)
+        rank, es = arr.ndim, arr.dtype.itemsize
+        csize = int(np.prod(cd)) * es
+        entries = []
+        for off in itertools.product(*[range(0, d, c) for d, c in zip(arr.shape, cd)]):
+            chunk = np.zeros(cd, arr.dtype)
+            sl = tuple(slice(o, min(o + c, d)) for o, c, d in zip(off, cd, arr.shape))
+            chunk[tuple(slice(0, s.stop - s.start) for s in sl)] = arr[sl]
+            entries.append((off, self.alloc(chunk.astype(arr.dtype.newbyteorder("<")).tobytes())))
+        if len(entries) > 64:
+            raise ValueError("too many chunks for a one-level chunk B-tree")
+
+        def key(off, nbytes):
+            return struct.pack("<II", nbytes, 0) + b"".join(struct.pack("<Q", o) for o in off) + struct.pack("<Q", 0)
+
+        node = b"TREE" + struct.pack("<BBHQQ", 1, 0, len(entries), UNDEF, UNDEF)
+        for off, addr in entries:
+            node += key(off, csize) + struct.pack("<Q", addr)
+        node += key(arr.shape, 0)  # the closing key: one past the last chunk
+        btree = self.alloc(node)
+        return struct.pack("<BBB", 3, 2, rank + 1) + struct.pack("<Q", btree) + b"".join(
+            struct.pack("<I", c) for c in cd) + struct.pack("<I", es)
 
     def group(self, children, attrs):
         """children: {name: object-header address} -> (object header address, btree, heap)."""

@@ -134,15 +134,16 @@ def test_property_random_trees_and_dtypes(tmp_path):
 
     @settings(max_examples=40, deadline=None)
     @given(layers=st.lists(layer, min_size=1, max_size=12), av=st.sampled_from([1, 2, 3]), sv=st.sampled_from([1, 2]),
-           cont=st.booleans(), comp=st.booleans(), vl=st.booleans(), sb=st.sampled_from([0, 1, 2]), seed=st.integers(0, 99))
-    def check(layers, av, sv, cont, comp, vl, sb, seed):
+           cont=st.booleans(), comp=st.booleans(), vl=st.booleans(), sb=st.sampled_from([0, 1, 2]), seed=st.integers(0, 99),
+           chunks=st.sampled_from([None, None, 2, 3]))
+    def check(layers, av, sv, cont, comp, vl, sb, seed, chunks):
         rng = np.random.default_rng(seed)
         L = []
         for i, ws in enumerate(layers):
             name = f"layer_{i}"
             L.append((name, [(f"{name}/w{j}:0", (rng.standard_normal(s) * 50).astype(dt)) for j, (s, dt) in enumerate(ws)]))
         kh.write_keras_weights(p, L, attr_version=av, space_version=sv, continuation=cont, compact=comp,
-                               vlen_names=vl, superblock=sb)
+                               vlen_names=vl, superblock=sb, chunks=chunks)
         got = kh.read_keras_weights(p)
         assert [n for n, _ in got] == [n for n, _ in L]
         for (_, w), (_, w2) in zip(L, got):
@@ -152,3 +153,12 @@ def test_property_random_trees_and_dtypes(tmp_path):
                 assert a.tobytes() == b.tobytes()
 
     check()
+
+
+def test_chunked_unfiltered_datasets(tmp_path):
+    arrs = _head(np.random.default_rng(4), 13, 7, 5, 2)
+    layers = [(f"dense_{i}", [(f"dense_{i}/kernel:0", arrs[2 * i - 2]), (f"dense_{i}/bias:0", arrs[2 * i - 1])]) for i in (1, 2, 3)]
+    p = str(tmp_path / "c.h5")
+    kh.write_keras_weights(p, layers, chunks=4)  # 13 x 7 in 4 x 4 chunks: edge chunks are cropped
+    for a, b in zip(arrs, kh.load_head_weights(p, 13, 7, 5, 2)):
+        np.testing.assert_array_equal(a, b)
