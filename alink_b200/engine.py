@@ -8,6 +8,8 @@ Responsibilities (all thin; the arithmetic lives in csrc/):
 """
 from __future__ import annotations
 
+import itertools
+import weakref
 from dataclasses import dataclass
 from typing import List, Optional, Sequence
 
@@ -29,10 +31,14 @@ def get_compute_mode() -> int:
     return _COMPUTE["mode"]
 
 
+_UIDS = itertools.count(1)  # process-unique tokens: id() of a freed object is reused by CPython
+
+
 class HeadSpec:
     """Weights of one learner in Keras layout (what SiameseNetwork owns)."""
 
     def __init__(self, D_in, H1, H2, C, act, feat_mode=0):
+        self.uid = next(_UIDS)
         self.D_in, self.H1, self.H2, self.C, self.act, self.feat_mode = D_in, H1, H2, C, act, feat_mode
         self.W1 = self.b1 = self.W2 = self.b2 = self.W3 = self.b3 = None
         self.version = 0
@@ -73,11 +79,16 @@ class _GroupCache:
     def invalidate_all(cls):
         cls._by_ctx.clear()
 
+    @staticmethod
+    def key_of(specs: Sequence[HeadSpec]):
+        """(uid, version) per learner + the compute mode: uids are never reused, unlike id()."""
+        return tuple((s.uid, s.version) for s in specs) + (_COMPUTE["mode"],)
+
     @classmethod
     def group_for(cls, ctx: _ffi.Context, specs: Sequence[HeadSpec]) -> int:
         ngroups = 4
-        st = cls._by_ctx.setdefault(id(ctx), {"keys": [None] * ngroups, "clock": 0, "used": [0] * ngroups})
-        key = tuple((id(s), s.version) for s in specs) + (_COMPUTE["mode"],)
+        st = cls._by_ctx.setdefault(_ctx_uid(ctx), {"keys": [None] * ngroups, "clock": 0, "used": [0] * ngroups})
+        key = cls.key_of(specs)
         st["clock"] += 1
         if key in st["keys"]:
             g = st["keys"].index(key)
@@ -97,6 +108,16 @@ class _GroupCache:
         st["keys"][g] = key
         st["used"][g] = st["clock"]
         return g
+
+
+def _ctx_uid(ctx) -> int:
+    """A process-unique token per context object (dropped from the cache when the context is collected)."""
+    uid = getattr(ctx, "_alink_uid", None)
+    if uid is None:
+        uid = next(_UIDS)
+        ctx._alink_uid = uid
+        weakref.finalize(ctx, _GroupCache._by_ctx.pop, uid, None)
+    return uid
 
 
 def _as_pair(X):
@@ -119,14 +140,42 @@ class PairPool:
     (code/readDFW.py:222-244, utilities/generateMatrixDFW.py:28-33). Tables / indices may be numpy
     arrays (copied to the GPU once, here) or torch CUDA tensors (borrowed)."""
 
-    _next_slot = 0
+    # Table slots 0 .. POOL_SLOTS-1 belong to pools; MAX_SLOTS-3 is reserved for testAccuracy / score_matrix and
+    # MAX_SLOTS-2 / -1 for the dense [X_left, X_right] staging (alink_score_dense). A slot is owned by ONE live pool:
+    # asking for more pools than there are slots raises instead of silently overwriting a live pool's table.
+    POOL_SLOTS = _ffi.MAX_SLOTS - 3
+    _owners = {}  # context uid -> [weakref to the owning PairPool or None] * POOL_SLOTS
+
+    @classmethod
+    def _claim(cls, ctx, pool, n):
+        own = cls._owners.setdefault(_ctx_uid(ctx), [None] * cls.POOL_SLOTS)
+        free = [i for i, w in enumerate(own) if w is None or w() is None]
+        if len(free) < n:
+            raise _ffi.AlinkError(f"no free embedding-table slot: {cls.POOL_SLOTS} pool slots per context are all owned "
+                                  "by live PairPools (close() or drop one first)")
+        for i in free[:n]:
+            own[i] = weakref.ref(pool)
+        return free[:n]
+
+    def close(self):
+        """Give the pool's table slots back (also happens when the pool is garbage-collected)."""
+        own = PairPool._owners.get(getattr(self.ctx, "_alink_uid", None))
+        if own is not None:
+            for i, w in enumerate(own):
+                if w is not None and w() is self:
+                    own[i] = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
 
     def __init__(self, table_a, ia, ib, table_b=None, ctx: Optional[_ffi.Context] = None, slots=None):
         self.ctx = ctx or _ffi.default_context()
         if slots is None:
-            s = PairPool._next_slot
-            PairPool._next_slot = (s + 2) % (_ffi.MAX_SLOTS - 2)
-            slots = (s, s + 1)
+            got = PairPool._claim(self.ctx, self, 1 if table_b is None else 2)
+            slots = (got[0], got[-1])
         self.slot_a, self.slot_b = slots
         self.ctx.set_table(self.slot_a, table_a)
         if table_b is None:

@@ -8,7 +8,7 @@
         .predict(X)       (N,)      classes_[argmax]                             :316-332
 
 One fused GPU call scores all K learners; the float64 containers the reference builds with
-`np.zeros` are kept (dtype only — the values are the fp32 scores). BayesianOptimizer and
+`np.zeros` are kept (the per-learner values are the fp32 scores; `predict_proba` is their float64 mean, :345). BayesianOptimizer and
 CommitteeRegressor (regression / training, no driver uses them) are out of scope.
 """
 from __future__ import annotations
@@ -60,8 +60,9 @@ class Committee(BaseCommittee):
         return per.astype(np.float64)
 
     def predict_proba(self, X, **predict_proba_kwargs):
-        _, cons = self._widened(X)
-        return cons.astype(np.float64)
+        # code/learners.py:345: np.mean over the float64 (N, K, C) container — a float64 mean of the fp32 scores,
+        # not the fp32 Bagging mean of committee.py:18 (they differ by up to one fp32 ulp)
+        return np.mean(self.vote_proba(X, **predict_proba_kwargs), axis=1)
 
     def vote(self, X, **predict_kwargs):
         per, _ = self._widened(X)
