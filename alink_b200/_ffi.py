@@ -40,6 +40,7 @@ SYMBOLS = (
     "alink_set_refine_eps", "alink_refine_stats", "alink_refine_detail", "alink_score_allpairs", "alink_query_allpairs",
     "alink_disparity_hist", "alink_disparity_select_sharded", "alink_roc_counts",
     "alink_train_step", "alink_get_train_state", "alink_set_train_state",
+    "alink_set_refine_eps2", "alink_refine_report_get",
 )
 
 
@@ -54,6 +55,16 @@ class Timing(C.Structure):
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}
+
+
+class RefineReport(C.Structure):
+    _fields_ = [("version", C.c_int32), ("filter_f16", C.c_int32), ("rounds", C.c_int32), ("reserved", C.c_int32),
+                ("n_stage2", C.c_int64), ("n_exact", C.c_int64), ("n_sample", C.c_int64), ("n_sample_exact", C.c_int64),
+                ("eps1_used", C.c_double), ("eps1_apriori", C.c_double), ("eps2_used", C.c_double), ("eps1_worst", C.c_double),
+                ("err1_max", C.c_float), ("err1_rms", C.c_float), ("err2_max", C.c_float), ("err2_rms", C.c_float)]
+
+    def as_dict(self):
+        return {k: getattr(self, k) for k, _ in self._fields_ if k != "reserved"}
 
 
 _lib = None
@@ -140,6 +151,10 @@ def load():
                                                  C.POINTER(i64), C.POINTER(i64)]
     L.alink_refine_detail.restype = i32
     L.alink_refine_detail.argtypes = [vp, C.POINTER(C.c_int), C.POINTER(dbl), C.POINTER(C.c_float), C.POINTER(C.c_int)]
+    L.alink_set_refine_eps2.restype = i32
+    L.alink_set_refine_eps2.argtypes = [vp, dbl]
+    L.alink_refine_report_get.restype = i32
+    L.alink_refine_report_get.argtypes = [vp, C.POINTER(RefineReport)]
     _lib = L
     return L
 
@@ -462,6 +477,15 @@ class Context:
 
     def set_refine_eps(self, eps):
         self._check(self._L.alink_set_refine_eps(self._h, float(eps)))
+
+    def set_refine_eps2(self, eps2):
+        self._check(self._L.alink_set_refine_eps2(self._h, C.c_double(float(eps2))))
+
+    def refine_report(self):
+        """dict of what the last FP32_REFINE query did (include/alink_b200.h: alink_refine_report)."""
+        r = RefineReport()
+        self._check(self._L.alink_refine_report_get(self._h, C.byref(r)))
+        return r.as_dict()
 
     def refine_stats(self):
         """(candidates re-scored exactly, max |approx - exact| utility among them) of the last query."""

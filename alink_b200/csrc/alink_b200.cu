@@ -8,6 +8,7 @@
 #include "utility.cuh"
 #include "topk.cuh"
 #include "disparity.cuh"
+#include "head_tc_split.cuh"
 #include "refine.cuh"
 #include "roc.cuh"
 #include "train.cuh"
@@ -54,7 +55,7 @@ int alink_create(alink_ctx **out, int device, unsigned flags) {
 }
 
 static void free_group(HeadGroup &g) {
-  void *ptrs[] = {g.W1, g.b1, g.W2, g.b2, g.W3, g.b3, (void *)g.pW1, g.W1t, g.W2t, g.W1h, g.W2h};
+  void *ptrs[] = {g.W1, g.b1, g.W2, g.b2, g.W3, g.b3, (void *)g.pW1, g.W1t, g.W2t, g.W1h, g.W2h, g.S1hi, g.S1lo, g.S2hi, g.S2lo};
   for (void *p : ptrs)
     if (p) cudaFree(p);
   for (int t = 0; t < 6; ++t) {
@@ -73,8 +74,9 @@ int alink_destroy(alink_ctx *ctx) {
   DevBuf *bufs[] = {&ctx->idx_a, &ctx->idx_b, &ctx->h1ws, &ctx->probs, &ctx->cons, &ctx->util, &ctx->sel_state,
                     &ctx->sel_keys, &ctx->sel_idx, &ctx->sel_util, &ctx->sel_in, &ctx->misc0, &ctx->misc1,
                     &ctx->misc2, &ctx->misc3, &ctx->cand, &ctx->cia, &ctx->cib, &ctx->util_c, &ctx->rstat, &ctx->xscratch,
-                    &ctx->train_ws, &ctx->train_y, &ctx->train_out};
+                    &ctx->train_ws, &ctx->train_y, &ctx->train_out, &ctx->util2, &ctx->cia2, &ctx->cib2, &ctx->map2, &ctx->src2};
   for (DevBuf *b : bufs) dev_release(*b);
+  if (ctx->rs_host) cudaFreeHost(ctx->rs_host);
   for (int i = 0; i < 8; ++i)
     if (ctx->ev[i]) cudaEventDestroy(ctx->ev[i]);
   if (ctx->copy_stream) {
@@ -150,6 +152,7 @@ int alink_set_heads(alink_ctx *ctx, int group, int K, int D_in, int H1, int H2, 
   free_group(g);
   g.K = K; g.D_in = D_in; g.H1 = H1; g.H2 = H2; g.C = C; g.act = out_act; g.feat_mode = feat_mode;
   g.compute = compute;
+  ctx->refine_eps_hint[group] = 0.0;
   ALINK_TRY(upload_stack(ctx, W1, K, (size_t)D_in * H1, &g.W1));
   ALINK_TRY(upload_stack(ctx, b1, K, (size_t)H1, &g.b1));
   ALINK_TRY(upload_stack(ctx, W2, K, (size_t)H1 * H2, &g.W2));
@@ -179,22 +182,78 @@ int alink_set_heads(alink_ctx *ctx, int group, int K, int D_in, int H1, int H2, 
     // shapes the tensor-core head cannot take run fully exact
     g.tc_ok = tc_prepare_heads(ctx, g, 3) == ALINK_OK;
     if (!g.tc_ok) ctx->err[0] = 0;
-    std::vector<double> col((size_t)H1);
+    // weight statistics: the overflow guard of the half-precision filter, the power-of-two scales of the split
+    // stage and the a-priori error model of the filter (refine_apriori_eps)
+    std::vector<double> col((size_t)H1), col2((size_t)H1), v((size_t)H1), t((size_t)D_in);
     for (int k = 0; k < K; ++k) {
       std::fill(col.begin(), col.end(), 0.0);
+      std::fill(col2.begin(), col2.end(), 0.0);
       for (int i = 0; i < D_in; ++i) {
         const float *row = W1[k] + (size_t)i * H1;
-        for (int j = 0; j < H1; ++j) col[j] += fabs((double)row[j]);
+        for (int j = 0; j < H1; ++j) {
+          const double w = fabs((double)row[j]);
+          col[j] += w;
+          col2[j] += w * w;
+          if (!(w <= g.w1_absmax)) g.w1_absmax = w;
+        }
       }
+      double b1ss = 0.0;
       for (int j = 0; j < H1; ++j) {
         if (!(col[j] <= g.w1_col_l1)) g.w1_col_l1 = col[j];  // NaN-propagating max
+        const double c2 = sqrt(col2[j]);
+        if (!(c2 <= g.w1_col_l2)) g.w1_col_l2 = c2;
         const double b = fabs((double)b1[k][j]);
         if (!(b <= g.b1_absmax)) g.b1_absmax = b;
+        b1ss += b * b;
       }
-      for (size_t i = 0; i < (size_t)H1 * H2; ++i) {
-        const double w = fabs((double)W2[k][i]);
-        if (!(w <= g.w_absmax)) g.w_absmax = w;
+      if (!(sqrt(b1ss) <= g.b1_l2)) g.b1_l2 = sqrt(b1ss);
+      std::vector<double> c22((size_t)H2, 0.0);
+      for (int i = 0; i < H1; ++i)
+        for (int j = 0; j < H2; ++j) {
+          const double w = fabs((double)W2[k][(size_t)i * H2 + j]);
+          if (!(w <= g.w_absmax)) g.w_absmax = w;
+          c22[j] += w * w;
+        }
+      for (int j = 0; j < H2; ++j)
+        if (!(sqrt(c22[j]) <= g.w2_col_l2)) g.w2_col_l2 = sqrt(c22[j]);
+      double w3ss = 0.0;  // the logit the probability depends on: z1 - z0 (softmax-2) or z (sigmoid-1)
+      for (int j = 0; j < H2; ++j) {
+        const double d = C == 2 ? (double)W3[k][(size_t)j * 2 + 1] - (double)W3[k][(size_t)j * 2] : (double)W3[k][j];
+        w3ss += d * d;
       }
+      if (!(sqrt(w3ss) <= g.w3_gain)) g.w3_gain = sqrt(w3ss);
+      g.w3_gain_ms += w3ss / (double)K;
+      if (!(b1ss / (double)H1 <= g.b1_ms)) g.b1_ms = b1ss / (double)H1;
+      // spectral norm of W1 (D_in x H1) by power iteration on W1^T W1 (it approaches from below: + 10 %)
+      for (int j = 0; j < H1; ++j) v[j] = 1.0 / sqrt((double)H1);
+      double sigma = 0.0;
+      for (int it = 0; it < 12; ++it) {
+        for (int i = 0; i < D_in; ++i) {
+          const float *row = W1[k] + (size_t)i * H1;
+          double acc = 0.0;
+          for (int j = 0; j < H1; ++j) acc += (double)row[j] * v[j];
+          t[i] = acc;
+        }
+        std::fill(v.begin(), v.end(), 0.0);
+        for (int i = 0; i < D_in; ++i) {
+          const float *row = W1[k] + (size_t)i * H1;
+          const double ti = t[i];
+          for (int j = 0; j < H1; ++j) v[j] += (double)row[j] * ti;
+        }
+        double nv = 0.0;
+        for (int j = 0; j < H1; ++j) nv += v[j] * v[j];
+        nv = sqrt(nv);
+        sigma = sqrt(nv);  // ||W^T W v|| -> sigma^2 for unit v
+        if (!(nv > 0.0)) break;
+        for (int j = 0; j < H1; ++j) v[j] /= nv;
+      }
+      sigma *= 1.10;
+      if (!(sigma <= g.w1_spec)) g.w1_spec = sigma;
+    }
+    g.split_ok = false;
+    if (g.tc_ok && split_supported(ctx, g) && g.w1_absmax < 1e30 && g.w_absmax < 1e30) {
+      g.split_ok = split_prepare_heads(ctx, g) == ALINK_OK;
+      if (!g.split_ok) ctx->err[0] = 0;
     }
   }
   ALINK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));  // host_ptrs / caller buffers may go away
@@ -358,7 +417,7 @@ __global__ void __launch_bounds__(256) index_range_kernel(const int32_t *__restr
 
 static int check_indices(alink_ctx *ctx, const int32_t *dia, const int32_t *dib, int64_t N, int slot_a, int slot_b) {
   if (!(ctx->flags & ALINK_FLAG_CHECK_INDICES) || !dia || N <= 0) return ALINK_OK;
-  ALINK_TRY(dev_reserve(ctx, ctx->rstat, 32));
+  ALINK_TRY(dev_reserve(ctx, ctx->rstat, 256));
   unsigned int *d = (unsigned int *)ctx->rstat.p + 6;
   ALINK_CUDA(ctx, cudaMemsetAsync(d, 0, 8, ctx->stream));
   int64_t blocks = (N + 2047) / 2048;
@@ -529,24 +588,33 @@ int alink_topk_keys(alink_ctx *ctx, const uint64_t *keys, int64_t n, int64_t B, 
 // FP32_REFINE (refine.cuh): bf16 tensor-core filter over all N pairs, bit-exact re-score of the candidates.
 // On return ctx->sel_keys holds the B selected keys (device, sorted). ev (6 events) may be null.
 // max |element| of an fp32 table, computed once per alink_set_table (one streaming pass)
-static int table_absmax(alink_ctx *ctx, Table &t, double *out) {
+static int table_absmax(alink_ctx *ctx, Table &t, double *out, double *rownorm = nullptr) {
   if (t.absmax < 0.0) {
-    ALINK_TRY(dev_reserve(ctx, ctx->rstat, 32));
-    unsigned int *bits = (unsigned int *)ctx->rstat.p;
-    ALINK_CUDA(ctx, cudaMemsetAsync(bits, 0, 4, ctx->stream));
-    absmax_kernel<<<ctx->sm_count * 8, 256, 0, ctx->stream>>>((const float4 *)t.p, t.M * t.D / 4, bits);
+    ALINK_TRY(dev_reserve(ctx, ctx->rstat, 256));
+    unsigned int *bits = (unsigned int *)ctx->rstat.p + 32;
+    ALINK_CUDA(ctx, cudaMemsetAsync(bits, 0, 16, ctx->stream));
+    table_stats_kernel<<<ctx->sm_count * 8, 256, 0, ctx->stream>>>((const float *)t.p, t.M, t.D, bits);
     ALINK_LAUNCHED(ctx);
-    unsigned int h = 0;
-    ALINK_CUDA(ctx, cudaMemcpyAsync(&h, bits, 4, cudaMemcpyDeviceToHost, ctx->stream));
+    unsigned int h[4] = {0, 0, 0, 0};
+    ALINK_CUDA(ctx, cudaMemcpyAsync(h, bits, 16, cudaMemcpyDeviceToHost, ctx->stream));
     ALINK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-    float f;
-    memcpy(&f, &h, 4);
+    float f, n2;
+    double tot;
+    memcpy(&f, &h[0], 4);
+    memcpy(&n2, &h[1], 4);
+    memcpy(&tot, &h[2], 8);
     t.absmax = (double)f;  // +inf stays +inf (fails the bound); NaN inputs never reach a finite utility anyway
+    t.rownorm = sqrt((double)n2);
+    t.rowms = tot / (double)t.M;
   }
   *out = t.absmax;
+  if (rownorm) *rownorm = t.rownorm;
   return ALINK_OK;
 }
 
+// per-measure factor between an error of a PROBABILITY and the error of the utility near the top
+// (margin = p(1) - p(2) doubles it; KL-max compares a learner with the mean: measured 4.3x)
+static const double REFINE_SCALE[ALINK_UTIL_COUNT] = {1.0, 2.0, 1.25, 1.0, 1.25, 5.0};
 static const double REFINE_EPS_BF16 = 1.2e-2;  // measured max |dp| 9.0e-3 (profiles/r1_refine_filter_error.txt)
 static const double REFINE_EPS_F16 = 1.5e-3;   // measured max |dp| 8.4e-4, rms 1.2e-4 (same file)
 
@@ -568,7 +636,7 @@ static int refine_query(alink_ctx *ctx, const HeadGroup &g, Table &A, Table &Bt,
   ALINK_TRY(dev_reserve(ctx, ctx->util, sizeof(float) * (size_t)N));
   ALINK_TRY(dev_reserve(ctx, ctx->sel_state, 2 * sizeof(SelectState)));
   ALINK_TRY(dev_reserve(ctx, ctx->cand, sizeof(uint32_t) * (size_t)N));
-  ALINK_TRY(dev_reserve(ctx, ctx->rstat, 32));
+  ALINK_TRY(dev_reserve(ctx, ctx->rstat, 256));
   float *util_a = (float *)ctx->util.p;
   // second state slot: tau must survive the exact top-B of step (5), which runs in slot 0, for a widening round
   SelectState *st = (SelectState *)ctx->sel_state.p + 1;
@@ -584,14 +652,14 @@ static int refine_query(alink_ctx *ctx, const HeadGroup &g, Table &A, Table &Bt,
   if (blocks > cap) blocks = cap;
   // eps bounds the error of a PROBABILITY; a measure moves by at most `scale` times that near the top
   // (margin = p(1) - p(2) doubles it; KL-max compares a learner with the mean: measured 4.3x)
-  static const double scale[ALINK_UTIL_COUNT] = {1.0, 2.0, 1.25, 1.0, 1.25, 5.0};
+  const double *scale = REFINE_SCALE;
   double eps = ctx->refine_eps > 0.0 ? ctx->refine_eps : (f16 ? REFINE_EPS_F16 : REFINE_EPS_BF16);
   ctx->refine_f16 = f16 ? 1 : 0;
   // marks the candidates (ctx->cand, count -> *M_out) and scores them exactly (ctx->probs, ctx->util_c)
   auto mark_and_rescore = [&](const unsigned int *pilot_min, float margin, int64_t *M_out, int64_t *cb_out) -> int {
     ALINK_CUDA(ctx, cudaMemsetAsync(rstat, 0, 16, ctx->stream));
     refine_mark_kernel<<<(unsigned)blocks, 256, 0, ctx->stream>>>(util_a, N, st, pilot_min, margin, (uint32_t *)ctx->cand.p,
-                                                                  rstat);
+                                                                  rstat, 0xFFFFFFFFu);
     ALINK_LAUNCHED(ctx);
     unsigned int hM = 0;
     ALINK_CUDA(ctx, cudaMemcpyAsync(&hM, rstat, 4, cudaMemcpyDeviceToHost, ctx->stream));
@@ -664,10 +732,268 @@ static int refine_query(alink_ctx *ctx, const HeadGroup &g, Table &A, Table &Bt,
   return ALINK_OK;
 }
 
+static const double REFINE_EPS2 = 2.0e-5;  // default stage-2 (split operand) bound; measured: profiles/r2_refine_errors.txt
+
+// A-priori error of the half-precision filter for this group and these tables. Rounding errors of the
+// operands are modelled as independent with relative rms delta = u / sqrt 6 (u = the format's unit roundoff; a
+// significand uniform in [1, 2)) and propagated through the three layers:
+//   layer 1, active unit:  s1^2 = 2 delta^2 |x|^2 c1^2 / D_in                    (c1 = column L2 norm of W1)
+//   layer 2, active unit:  s2^2 = c2^2 (s1^2 / 2 + 2 delta^2 |h1|^2 / H1)        (relu passes half of the units)
+//   logit z1 - z0:         sd^2 = s2^2 |w3d|^2 / 2 ;  probability: sd / 4 ;  mean of K independent learners: / sqrt K
+// refine_model_eps  uses TYPICAL norms (|x|^2 = mean row energy of both tables, |h1|^2 from it) and returns z = 8
+//                   standard deviations: checked against an emulation of the filter (1.4x above its measured rms) and
+//                   used as the filter width together with the per-format default;
+// refine_worst_eps  propagates the same model with WORST-CASE norms (max row norm, max |W|, spectral norm of W1) and no
+//                   averaging: 30-70x the observed error — it would make a third of the pool candidates — so it is
+//                   reported only.
+// Neither is a proof: the per-query check (max over all candidates, the stratified sample of non-candidates, and 8 x the
+// candidates' rms) is what detects a violation, and the width is then raised and the stages repeated.
+static double refine_model_eps(const HeadGroup &g, const Table &A, const Table &B, bool f16, double z = 8.0) {
+  const double u = f16 ? 1.0 / 2048.0 : 1.0 / 256.0, d2 = u * u / 6.0;
+  double xn2 = A.rowms + B.rowms;
+  if (g.feat_mode == ALINK_FEAT_ABSDIFF_HADAMARD) xn2 += A.rowms * B.absmax * B.absmax;
+  const double pre = xn2 * g.w1_col_l2 * g.w1_col_l2 / (double)g.D_in;  // variance of a layer-1 pre-activation
+  const double s1 = 2.0 * d2 * pre;
+  const double h1n2 = (double)g.H1 * (0.5 * pre + g.b1_ms);
+  const double s2 = g.w2_col_l2 * g.w2_col_l2 * (0.5 * s1 + 2.0 * d2 * h1n2 / (double)g.H1);
+  const double sd = sqrt(0.5 * s2 * g.w3_gain_ms / (double)g.K);
+  return z * sd * 0.25;
+}
+static double refine_worst_eps(const HeadGroup &g, double xmax, double xnorm, bool f16, double z = 6.0) {
+  const double u = f16 ? 1.0 / 2048.0 : 1.0 / 256.0, delta = u / sqrt(3.0);
+  const double a1 = xmax * g.w1_col_l2, b1 = xnorm * g.w1_absmax;
+  const double s1 = delta * sqrt(2.0) * (a1 < b1 ? a1 : b1);
+  const double h1max = xmax * g.w1_col_l1 + g.b1_absmax, h1norm = xnorm * g.w1_spec + g.b1_l2;
+  const double a2 = h1max * g.w2_col_l2, b2 = h1norm * g.w_absmax;
+  const double r2 = delta * sqrt(2.0) * (a2 < b2 ? a2 : b2);
+  const double s2 = sqrt(s1 * g.w2_col_l2 * s1 * g.w2_col_l2 + r2 * r2);
+  return z * s2 * g.w3_gain * 0.25;
+}
+
+// FP32_REFINE in three stages with device-resident counts (refine.cuh): ONE host synchronisation, at the end, which
+// brings the result and 64 bytes of statistics. Emits the selection itself; falls back to refine_query (filter +
+// FFMA, host-sized grids) for shapes the split kernel does not take, B > 4096, or when a candidate list overflows.
+static int refine_query_v2(alink_ctx *ctx, const HeadGroup &g, Table &A, Table &Bt, const int32_t *ia, const int32_t *ib,
+                           int64_t N, int measure, int64_t B, int64_t base, cudaEvent_t *ev, int64_t *idx_out,
+                           float *util_out, uint64_t *keys_out, int out_space) {
+  static const int ver_env = [] { const char *e = getenv("ALINK_REFINE_V"); return e ? atoi(e) : 2; }();
+  static const int fmt_env = [] { const char *e = getenv("ALINK_REFINE_FMT"); return e ? atoi(e) : 0; }();  // 1 = force bf16
+  double ma = 0, mb = 0, ra = 0, rb = 0;
+  bool ok = ver_env != 1 && g.split_ok && !g.bounds_stale && g.W1h && g.W2h && fmt_env != 1 && B <= 4096 && B >= 1;
+  double xmax = 0, xnorm = 0, h1max = 0;
+  if (ok) {
+    ALINK_TRY(table_absmax(ctx, A, &ma, &ra));
+    ALINK_TRY(table_absmax(ctx, Bt, &mb, &rb));
+    xmax = ma + mb;
+    xnorm = ra + rb;
+    if (g.feat_mode == ALINK_FEAT_ABSDIFF_HADAMARD) {
+      if (ma * mb > xmax) xmax = ma * mb;
+      const double hn = ra * mb < rb * ma ? ra * mb : rb * ma;
+      xnorm = sqrt(xnorm * xnorm + hn * hn);
+    }
+    h1max = xmax * g.w1_col_l1 + g.b1_absmax;
+    ok = xmax < 6.0e4 && h1max < 6.0e4 && g.w_absmax < 6.0e4 && xmax > 0.0;  // the half filter cannot overflow
+  }
+  if (!ok) {
+    ctx->refine_version = 1;
+    ALINK_TRY(refine_query(ctx, g, A, Bt, ia, ib, N, measure, B, base, ev));
+    if (ev) ALINK_CUDA(ctx, cudaEventRecord(ev[4], ctx->stream));
+    return emit_selection(ctx, B, idx_out, util_out, keys_out, out_space);
+  }
+  ctx->refine_version = 2;
+  ctx->N = N; ctx->sK = g.K; ctx->sC = g.C; ctx->util_valid = false; ctx->probs_full = false;
+  ctx->refine_f16 = 1;
+  const unsigned int wave = (unsigned int)(ctx->sm_count / 2) * 2u * tc::TILE_M;  // rows of one wave of the split kernel
+  const unsigned int ns_min = N < 4096 ? (unsigned int)N : 4096u, ns_max = ns_min > wave ? ns_min : wave, ns2_max = 256;
+  int64_t cap1 = N < (1 << 18) ? N : (1 << 18);
+  const unsigned int cap2 = 8192;
+  const int64_t rows1 = cap1 + ns_max, rows2 = (int64_t)cap2 + ns2_max;
+  ALINK_TRY(dev_reserve(ctx, ctx->util, sizeof(float) * (size_t)N));
+  ALINK_TRY(dev_reserve(ctx, ctx->sel_state, 2 * sizeof(SelectState)));
+  ALINK_TRY(dev_reserve(ctx, ctx->rstat, 256));
+  ALINK_TRY(dev_reserve(ctx, ctx->cand, sizeof(uint32_t) * (size_t)(N > rows1 ? N : rows1)));
+  ALINK_TRY(dev_reserve(ctx, ctx->cia, sizeof(int32_t) * (size_t)rows1));
+  ALINK_TRY(dev_reserve(ctx, ctx->cib, sizeof(int32_t) * (size_t)rows1));
+  ALINK_TRY(dev_reserve(ctx, ctx->util2, sizeof(float) * (size_t)rows1));
+  ALINK_TRY(dev_reserve(ctx, ctx->cia2, sizeof(int32_t) * (size_t)rows2));
+  ALINK_TRY(dev_reserve(ctx, ctx->cib2, sizeof(int32_t) * (size_t)rows2));
+  ALINK_TRY(dev_reserve(ctx, ctx->map2, sizeof(uint32_t) * (size_t)rows2));
+  ALINK_TRY(dev_reserve(ctx, ctx->src2, sizeof(uint32_t) * (size_t)rows2));
+  ALINK_TRY(dev_reserve(ctx, ctx->util_c, sizeof(float) * (size_t)rows2));
+  ALINK_TRY(dev_reserve(ctx, ctx->probs, sizeof(float) * (size_t)rows2 * g.K * g.C));
+  ALINK_TRY(dev_reserve(ctx, ctx->h1ws, sizeof(float) * (size_t)rows2 * g.H1 * g.K));
+  const int64_t npad = next_pow2(B);
+  ALINK_TRY(dev_reserve(ctx, ctx->sel_keys, sizeof(uint64_t) * (size_t)npad));
+  if (!ctx->rs_host) ALINK_CUDA(ctx, cudaMallocHost((void **)&ctx->rs_host, RS_WORDS * sizeof(unsigned int)));
+  float *util_a = (float *)ctx->util.p;
+  SelectState *st = (SelectState *)ctx->sel_state.p + 1;
+  unsigned int *rs = (unsigned int *)ctx->rstat.p + 40;
+  // the bounds: caller's value, else the larger of the per-format default and the a-priori statistical model
+  const double apriori = refine_model_eps(g, A, Bt, true);
+  ctx->refine_eps_apriori = apriori;
+  ctx->refine_eps_worst = refine_worst_eps(g, xmax, xnorm, true);
+  const int gi = (int)(&g - ctx->groups);
+  double eps1 = ctx->refine_eps > 0.0 ? ctx->refine_eps : (REFINE_EPS_F16 > apriori ? REFINE_EPS_F16 : apriori);
+  if (ctx->refine_eps <= 0.0 && ctx->refine_eps_hint[gi] > eps1) eps1 = ctx->refine_eps_hint[gi];
+  double eps2 = ctx->refine_eps2 > 0.0 ? ctx->refine_eps2 : REFINE_EPS2;
+  const double sc = REFINE_SCALE[measure];
+  // (1) approximate utilities of every pair (fused K-learner reduction in the kernel's epilogue)
+  ALINK_TRY(tc_score(ctx, g, A, Bt, ia, ib, N, nullptr, util_a, measure, true));
+  if (ev) ALINK_CUDA(ctx, cudaEventRecord(ev[2], ctx->stream));
+  // (2) B-th largest approximate utility tau1
+  KeySrc asrc{util_a, nullptr, 0, nullptr};
+  ALINK_TRY(select_threshold(ctx, asrc, N, B, st, 3));
+  int64_t blocks = (N + 2047) / 2048;
+  const int64_t capb = (int64_t)ctx->sm_count * 8;
+  if (blocks > capb) blocks = capb;
+  for (int round = 1;; ++round) {
+    if (eps2 * 4.0 > eps1) eps2 = eps1 / 4.0;
+    ALINK_CUDA(ctx, cudaMemsetAsync(rs, 0, RS_WORDS * sizeof(unsigned int), ctx->stream));
+    // (3) C1 = {u~ >= tau1 - 2 eps1}; + the stratified sample; table rows of both
+    refine_mark_kernel<<<(unsigned)blocks, 256, 0, ctx->stream>>>(util_a, N, st, nullptr, (float)(2.0 * eps1 * sc),
+                                                                  (uint32_t *)ctx->cand.p, rs + RS_COUNT1, (unsigned int)cap1);
+    ALINK_LAUNCHED(ctx);
+    refine_stage1_finish_kernel<<<64, 256, 0, ctx->stream>>>(rs, (unsigned int)cap1, N, ns_min, ns_max, wave, (uint32_t *)ctx->cand.p,
+                                                             ia, ib, ia ? 0u : ctx->ap_G, ctx->ap_pair0, (int32_t *)ctx->cia.p,
+                                                             (int32_t *)ctx->cib.p);
+    ALINK_LAUNCHED(ctx);
+    // (4) split-operand tensor-core utilities u2 of C1 u S
+    {
+      const uint32_t apG = ctx->ap_G;
+      ctx->ap_G = 0;  // the rows are explicit now
+      const int rc = tc_score_split(ctx, g, A, Bt, (const int32_t *)ctx->cia.p, (const int32_t *)ctx->cib.p, rows1, rs + RS_M1, nullptr,
+                                    (float *)ctx->util2.p, measure, xmax, h1max);
+      ctx->ap_G = apG;
+      ALINK_TRY(rc);
+    }
+    // (5) tau2, C2 = {u2 >= tau2 - 2 eps2} + every 16th sample row; their table rows
+    refine_stage2_kernel<<<1, 1024, 0, ctx->stream>>>(rs, (const float *)ctx->util2.p, (unsigned long long)B, (float)(2.0 * eps2 * sc), cap2,
+                                                      ns2_max, (const uint32_t *)ctx->cand.p, (const int32_t *)ctx->cia.p,
+                                                      (const int32_t *)ctx->cib.p, (int32_t *)ctx->cia2.p, (int32_t *)ctx->cib2.p,
+                                                      (uint32_t *)ctx->map2.p, (uint32_t *)ctx->src2.p);
+    ALINK_LAUNCHED(ctx);
+    // (6) bit-exact re-score of C2 u S2 (oracle summation order, CUDA cores)
+    {
+      const uint32_t apG = ctx->ap_G;
+      ctx->ap_G = 0;
+      const int rc = ffma_head_chunk(ctx, g, (const float *)A.p, (const float *)Bt.p, A.D, (const int32_t *)ctx->cia2.p,
+                                     (const int32_t *)ctx->cib2.p, 0, (int)rows2, (float *)ctx->h1ws.p, rows2 * g.H1,
+                                     (float *)ctx->probs.p, rs + RS_M2);
+      ctx->ap_G = apG;
+      ALINK_TRY(rc);
+    }
+    // (7) exact utilities + the error statistics of both filters
+    {
+      const unsigned fb = 48;
+#define ALINK_FINISH(KT)                                                                                                   \
+  refine_finish_kernel<KT><<<fb, 256, 0, ctx->stream>>>(rs, (const float *)ctx->probs.p, g.K, g.C, measure, util_a,        \
+                                                        (const float *)ctx->util2.p, (const uint32_t *)ctx->cand.p,        \
+                                                        (const uint32_t *)ctx->map2.p, (const uint32_t *)ctx->src2.p,      \
+                                                        (float *)ctx->util_c.p)
+      switch (g.K) {
+        case 1: ALINK_FINISH(1); break;
+        case 3: ALINK_FINISH(3); break;
+        case 5: ALINK_FINISH(5); break;
+        default: ALINK_FINISH(0); break;
+      }
+#undef ALINK_FINISH
+      ALINK_LAUNCHED(ctx);
+    }
+    if (ev && round == 1) ALINK_CUDA(ctx, cudaEventRecord(ev[3], ctx->stream));
+    // (8) exact top-B of C2, keyed by the pairs' original indices
+    KeySrc csrc{(const float *)ctx->util_c.p, nullptr, (uint64_t)base, (const uint32_t *)ctx->map2.p};
+    topk_small_kernel<<<1, 1024, 0, ctx->stream>>>(csrc, (int)cap2, (int)B, (int)(npad < 2 ? 2 : npad), (uint64_t *)ctx->sel_keys.p,
+                                                   rs + RS_N2);
+    ALINK_LAUNCHED(ctx);
+    ALINK_CUDA(ctx, cudaMemcpyAsync(ctx->rs_host, rs, RS_WORDS * sizeof(unsigned int), cudaMemcpyDeviceToHost, ctx->stream));
+    if (ev && round == 1) ALINK_CUDA(ctx, cudaEventRecord(ev[4], ctx->stream));
+    ALINK_TRY(emit_selection(ctx, B, idx_out, util_out, keys_out, out_space));
+    ALINK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));  // the one host synchronisation of the step
+    const unsigned int *h = ctx->rs_host;
+    float e1, e2, ea;
+    double ss2;
+    memcpy(&e1, h + RS_ERR1, 4);
+    memcpy(&e2, h + RS_ERR2, 4);
+    memcpy(&ea, h + RS_ERRA, 4);
+    memcpy(&ss2, h + RS_SS2, 8);
+    double ss1;
+    memcpy(&ss1, h + RS_SS1, 8);
+    ctx->refine_survivors = h[RS_N2];
+    ctx->refine_n1 = h[RS_N1];
+    ctx->refine_nsample = (int64_t)h[RS_M1] - (int64_t)h[RS_N1];
+    ctx->refine_nsample2 = (int64_t)h[RS_M2] - (int64_t)h[RS_N2];
+    ctx->refine_err1 = e1;
+    ctx->refine_err2 = e2;
+    ctx->refine_max_err = ea > e1 ? ea : e1;                       // the stage-1 filter's largest observed error
+    ctx->refine_rms_err = h[RS_N1] ? (float)sqrt(ss1 / (double)h[RS_N1]) : 0.0f;
+    ctx->refine_rms2 = h[RS_M2] ? (float)sqrt(ss2 / (double)h[RS_M2]) : 0.0f;
+    ctx->refine_eps_used = eps1;
+    ctx->refine_eps2_used = eps2;
+    ctx->refine_rounds = round;
+    if (h[RS_FLAGS]) {  // a candidate list overflowed (plateaus of tied utilities): the host-sized pipeline takes any size
+      ctx->refine_version = 1;
+      ALINK_TRY(refine_query(ctx, g, A, Bt, ia, ib, N, measure, B, base, nullptr));
+      return emit_selection(ctx, B, idx_out, util_out, keys_out, out_space);
+    }
+    // Both bounds must hold on everything we can check: stage 2 against the exact values (C2 u S2), stage 1 against
+    // stage 2 (C1 u S, to within eps2) and against the exact values. Otherwise widen past what was seen and redo.
+    const double seen2 = (double)e2 / sc;
+    const double s1a = (double)e1 / sc + eps2, s1b = (double)ea / sc;  // |u~ - u| <= |u~ - u2| + eps2
+    double seen1 = s1a > s1b ? s1a : s1b;
+    const double tail1 = 8.0 * (double)ctx->refine_rms_err / sc;  // 8 sigma of the candidates' error must fit as well
+    const bool bad2 = seen2 > eps2, bad1 = seen1 > eps1 || tail1 > eps1;
+    if (tail1 > 2.0 * seen1) seen1 = 0.5 * tail1;
+    if ((!bad1 && !bad2) || round >= 5) {
+      if (bad1 || bad2) {  // could not be verified in 5 rounds: run it exactly
+        ctx->refine_version = 1;
+        ALINK_TRY(refine_query(ctx, g, A, Bt, ia, ib, N, measure, B, base, nullptr));
+        return emit_selection(ctx, B, idx_out, util_out, keys_out, out_space);
+      }
+      break;
+    }
+    if (bad2) eps2 = 2.0 * seen2;
+    if (bad1) {
+      eps1 = 2.0 * seen1;
+      if (ctx->refine_eps <= 0.0) ctx->refine_eps_hint[gi] = eps1;  // the group's next query starts from here
+    }
+  }
+  return ALINK_OK;
+}
+
 int alink_set_refine_eps(alink_ctx *ctx, double eps) {
   if (!ctx) return ALINK_E_INVALID;
   if (!(eps >= 0.0 && eps < 1.0)) return alink_fail(ctx, ALINK_E_INVALID, "eps outside [0, 1) (0 = per-format default)");
   ctx->refine_eps = eps;
+  return ALINK_OK;
+}
+
+int alink_set_refine_eps2(alink_ctx *ctx, double eps2) {
+  if (!ctx) return ALINK_E_INVALID;
+  if (!(eps2 >= 0.0 && eps2 < 1.0)) return alink_fail(ctx, ALINK_E_INVALID, "eps2 outside [0, 1) (0 = default)");
+  ctx->refine_eps2 = eps2;
+  return ALINK_OK;
+}
+
+int alink_refine_report_get(const alink_ctx *ctx, alink_refine_report *out) {
+  if (!ctx || !out) return ALINK_E_INVALID;
+  memset(out, 0, sizeof(*out));
+  out->version = ctx->refine_version;
+  out->filter_f16 = ctx->refine_f16;
+  out->rounds = ctx->refine_rounds;
+  out->n_exact = ctx->refine_survivors;
+  out->eps1_used = ctx->refine_eps_used;
+  out->err1_max = ctx->refine_max_err;
+  out->err1_rms = ctx->refine_rms_err;
+  if (ctx->refine_version == 2) {
+    out->n_stage2 = ctx->refine_n1;
+    out->n_sample = ctx->refine_nsample;
+    out->n_sample_exact = ctx->refine_nsample2;
+    out->eps1_apriori = ctx->refine_eps_apriori;
+    out->eps1_worst = ctx->refine_eps_worst;
+    out->eps2_used = ctx->refine_eps2_used;
+    out->err2_max = ctx->refine_err2;
+    out->err2_rms = ctx->refine_rms2;
+  }
   return ALINK_OK;
 }
 
@@ -711,6 +1037,7 @@ int alink_query(alink_ctx *ctx, int group, int slot_a, int slot_b, const int32_t
   ALINK_TRY(table_wait(ctx, slot_b));
   ctx->refine_survivors = 0;
   ctx->refine_max_err = 0.0f;
+  ctx->refine_version = 0;
   if (group >= 0 && group < ALINK_MAX_GROUPS && ctx->groups[group].set &&
       ctx->groups[group].compute == ALINK_COMPUTE_FP32_REFINE && ctx->groups[group].tc_ok &&
       measure != ALINK_UTIL_VOTE_ENTROPY && B > 0 && N >= 8192) {
@@ -721,10 +1048,8 @@ int alink_query(alink_ctx *ctx, int group, int slot_a, int slot_b, const int32_t
       return alink_fail(ctx, ALINK_E_INVALID, "FP32_REFINE needs fp32 tables matching the heads' fan-in");
     if (!dia && !ctx->ap_G && (N > TA.M || N > TB.M))
       return alink_fail(ctx, ALINK_E_INVALID, "identity pairs exceed table rows");
-    ALINK_TRY(refine_query(ctx, g, TA, TB, (const int32_t *)dia, (const int32_t *)dib, N, measure, B, base,
-                           timing ? e : nullptr));
-    if (timing) ALINK_CUDA(ctx, cudaEventRecord(e[4], ctx->stream));
-    ALINK_TRY(emit_selection(ctx, B, idx_out, util_out, keys_out, out_space));
+    ALINK_TRY(refine_query_v2(ctx, g, TA, TB, (const int32_t *)dia, (const int32_t *)dib, N, measure, B, base,
+                              timing ? e : nullptr, idx_out, util_out, keys_out, out_space));
     if (timing) {
       ALINK_CUDA(ctx, cudaEventRecord(e[5], ctx->stream));
       ALINK_CUDA(ctx, cudaEventSynchronize(e[5]));

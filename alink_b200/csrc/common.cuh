@@ -27,9 +27,19 @@ struct HeadGroup {
   __nv_bfloat16 *W1t = nullptr, *W2t = nullptr;
   // the same images in IEEE half (FP32_REFINE's default filter format)
   __half *W1h = nullptr, *W2h = nullptr;
+  // scaled hi / lo half images for the split-operand second stage of FP32_REFINE (head_tc_split.cuh)
+  __half *S1hi = nullptr, *S1lo = nullptr, *S2hi = nullptr, *S2lo = nullptr;
+  float sw1 = 1.0f, sw2 = 1.0f;  // their power-of-two scales
+  bool split_ok = false;
   bool tc_ok = false;  // the tensor-core images exist (shape supported by head_tc.cuh)
   // bound for "no half overflow": max_j sum_k |W1[k][j]| over learners, max |b1| (host, at alink_set_heads)
-  double w1_col_l1 = 0.0, b1_absmax = 0.0, w_absmax = 0.0;
+  double w1_col_l1 = 0.0, b1_absmax = 0.0, w_absmax = 0.0;  // w_absmax: max |W2|
+  double w1_absmax = 0.0;
+  // a-priori (statistical) error model of the half-precision filter, per group (alink_set_heads; refine_apriori_eps):
+  // max column L2 norms of W1 / W2, max |W1| / |W2| element, spectral norm of W1 (power iteration), ||b1||_2,
+  // and max over learners of ||W3[:,1] - W3[:,0]||_2 (or ||W3||_2 for the sigmoid head)
+  double w1_col_l2 = 0.0, w2_col_l2 = 0.0, w1_spec = 0.0, b1_l2 = 0.0, w3_gain = 0.0;
+  double w3_gain_ms = 0.0, b1_ms = 0.0;  // mean over learners of ||w3d||^2; max over learners of mean b1^2
   bool bounds_stale = false;  // weights changed on the device (train.cuh) since those bounds were computed
   // Adadelta accumulators of the finetune step (train.cuh), same [K][...] layout as the six tensors; lazy, zeroed
   float *opt_a[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
@@ -43,6 +53,8 @@ struct Table {
   int dtype = ALINK_F32;
   DevBuf own;
   double absmax = -1.0;  // max |element| (lazy, refine.cuh; reset by alink_set_table)
+  double rownorm = -1.0; // max row L2 norm (same pass)
+  double rowms = 0.0;    // mean row sum of squares (same pass)
   cudaEvent_t ready = nullptr;  // alink_set_table_async: recorded on the copy stream behind the upload
   bool pending = false;         // the compute stream has not yet been made to wait for `ready`
 };
@@ -89,6 +101,15 @@ struct alink_ctx {
   int refine_f16 = 0;             // the last query's filter ran on half (1) or bf16 (0) operands
   bool probs_full = true;         // ctx->probs holds all N pairs (false after a refine query)
   DevBuf cand, cia, cib, util_c, rstat;
+  DevBuf util2, cia2, cib2, map2, src2;     // stage 2 / 3 of refine_query_v2
+  unsigned int *rs_host = nullptr;          // pinned copy of the statistics words (read with the result)
+  double refine_eps2 = 0.0, refine_eps2_used = 0.0;  // stage-2 (split operand) bound: caller's / used
+  double refine_eps_apriori = 0.0;          // a-priori statistical MODEL of the stage-1 filter error (8 sigma) for the last query
+  double refine_eps_worst = 0.0;            // the same propagated with worst-case norms (reported, too loose to filter with)
+  double refine_eps_hint[ALINK_MAX_GROUPS] = {0, 0, 0, 0};  // bound a previous query of the group had to widen to
+  float refine_err1 = 0.0f, refine_err2 = 0.0f, refine_rms2 = 0.0f;  // max |u~ - u2| over C1 u S; max / rms |u2 - u| over C2 u S2
+  int64_t refine_n1 = 0, refine_nsample = 0, refine_nsample2 = 0;
+  int refine_version = 0;                   // pipeline the last query ran (2 = three stages, 1 = filter + FFMA)
   // all-pairs enumeration (alink_*_allpairs): pair n = (probe row (ap_pair0 + n) / ap_G, gallery row (..) % ap_G)
   uint32_t ap_G = 0;
   int64_t ap_pair0 = 0;

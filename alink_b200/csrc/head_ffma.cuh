@@ -30,6 +30,7 @@ struct FfmaArgs {
   int D;
   int64_t row0;                // first pair of this chunk
   int M;                       // rows (pairs) in this chunk
+  const unsigned int *m_dev;   // optional: the row count lives on the device (M is then its capacity: the grid)
   int Kdim;                    // fan-in
   int Ncols;                   // fan-out of this layer
   int ntiles;                  // column tiles
@@ -59,11 +60,17 @@ __global__ void __launch_bounds__(256, 2) ffma_layer_kernel(const FfmaArgs a) {
   const int learner = blockIdx.x / a.ntiles;
   const int mtile = blockIdx.y;
   const int n0 = ntile * BN;
+  int Mrows = a.M;
+  if (a.m_dev) {
+    const unsigned int md = __ldg(a.m_dev);
+    if (md < (unsigned int)Mrows) Mrows = (int)md;
+    if (mtile * BM >= Mrows) return;  // the whole CTA: grids are sized for the capacity
+  }
 
   // ---- A loader state: this thread owns row (tid>>1), k-quads (tid&1)*4*NA + 4*i of every chunk
   const int lrow = tid >> 1, kq = (tid & 1) * 4 * NA;
   int grow = mtile * BM + lrow;
-  if (grow >= a.M) grow = a.M - 1;
+  if (grow >= Mrows) grow = Mrows - 1;
   const float *pa, *pb = nullptr;
   if constexpr (AMODE == 0) {
     pa = a.A + (size_t)learner * a.a_learner_stride + (size_t)grow * a.lda;
@@ -195,7 +202,7 @@ __global__ void __launch_bounds__(256, 2) ffma_layer_kernel(const FfmaArgs a) {
 #pragma unroll
     for (int i = 0; i < TM; ++i) {
       const int row = mtile * BM + row_of(i);
-      if (row >= a.M) continue;
+      if (row >= Mrows) continue;
 #pragma unroll
       for (int j0 = 0; j0 < TN; j0 += (TN >= 4 ? 4 : 2)) {
         const int col = n0 + col_of(j0);
@@ -226,7 +233,7 @@ __global__ void __launch_bounds__(256, 2) ffma_layer_kernel(const FfmaArgs a) {
     __syncthreads();
     if (tid < BM) {
       const int row = mtile * BM + tid;
-      if (row < a.M) {
+      if (row < Mrows) {
         const float *w3 = a.W3[learner];
         const float *b3 = a.b3[learner];
         float *out = a.probs + ((size_t)(a.row0 + row) * a.K + learner) * a.C;
@@ -258,12 +265,12 @@ __global__ void __launch_bounds__(256, 2) ffma_layer_kernel(const FfmaArgs a) {
 // Launch both layers for one chunk of pairs. H1 workspace layout [K][Mc][H1].
 static int ffma_head_chunk(alink_ctx *ctx, const HeadGroup &g, const float *ta, const float *tb, int D,
                            const int32_t *ia, const int32_t *ib, int64_t row0, int Mc, float *h1ws,
-                           int64_t h1_learner_stride, float *probs) {
+                           int64_t h1_learner_stride, float *probs, const unsigned int *m_dev = nullptr) {
   FfmaArgs a;
   memset(&a, 0, sizeof(a));
   a.ta = ta; a.tb = tb; a.ia = ia; a.ib = ib; a.D = D;
   a.G = ia ? 0u : ctx->ap_G; a.pair0 = ctx->ap_pair0;
-  a.row0 = row0; a.M = Mc; a.Kdim = g.D_in; a.Ncols = g.H1;
+  a.row0 = row0; a.M = Mc; a.m_dev = m_dev; a.Kdim = g.D_in; a.Ncols = g.H1;
   a.ntiles = (g.H1 + 127) / 128;
   a.W = g.pW1; a.bias = g.pb1;
   a.H = h1ws; a.h_learner_stride = h1_learner_stride;
@@ -278,7 +285,7 @@ static int ffma_head_chunk(alink_ctx *ctx, const HeadGroup &g, const float *ta, 
   FfmaArgs b;
   memset(&b, 0, sizeof(b));
   b.A = h1ws; b.lda = g.H1; b.a_learner_stride = h1_learner_stride;
-  b.row0 = row0; b.M = Mc; b.Kdim = g.H1; b.Ncols = g.H2; b.ntiles = 1;
+  b.row0 = row0; b.M = Mc; b.m_dev = m_dev; b.Kdim = g.H1; b.Ncols = g.H2; b.ntiles = 1;
   b.W = g.pW2; b.bias = g.pb2;
   b.W3 = g.pW3; b.b3 = g.pb3; b.C = g.C; b.act = g.act; b.K = g.K; b.probs = probs;
   dim3 grid2(g.K, (Mc + 127) / 128);

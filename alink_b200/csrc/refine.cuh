@@ -28,7 +28,8 @@
 // pilot set (an order-preserving uint, refine_min_kernel)
 __global__ void __launch_bounds__(256) refine_mark_kernel(const float *__restrict__ util, int64_t N, const SelectState *st,
                                                           const unsigned int *__restrict__ pilot_min, float margin,
-                                                          uint32_t *__restrict__ cand, unsigned int *__restrict__ count) {
+                                                          uint32_t *__restrict__ cand, unsigned int *__restrict__ count,
+                                                          unsigned int cap) {
   const float tau = alink_key_utility(st->prefix << 32);
   // never above tau: the pilot set itself always stays in (it matters when the caller's bound is too tight)
   const float thr = pilot_min ? fminf(__fsub_rn(alink_unorderable(*pilot_min), margin), tau) : __fsub_rn(tau, margin);
@@ -43,7 +44,8 @@ __global__ void __launch_bounds__(256) refine_mark_kernel(const float *__restric
       unsigned int basepos = 0;
       if (lane == first) basepos = atomicAdd(count, (unsigned int)__popc(m));
       basepos = __shfl_sync(0xffffffffu, basepos, first);
-      if (keep) cand[basepos + __popc(m & ((1u << lane) - 1u))] = (uint32_t)n;
+      const unsigned int pos = basepos + __popc(m & ((1u << lane) - 1u));
+      if (keep && pos < cap) cand[pos] = (uint32_t)n;  // *count may exceed cap: the caller sees the overflow
     }
   }
 }
@@ -109,4 +111,195 @@ __global__ void __launch_bounds__(256) absmax_kernel(const float4 *__restrict__ 
   for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
   // NaN/Inf elements: fmaxf drops NaN, so test the bit pattern of what remains and flag non-finite separately
   if ((threadIdx.x & 31) == 0) atomicMax(out_bits, __float_as_uint(m));
+}
+
+
+// ======================================================================================================================
+// FP32_REFINE, three stages without host round trips (refine_query_v2 in alink_b200.cu):
+//   stage 1  half-precision tensor-core filter over all N pairs (u~, error <= eps1) -> candidates C1 = {u~ >= tau1 - 2 eps1}
+//   stage 2  split-operand tensor-core re-score of C1 (u2, error <= eps2 ~ 1e-5, head_tc_split.cuh)
+//            -> C2 = {n in C1 : u2 >= tau2 - 2 eps2}   (tau = the B-th largest value of the stage)
+//   stage 3  bit-exact FFMA re-score of C2 (u), exact top-B with the pairs' original indices in the keys.
+// Both bounds are CHECKED on every query, also on pairs OUTSIDE the candidate sets: a deterministic stratified sample S
+// of the pool (>= 4096 pairs, as many as fill the last wave of the split kernel) rides through stage 2 — it verifies
+// eps1 against u2 — and every 16th of those rides through stage 3 — it verifies eps2 against the exact value.
+// Counts stay on the device (grids are sized for the capacities); the host reads 64 bytes of statistics with the result.
+// rs[] words: 0 count1 | 1 M1 = n1 + |S| | 2 count2 | 3 M2 = n2 + |S2| | 4 flags (1: C1 overflow, 2: C2 overflow)
+//             5 max |u~ - u2| over C1 u S | 6 max |u2 - u| over C2 u S2 | 7 max |u~ - u| over C2 u S2 | 8-9 sum sq of |u~ - u2| over C1 (double)
+//             10-11 sum sq of 6 (double) | 12 n1 = min(count1, cap1) | 13 n2 = min(count2, cap2)
+enum { RS_COUNT1 = 0, RS_M1 = 1, RS_COUNT2 = 2, RS_M2 = 3, RS_FLAGS = 4, RS_ERR1 = 5, RS_ERR2 = 6, RS_ERRA = 7, RS_SS1 = 8,
+       RS_SS2 = 10, RS_N1 = 12, RS_N2 = 13, RS_WORDS = 16 };
+
+// after refine_mark_kernel: clamp the count, append the stratified sample, translate rows to table rows
+__global__ void __launch_bounds__(256) refine_stage1_finish_kernel(unsigned int *__restrict__ rs, unsigned int cap1, int64_t N,
+                                                                   unsigned int ns_min, unsigned int ns_max, unsigned int wave_rows,
+                                                                   uint32_t *__restrict__ cand1, const int32_t *__restrict__ ia,
+                                                                   const int32_t *__restrict__ ib, uint32_t G, int64_t pair0,
+                                                                   int32_t *__restrict__ cia, int32_t *__restrict__ cib) {
+  const unsigned int count1 = rs[RS_COUNT1];
+  const unsigned int n1 = count1 < cap1 ? count1 : cap1;
+  // the sample fills the last wave of the split kernel (at least ns_min pairs, at most ns_max)
+  unsigned int ns = ((n1 + ns_min + wave_rows - 1) / wave_rows) * wave_rows - n1;
+  if (ns > ns_max) ns = ns_max;
+  if ((int64_t)ns > N) ns = (unsigned int)N;
+  const unsigned int M1 = n1 + ns;
+  for (unsigned int r = blockIdx.x * 256 + threadIdx.x; r < M1; r += gridDim.x * 256) {
+    uint32_t n;
+    if (r < n1) {
+      n = cand1[r];
+    } else {  // pair floor((j + 1/2) N / ns): one per stratum of N / ns consecutive pairs
+      const unsigned long long j = r - n1;
+      n = (uint32_t)(((2ull * j + 1ull) * (unsigned long long)N) / (2ull * ns));
+      cand1[r] = n;
+    }
+    if (ia) {
+      cia[r] = __ldg(ia + n);
+      cib[r] = __ldg(ib + n);
+    } else if (G) {
+      const int64_t p = pair0 + n;
+      const int64_t ra = p / G;
+      cia[r] = (int32_t)ra;
+      cib[r] = (int32_t)(p - ra * G);
+    } else {
+      cia[r] = cib[r] = (int32_t)n;
+    }
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    rs[RS_M1] = M1;
+    rs[RS_N1] = n1;
+    if (count1 > cap1) atomicOr(rs + RS_FLAGS, 1u);
+  }
+}
+
+// stage 2 -> stage 3 hand-over in ONE CTA: B-th largest split-operand utility among the n1 candidates (radix select on
+// the utility bits), C2 = rows within `margin` of it, plus every (|S| / ns2)-th sample row; emits the table rows, the
+// original pair index and the stage-2 row of every selected row.
+__global__ void __launch_bounds__(1024) refine_stage2_kernel(unsigned int *__restrict__ rs, const float *__restrict__ util2,
+                                                             unsigned long long B, float margin, unsigned int cap2,
+                                                             unsigned int ns2_max, const uint32_t *__restrict__ cand1,
+                                                             const int32_t *__restrict__ cia1, const int32_t *__restrict__ cib1,
+                                                             int32_t *__restrict__ cia2, int32_t *__restrict__ cib2,
+                                                             uint32_t *__restrict__ map2, uint32_t *__restrict__ src2) {
+  __shared__ unsigned int sh[2048];
+  __shared__ unsigned int part[256];
+  __shared__ unsigned long long s_prefix, s_remaining;
+  __shared__ unsigned int s_count;
+  const int tid = threadIdx.x;
+  const unsigned int n1 = rs[RS_N1], M1 = rs[RS_M1];
+  if (tid == 0) s_count = 0;
+  KeySrc src{util2, nullptr, 0, nullptr};
+  radix_select_cta(src, (int)n1, B < n1 ? B : (unsigned long long)(n1 ? n1 : 1), 3, sh, part, s_prefix, s_remaining);
+  const float thr = __fsub_rn(alink_key_utility(s_prefix << 32), margin);
+  for (unsigned int r = tid; r < n1; r += 1024) {
+    if (util2[r] >= thr) {
+      const unsigned int pos = atomicAdd(&s_count, 1u);
+      if (pos < cap2) {
+        src2[pos] = r;
+        map2[pos] = cand1[r];
+        cia2[pos] = cia1[r];
+        cib2[pos] = cib1[r];
+      }
+    }
+  }
+  __syncthreads();
+  const unsigned int count2 = s_count, n2 = count2 < cap2 ? count2 : cap2;
+  const unsigned int nsamp = M1 - n1;
+  const unsigned int ns2 = nsamp < ns2_max ? nsamp : ns2_max;
+  for (unsigned int j = tid; j < ns2; j += 1024) {
+    const unsigned int r = n1 + (unsigned int)(((unsigned long long)j * nsamp) / ns2);
+    src2[n2 + j] = r;
+    map2[n2 + j] = cand1[r];
+    cia2[n2 + j] = cia1[r];
+    cib2[n2 + j] = cib1[r];
+  }
+  if (tid == 0) {
+    rs[RS_COUNT2] = count2;
+    rs[RS_N2] = n2;
+    rs[RS_M2] = n2 + ns2;
+    if (count2 > cap2 || n1 < B) atomicOr(rs + RS_FLAGS, 2u);
+  }
+}
+
+// exact utilities of the stage-3 rows from their per-learner probabilities, and the error statistics of both filters
+template <int KT>
+__global__ void __launch_bounds__(256) refine_finish_kernel(unsigned int *__restrict__ rs, const float *__restrict__ probs, int K,
+                                                            int C, int measure, const float *__restrict__ util_a,
+                                                            const float *__restrict__ util2, const uint32_t *__restrict__ cand1,
+                                                            const uint32_t *__restrict__ map2, const uint32_t *__restrict__ src2,
+                                                            float *__restrict__ util_c) {
+  const int KK = KT > 0 ? KT : K;
+  const unsigned int M1 = rs[RS_M1], M2 = rs[RS_M2], n1 = rs[RS_N1];
+  float m1 = 0.0f, m2 = 0.0f, ma = 0.0f, ss1 = 0.0f, ss2 = 0.0f;
+  for (unsigned int j = blockIdx.x * 256 + threadIdx.x; j < M2; j += gridDim.x * 256) {
+    float rows[2 * (KT > 0 ? KT : ALINK_MAX_K)];
+    if (C == 2) {
+      const float2 *src = reinterpret_cast<const float2 *>(probs) + (size_t)j * KK;
+#pragma unroll
+      for (int k = 0; k < KK; ++k) {
+        const float2 v = src[k];
+        rows[2 * k] = v.x;
+        rows[2 * k + 1] = v.y;
+      }
+    } else {
+#pragma unroll
+      for (int k = 0; k < KK; ++k) {
+        const float p = probs[(size_t)j * KK + k];
+        rows[2 * k] = __fsub_rn(1.0f, p);  // keras_wrapper.py:268
+        rows[2 * k + 1] = p;
+      }
+    }
+    float c0, c1;
+    alink_consensus2(rows, KK, &c0, &c1);
+    const float u = alink_utility2(measure, rows, KK, c0, c1);
+    util_c[j] = u;
+    const float e2 = fabsf(__fsub_rn(util2[src2[j]], u));
+    const float ea = fabsf(__fsub_rn(__ldg(util_a + map2[j]), u));
+    m2 = fmaxf(m2, e2);
+    ma = fmaxf(ma, ea);
+    ss2 = __fmaf_rn(e2, e2, ss2);
+  }
+  for (unsigned int r = blockIdx.x * 256 + threadIdx.x; r < M1; r += gridDim.x * 256) {
+    const float e1 = fabsf(__fsub_rn(__ldg(util_a + cand1[r]), util2[r]));
+    m1 = fmaxf(m1, e1);
+    if (r < n1) ss1 = __fmaf_rn(e1, e1, ss1);  // rms over the candidates (the pairs at risk: p near 1/2, largest slope)
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    m1 = fmaxf(m1, __shfl_xor_sync(0xffffffffu, m1, o));
+    m2 = fmaxf(m2, __shfl_xor_sync(0xffffffffu, m2, o));
+    ma = fmaxf(ma, __shfl_xor_sync(0xffffffffu, ma, o));
+    ss1 += __shfl_xor_sync(0xffffffffu, ss1, o);
+    ss2 += __shfl_xor_sync(0xffffffffu, ss2, o);
+  }
+  if ((threadIdx.x & 31) == 0) {
+    if (m1 > 0.0f) atomicMax(rs + RS_ERR1, __float_as_uint(m1));
+    if (m2 > 0.0f) atomicMax(rs + RS_ERR2, __float_as_uint(m2));
+    if (ma > 0.0f) atomicMax(rs + RS_ERRA, __float_as_uint(ma));
+    if (ss1 > 0.0f) atomicAdd(reinterpret_cast<double *>(rs + RS_SS1), (double)ss1);
+    if (ss2 > 0.0f) atomicAdd(reinterpret_cast<double *>(rs + RS_SS2), (double)ss2);
+  }
+}
+
+// max |element| and max row L2 norm of an fp32 table: one warp per row (D % 4 == 0)
+// out[0] max |element| bits, out[1] max row sum of squares bits, out[2..3] double: sum over rows of the row sum of squares
+__global__ void __launch_bounds__(256) table_stats_kernel(const float *__restrict__ x, int64_t M, int D, unsigned int *__restrict__ out) {
+  const int lane = threadIdx.x & 31;
+  float amax = 0.0f, nmax = 0.0f, nsum = 0.0f;
+  for (int64_t row = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5); row < M; row += (int64_t)gridDim.x * 8) {
+    const float4 *p = reinterpret_cast<const float4 *>(x + (size_t)row * D);
+    float ss = 0.0f;
+    for (int i = lane; i < D / 4; i += 32) {
+      const float4 v = __ldg(p + i);
+      amax = fmaxf(amax, fmaxf(fmaxf(fabsf(v.x), fabsf(v.y)), fmaxf(fabsf(v.z), fabsf(v.w))));
+      ss = __fmaf_rn(v.x, v.x, ss); ss = __fmaf_rn(v.y, v.y, ss); ss = __fmaf_rn(v.z, v.z, ss); ss = __fmaf_rn(v.w, v.w, ss);
+    }
+    for (int o = 16; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
+    nmax = fmaxf(nmax, ss);
+    nsum += ss;
+  }
+  for (int o = 16; o > 0; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
+  if (lane == 0) {
+    atomicMax(out, __float_as_uint(amax));        // non-finite elements: fmaxf drops NaN, inf stays inf (fails the bounds)
+    atomicMax(out + 1, __float_as_uint(nmax));    // max over rows of sum of squares (>= 0: uint order == float order)
+    atomicAdd(reinterpret_cast<double *>(out + 2), (double)nsum);
+  }
 }

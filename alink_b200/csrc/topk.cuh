@@ -177,7 +177,13 @@ __global__ void __launch_bounds__(1024) radix_select_small_kernel(KeySrc src, in
 
 // Whole top-B of a small source in one launch: select the B-th key, gather the B keys >= it into shared
 // memory, bitonic-sort them descending, write them out (B <= npad <= 4096).
-__global__ void __launch_bounds__(1024) topk_small_kernel(KeySrc src, int n, int B, int npad, uint64_t *__restrict__ out) {
+// n_dev: the source length lives on the device (FP32_REFINE's candidate count); n is then its capacity
+__global__ void __launch_bounds__(1024) topk_small_kernel(KeySrc src, int n, int B, int npad, uint64_t *__restrict__ out,
+                                                          const unsigned int *__restrict__ n_dev = nullptr) {
+  if (n_dev) {
+    const unsigned int nd = *n_dev;
+    if (nd < (unsigned int)n) n = (int)nd;
+  }
   __shared__ unsigned int sh[2048];
   __shared__ unsigned int part[256];
   __shared__ unsigned long long s_prefix, s_remaining;

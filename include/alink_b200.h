@@ -152,6 +152,32 @@ int alink_set_refine_eps(alink_ctx *ctx, double eps);
 int alink_refine_stats(const alink_ctx *ctx, int64_t *survivors, float *max_err);
 int alink_refine_detail(const alink_ctx *ctx, int *filter_f16, double *eps_used, float *rms_err, int *rounds);
 
+/* FP32_REFINE since round 2 runs in THREE stages without host round trips (csrc/refine.cuh): (1) the half-precision
+ * tensor-core filter over all N pairs, bound eps1; (2) a split-operand (hi + lo halves, three MMAs per product)
+ * tensor-core re-score of the candidates, bound eps2 ~ 1e-5; (3) the bit-exact CUDA-core re-score of the few pairs within
+ * 2 eps2 of the B-th value. Both bounds are verified on every query — on the candidates AND on a deterministic stratified
+ * sample of >= 4096 pairs outside them — and widened (stages repeated) when they fail. eps1 defaults to the larger of the
+ * per-format default and an a-priori statistical bound computed from the heads' norms and the tables' element / row-norm
+ * maxima. alink_set_refine_eps2: caller's eps2 (0 = default 2e-5). alink_refine_report_get: what the last query did. */
+typedef struct alink_refine_report {
+  int32_t version;        /* 2 = three stages; 1 = filter + exact re-score with host-sized grids (fallback); 0 = none */
+  int32_t filter_f16;     /* stage-1 operand format: 1 = IEEE half, 0 = bf16 */
+  int32_t rounds;         /* 1 unless a bound had to be widened */
+  int32_t reserved;
+  int64_t n_stage2;       /* candidates re-scored with split operands (|C1|) */
+  int64_t n_exact;        /* candidates re-scored exactly (|C2|) */
+  int64_t n_sample;       /* non-candidate sample carried through stage 2 */
+  int64_t n_sample_exact; /* part of it carried through stage 3 */
+  double eps1_used, eps1_apriori, eps2_used;  /* eps1_apriori: the statistical model (8 sigma, typical norms) */
+  double eps1_worst;      /* the same model with worst-case norms: reported, not used */
+  float err1_max;         /* max |stage-1 utility - best available reference| over C1, the sample and C2 */
+  float err1_rms;
+  float err2_max;         /* max |stage-2 utility - exact utility| over C2 and the exact sample */
+  float err2_rms;
+} alink_refine_report;
+int alink_set_refine_eps2(alink_ctx *ctx, double eps2);
+int alink_refine_report_get(const alink_ctx *ctx, alink_refine_report *out);
+
 /* Top-B of the context's utility vector. Replaces modAL multi_argmax (code/uncertainty.py:155,183,213).
  * idx_out (B int64), util_out (B fp32), keys_out (B packed u64 keys for cross-shard merging): any may
  * be NULL. */
