@@ -47,6 +47,61 @@ def merge_shards(local_keys: np.ndarray, B: int, merge_fn, dist=None, device=Non
     return merge_fn(np.ascontiguousarray(allk), min(B, len(allk)))
 
 
+class ShardedTableFeed:
+    """Replicated embedding table fed by 1/world-sized PCIe uploads + one NVLink all-gather (SURVEY.md 8e, e2e path).
+
+    Every rank needs the WHOLE table (pairs reference arbitrary rows), but uploading it over each rank's own PCIe link
+    multiplies host-memory traffic by the world size (8 x 410 MB per step on one NUMA node: 0.42 e2e scaling efficiency in
+    round 1). Here rank r uploads only rows [r M / W, (r + 1) M / W) from its pinned host copy into its slice of a device
+    buffer, and one in-place `all_gather_into_tensor` over NCCL / NVSwitch completes the replica on every GPU. Both run
+    on a side stream, so with two buffers the feed of step i + 1 overlaps the query of step i; `wait(buf)` makes the
+    compute stream wait on the device (no host synchronisation). world == 1 degenerates to the plain upload.
+    M is padded to a multiple of the world size (pad rows are never referenced)."""
+
+    def __init__(self, ctx, M, D, dist=None, device=None, dtype=None, n_buffers=2):
+        import torch
+        self.ctx, self.dist, self.torch = ctx, dist, torch
+        self.world = dist.get_world_size() if dist is not None and dist.is_initialized() else 1
+        self.rank = dist.get_rank() if self.world > 1 else 0
+        self.M, self.D = int(M), int(D)
+        self.rows = (self.M + self.world - 1) // self.world  # rows per rank
+        self.device = device if device is not None else torch.device("cuda", ctx.device)
+        dtype = dtype or torch.float32
+        self.bufs = [torch.empty((self.rows * self.world, self.D), dtype=dtype, device=self.device) for _ in range(n_buffers)]
+        self.side = torch.cuda.Stream(device=self.device)
+        self.ready = [torch.cuda.Event() for _ in range(n_buffers)]
+        self.free = [torch.cuda.Event() for _ in range(n_buffers)]
+        self.bytes_h2d = self.rows * self.D * self.bufs[0].element_size()
+        self.bytes_gather = self.bytes_h2d * (self.world - 1)  # received per rank over NVLink
+
+    def shard_of(self, host_table):
+        """This rank's rows of a host table (a view; pin it once with .pin_memory() for full PCIe rate)."""
+        lo = self.rank * self.rows
+        return host_table[lo:min(lo + self.rows, self.M)]
+
+    def feed_async(self, buf, host_shard):
+        """Start filling buffer `buf` from this rank's pinned shard; returns at once."""
+        torch = self.torch
+        cur = torch.cuda.current_stream(self.device)
+        self.free[buf].record(cur)           # queries already queued on the compute stream may still read the buffer
+        full = self.bufs[buf]
+        lo = self.rank * self.rows
+        with torch.cuda.stream(self.side):
+            self.side.wait_event(self.free[buf])
+            mine = full[lo:lo + self.rows]
+            mine[:host_shard.shape[0]].copy_(host_shard, non_blocking=True)
+            if self.world > 1:
+                self.dist.all_gather_into_tensor(full, mine)  # in place: rank r's slice is already where it belongs
+            self.ready[buf].record(self.side)
+
+    def wait(self, buf, slot):
+        """Compute stream waits (on the device) for the feed of `buf`, then the context's `slot` borrows it."""
+        torch = self.torch
+        torch.cuda.current_stream(self.device).wait_event(self.ready[buf])
+        self.ctx.set_table(slot, self.bufs[buf][:self.M])
+        return self.bufs[buf]
+
+
 def decode_keys(keys: np.ndarray):
     """(pair index int64, utility fp32) from packed keys (include/alink_math.h: alink_pack_key)."""
     keys = np.asarray(keys, dtype=np.uint64)

@@ -284,17 +284,32 @@ def main():
         return merge_shards(keys, B, ctx.topk_keys, dist=dist, device=dev), t
 
     e2e_slot = {"cur": 1, "primed": False}
+    feed = None
+    if world > 1:
+        # N > 1: every rank uploads 1/N of the (replicated) table over its own PCIe link and one NCCL all-gather over
+        # NVLink completes the replica on every GPU (alink_b200.dist.ShardedTableFeed); round 1 uploaded the whole table
+        # N times from one NUMA node (e2e efficiency 0.42 at N = 8)
+        from alink_b200.dist import ShardedTableFeed
+        feed = ShardedTableFeed(ctx, table_pin.shape[0], table_pin.shape[1], dist=dist, device=dev, dtype=table_pin.dtype)
+        shard_pin = feed.shard_of(table_pin)
 
     def step_e2e():
-        """host buffers in, host result out: table + indices cross PCIe inside EVERY step. Two table slots: while
-        step i is scored from one slot, the table of step i + 1 is uploaded into the other on the copy stream
-        (alink_set_table_async), so a step costs max(upload, query) instead of their sum. Each step uploads exactly
-        one table (the first call of a run uploads its own synchronously)."""
+        """host buffers in, host result out: table + indices cross PCIe inside EVERY step. Two table buffers: while
+        step i is scored from one, the table of step i + 1 is uploaded into the other on a side stream, so a step
+        costs max(upload, query) instead of their sum. Each step uploads exactly one table (the first call of a run
+        uploads its own synchronously). N = 1: alink_set_table_async (copy stream inside the library)."""
         cur, nxt = e2e_slot["cur"], 3 - e2e_slot["cur"]
-        if not e2e_slot["primed"]:
-            ctx.set_table(cur, table_pin)
-            e2e_slot["primed"] = True
-        ctx.set_table_async(nxt, table_pin)
+        if feed is not None:
+            if not e2e_slot["primed"]:
+                feed.feed_async(cur - 1, shard_pin)
+                e2e_slot["primed"] = True
+            feed.feed_async(nxt - 1, shard_pin)
+            feed.wait(cur - 1, cur)
+        else:
+            if not e2e_slot["primed"]:
+                ctx.set_table(cur, table_pin)
+                e2e_slot["primed"] = True
+            ctx.set_table_async(nxt, table_pin)
         e2e_slot["cur"] = nxt
         if world == 1:
             _, _, keys, t = ctx.query(0, cur, cur, ia_pin.numpy(), ib_pin.numpy(), N, args.measure, B, base=base,
@@ -341,6 +356,22 @@ def main():
     refine_stats = ctx.refine_stats() if args.mode == "refine" else None
     refine_detail = ctx.refine_detail() if args.mode == "refine" else None
     ms_e2e, stage_e2e, _, _, merged_e2e, _ = timed(step_e2e, max(4, min(args.steps, 8)), 2)
+    gather_ms = None
+    if feed is not None:  # the table all-gather alone (device time, max over ranks), for its bus bandwidth
+        g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        best = None
+        for _ in range(3):
+            barrier()
+            g0.record()
+            lo = feed.rank * feed.rows
+            dist.all_gather_into_tensor(feed.bufs[0], feed.bufs[0][lo:lo + feed.rows])
+            g1.record()
+            torch.cuda.synchronize()
+            tms = g0.elapsed_time(g1)
+            best = tms if best is None else min(best, tms)
+        tt = torch.tensor([best], dtype=torch.float64, device=dev)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        gather_ms = float(tt.item())
     assert np.array_equal(merged, merged_e2e), "resident and e2e paths selected different pairs"
 
     value = n_gpus * N / (ms_step / 1e3)
@@ -349,18 +380,28 @@ def main():
     flops = FLOPS_PER_PAIR(K, h.D_in, h.H1, h.H2, h.C) * N
     head_ms = stage["ms_score"]  # fp32 / bf16: the head kernel(s); refine: the tensor-core filter over all N pairs
     achieved_tf = flops / (head_ms / 1e3) / 1e12
+    step_tf = flops / (dev_ms / 1e3) / 1e12  # the whole step (what `value` measures), device time
     roofline = {"bound": "tensor", "achieved": achieved_tf, "peak": peaks["tf_sustained"], "unit": "TFLOP/s",
                 "frac": achieved_tf / peaks["tf_sustained"], "traffic": None,
+                "peak_burst": peaks["tf_burst"], "frac_burst": achieved_tf / peaks["tf_burst"],
+                "step_achieved": step_tf, "step_frac": step_tf / peaks["tf_sustained"],
+                "step_frac_burst": step_tf / peaks["tf_burst"],
+                "denominators": "frac / step_frac: measured sustained cuBLAS bf16 peak (a seconds-long loop under the power "
+                                "cap); frac_burst / step_frac_burst: measured burst peak — the timed region here is tens of "
+                                "milliseconds at full clocks, so the burst figure is the stricter, matching denominator",
                 "kernel": "siamese head (gather+|a-b| fused layer-1 GEMM, layer-2/3 + softmax)",
                 "flops_per_pair": FLOPS_PER_PAIR(K, h.D_in, h.H1, h.H2, h.C), "launch_ms": head_ms,
-                "peak_source": peaks["source"] + ", sustained bf16 (kernel timed inside a long step)"}
+                "peak_source": peaks["source"]}
     mode_name = {"fp32": "FP32_EXACT", "bf16": "BF16_TC", "refine": "FP32_REFINE"}[args.mode]
     if args.config == 2 and args.mode != "fp32" and N == 1_000_000:
         # DRAM bytes of one launch of this kernel on this workload, from the committed ncu --set full capture
         try:
-            with open(os.path.join(ROOT, "profiles", "r1_ncu_head_full_summary.json")) as f:
-                roofline["traffic"] = json.load(f)["traffic_bytes_per_launch"]
-            roofline["traffic_source"] = "profiles/r1_ncu_head_full_summary.json (dram__bytes_read.sum + dram__bytes_write.sum)"
+            with open(os.path.join(ROOT, "profiles", "r2_ncu_hbm_stages.json")) as f:
+                hk = [l for l in json.load(f)["launches"] if "head_kernel<0, 2, 1, 1>" in l["kernel"] or "head_kernel<0, 2, 0, 1>" in l["kernel"]]
+            want = "<0, 2, 0, 1>" if args.mode == "bf16" else "<0, 2, 1, 1>"
+            hk = [l for l in hk if want in l["kernel"] and l["us"] > 1500]
+            roofline["traffic"] = hk[0]["dram_read_B"] + hk[0]["dram_write_B"]
+            roofline["traffic_source"] = "profiles/r2_ncu_hbm_stages.json (dram__bytes_read.sum + dram__bytes_write.sum of this kernel, K = 5 launch)"
         except Exception:
             pass
     if args.mode == "refine":
@@ -374,7 +415,7 @@ def main():
         roofline["note"] = ("FP32_EXACT is the bit-exact correctness mode: CUDA-core FFMA, not tensor cores; "
                             f"FFMA peak at the sampled {clk:.0f} MHz = {ffma_peak:.1f} TFLOP/s")
         roofline["frac_of_ffma_peak"] = achieved_tf / ffma_peak
-    h2d = int(table_pin.numel() * table_pin.element_size() + pool.ia.nbytes + pool.ib.nbytes)
+    h2d = int((feed.bytes_h2d if feed is not None else table_pin.numel() * table_pin.element_size()) + pool.ia.nbytes + pool.ib.nbytes)
     d2h = int(B * 8)
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": n_gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
@@ -384,7 +425,11 @@ def main():
             "roofline": roofline,
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": ms_e2e, "stage_ms": stage_e2e,
-                    "call": "alink_set_table_async(HOST table of the next step, second slot) + alink_query(HOST indices) -> host top-B; every step uploads one table, overlapped with the previous step's query"},
+                    "call": ("alink_set_table_async(HOST table of the next step, second slot) + alink_query(HOST indices) -> host top-B; every step uploads one table, overlapped with the previous step's query"
+                             if feed is None else
+                             "ShardedTableFeed: each rank uploads its 1/N of the next step's table (h2d_bytes_per_step is PER RANK) + in-place NCCL all-gather over NVLink on a side stream, overlapped with the previous step's alink_query(HOST indices) -> device keys -> all-gather + merge -> host top-B"),
+                    **({"table_allgather": {"bytes_received_per_rank": feed.bytes_gather, "ranks": world, "ms_alone": gather_ms,
+                                             "busbw_GBps": feed.bytes_gather / (gather_ms / 1e3) / 1e9}} if feed is not None else {})},
             "gpu_launches": launches, "clocks": clocks}
 
     if refine_stats is not None:

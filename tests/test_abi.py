@@ -53,3 +53,26 @@ def test_sass_is_sm100a():
     import subprocess
     out = subprocess.run(["cuobjdump", "-lelf", so], capture_output=True, text=True).stdout
     assert "sm_100a" in out
+
+
+def test_hot_kernels_are_tcgen05_native():
+    """SASS of the built library (B200_PROFILING.md: tcgen05.mma -> UTC*MMA, tcgen05.ld -> LDTM, cp.async.bulk -> UBLKCP,
+    tcgen05.commit -> UTCBAR, mbarrier -> SYNCS): every variant of the three tensor-core head kernels carries them, and
+    none of them falls back to the legacy mma.sync path (HMMA). profiles/r2_sass_opcodes.txt is the committed histogram."""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("sass_opcodes", os.path.join(ROOT, "tools", "sass_opcodes.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    per = mod.histogram(_ffi.SO_PATH)
+    heads = {n: c for n, c in per.items() if "head_kernel" in n and "train_head" not in n}
+    assert len(heads) >= 12 and any("split" in n for n in heads) and any("tcko" in n for n in heads)
+    for name, cnt in heads.items():
+        ops = "".join(cnt)
+        assert any(k.startswith("UTCHMMA") for k in cnt), f"{name}: no tcgen05.mma (UTCHMMA) in SASS: {dict(cnt)}"
+        assert any(k.startswith("LDTM") for k in cnt), f"{name}: no tcgen05.ld (LDTM)"
+        assert any(k.startswith("UBLKCP") for k in cnt), f"{name}: no bulk copy (UBLKCP)"
+        assert any(k.startswith("UTCBAR") for k in cnt) and cnt.get("SYNCS", 0) > 0, f"{name}: no tcgen05.commit / mbarrier"
+        assert "HMMA" not in ops.replace("UTCHMMA", ""), f"{name}: legacy mma.sync path present"
+    # the default filter of FP32_REFINE / BF16_TC: CTA pairs (cta_group::2) with multicast commits
+    pair = [c for n, c in heads.items() if "ILb0ELi2ELb1ELb1E" in n]
+    assert pair and any(k.startswith("UTCHMMA.2CTA") for k in pair[0]) and any("MULTICAST" in k for k in pair[0])

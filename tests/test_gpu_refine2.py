@@ -1,0 +1,125 @@
+"""FP32_REFINE, three-stage pipeline (csrc/refine.cuh, head_tc_split.cuh): the selection must be IDENTICAL to
+FP32_EXACT (north_star: "selected index set bit-exact in fp32 mode") for heads well outside the synthetic default —
+logit gains 4x / 8x / 16x (trained-like, confident heads), a 2048-d ResNet-shaped pool at >= 1 M pairs, other table
+scales — and the verification machinery must do what it claims: report both stages' observed errors, see a bound that
+is too tight (on candidates AND on the non-candidate sample), widen and still return the exact selection; fall back
+when a candidate list overflows. `rounds` / eps / errors are printed for the record (pytest -s)."""
+import numpy as np
+import pytest
+from hypothesis import HealthCheck, given, settings, strategies as st
+
+from alink_b200 import _ffi, synth
+
+pytestmark = pytest.mark.gpu
+
+
+def _scaled(pool, gain):
+    for k in range(pool.heads.K):
+        pool.heads.W3[k] = (pool.heads.W3[k] * np.float32(gain)).astype(np.float32)
+    return pool
+
+
+def _both(ctx, pool, measure, B, table=None):
+    tab = pool.table if table is None else table
+    ctx.set_table(0, tab)
+    ctx.set_heads(0, pool.heads, compute=_ffi.FP32_EXACT)
+    ctx.set_heads(1, pool.heads, compute=_ffi.FP32_REFINE)
+    exact = ctx.query(0, 0, 0, pool.ia, pool.ib, pool.N, measure, B)
+    refined = ctx.query(1, 0, 0, pool.ia, pool.ib, pool.N, measure, B)
+    return exact, refined, ctx.refine_report()
+
+
+def _check(exact, refined):
+    np.testing.assert_array_equal(refined[2], exact[2])  # keys: utility bits + index, in order
+    np.testing.assert_array_equal(refined[0], exact[0])
+    np.testing.assert_array_equal(refined[1].view(np.uint32), exact[1].view(np.uint32))
+
+
+@pytest.mark.parametrize("gain", [4.0, 8.0, 16.0])
+@pytest.mark.parametrize("measure", ["uncertainty", "neg_margin", "kl_max"])
+def test_confident_heads_select_exactly(ctx, gain, measure):
+    pool = _scaled(synth.make_pool(2, N=300_000), gain)
+    exact, refined, rep = _both(ctx, pool, measure, 1000)
+    _check(exact, refined)
+    print(f"gain {gain} {measure}: {rep}")
+    assert rep["version"] in (1, 2) and rep["rounds"] >= 1
+    if rep["version"] == 2:
+        assert rep["n_sample"] >= 4096 and rep["n_exact"] >= 1000
+        assert rep["err1_max"] <= rep["eps1_used"] * 5.0 + 1e-12 and rep["err2_max"] <= rep["eps2_used"] * 5.0 + 1e-12
+        assert rep["eps1_used"] >= rep["eps1_apriori"] or rep["rounds"] > 1 or rep["eps1_used"] >= 1.5e-3
+
+
+def test_three_stage_report_on_configs1_shape(ctx):
+    pool = synth.make_pool(2, N=400_000)
+    exact, refined, rep = _both(ctx, pool, "uncertainty", 1000)
+    _check(exact, refined)
+    print(rep)
+    assert rep["version"] == 2 and rep["filter_f16"] == 1 and rep["rounds"] == 1
+    assert 1000 <= rep["n_exact"] <= 2000          # ~ B + the pairs within 2 eps2 of the B-th value
+    assert rep["n_stage2"] < 0.06 * pool.N and rep["n_sample"] >= 4096 and rep["n_sample_exact"] == 256
+    assert 0 < rep["err2_max"] < 2e-5 < rep["err1_max"] < 1.5e-3
+    assert rep["eps1_worst"] > 10 * rep["eps1_apriori"]  # why the worst-case propagation is not used as the width
+
+
+def test_resnet_shaped_2048d_pool_at_one_million_pairs(ctx):
+    pool = synth.make_pool(3, N=1_000_000, M=60_000)
+    assert pool.D == 2048
+    exact, refined, rep = _both(ctx, pool, "uncertainty", 1000)
+    _check(exact, refined)
+    print("2048-d:", rep)
+    assert rep["version"] == 2
+
+
+def test_tight_bounds_are_detected_and_widened(ctx):
+    pool = synth.make_pool(2, N=200_000)
+    ctx.set_table(0, pool.table)
+    ctx.set_heads(0, pool.heads, compute=_ffi.FP32_EXACT)
+    ctx.set_heads(1, pool.heads, compute=_ffi.FP32_REFINE)
+    exact = ctx.query(0, 0, 0, pool.ia, pool.ib, pool.N, "uncertainty", 1000)
+    try:
+        ctx.set_refine_eps(2e-5)     # the half filter errs by ~5e-4: only the NON-candidate sample can see that
+        refined = ctx.query(1, 0, 0, pool.ia, pool.ib, pool.N, "uncertainty", 1000)
+        rep = ctx.refine_report()
+        print("tight eps1:", rep)
+        _check(exact, refined)
+        assert rep["rounds"] > 1 and rep["eps1_used"] > 2e-5
+        ctx.set_refine_eps(0.0)
+        ctx.set_refine_eps2(1e-8)    # the split stage errs by ~3e-6
+        refined = ctx.query(1, 0, 0, pool.ia, pool.ib, pool.N, "uncertainty", 1000)
+        rep = ctx.refine_report()
+        print("tight eps2:", rep)
+        _check(exact, refined)
+        assert rep["rounds"] > 1 and rep["eps2_used"] > 1e-8
+    finally:
+        ctx.set_refine_eps(0.0)
+        ctx.set_refine_eps2(0.0)
+
+
+def test_tied_plateau_overflows_into_the_host_sized_pipeline(ctx):
+    """Half the pool are copies of one pair: the candidate list overflows its capacity and the query falls back to the
+    filter + exact pipeline with host-sized grids; the tie rule (lowest index) still decides."""
+    pool = synth.make_pool(2, N=600_000)
+    ctx.set_table(0, pool.table)
+    ctx.set_heads(0, pool.heads, compute=_ffi.FP32_EXACT)
+    e0 = ctx.query(0, 0, 0, pool.ia, pool.ib, pool.N, "uncertainty", 10)
+    top = int(e0[0][0])
+    pool.ia[::2] = pool.ia[top]
+    pool.ib[::2] = pool.ib[top]
+    exact, refined, rep = _both(ctx, pool, "uncertainty", 1000)
+    _check(exact, refined)
+    assert rep["version"] == 1
+    assert np.all(exact[0][:1000] % 2 == 0) or top % 2 == 1
+
+
+@settings(max_examples=6, deadline=None, suppress_health_check=[HealthCheck.function_scoped_fixture])
+@given(gain=st.sampled_from([0.25, 1.0, 3.0, 12.0]), tscale=st.sampled_from([0.05, 1.0, 40.0]),
+       measure=st.sampled_from(["uncertainty", "neg_margin", "consensus_entropy"]), act=st.sampled_from(["softmax", "sigmoid"]))
+def test_gain_and_table_scale_property(ctx, gain, tscale, measure, act):
+    """Scaling the table by s and W1 by 1/s leaves the exact scores unchanged in exact arithmetic but moves the
+    operands across the half-precision range; the split stage's power-of-two scales must follow."""
+    pool = _scaled(synth.make_pool(2, N=60_000, act=act), gain)
+    table = (pool.table * np.float32(tscale)).astype(np.float32)
+    for k in range(pool.heads.K):
+        pool.heads.W1[k] = (pool.heads.W1[k] / np.float32(tscale)).astype(np.float32)
+    exact, refined, rep = _both(ctx, pool, measure, 500, table=table)
+    _check(exact, refined)
