@@ -12,6 +12,7 @@
 #include "refine.cuh"
 #include "roc.cuh"
 #include "train.cuh"
+#include "de.cuh"
 
 #include <math.h>
 #include <new>
@@ -76,6 +77,9 @@ int alink_destroy(alink_ctx *ctx) {
                     &ctx->misc2, &ctx->misc3, &ctx->cand, &ctx->cia, &ctx->cib, &ctx->util_c, &ctx->rstat, &ctx->xscratch,
                     &ctx->train_ws, &ctx->train_y, &ctx->train_out, &ctx->util2, &ctx->cia2, &ctx->cib2, &ctx->map2, &ctx->src2};
   for (DevBuf *b : bufs) dev_release(*b);
+  DevBuf *debufs[] = {&ctx->de.pop, &ctx->de.trial, &ctx->de.e_pop, &ctx->de.e_trial, &ctx->de.viol, &ctx->de.rows, &ctx->de.ia,
+                      &ctx->de.ib, &ctx->de.consts, &ctx->de.aux};
+  for (DevBuf *b : debufs) dev_release(*b);
   if (ctx->rs_host) cudaFreeHost(ctx->rs_host);
   for (int i = 0; i < 8; ++i)
     if (ctx->ev[i]) cudaEventDestroy(ctx->ev[i]);
@@ -1275,6 +1279,187 @@ int alink_get_train_state(alink_ctx *ctx, int group, int learner, int which, flo
 int alink_set_train_state(alink_ctx *ctx, int group, int learner, int which, const float *const *host_in) {
   if (which == 0) return ctx ? alink_fail(ctx, ALINK_E_INVALID, "parameters are set with alink_set_heads") : ALINK_E_INVALID;
   return train_state_xfer(ctx, group, learner, which, (float *const *)host_in, false);
+}
+
+
+// ------------------------------------------------------------------------------------------ adversarial pool (DE)
+static size_t de_al(size_t x) { return (x + 255) & ~(size_t)255; }
+
+int alink_de_init(alink_ctx *ctx, int P, int n, int G, const double *pop, int slot_left, int slot_right, const int32_t *il,
+                  const int32_t *ir, const int32_t *targets, const double *lo, const double *hi) {
+  if (!ctx) return ALINK_E_INVALID;
+  if (P < 1 || n < 5 || G < 2 || (G & 1) || !pop || !il || !ir || !targets || !lo || !hi)
+    return alink_fail(ctx, ALINK_E_INVALID, "bad DE shape (P=%d problems, n=%d >= 5 members, G=%d genes: (index, value) pairs)", P, n, G);
+  if ((int64_t)P * n > 0x7FFFFFFFll / 8) return alink_fail(ctx, ALINK_E_INVALID, "P * n too large");
+  if (slot_left < 0 || slot_left >= ALINK_MAX_SLOTS || slot_right < 0 || slot_right >= ALINK_MAX_SLOTS)
+    return alink_fail(ctx, ALINK_E_INVALID, "bad slot");
+  ALINK_CUDA(ctx, cudaSetDevice(ctx->device));
+  DeState &d = ctx->de;
+  d.P = P; d.n = n; d.G = G; d.slot_left = slot_left; d.slot_right = slot_right; d.evaluated = false;
+  const size_t npg = (size_t)P * n * G, np_ = (size_t)P * n;
+  ALINK_TRY(dev_reserve(ctx, d.pop, sizeof(double) * npg));
+  ALINK_TRY(dev_reserve(ctx, d.trial, sizeof(double) * npg));
+  ALINK_TRY(dev_reserve(ctx, d.e_pop, sizeof(float) * np_));
+  ALINK_TRY(dev_reserve(ctx, d.e_trial, sizeof(float) * np_));
+  ALINK_TRY(dev_reserve(ctx, d.viol, sizeof(uint32_t) * (npg + P)));
+  ALINK_TRY(dev_reserve(ctx, d.consts, de_al(12 * (size_t)P) + de_al(16 * (size_t)G) + de_al((size_t)P)));
+  char *c = (char *)d.consts.p;
+  ALINK_CUDA(ctx, cudaMemcpyAsync(d.pop.p, pop, sizeof(double) * npg, cudaMemcpyHostToDevice, ctx->stream));
+  ALINK_CUDA(ctx, cudaMemcpyAsync(c, il, 4 * (size_t)P, cudaMemcpyHostToDevice, ctx->stream));
+  ALINK_CUDA(ctx, cudaMemcpyAsync(c + 4 * (size_t)P, ir, 4 * (size_t)P, cudaMemcpyHostToDevice, ctx->stream));
+  ALINK_CUDA(ctx, cudaMemcpyAsync(c + 8 * (size_t)P, targets, 4 * (size_t)P, cudaMemcpyHostToDevice, ctx->stream));
+  char *c2 = c + de_al(12 * (size_t)P);
+  ALINK_CUDA(ctx, cudaMemcpyAsync(c2, lo, 8 * (size_t)G, cudaMemcpyHostToDevice, ctx->stream));
+  ALINK_CUDA(ctx, cudaMemcpyAsync(c2 + 8 * (size_t)G, hi, 8 * (size_t)G, cudaMemcpyHostToDevice, ctx->stream));
+  ALINK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return ALINK_OK;
+}
+
+int alink_de_mutate(alink_ctx *ctx, const double *scale, const int32_t *r0, const int32_t *r1, const uint8_t *cross, uint64_t seed,
+                    uint64_t gen, double dither_lo, double dither_hi, double cr, uint32_t *nviol_out) {
+  if (!ctx) return ALINK_E_INVALID;
+  DeState &d = ctx->de;
+  if (d.P < 1) return alink_fail(ctx, ALINK_E_STATE, "alink_de_init first");
+  if ((r0 == nullptr) != (r1 == nullptr) || (r0 && !scale)) return alink_fail(ctx, ALINK_E_INVALID, "scale, r0 and r1 come together");
+  ALINK_CUDA(ctx, cudaSetDevice(ctx->device));
+  const size_t npg = (size_t)d.P * d.n * d.G, np_ = (size_t)d.P * d.n;
+  const double *dscale = nullptr;
+  const int32_t *dr0 = nullptr, *dr1 = nullptr;
+  const uint8_t *dcross = nullptr;
+  uint32_t *viol = (uint32_t *)d.viol.p, *nviol = viol + npg;
+  if (r0) {  // the reference's random stream, drawn on the host
+    const size_t o1 = de_al(8 * (size_t)d.P), o2 = o1 + de_al(4 * np_), o3 = o2 + de_al(4 * np_);
+    ALINK_TRY(dev_reserve(ctx, d.aux, o3 + (cross ? npg : 0) + 256));
+    char *a = (char *)d.aux.p;
+    ALINK_CUDA(ctx, cudaMemcpyAsync(a, scale, 8 * (size_t)d.P, cudaMemcpyHostToDevice, ctx->stream));
+    ALINK_CUDA(ctx, cudaMemcpyAsync(a + o1, r0, 4 * np_, cudaMemcpyHostToDevice, ctx->stream));
+    ALINK_CUDA(ctx, cudaMemcpyAsync(a + o2, r1, 4 * np_, cudaMemcpyHostToDevice, ctx->stream));
+    if (cross) ALINK_CUDA(ctx, cudaMemcpyAsync(a + o3, cross, npg, cudaMemcpyHostToDevice, ctx->stream));
+    dscale = (const double *)a;
+    dr0 = (const int32_t *)(a + o1);
+    dr1 = (const int32_t *)(a + o2);
+    dcross = cross ? (const uint8_t *)(a + o3) : nullptr;
+    ALINK_CUDA(ctx, cudaMemsetAsync(nviol, 0, 4 * (size_t)d.P, ctx->stream));
+  }
+  size_t blocks = (npg + 255) / 256;
+  if (blocks > (size_t)ctx->sm_count * 16) blocks = (size_t)ctx->sm_count * 16;
+  de_mutate_kernel<<<(unsigned)blocks, 256, 0, ctx->stream>>>((const double *)d.pop.p, d.P, d.n, d.G, dscale, dr0, dr1, dcross, seed, gen,
+                                                              dither_lo, dither_hi, cr, (double *)d.trial.p, r0 ? viol : nullptr, nviol);
+  ALINK_LAUNCHED(ctx);
+  if (r0 && nviol_out) {
+    ALINK_CUDA(ctx, cudaMemcpyAsync(nviol_out, nviol, 4 * (size_t)d.P, cudaMemcpyDeviceToHost, ctx->stream));
+    ALINK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  }
+  return ALINK_OK;
+}
+
+int alink_de_repair(alink_ctx *ctx, const double *rnd, const int64_t *off) {
+  if (!ctx) return ALINK_E_INVALID;
+  DeState &d = ctx->de;
+  if (d.P < 1 || !off) return alink_fail(ctx, ALINK_E_STATE, "alink_de_init / alink_de_mutate first");
+  const int64_t total = off[d.P];
+  if (total <= 0) return ALINK_OK;
+  if (!rnd) return alink_fail(ctx, ALINK_E_INVALID, "null repair values");
+  ALINK_CUDA(ctx, cudaSetDevice(ctx->device));
+  const size_t o1 = de_al(8 * (size_t)total);
+  ALINK_TRY(dev_reserve(ctx, d.aux, o1 + 8 * (size_t)(d.P + 1)));
+  char *a = (char *)d.aux.p;
+  ALINK_CUDA(ctx, cudaMemcpyAsync(a, rnd, 8 * (size_t)total, cudaMemcpyHostToDevice, ctx->stream));
+  ALINK_CUDA(ctx, cudaMemcpyAsync(a + o1, off, 8 * (size_t)(d.P + 1), cudaMemcpyHostToDevice, ctx->stream));
+  de_repair_kernel<<<d.P, 256, 0, ctx->stream>>>((double *)d.trial.p, (const uint32_t *)d.viol.p, d.n, d.G, (const double *)a,
+                                                 (const int64_t *)(a + o1));
+  ALINK_LAUNCHED(ctx);
+  ALINK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));  // rnd / off are the caller's
+  return ALINK_OK;
+}
+
+// which = 0: the population (first evaluation; the best member swaps into slot 0); 1: the trials; 2: the best members only
+// (probs_out: host [P][K][C] per-learner probabilities of the perturbed pairs; rows_out: host [P][D] perturbed left rows)
+int alink_de_evaluate(alink_ctx *ctx, int group, int which, float *probs_out, float *rows_out) {
+  if (!ctx) return ALINK_E_INVALID;
+  DeState &d = ctx->de;
+  if (d.P < 1) return alink_fail(ctx, ALINK_E_STATE, "alink_de_init first");
+  if (which < 0 || which > 2) return alink_fail(ctx, ALINK_E_INVALID, "which outside 0..2");
+  if (group < 0 || group >= ALINK_MAX_GROUPS || !ctx->groups[group].set) return alink_fail(ctx, ALINK_E_STATE, "head group %d not set", group);
+  ALINK_CUDA(ctx, cudaSetDevice(ctx->device));
+  ALINK_TRY(table_wait(ctx, d.slot_left));
+  ALINK_TRY(table_wait(ctx, d.slot_right));
+  const Table &L = ctx->tables[d.slot_left], &R = ctx->tables[d.slot_right];
+  if (!L.p || !R.p || L.dtype != ALINK_F32 || R.dtype != ALINK_F32 || L.D != R.D)
+    return alink_fail(ctx, ALINK_E_STATE, "the DE objective needs fp32 tables of one width in both slots");
+  const HeadGroup &g = ctx->groups[group];
+  const int D = L.D, nn = which == 2 ? 1 : d.n;
+  const int64_t N = (int64_t)d.P * nn;
+  ALINK_TRY(dev_reserve(ctx, d.rows, sizeof(float) * (size_t)N * D));
+  ALINK_TRY(dev_reserve(ctx, d.ia, sizeof(int32_t) * (size_t)N));
+  ALINK_TRY(dev_reserve(ctx, d.ib, sizeof(int32_t) * (size_t)N));
+  const char *c = (const char *)d.consts.p;
+  const int32_t *il = (const int32_t *)c, *ir = il + d.P, *tg = ir + d.P;
+  const double *lo = (const double *)(c + de_al(12 * (size_t)d.P)), *hi = lo + d.G;
+  // which == 2 reads member 0 of every problem: a population of stride n * G with n = 1 member taken
+  const double *genes = which == 1 ? (const double *)d.trial.p : (const double *)d.pop.p;
+  int64_t blocks = (N + 7) / 8;
+  if (blocks > (int64_t)ctx->sm_count * 16) blocks = (int64_t)ctx->sm_count * 16;
+  if (which == 2) {
+    de_perturb_kernel<<<(unsigned)blocks, 256, 0, ctx->stream>>>(genes, d.P, 1, d.G, (int64_t)d.G * d.n, (const float *)L.p, il, ir, D, lo, hi,
+                                                                 (float *)d.rows.p, (int32_t *)d.ia.p, (int32_t *)d.ib.p);
+  } else {
+    de_perturb_kernel<<<(unsigned)blocks, 256, 0, ctx->stream>>>(genes, d.P, d.n, d.G, (int64_t)d.G, (const float *)L.p, il, ir, D, lo, hi,
+                                                                 (float *)d.rows.p, (int32_t *)d.ia.p, (int32_t *)d.ib.p);
+  }
+  ALINK_LAUNCHED(ctx);
+  Table A;
+  A.p = d.rows.p; A.M = N; A.D = D; A.dtype = ALINK_F32;
+  const uint32_t apG = ctx->ap_G;
+  ctx->ap_G = 0;
+  const int rc = score_impl(ctx, group, A, R, (const int32_t *)d.ia.p, (const int32_t *)d.ib.p, N);
+  ctx->ap_G = apG;
+  ALINK_TRY(rc);
+  if (which == 2) {
+    if (probs_out) ALINK_TRY(copy_out(ctx, probs_out, ctx->probs.p, sizeof(float) * (size_t)N * g.K * g.C, ALINK_HOST));
+    if (rows_out) ALINK_TRY(copy_out(ctx, rows_out, d.rows.p, sizeof(float) * (size_t)N * D, ALINK_HOST));
+    ALINK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return ALINK_OK;
+  }
+  float *e = which == 1 ? (float *)d.e_trial.p : (float *)d.e_pop.p;
+  int64_t eb = (N + 255) / 256;
+  if (eb > (int64_t)ctx->sm_count * 8) eb = (int64_t)ctx->sm_count * 8;
+  de_energy_kernel<<<(unsigned)eb, 256, 0, ctx->stream>>>((const float *)ctx->probs.p, N, d.n, g.K, g.C, tg, e);
+  ALINK_LAUNCHED(ctx);
+  if (which == 0) {
+    de_best_first_kernel<<<d.P, 256, 0, ctx->stream>>>((double *)d.pop.p, (float *)d.e_pop.p, d.n, d.G);
+    ALINK_LAUNCHED(ctx);
+    d.evaluated = true;
+  }
+  return ALINK_OK;
+}
+
+int alink_de_select(alink_ctx *ctx, const uint8_t *active) {
+  if (!ctx) return ALINK_E_INVALID;
+  DeState &d = ctx->de;
+  if (d.P < 1 || !d.evaluated) return alink_fail(ctx, ALINK_E_STATE, "evaluate the population (which = 0) and the trials (which = 1) first");
+  ALINK_CUDA(ctx, cudaSetDevice(ctx->device));
+  uint8_t *dact = nullptr;
+  if (active) {
+    dact = (uint8_t *)d.consts.p + de_al(12 * (size_t)d.P) + de_al(16 * (size_t)d.G);
+    ALINK_CUDA(ctx, cudaMemcpyAsync(dact, active, (size_t)d.P, cudaMemcpyHostToDevice, ctx->stream));
+  }
+  de_select_kernel<<<d.P, 256, 0, ctx->stream>>>((double *)d.pop.p, (float *)d.e_pop.p, (const double *)d.trial.p, (const float *)d.e_trial.p,
+                                                 d.n, d.G, dact);
+  ALINK_LAUNCHED(ctx);
+  if (active) ALINK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return ALINK_OK;
+}
+
+int alink_de_get(alink_ctx *ctx, double *pop_out, float *e_out) {
+  if (!ctx) return ALINK_E_INVALID;
+  DeState &d = ctx->de;
+  if (d.P < 1) return alink_fail(ctx, ALINK_E_STATE, "alink_de_init first");
+  ALINK_CUDA(ctx, cudaSetDevice(ctx->device));
+  if (pop_out) ALINK_TRY(copy_out(ctx, pop_out, d.pop.p, sizeof(double) * (size_t)d.P * d.n * d.G, ALINK_HOST));
+  if (e_out) ALINK_TRY(copy_out(ctx, e_out, d.e_pop.p, sizeof(float) * (size_t)d.P * d.n, ALINK_HOST));
+  ALINK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return ALINK_OK;
 }
 
 // ------------------------------------------------------------------------------------------ ROC counts

@@ -61,6 +61,19 @@ struct Table {
 
 struct SelectState;  // topk.cuh
 
+// batched differential evolution (de.cuh): P problems x n members x G genes, device resident
+struct DeState {
+  int P = 0, n = 0, G = 0;     // problems, members, genes
+  int slot_left = 0, slot_right = 0;
+  DevBuf pop, trial;           // double [P][n][G], in [0, 1]
+  DevBuf e_pop, e_trial;       // float  [P][n]
+  DevBuf viol;                 // uint32 [P][n][G] flags of out-of-range genes, then [P] counts
+  DevBuf rows, ia, ib;         // perturbed left rows [P*n][D] and the identity / right-row index arrays
+  DevBuf consts;               // il[P] ir[P] targets[P] (int32) | lo[G] hi[G] (double) | active[P] (uint8)
+  DevBuf aux;                  // uploaded scales / samples / crossover masks / repair values
+  bool evaluated = false;      // the initial population has energies
+};
+
 struct alink_ctx {
   int device = 0;
   int sm_count = 148;
@@ -116,6 +129,7 @@ struct alink_ctx {
   DevBuf xscratch;  // head_tc_ko.cuh: per-CTA bf16 feature-tile images
   DevBuf train_ws, train_y, train_out;  // train.cuh: activations / gradients of one minibatch
   unsigned long long *wd_host = nullptr;  // host-mapped watchdog record (ptx.cuh: mbar_timeout)
+  DeState de;
 };
 
 static inline int alink_fail(alink_ctx *ctx, int code, const char *fmt, ...) {

@@ -258,6 +258,36 @@ int alink_roc_counts(alink_ctx *ctx, const float *scores, const int32_t *mask, i
                      int roc_case, const double *thresholds, int nthr, int in_space, uint64_t *tp, uint64_t *fp,
                      uint64_t *n_genuine, uint64_t *n_impostor);
 
+/* Embedding-space adversarial pool generator: batched differential evolution with the siamese head as the objective
+ * (SURVEY.md 8f.3). Replaces the solver loop of code/differential_evolution.py:540-760 (SciPy fork, whole population scored
+ * in one call :630-645, :692-714) as code/attack.py:59-103 drives it (best1bin, dither [0.5, 1), recombination 1, no
+ * polish). P problems (one per pair) x n members x G genes in [0, 1]; genes come in (coordinate index, value) pairs scaled
+ * to [lo, hi] like _scale_parameters (:763-767); a member assigns left_row[int(index)] = (float) value for each pair
+ * (perturb_image, attack.py:5-29, in embedding space) and its energy is 1 - P(target class) of the head group's mean.
+ *   alink_de_init      population (host, [P][n][G] float64), table slots, per-problem left / right rows and target class,
+ *                      per-gene bounds.
+ *   alink_de_mutate    trial = where(cross, pop[0] + scale (pop[r0] - pop[r1]), pop[c]) in float64. r0 != NULL: the caller
+ *                      supplies the reference's random stream (scale [P], r0 / r1 [P][n], cross [P][n][G] or NULL = all
+ *                      true); genes outside [0, 1] are counted per problem (nviol_out, host [P]) and wait for
+ *                      alink_de_repair. r0 == NULL: a counter-based device stream keyed on (seed, problem, gen, member, gene)
+ *                      draws everything, repairs in place, and nothing returns to the host.
+ *   alink_de_repair    _ensure_constraint (:775-780): the k-th flagged gene of problem p, in (member, gene) order, takes
+ *                      rnd[off[p] + k] (host arrays; off has P + 1 entries).
+ *   alink_de_evaluate  which = 0 population (first call: the best member swaps into slot 0, :660-668), 1 trials, 2 the best
+ *                      member of every problem only -> probs_out (host [P][K][C]) and rows_out (host [P][D], the
+ *                      perturbed left rows: the generator's product). Scores with `group` in its compute mode.
+ *   alink_de_select    :704-714 for every problem; active (host [P] bytes, may be NULL) freezes problems whose callback
+ *                      asked to stop (attack.py:83-84).
+ *   alink_de_get       population / energies back to the host (either may be NULL). */
+int alink_de_init(alink_ctx *ctx, int P, int n, int G, const double *pop, int slot_left, int slot_right, const int32_t *il,
+                  const int32_t *ir, const int32_t *targets, const double *lo, const double *hi);
+int alink_de_mutate(alink_ctx *ctx, const double *scale, const int32_t *r0, const int32_t *r1, const uint8_t *cross, uint64_t seed,
+                    uint64_t gen, double dither_lo, double dither_hi, double cr, uint32_t *nviol_out);
+int alink_de_repair(alink_ctx *ctx, const double *rnd, const int64_t *off);
+int alink_de_evaluate(alink_ctx *ctx, int group, int which, float *probs_out, float *rows_out);
+int alink_de_select(alink_ctx *ctx, const uint8_t *active);
+int alink_de_get(alink_ctx *ctx, double *pop_out, float *e_out);
+
 #ifdef __cplusplus
 }
 #endif
