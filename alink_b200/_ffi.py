@@ -41,6 +41,7 @@ SYMBOLS = (
     "alink_disparity_hist", "alink_disparity_select_sharded", "alink_roc_counts",
     "alink_train_step", "alink_get_train_state", "alink_set_train_state",
     "alink_set_refine_eps2", "alink_refine_report_get",
+    "alink_de_init", "alink_de_mutate", "alink_de_repair", "alink_de_evaluate", "alink_de_select", "alink_de_get",
 )
 
 
@@ -58,13 +59,13 @@ class Timing(C.Structure):
 
 
 class RefineReport(C.Structure):
-    _fields_ = [("version", C.c_int32), ("filter_f16", C.c_int32), ("rounds", C.c_int32), ("reserved", C.c_int32),
+    _fields_ = [("version", C.c_int32), ("filter_f16", C.c_int32), ("rounds", C.c_int32), ("fallback", C.c_int32),
                 ("n_stage2", C.c_int64), ("n_exact", C.c_int64), ("n_sample", C.c_int64), ("n_sample_exact", C.c_int64),
                 ("eps1_used", C.c_double), ("eps1_apriori", C.c_double), ("eps2_used", C.c_double), ("eps1_worst", C.c_double),
                 ("err1_max", C.c_float), ("err1_rms", C.c_float), ("err2_max", C.c_float), ("err2_rms", C.c_float)]
 
     def as_dict(self):
-        return {k: getattr(self, k) for k, _ in self._fields_ if k != "reserved"}
+        return {k: getattr(self, k) for k, _ in self._fields_}
 
 
 _lib = None
@@ -155,6 +156,18 @@ def load():
     L.alink_set_refine_eps2.argtypes = [vp, dbl]
     L.alink_refine_report_get.restype = i32
     L.alink_refine_report_get.argtypes = [vp, C.POINTER(RefineReport)]
+    L.alink_de_init.restype = i32
+    L.alink_de_init.argtypes = [vp, i32, i32, i32, vp, i32, i32, vp, vp, vp, vp, vp]
+    L.alink_de_mutate.restype = i32
+    L.alink_de_mutate.argtypes = [vp, vp, vp, vp, vp, u64, u64, dbl, dbl, dbl, vp]
+    L.alink_de_repair.restype = i32
+    L.alink_de_repair.argtypes = [vp, vp, vp]
+    L.alink_de_evaluate.restype = i32
+    L.alink_de_evaluate.argtypes = [vp, i32, i32, vp, vp]
+    L.alink_de_select.restype = i32
+    L.alink_de_select.argtypes = [vp, vp]
+    L.alink_de_get.restype = i32
+    L.alink_de_get.argtypes = [vp, vp, vp]
     _lib = L
     return L
 
@@ -477,6 +490,60 @@ class Context:
 
     def set_refine_eps(self, eps):
         self._check(self._L.alink_set_refine_eps(self._h, float(eps)))
+
+    # ---- batched differential evolution (csrc/de.cuh; alink_b200/attack.py drives it)
+    def de_init(self, pop, slot_left, slot_right, il, ir, targets, lo, hi):
+        pop = np.ascontiguousarray(pop, dtype=np.float64)
+        P, n, G = pop.shape
+        il, ir, tg = (np.ascontiguousarray(a, dtype=np.int32) for a in (il, ir, targets))
+        lo, hi = np.ascontiguousarray(lo, dtype=np.float64), np.ascontiguousarray(hi, dtype=np.float64)
+        assert il.shape == ir.shape == tg.shape == (P,) and lo.shape == hi.shape == (G,)
+        self._check(self._L.alink_de_init(self._h, P, n, G, pop.ctypes.data, slot_left, slot_right, il.ctypes.data,
+                                          ir.ctypes.data, tg.ctypes.data, lo.ctypes.data, hi.ctypes.data))
+        self._de_shape = (P, n, G)
+
+    def de_mutate_reference(self, scale, r0, r1, cross=None):
+        """Trials from the caller's (the reference's) random stream; returns the per-problem count of out-of-range genes."""
+        P, n, G = self._de_shape
+        scale = np.ascontiguousarray(scale, dtype=np.float64)
+        r0, r1 = np.ascontiguousarray(r0, dtype=np.int32), np.ascontiguousarray(r1, dtype=np.int32)
+        assert scale.shape == (P,) and r0.shape == r1.shape == (P, n)
+        cr = None if cross is None else np.ascontiguousarray(cross, dtype=np.uint8)
+        nv = np.zeros((P,), np.uint32)
+        self._check(self._L.alink_de_mutate(self._h, scale.ctypes.data, r0.ctypes.data, r1.ctypes.data,
+                                            None if cr is None else cr.ctypes.data, 0, 0, 0.0, 0.0, 1.0, nv.ctypes.data))
+        return nv
+
+    def de_mutate_device(self, seed, gen, dither=(0.5, 1.0), recombination=1.0):
+        self._check(self._L.alink_de_mutate(self._h, None, None, None, None, int(seed), int(gen), float(dither[0]),
+                                            float(dither[1]), float(recombination), None))
+
+    def de_repair(self, rnd, off):
+        rnd = np.ascontiguousarray(rnd, dtype=np.float64)
+        off = np.ascontiguousarray(off, dtype=np.int64)
+        self._check(self._L.alink_de_repair(self._h, rnd.ctypes.data if rnd.size else None, off.ctypes.data))
+
+    def de_evaluate(self, group, which, K=1, Cc=2, D=None, want_rows=False):
+        """which: 0 population (first evaluation), 1 trials, 2 best members -> (probs (P, K, C), rows (P, D) or None)."""
+        if which != 2:
+            self._check(self._L.alink_de_evaluate(self._h, group, which, None, None))
+            return None
+        P = self._de_shape[0]
+        probs = np.empty((P, K, Cc), np.float32)
+        rows = np.empty((P, D), np.float32) if want_rows else None
+        self._check(self._L.alink_de_evaluate(self._h, group, 2, probs.ctypes.data, None if rows is None else rows.ctypes.data))
+        return probs, rows
+
+    def de_select(self, active=None):
+        a = None if active is None else np.ascontiguousarray(active, dtype=np.uint8)
+        self._check(self._L.alink_de_select(self._h, None if a is None else a.ctypes.data))
+
+    def de_get(self, want_pop=True):
+        P, n, G = self._de_shape
+        pop = np.empty((P, n, G), np.float64) if want_pop else None
+        e = np.empty((P, n), np.float32)
+        self._check(self._L.alink_de_get(self._h, None if pop is None else pop.ctypes.data, e.ctypes.data))
+        return pop, e
 
     def set_refine_eps2(self, eps2):
         self._check(self._L.alink_set_refine_eps2(self._h, C.c_double(float(eps2))))

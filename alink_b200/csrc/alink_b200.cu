@@ -798,8 +798,10 @@ static int refine_query_v2(alink_ctx *ctx, const HeadGroup &g, Table &A, Table &
     h1max = xmax * g.w1_col_l1 + g.b1_absmax;
     ok = xmax < 6.0e4 && h1max < 6.0e4 && g.w_absmax < 6.0e4 && xmax > 0.0;  // the half filter cannot overflow
   }
+  ctx->refine_fallback = 0;
   if (!ok) {
     ctx->refine_version = 1;
+    ctx->refine_fallback = 1;
     ALINK_TRY(refine_query(ctx, g, A, Bt, ia, ib, N, measure, B, base, ev));
     if (ev) ALINK_CUDA(ctx, cudaEventRecord(ev[4], ctx->stream));
     return emit_selection(ctx, B, idx_out, util_out, keys_out, out_space);
@@ -936,6 +938,7 @@ static int refine_query_v2(alink_ctx *ctx, const HeadGroup &g, Table &A, Table &
     ctx->refine_rounds = round;
     if (h[RS_FLAGS]) {  // a candidate list overflowed (plateaus of tied utilities): the host-sized pipeline takes any size
       ctx->refine_version = 1;
+      ctx->refine_fallback = 2 + (int)(h[RS_FLAGS] & 3u);  // 3: stage-1 list, 4: stage-2 list, 5: both
       ALINK_TRY(refine_query(ctx, g, A, Bt, ia, ib, N, measure, B, base, nullptr));
       return emit_selection(ctx, B, idx_out, util_out, keys_out, out_space);
     }
@@ -950,6 +953,7 @@ static int refine_query_v2(alink_ctx *ctx, const HeadGroup &g, Table &A, Table &
     if ((!bad1 && !bad2) || round >= 5) {
       if (bad1 || bad2) {  // could not be verified in 5 rounds: run it exactly
         ctx->refine_version = 1;
+        ctx->refine_fallback = 6;
         ALINK_TRY(refine_query(ctx, g, A, Bt, ia, ib, N, measure, B, base, nullptr));
         return emit_selection(ctx, B, idx_out, util_out, keys_out, out_space);
       }
@@ -984,6 +988,7 @@ int alink_refine_report_get(const alink_ctx *ctx, alink_refine_report *out) {
   out->version = ctx->refine_version;
   out->filter_f16 = ctx->refine_f16;
   out->rounds = ctx->refine_rounds;
+  out->fallback = ctx->refine_fallback;
   out->n_exact = ctx->refine_survivors;
   out->eps1_used = ctx->refine_eps_used;
   out->err1_max = ctx->refine_max_err;

@@ -122,6 +122,7 @@ struct alink_ctx {
   double refine_eps_hint[ALINK_MAX_GROUPS] = {0, 0, 0, 0};  // bound a previous query of the group had to widen to
   float refine_err1 = 0.0f, refine_err2 = 0.0f, refine_rms2 = 0.0f;  // max |u~ - u2| over C1 u S; max / rms |u2 - u| over C2 u S2
   int64_t refine_n1 = 0, refine_nsample = 0, refine_nsample2 = 0;
+  int refine_fallback = 0;                  // why the last query left the three-stage pipeline (alink_refine_report.fallback)
   int refine_version = 0;                   // pipeline the last query ran (2 = three stages, 1 = filter + FFMA)
   // all-pairs enumeration (alink_*_allpairs): pair n = (probe row (ap_pair0 + n) / ap_G, gallery row (..) % ap_G)
   uint32_t ap_G = 0;

@@ -163,7 +163,8 @@ typedef struct alink_refine_report {
   int32_t version;        /* 2 = three stages; 1 = filter + exact re-score with host-sized grids (fallback); 0 = none */
   int32_t filter_f16;     /* stage-1 operand format: 1 = IEEE half, 0 = bf16 */
   int32_t rounds;         /* 1 unless a bound had to be widened */
-  int32_t reserved;
+  int32_t fallback;       /* 0 stayed in three stages; 1 shape / format not taken; 3 / 4 / 5 stage-1 / stage-2 / both candidate lists
+                             overflowed (tied plateaus); 6 bounds not verifiable in 5 rounds */
   int64_t n_stage2;       /* candidates re-scored with split operands (|C1|) */
   int64_t n_exact;        /* candidates re-scored exactly (|C2|) */
   int64_t n_sample;       /* non-candidate sample carried through stage 2 */

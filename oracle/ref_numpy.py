@@ -292,3 +292,45 @@ def create_mini_batch_mtp(X_plain):
                     X_right.append(y)
                     Y.append([1] if i == j else [0])
     return [np.stack(X_left), np.stack(X_right)], np.stack(Y)
+
+
+# ---- batched differential evolution, one generation (code/differential_evolution.py:673-748) in the PARALLEL form the
+# CUDA kernels use (alink_b200/csrc/de.cuh); checked against the reference solver's own output (tests/golden/ref_de.npz)
+def de_mutate(pop, scale, r0, r1, cross=None):
+    """best1bin trial vectors of one problem: pop (n, G) float64 -> (trial, flags of genes outside [0, 1])."""
+    bprime = pop[0][None, :] + scale * (pop[r0] - pop[r1])  # :820-826
+    trial = bprime if cross is None else np.where(cross.astype(bool), bprime, pop)
+    return trial, (trial < 0) | (trial > 1)
+
+
+def de_repair(trial, flags, rnd):
+    """_ensure_constraint (:775-780): the k-th flagged gene in (member, gene) order takes rnd[k]."""
+    t = trial.copy()
+    t[flags] = rnd[: int(flags.sum())]  # boolean indexing enumerates row-major = (member, gene) order
+    return t
+
+
+def de_first(pop, e):
+    """_calculate_population_energies (:660-668): the best member swaps into slot 0."""
+    m = int(np.argmin(e))
+    pop, e = pop.copy(), e.copy()
+    e[[0, m]] = e[[m, 0]]
+    pop[[0, m]] = pop[[m, 0]]
+    return pop, e
+
+
+def de_select(pop, e, trial, e_trial):
+    """:704-714 without the sequential loop: member c takes a LOWER-energy trial; slot 0 then takes the accepted trial
+    (c > 0) of lowest energy if it beats slot 0 — the first such member on ties."""
+    pop, e = pop.copy(), e.copy()
+    acc = e_trial < e
+    pop[acc] = trial[acc]
+    e[acc] = e_trial[acc]
+    cand = np.nonzero(acc)[0]
+    cand = cand[cand > 0]
+    if len(cand):
+        c = cand[np.argmin(e_trial[cand])]  # argmin: first minimum
+        if e_trial[c] < e[0]:
+            e[0] = e_trial[c]
+            pop[0] = trial[c]
+    return pop, e
