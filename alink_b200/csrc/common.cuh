@@ -7,6 +7,7 @@
 #include <stdio.h>
 #include <string.h>
 #include <stdarg.h>
+#include <stdlib.h>
 
 #include "../../include/alink_b200.h"
 #include "../../include/alink_math.h"
@@ -209,10 +210,11 @@ static inline int stage_in(alink_ctx *ctx, const void *src, size_t bytes, int sp
     return ALINK_OK;
   }
   ALINK_TRY(dev_reserve(ctx, stage, bytes));
-  // While an asynchronous table upload occupies the host-to-device copy engine (alink_set_table_async), a
-  // cudaMemcpyAsync of this call's small inputs would queue behind it; page-locked inputs are then read by a
-  // kernel instead, sharing the link with the upload.
-  if (ctx->copy_busy && bytes % 16 == 0 && ((uintptr_t)src & 15u) == 0) {
+  // Page-locked inputs are read by a kernel straight over PCIe instead of a cudaMemcpyAsync: a copy would queue on the
+  // host-to-device copy engine behind any table upload in flight (alink_set_table_async, or the caller's own side
+  // stream: alink_b200.dist.ShardedTableFeed), serialising the step behind it; the kernel shares the link instead.
+  static const int zc_env = [] { const char *e = getenv("ALINK_ZERO_COPY_IN"); return e ? atoi(e) : 1; }();
+  if ((zc_env == 1 || ctx->copy_busy) && zc_env != 2 && bytes % 16 == 0 && ((uintptr_t)src & 15u) == 0 && bytes <= (64u << 20)) {
     cudaPointerAttributes at;
     if (cudaPointerGetAttributes(&at, src) == cudaSuccess && at.type == cudaMemoryTypeHost && at.devicePointer) {
       const size_t n16 = bytes / 16;
@@ -233,6 +235,15 @@ static inline int stage_in(alink_ctx *ctx, const void *src, size_t bytes, int sp
 
 static inline int copy_out(alink_ctx *ctx, void *dst, const void *src_dev, size_t bytes, int space) {
   if (!dst || bytes == 0) return ALINK_OK;
+  if (space == ALINK_DEVICE && bytes % 16 == 0 && bytes <= (1u << 20) && (((uintptr_t)dst | (uintptr_t)src_dev) & 15u) == 0) {
+    // small device-to-device results (the B keys of a shard): a kernel, not a copy-engine job that could queue behind an upload
+    const size_t n16 = bytes / 16;
+    size_t blocks = (n16 + 255) / 256;
+    if (blocks > 64) blocks = 64;
+    zero_copy_in_kernel<<<(unsigned)blocks, 256, 0, ctx->stream>>>((const uint4 *)src_dev, (uint4 *)dst, n16);
+    ALINK_LAUNCHED(ctx);
+    return ALINK_OK;
+  }
   ALINK_CUDA(ctx, cudaMemcpyAsync(dst, src_dev, bytes,
                                   space == ALINK_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost,
                                   ctx->stream));

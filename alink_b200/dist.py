@@ -83,6 +83,9 @@ class ShardedTableFeed:
         """Start filling buffer `buf` from this rank's pinned shard; returns at once."""
         torch = self.torch
         cur = torch.cuda.current_stream(self.device)
+        if cur.cuda_stream == 0:
+            raise RuntimeError("ShardedTableFeed needs a non-default compute stream (torch.cuda.set_stream(torch.cuda.Stream())): "
+                               "the legacy default stream synchronises with the feed's side stream and serialises the overlap")
         self.free[buf].record(cur)           # queries already queued on the compute stream may still read the buffer
         full = self.bufs[buf]
         lo = self.rank * self.rows

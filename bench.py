@@ -202,6 +202,7 @@ def main():
     ap.add_argument("--cpu-sample", type=int, default=100_000)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-mode-compare", action="store_true")
+    ap.add_argument("--no-target", action="store_true", help="skip the north-star target block at --gpus 8")
     ap.add_argument("--no-clock-sampling", action="store_true", help="for runs under ncu: no NVML polling thread")
     args = ap.parse_args()
 
@@ -259,6 +260,9 @@ def main():
     base = rank * N  # global pair index of this shard's first pair
     mode = _ffi.COMPUTE_ID[args.mode]
 
+    # a non-default stream for everything timed: the legacy default stream synchronises implicitly with every blocking
+    # stream, which would serialise the e2e pipeline (table feed on a side stream) behind each kernel of the query
+    torch.cuda.set_stream(torch.cuda.Stream(device=dev))
     ctx = _ffi.Context(local_rank)
     ctx.set_stream(torch.cuda.current_stream().cuda_stream)
     ctx.set_heads(0, pool.heads, compute=mode)
@@ -355,6 +359,7 @@ def main():
     ms_step, stage, launches, clocks, merged, dev_ms = timed(step_resident, args.steps, args.warmup, sample_clocks=not args.no_clock_sampling)
     refine_stats = ctx.refine_stats() if args.mode == "refine" else None
     refine_detail = ctx.refine_detail() if args.mode == "refine" else None
+    refine_report = ctx.refine_report() if args.mode == "refine" else None
     ms_e2e, stage_e2e, _, _, merged_e2e, _ = timed(step_e2e, max(4, min(args.steps, 8)), 2)
     gather_ms = None
     if feed is not None:  # the table all-gather alone (device time, max over ranks), for its bus bandwidth
@@ -432,9 +437,31 @@ def main():
                                              "busbw_GBps": feed.bytes_gather / (gather_ms / 1e3) / 1e9}} if feed is not None else {})},
             "gpu_launches": launches, "clocks": clocks}
 
+    if world == 8 and args.config == 2 and not args.no_target:
+        # north_star target shape, measured by the same run: 10 M pairs x 512-d, K = 5, top-1000 over 8 GPUs (1.25 M pairs per
+        # GPU), fp32-identical selection (FP32_REFINE); device-resident, same timing protocol, outside the headline value
+        NT = 10_000_000 // world
+        ta, tb, _ = synth.make_pairs(NT, pool.table.shape[0], 50_000, seed=synth.BASE_SEED + 202 + 1000 * rank)
+        ta_dev, tb_dev = torch.from_numpy(ta).to(dev), torch.from_numpy(tb).to(dev)
+        tbase = rank * NT
+
+        def step_target():
+            _, _, keys, t = ctx.query(0, 0, 0, ta_dev, tb_dev, NT, args.measure, B, base=tbase, timing=True, out=out_dev)
+            return merge_shards(keys, B, ctx.topk_keys, dist=dist, device=dev), t
+
+        ms_t, stage_t, _, _, merged_t, dev_t = timed(step_target, max(3, args.steps), 3)
+        tflops = FLOPS_PER_PAIR(K, h.D_in, h.H1, h.H2, h.C) * NT
+        tf_gpu = tflops / (ms_t / 1e3) / 1e12
+        line["target"] = {"shape": "north_star: 10,000,000 pairs x 512-d, K=5, top-1000 over 8 GPUs, FP32_REFINE (selection identical to fp32)",
+                          "pairs_total": NT * world, "ms_per_step": ms_t, "pairs_per_s": NT * world / (ms_t / 1e3), "stage_ms": stage_t,
+                          "tflops_per_gpu_whole_step": tf_gpu, "step_frac": tf_gpu / peaks["tf_sustained"],
+                          "step_frac_burst": tf_gpu / peaks["tf_burst"],
+                          "head_frac": tflops / (stage_t["ms_score"] / 1e3) / 1e12 / peaks["tf_sustained"],
+                          "head_frac_burst": tflops / (stage_t["ms_score"] / 1e3) / 1e12 / peaks["tf_burst"],
+                          "refine": ctx.refine_report(), "top1": [int(v) for v in decode_keys(merged_t[:1])[0]]}
     if refine_stats is not None:
         line["refine"] = {"survivors_rescored_exactly": refine_stats[0], "max_abs_utility_error_seen": refine_stats[1],
-                          **refine_detail, "stage_ms": {"tc_filter": stage["ms_score"], "mark_and_exact_rescore": stage["ms_utility"],
+                          **refine_detail, "report": refine_report, "stage_ms": {"tc_filter": stage["ms_score"], "mark_and_exact_rescore": stage["ms_utility"],
                                                     "select": stage["ms_select"]}}
     if n_gpus == 1 and not args.no_mode_compare and args.config == 2:
         # outside the timed region: the same step in the other compute modes, and how the selections compare
