@@ -41,6 +41,7 @@ SYMBOLS = (
     "alink_disparity_hist", "alink_disparity_select_sharded", "alink_roc_counts",
     "alink_train_step", "alink_get_train_state", "alink_set_train_state",
     "alink_set_refine_eps2", "alink_refine_report_get",
+    "alink_perturb_rows", "alink_score_column", "alink_min_disparity",
     "alink_de_init", "alink_de_mutate", "alink_de_repair", "alink_de_evaluate", "alink_de_select", "alink_de_get",
 )
 
@@ -156,6 +157,12 @@ def load():
     L.alink_set_refine_eps2.argtypes = [vp, dbl]
     L.alink_refine_report_get.restype = i32
     L.alink_refine_report_get.argtypes = [vp, C.POINTER(RefineReport)]
+    L.alink_perturb_rows.restype = i32
+    L.alink_perturb_rows.argtypes = [vp, i32, vp, i64, i32, i32, i32, u64, i64, i32, dbl, i32, i32]
+    L.alink_score_column.restype = i32
+    L.alink_score_column.argtypes = [vp, i32, i32, vp, i32]
+    L.alink_min_disparity.restype = i32
+    L.alink_min_disparity.argtypes = [vp, vp, vp, i64, i32, i32, vp, i32]
     L.alink_de_init.restype = i32
     L.alink_de_init.argtypes = [vp, i32, i32, i32, vp, i32, i32, vp, vp, vp, vp, vp]
     L.alink_de_mutate.restype = i32
@@ -392,15 +399,18 @@ class Context:
         return (idx, util, keys, t) if timing else (idx, util, keys)
 
     def disparity_select(self, p2, p1, ratio=0.25, eps=0.05, blind=False, y=None):
-        p2 = _f32(p2)
-        p1 = _f32(p1)
-        T, N = p2.shape
-        yy = None if y is None else _f32(y).reshape(-1)
+        """p2 (T, N), p1 (N,), y (N,) or None: numpy (host) or torch cuda float32 tensors (used in place, no host hop)."""
+        dev_in = _is_torch(p2) and p2.is_cuda
+        if not dev_in:
+            p2, p1 = _f32(p2), _f32(p1)
+        T, N = int(p2.shape[0]), int(p2.shape[1])
+        yy = None if y is None else (y if _is_torch(y) else _f32(y).reshape(-1))
+        sp = _space_of(p2, p1) if yy is None else _space_of(p2, p1, yy)
         idx = np.empty((max(N, 1),), np.int64)
         n_out, active = C.c_int64(0), C.c_int64(0)
         self._check(self._L.alink_disparity_select(self._h, _ptr_space(p2)[0], _ptr_space(p1)[0], N, T,
                                                    float(ratio), float(eps), int(bool(blind)),
-                                                   _ptr_space(yy)[0], HOST, _ptr_space(idx)[0], HOST,
+                                                   _ptr_space(yy)[0], sp, _ptr_space(idx)[0], HOST,
                                                    C.byref(n_out), C.byref(active)))
         return idx[:n_out.value].copy(), int(active.value)
 
@@ -490,6 +500,28 @@ class Context:
 
     def set_refine_eps(self, eps):
         self._check(self._L.alink_set_refine_eps(self._h, float(eps)))
+
+    # ---- the A2-LINK noise-augmented pool on the device (csrc/perturb.cuh)
+    def perturb_rows(self, slot_src, idx, N, side, t, seed, slot_dst, pair_base=0, ncoord=40, vmax=0.25, normalize=True):
+        p, sp = _ptr_space(idx)
+        self._check(self._L.alink_perturb_rows(self._h, slot_src, p, int(N), sp, int(side), int(t), int(seed), int(pair_base),
+                                               int(ncoord), float(vmax), int(bool(normalize)), slot_dst))
+
+    def score_column(self, learner, col, out=None, N=None):
+        """Column of the last scores (learner -1 = Bagging mean) into a torch cuda float32 tensor `out`, or a new host array."""
+        if out is None:
+            out = np.empty((N,), np.float32)
+        p, sp = _ptr_space(out)
+        self._check(self._L.alink_score_column(self._h, int(learner), int(col), p, sp))
+        return out
+
+    def min_disparity(self, p2, p1, want=False):
+        """util[j] = min_t |p2[t][j] - p1[j]|, left in the context for select_topk (p2 (T, N), p1 (N,): host or cuda)."""
+        T, N = int(p2.shape[0]), int(p2.shape[1])
+        sp = _space_of(p2, p1)
+        u = np.empty((N,), np.float32) if want else None
+        self._check(self._L.alink_min_disparity(self._h, _ptr_space(p2)[0], _ptr_space(p1)[0], N, T, sp, _ptr_space(u)[0], HOST))
+        return u
 
     # ---- batched differential evolution (csrc/de.cuh; alink_b200/attack.py drives it)
     def de_init(self, pop, slot_left, slot_right, il, ir, targets, lo, hi):

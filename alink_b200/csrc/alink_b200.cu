@@ -13,6 +13,7 @@
 #include "roc.cuh"
 #include "train.cuh"
 #include "de.cuh"
+#include "perturb.cuh"
 
 #include <math.h>
 #include <new>
@@ -1286,6 +1287,91 @@ int alink_set_train_state(alink_ctx *ctx, int group, int learner, int which, con
   return train_state_xfer(ctx, group, learner, which, (float *const *)host_in, false);
 }
 
+
+// ------------------------------------------------------------------------------------------ A2-LINK pool
+int alink_perturb_rows(alink_ctx *ctx, int slot_src, const int32_t *idx, int64_t N, int in_space, int side, int t, uint64_t seed,
+                       int64_t pair_base, int ncoord, double vmax, int normalize, int slot_dst) {
+  if (!ctx) return ALINK_E_INVALID;
+  if (slot_src < 0 || slot_src >= ALINK_MAX_SLOTS || slot_dst < 0 || slot_dst >= ALINK_MAX_SLOTS || slot_src == slot_dst)
+    return alink_fail(ctx, ALINK_E_INVALID, "bad slots");
+  if (N < 1 || side < 0 || side > 1 || t < 0 || ncoord < 0 || pair_base < 0) return alink_fail(ctx, ALINK_E_INVALID, "bad arguments");
+  ALINK_CUDA(ctx, cudaSetDevice(ctx->device));
+  ALINK_TRY(table_wait(ctx, slot_src));
+  const Table &S = ctx->tables[slot_src];
+  if (!S.p || S.dtype != ALINK_F32) return alink_fail(ctx, ALINK_E_STATE, "the source slot needs an fp32 table");
+  if (!idx && N > S.M) return alink_fail(ctx, ALINK_E_INVALID, "identity rows exceed the table");
+  const void *didx;
+  ALINK_TRY(stage_in(ctx, idx, sizeof(int32_t) * (size_t)N, in_space, side ? ctx->idx_b : ctx->idx_a, &didx));
+  Table &T = ctx->tables[slot_dst];
+  if (T.pending) {
+    ALINK_CUDA(ctx, cudaEventSynchronize(T.ready));
+    T.pending = false;
+  }
+  ALINK_TRY(dev_reserve(ctx, T.own, sizeof(float) * (size_t)N * S.D));
+  T.p = T.own.p; T.M = N; T.D = S.D; T.dtype = ALINK_F32; T.absmax = -1.0;
+  const size_t smem = sizeof(float) * 8 * (size_t)S.D;
+  if (smem > 48 * 1024) ALINK_CUDA(ctx, cudaFuncSetAttribute(perturb_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int64_t blocks = (N + 7) / 8;
+  if (blocks > (int64_t)ctx->sm_count * 16) blocks = (int64_t)ctx->sm_count * 16;
+  perturb_rows_kernel<<<(unsigned)blocks, 256, smem, ctx->stream>>>((const float *)S.p, (const int32_t *)didx, N, S.D, side, t, seed,
+                                                                    (uint64_t)pair_base, ncoord, (float)vmax, normalize, (float *)T.own.p);
+  ALINK_LAUNCHED(ctx);
+  return ALINK_OK;
+}
+
+int alink_score_column(alink_ctx *ctx, int learner, int col, float *out, int out_space) {
+  if (!ctx) return ALINK_E_INVALID;
+  if (!ctx->probs.p || !ctx->probs_full) return alink_fail(ctx, ALINK_E_STATE, "no scores: call alink_score_* first");
+  if (learner < -1 || learner >= ctx->sK || col < 0 || col > 1 || !out) return alink_fail(ctx, ALINK_E_INVALID, "bad learner / column");
+  ALINK_CUDA(ctx, cudaSetDevice(ctx->device));
+  const int64_t N = ctx->N;
+  if (N == 0) return ALINK_OK;
+  const float *src = (const float *)ctx->probs.p;
+  int K = ctx->sK, lrn = learner;
+  if (learner < 0) {  // the Bagging mean (code/committee.py:18) first, then its column
+    ALINK_TRY(dev_reserve(ctx, ctx->cons, sizeof(float) * (size_t)N * ctx->sC));
+    ALINK_TRY(launch_utility(ctx, src, N, ctx->sK, ctx->sC, 0, nullptr, (float *)ctx->cons.p));
+    src = (const float *)ctx->cons.p;
+    K = 1;
+    lrn = 0;
+  }
+  float *dst = out;
+  if (out_space == ALINK_HOST) {
+    ALINK_TRY(dev_reserve(ctx, ctx->misc3, sizeof(float) * (size_t)N));
+    dst = (float *)ctx->misc3.p;
+  }
+  int64_t blocks = (N + 255) / 256;
+  if (blocks > (int64_t)ctx->sm_count * 8) blocks = (int64_t)ctx->sm_count * 8;
+  extract_col_kernel<<<(unsigned)blocks, 256, 0, ctx->stream>>>(src, N, K, ctx->sC, lrn, col, dst);
+  ALINK_LAUNCHED(ctx);
+  if (out_space == ALINK_HOST) {
+    ALINK_TRY(copy_out(ctx, out, dst, sizeof(float) * (size_t)N, ALINK_HOST));
+    ALINK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  }
+  return ALINK_OK;
+}
+
+int alink_min_disparity(alink_ctx *ctx, const float *p2, const float *p1, int64_t N, int T, int in_space, float *util, int out_space) {
+  if (!ctx) return ALINK_E_INVALID;
+  if (N < 0 || T < 1 || (N && (!p2 || !p1))) return alink_fail(ctx, ALINK_E_INVALID, "bad arguments");
+  ALINK_CUDA(ctx, cudaSetDevice(ctx->device));
+  const void *dp2, *dp1;
+  ALINK_TRY(stage_in(ctx, p2, sizeof(float) * (size_t)N * T, in_space, ctx->misc0, &dp2));
+  ALINK_TRY(stage_in(ctx, p1, sizeof(float) * (size_t)N, in_space, ctx->misc1, &dp1));
+  ALINK_TRY(dev_reserve(ctx, ctx->util, sizeof(float) * (size_t)(N ? N : 1)));
+  if (N > 0) {
+    int64_t blocks = (N + 255) / 256;
+    if (blocks > (int64_t)ctx->sm_count * 8) blocks = (int64_t)ctx->sm_count * 8;
+    min_disparity_kernel<<<(unsigned)blocks, 256, 0, ctx->stream>>>((const float *)dp2, (const float *)dp1, N, T, (float *)ctx->util.p);
+    ALINK_LAUNCHED(ctx);
+  }
+  ctx->N = N;
+  ctx->util_valid = true;
+  ctx->util_measure = -1;  // not one of the probability measures: alink_select_topk ranks it as it is
+  ALINK_TRY(copy_out(ctx, util, ctx->util.p, sizeof(float) * (size_t)N, out_space));
+  if (util && out_space == ALINK_HOST) ALINK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return ALINK_OK;
+}
 
 // ------------------------------------------------------------------------------------------ adversarial pool (DE)
 static size_t de_al(size_t x) { return (x + 255) & ~(size_t)255; }

@@ -71,6 +71,8 @@ class ShardedTableFeed:
         self.side = torch.cuda.Stream(device=self.device)
         self.ready = [torch.cuda.Event() for _ in range(n_buffers)]
         self.free = [torch.cuda.Event() for _ in range(n_buffers)]
+        self.idx = [None] * n_buffers
+        self.nidx = [0] * n_buffers
         self.bytes_h2d = self.rows * self.D * self.bufs[0].element_size()
         self.bytes_gather = self.bytes_h2d * (self.world - 1)  # received per rank over NVLink
 
@@ -79,8 +81,10 @@ class ShardedTableFeed:
         lo = self.rank * self.rows
         return host_table[lo:min(lo + self.rows, self.M)]
 
-    def feed_async(self, buf, host_shard):
-        """Start filling buffer `buf` from this rank's pinned shard; returns at once."""
+    def feed_async(self, buf, host_shard, host_indices=None):
+        """Start filling buffer `buf` from this rank's pinned shard; returns at once. host_indices: optional pinned
+        (ia, ib) int32 tensors of the SAME step — they ride on the side stream too (ahead of the table, so a query
+        never waits for them behind the upload) and `wait` hands back their device copies."""
         torch = self.torch
         cur = torch.cuda.current_stream(self.device)
         if cur.cuda_stream == 0:
@@ -91,6 +95,12 @@ class ShardedTableFeed:
         lo = self.rank * self.rows
         with torch.cuda.stream(self.side):
             self.side.wait_event(self.free[buf])
+            if host_indices is not None:
+                if self.idx[buf] is None or self.idx[buf][0].numel() < host_indices[0].numel():
+                    self.idx[buf] = tuple(torch.empty(t.numel(), dtype=torch.int32, device=self.device) for t in host_indices)
+                for d, h_ in zip(self.idx[buf], host_indices):
+                    d[:h_.numel()].copy_(h_, non_blocking=True)
+                self.nidx[buf] = int(host_indices[0].numel())
             mine = full[lo:lo + self.rows]
             mine[:host_shard.shape[0]].copy_(host_shard, non_blocking=True)
             if self.world > 1:
@@ -102,7 +112,9 @@ class ShardedTableFeed:
         torch = self.torch
         torch.cuda.current_stream(self.device).wait_event(self.ready[buf])
         self.ctx.set_table(slot, self.bufs[buf][:self.M])
-        return self.bufs[buf]
+        if self.idx[buf] is not None:
+            return tuple(t[:self.nidx[buf]] for t in self.idx[buf])
+        return None
 
 
 def decode_keys(keys: np.ndarray):

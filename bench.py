@@ -305,10 +305,10 @@ def main():
         cur, nxt = e2e_slot["cur"], 3 - e2e_slot["cur"]
         if feed is not None:
             if not e2e_slot["primed"]:
-                feed.feed_async(cur - 1, shard_pin)
+                feed.feed_async(cur - 1, shard_pin, (ia_pin, ib_pin))
                 e2e_slot["primed"] = True
-            feed.feed_async(nxt - 1, shard_pin)
-            feed.wait(cur - 1, cur)
+            feed.feed_async(nxt - 1, shard_pin, (ia_pin, ib_pin))  # the next step's table shard AND pair indices
+            ia_e, ib_e = feed.wait(cur - 1, cur)
         else:
             if not e2e_slot["primed"]:
                 ctx.set_table(cur, table_pin)
@@ -319,8 +319,7 @@ def main():
             _, _, keys, t = ctx.query(0, cur, cur, ia_pin.numpy(), ib_pin.numpy(), N, args.measure, B, base=base,
                                       timing=True, out=out)
             return keys, t
-        _, _, keys, t = ctx.query(0, cur, cur, ia_pin.numpy(), ib_pin.numpy(), N, args.measure, B, base=base,
-                                  timing=True, out=out_dev)
+        _, _, keys, t = ctx.query(0, cur, cur, ia_e, ib_e, N, args.measure, B, base=base, timing=True, out=out_dev)
         return merge_shards(keys, B, ctx.topk_keys, dist=dist, device=dev), t
 
     def barrier():
@@ -432,7 +431,7 @@ def main():
                     "ms_per_step": ms_e2e, "stage_ms": stage_e2e,
                     "call": ("alink_set_table_async(HOST table of the next step, second slot) + alink_query(HOST indices) -> host top-B; every step uploads one table, overlapped with the previous step's query"
                              if feed is None else
-                             "ShardedTableFeed: each rank uploads its 1/N of the next step's table (h2d_bytes_per_step is PER RANK) + in-place NCCL all-gather over NVLink on a side stream, overlapped with the previous step's alink_query(HOST indices) -> device keys -> all-gather + merge -> host top-B"),
+                             "ShardedTableFeed: each rank uploads the next step's pair indices and its 1/N of the next step's table from pinned host memory (h2d_bytes_per_step is PER RANK) + in-place NCCL all-gather of the table over NVLink, all on a side stream overlapped with the current step's alink_query -> device keys -> all-gather + merge -> host top-B"),
                     **({"table_allgather": {"bytes_received_per_rank": feed.bytes_gather, "ranks": world, "ms_alone": gather_ms,
                                              "busbw_GBps": feed.bytes_gather / (gather_ms / 1e3) / 1e9}} if feed is not None else {})},
             "gpu_launches": launches, "clocks": clocks}

@@ -259,6 +259,20 @@ int alink_roc_counts(alink_ctx *ctx, const float *scores, const int32_t *mask, i
                      int roc_case, const double *thresholds, int nthr, int in_space, uint64_t *tp, uint64_t *fp,
                      uint64_t *n_genuine, uint64_t *n_impostor);
 
+/* The A2-LINK noise-augmented pool generated on the device (BASELINE configs[3]). Replaces the
+ * per-noise re-featurisation of code/ALINK.py:163-170 (bag.attackModel -> conversionModel.process) with its embedding-space
+ * analogue: row n of slot_dst = normalize(e + delta), e = row idx[n] (or n) of slot_src, delta = `ncoord` coordinates set to
+ * U(-vmax, vmax) (40 in code/attack.py:91), from a counter-based stream keyed on (seed, pair_base + n, side, t, draw), so the
+ * host oracle regenerates the same rows bit for bit and nothing crosses PCIe. slot_dst becomes a context-owned fp32 table
+ * of N rows (pair n = row n: score it with ia = ib = NULL).
+ *   alink_score_column   column `col` (0 | 1; the C = 1 head is widened) of learner `learner` (-1 = the Bagging mean) of the last scores -> out[N]:
+ *                        the p2[t] row / the p1 vector of the rule (ALINK.py:175-176), without a host hop.
+ *   alink_min_disparity  util[j] = min_t |p2[t][j] - p1[j]| (kept in the context: alink_select_topk then ranks it). */
+int alink_perturb_rows(alink_ctx *ctx, int slot_src, const int32_t *idx, int64_t N, int in_space, int side, int t, uint64_t seed,
+                       int64_t pair_base, int ncoord, double vmax, int normalize, int slot_dst);
+int alink_score_column(alink_ctx *ctx, int learner, int col, float *out, int out_space);
+int alink_min_disparity(alink_ctx *ctx, const float *p2, const float *p1, int64_t N, int T, int in_space, float *util, int out_space);
+
 /* Embedding-space adversarial pool generator: batched differential evolution with the siamese head as the objective
  * (SURVEY.md 8f.3). Replaces the solver loop of code/differential_evolution.py:540-760 (SciPy fork, whole population scored
  * in one call :630-645, :692-714) as code/attack.py:59-103 drives it (best1bin, dither [0.5, 1), recombination 1, no

@@ -334,3 +334,47 @@ def de_select(pop, e, trial, e_trial):
             e[0] = e_trial[c]
             pop[0] = trial[c]
     return pop, e
+
+
+# ---- A2-LINK noise-augmented pool: the counter-based stream and row arithmetic of csrc/perturb.cuh
+def _u01(seed, a, b, c, d):
+    """de_u01 of csrc/de.cuh on uint64 arrays (wrap-around arithmetic)."""
+    with np.errstate(over="ignore"):
+        u = np.uint64
+        z = u(seed) ^ (np.asarray(a, u) * u(0x9E3779B97F4A7C15)) ^ (np.asarray(b, u) * u(0xBF58476D1CE4E5B9)) \
+            ^ (np.asarray(c, u) * u(0x94D049BB133111EB)) ^ (np.asarray(d, u) * u(0xD6E8FEB86659FD93))
+        z = z + u(0x9E3779B97F4A7C15)
+        z = (z ^ (z >> u(30))) * u(0xBF58476D1CE4E5B9)
+        z = (z ^ (z >> u(27))) * u(0x94D049BB133111EB)
+        z = z ^ (z >> u(31))
+    return (z >> u(11)).astype(np.float64) * (1.0 / 9007199254740992.0)
+
+
+def perturb_rows(table, idx, side, t, seed, pair_base=0, ncoord=40, vmax=0.25, normalize=True):
+    """e' = normalize(e + delta), delta = ncoord coordinates set to U(-vmax, vmax); bit-identical to perturb_rows_kernel:
+    fp32 single operations, the sum of squares in the kernel's order (lane l takes float4 chunks l, l + 32, ...; xor tree)."""
+    table = np.asarray(table, np.float32)
+    rows = np.arange(len(table)) if idx is None else np.asarray(idx)
+    N, D = len(rows), table.shape[1]
+    out = table[rows].copy()
+    pair = (np.arange(N, dtype=np.uint64) + np.uint64(pair_base))
+    key = np.uint64(2 * t + side)
+    for j in range(ncoord):
+        c = np.minimum((_u01(seed, pair, key, 2 * j, 0x5EED) * float(D)).astype(np.int64), D - 1)
+        v = ((2.0 * _u01(seed, pair, key, 2 * j + 1, 0x5EED) - 1.0) * float(np.float32(vmax))).astype(np.float32)
+        out[np.arange(N), c] = table[rows, c] + v          # later draws overwrite; ONE fp32 addition to the base value
+    if not normalize:
+        return out
+    sq = out * out                                          # fp32 products
+    ch = sq.reshape(N, D // 4, 4)
+    nchunk = D // 4
+    lanes = np.zeros((N, 32), np.float32)
+    for i0 in range(0, nchunk, 32):                         # lane l: chunk i0 + l, elements x y z w in order
+        blk = ch[:, i0:i0 + 32, :]
+        for e in range(4):
+            lanes[:, :blk.shape[1]] = lanes[:, :blk.shape[1]] + blk[:, :, e]
+    for o in (16, 8, 4, 2, 1):                              # ss += shfl_xor(ss, o)
+        lanes = lanes + lanes[:, np.arange(32) ^ o]
+    ss = lanes[:, 0]
+    inv = (np.float32(1.0) / np.sqrt(ss)).astype(np.float32)
+    return (out * inv[:, None]).astype(np.float32)
