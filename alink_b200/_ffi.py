@@ -405,6 +405,9 @@ class Context:
             p2, p1 = _f32(p2), _f32(p1)
         T, N = int(p2.shape[0]), int(p2.shape[1])
         yy = None if y is None else (y if _is_torch(y) else _f32(y).reshape(-1))
+        if dev_in and yy is not None and not _is_torch(yy):
+            import torch
+            yy = torch.from_numpy(yy).to(p2.device)
         sp = _space_of(p2, p1) if yy is None else _space_of(p2, p1, yy)
         idx = np.empty((max(N, 1),), np.int64)
         n_out, active = C.c_int64(0), C.c_int64(0)
@@ -497,6 +500,9 @@ class Context:
                                                  MEASURE_ID[measure], B, _ptr_space(idx)[0], _ptr_space(util)[0],
                                                  _ptr_space(keys)[0], HOST, C.byref(t) if timing else None))
         return (idx, util, keys, t) if timing else (idx, util, keys)
+
+    def query_allpairs_keys(self, group, slot_probe, slot_gallery, row0, nrows, measure, B):
+        return self.query_allpairs(group, slot_probe, slot_gallery, row0, nrows, measure, B)
 
     def set_refine_eps(self, eps):
         self._check(self._L.alink_set_refine_eps(self._h, float(eps)))

@@ -812,8 +812,14 @@ static int refine_query_v2(alink_ctx *ctx, const HeadGroup &g, Table &A, Table &
   ctx->refine_f16 = 1;
   const unsigned int wave = (unsigned int)(ctx->sm_count / 2) * 2u * tc::TILE_M;  // rows of one wave of the split kernel
   const unsigned int ns_min = N < 4096 ? (unsigned int)N : 4096u, ns_max = ns_min > wave ? ns_min : wave, ns2_max = 256;
-  int64_t cap1 = N < (1 << 18) ? N : (1 << 18);
-  const unsigned int cap2 = 8192;
+  // candidate capacities grow with the pool: at 2.5 G pairs (the 50k x 50k all-pairs matrix) the half filter's band alone
+  // holds tens of millions of pairs, which is exactly what the split stage is for
+  int64_t cap1 = N / 32 > (1 << 18) ? N / 32 : (1 << 18);
+  if (cap1 > (1ll << 27)) cap1 = 1ll << 27;
+  if (cap1 > N) cap1 = N;
+  int64_t cap2l = N / 2048 > 8192 ? N / 2048 : 8192;
+  if (cap2l > (1 << 21)) cap2l = 1 << 21;
+  const unsigned int cap2 = (unsigned int)cap2l;
   const int64_t rows1 = cap1 + ns_max, rows2 = (int64_t)cap2 + ns2_max;
   ALINK_TRY(dev_reserve(ctx, ctx->util, sizeof(float) * (size_t)N));
   ALINK_TRY(dev_reserve(ctx, ctx->sel_state, 2 * sizeof(SelectState)));
@@ -860,7 +866,7 @@ static int refine_query_v2(alink_ctx *ctx, const HeadGroup &g, Table &A, Table &
     refine_mark_kernel<<<(unsigned)blocks, 256, 0, ctx->stream>>>(util_a, N, st, nullptr, (float)(2.0 * eps1 * sc),
                                                                   (uint32_t *)ctx->cand.p, rs + RS_COUNT1, (unsigned int)cap1);
     ALINK_LAUNCHED(ctx);
-    refine_stage1_finish_kernel<<<64, 256, 0, ctx->stream>>>(rs, (unsigned int)cap1, N, ns_min, ns_max, wave, (uint32_t *)ctx->cand.p,
+    refine_stage1_finish_kernel<<<(unsigned)(rows1 / 4096 > 64 ? (rows1 / 4096 > capb ? capb : rows1 / 4096) : 64), 256, 0, ctx->stream>>>(rs, (unsigned int)cap1, N, ns_min, ns_max, wave, (uint32_t *)ctx->cand.p,
                                                              ia, ib, ia ? 0u : ctx->ap_G, ctx->ap_pair0, (int32_t *)ctx->cia.p,
                                                              (int32_t *)ctx->cib.p);
     ALINK_LAUNCHED(ctx);
@@ -891,7 +897,9 @@ static int refine_query_v2(alink_ctx *ctx, const HeadGroup &g, Table &A, Table &
     }
     // (7) exact utilities + the error statistics of both filters
     {
-      const unsigned fb = 48;
+      int64_t fbl = rows1 / 4096 > 48 ? rows1 / 4096 : 48;
+      if (fbl > capb) fbl = capb;
+      const unsigned fb = (unsigned)fbl;
 #define ALINK_FINISH(KT)                                                                                                   \
   refine_finish_kernel<KT><<<fb, 256, 0, ctx->stream>>>(rs, (const float *)ctx->probs.p, g.K, g.C, measure, util_a,        \
                                                         (const float *)ctx->util2.p, (const uint32_t *)ctx->cand.p,        \

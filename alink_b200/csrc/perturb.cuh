@@ -28,16 +28,26 @@ __global__ void __launch_bounds__(256) perturb_rows_kernel(const float *__restri
     const float4 *src = reinterpret_cast<const float4 *>(table + (size_t)r * D);
     for (int i = lane; i < D / 4; i += 32) reinterpret_cast<float4 *>(row)[i] = __ldg(src + i);
     __syncwarp();
-    if (lane == 0) {  // delta: later draws overwrite earlier ones on the same coordinate; e + delta is ONE addition
-      const uint64_t pair = pair_base + (uint64_t)n;
-      for (int j = 0; j < ncoord; ++j) {
-        int c = (int)(perturb_u01(seed, pair, (uint64_t)side, (uint64_t)t, 2ull * j) * (double)D);
+    // delta: draw j sets coordinate c_j to base + v_j (ONE fp32 addition to the BASE value); later draws overwrite earlier
+    // ones on the same coordinate. Lanes compute the draws in parallel (the hashes and the base-value loads are the cost);
+    // the writes then go out in draw order.
+    const uint64_t pair = pair_base + (uint64_t)n;
+    for (int j0 = 0; j0 < ncoord; j0 += 32) {
+      const int j = j0 + lane;
+      int c = 0;
+      float nv = 0.0f;
+      if (j < ncoord) {
+        c = (int)(perturb_u01(seed, pair, (uint64_t)side, (uint64_t)t, 2ull * j) * (double)D);
         if (c > D - 1) c = D - 1;
         const float v = (float)((2.0 * perturb_u01(seed, pair, (uint64_t)side, (uint64_t)t, 2ull * j + 1) - 1.0) * (double)vmax);
-        row[c] = __fadd_rn(__ldg(table + (size_t)r * D + c), v);
+        nv = __fadd_rn(__ldg(table + (size_t)r * D + c), v);
+      }
+      const int cnt = ncoord - j0 < 32 ? ncoord - j0 : 32;
+      for (int k = 0; k < cnt; ++k) {
+        if (lane == k) row[c] = nv;
+        __syncwarp();
       }
     }
-    __syncwarp();
     float ss = 0.0f;  // lane l: chunks l, l + 32, ... in order, x y z w in order; then the xor butterfly 16, 8, 4, 2, 1
     for (int i = lane; i < D / 4; i += 32) {
       const float4 v = reinterpret_cast<const float4 *>(row)[i];

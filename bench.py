@@ -175,6 +175,131 @@ def run_reference(args, rank, emit):
     emit(line)
 
 
+def run_config45(args, rank, local_rank, world, dev, peaks, emit, torch, dist):
+    """BASELINE configs[3] (A2-LINK noise-augmented pool) and configs[4] (DFW-style all-pairs) through the product's
+    device-resident entry points; same timing protocol as the headline (W warm-up steps, K timed steps between barriers,
+    CUDA events + wall clock, max over ranks). These are parity-test shapes measured for the record (profiles/), not
+    the driver's bench line."""
+    from alink_b200 import _ffi, alink
+    from alink_b200.dist import decode_keys, merge_shards, sharded_disparity_select
+    torch.cuda.set_stream(torch.cuda.Stream(device=dev))
+    ctx = _ffi.Context(local_rank)
+    ctx.set_stream(torch.cuda.current_stream().cuda_stream)
+    mode = "bf16" if args.mode == "refine" and args.config == 4 else args.mode  # config 4 needs scores, not a selection
+    cid = _ffi.COMPUTE_ID[mode]
+    B = 1000
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps, warmup):
+        for _ in range(warmup):
+            fn()
+        sampler = None if args.no_clock_sampling else ClockSampler(local_rank, getattr(torch.cuda.get_device_properties(local_rank), "uuid", None))
+        barrier()
+        if sampler:
+            sampler.start()
+        l0 = ctx.launches
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0 = time.perf_counter()
+        e0.record()
+        for _ in range(steps):
+            res = fn()
+        e1.record()
+        barrier()
+        wall = 1e3 * (time.perf_counter() - t0)
+        ms = torch.tensor([max(wall, e0.elapsed_time(e1))], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item()) / steps, res, ctx.launches - l0, (sampler.stop() if sampler else None)
+
+    if args.config == 4:
+        T = args.noise_types
+        n_total = args.pairs or 1_000_000
+        pool = synth.make_pool(2, N=n_total)
+        lo, hi = (n_total * rank) // world, (n_total * (rank + 1)) // world
+        n = hi - lo
+        m2 = synth.make_pool(2, N=4096, K=1).heads
+        table = torch.from_numpy(pool.table).to(dev)
+        ia, ib = torch.from_numpy(pool.ia[lo:hi]).to(dev), torch.from_numpy(pool.ib[lo:hi]).to(dev)
+        y = torch.from_numpy(pool.genuine[lo:hi].astype(np.float32)).to(dev)
+        ctx.set_table(0, table)
+        ctx.set_heads(0, pool.heads, compute=cid)
+        ctx.set_heads(1, m2, compute=cid)
+        seed = synth.BASE_SEED + 4
+        K1 = pool.heads.K
+
+        def step():
+            idx, active, top_idx, top_util, (p1, p2) = alink.a2link_pool_select(
+                ctx, 0, 1, 0, ia, ib, n, K1, T=T, seed=seed, y=y if world == 1 else None, B=min(B, n), rule=(world == 1))
+            if world > 1:  # the per-noise prefix is a GLOBAL order statistic: distributed radix select, then local marks
+                idx, active = sharded_disparity_select(ctx, p2, p1, lo, n_total, 0.25, 0.05, False, y, dist=dist, device=dev)
+                keys = torch.zeros((B,), dtype=torch.int64, device=dev)
+                _, _, k = ctx.select_topk(min(B, n), base=lo)
+                keys[:len(k)] = torch.from_numpy(k.view(np.int64)).to(dev)
+                merged = merge_shards(keys, B, ctx.topk_keys, dist=dist, device=dev)
+                top_idx, top_util = decode_keys(merged)
+            return idx, active, top_idx, top_util
+
+        ms, (idx, active, top_idx, top_util), launches, clocks = timed(step, args.steps, args.warmup)
+        scorings = n_total * (1 + T)
+        h = pool.heads
+        flops = (FLOPS_PER_PAIR(K1, h.D_in, h.H1, h.H2, h.C) + T * FLOPS_PER_PAIR(1, h.D_in, h.H1, h.H2, h.C)) * n
+        gen_bytes = T * 2 * n * pool.D * 4 * 2  # perturbed rows: written once, read once by the M2 head
+        line = {"metric": METRIC, "value": scorings / (ms / 1e3), "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+                "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+                "dtype": "bf16" if mode == "bf16" else "f32", "data": "synthetic (perturbed copies generated on the device)",
+                "config": {"workload": f"BASELINE configs[3]: A2-LINK pool, {n_total:,} base pairs x T={T} perturbed copies of both sides "
+                                       f"(alink_perturb_rows, 40 coordinates, U(-0.25, 0.25), renormalised), M1 K={K1} on the base pairs + M2 K=1 "
+                                       f"on all {n_total * T:,} perturbed pairs, 512-d fp32 table, disparity rule (ratio 0.25, eps 0.05) + top-{B} by "
+                                       "min-disparity; a unit = one pair SCORING", "compute": mode, "pair_scorings_per_step": scorings,
+                           "sharding": f"base pairs split over {world} GPU(s)", "l2": "perturbed tables of 2 x 2 GB per noise type stream through HBM"},
+                "roofline": {"bound": "hbm", "achieved": gen_bytes / (ms / 1e3) / 1e9, "peak": peaks["hbm_gbs"], "unit": "GB/s",
+                             "frac": gen_bytes / (ms / 1e3) / 1e9 / peaks["hbm_gbs"], "traffic": None,
+                             "note": "whole step against the bytes of the generated pool alone (K = 1 scoring of fp32 rows is the HBM-bound case of SURVEY 8d)",
+                             "tensor_TFLOPs_whole_step": flops / (ms / 1e3) / 1e12},
+                "result": {"rule_selected": int(len(idx)), "active_count": int(active), "top1_pair": int(top_idx[0]), "top1_min_disparity": float(top_util[0])},
+                "gpu_launches": launches, "clocks": clocks}
+        if rank == 0:
+            emit(line)
+        return
+
+    # ---- config 5: P x G all-pairs, probe rows sharded over the ranks
+    P = G = args.probe_rows
+    pool = synth.make_pool(2, N=4096, M=P)
+    ctx.set_table(0, torch.from_numpy(pool.table).to(dev))
+    ctx.set_heads(0, pool.heads, compute=cid)
+    r0, r1 = (P * rank) // world, (P * (rank + 1)) // world
+
+    def step5():
+        _, _, keys = ctx.query_allpairs_keys(0, 0, 0, r0, r1 - r0, args.measure, B)
+        if world == 1:
+            return keys
+        kd = torch.from_numpy(keys.view(np.int64)).to(dev)
+        return merge_shards(kd, B, ctx.topk_keys, dist=dist, device=dev)
+
+    ms, merged, launches, clocks = timed(step5, args.steps, args.warmup)
+    n_pairs = P * G
+    h = pool.heads
+    tf_gpu = FLOPS_PER_PAIR(h.K, h.D_in, h.H1, h.H2, h.C) * (r1 - r0) * G / (ms / 1e3) / 1e12
+    idx, util = decode_keys(merged)
+    line = {"metric": METRIC, "value": n_pairs / (ms / 1e3), "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "bf16" if mode == "bf16" else "f32",
+            "data": "synthetic", "config": {"workload": f"BASELINE configs[4]: DFW-style all-pairs {P:,} x {G:,} x 512-d, K={h.K}, {args.measure} top-{B}, "
+                                                        f"probe rows sharded over {world} GPU(s) (pairs enumerated arithmetically, no index arrays)",
+                                            "compute": {"fp32": "FP32_EXACT", "bf16": "BF16_TC", "refine": "FP32_REFINE"}[mode], "pairs": n_pairs,
+                                            "l2": "2 x 102 MB tables: L2-resident gather"},
+            "roofline": {"bound": "tensor", "achieved": tf_gpu, "peak": peaks["tf_sustained"], "unit": "TFLOP/s", "frac": tf_gpu / peaks["tf_sustained"],
+                         "frac_burst": tf_gpu / peaks["tf_burst"], "traffic": None, "note": "whole step per GPU (filter + refine + select)"},
+            "result": {"top1_pair": [int(idx[0]) // G, int(idx[0]) % G], "top1_utility": float(util[0]),
+                       "refine": ctx.refine_report() if mode == "refine" else None},
+            "gpu_launches": launches, "clocks": clocks}
+    if rank == 0:
+        emit(line)
+
+
 def main():
     # stdout carries exactly ONE JSON line: libraries that print banners there (NCCL) go to stderr instead
     json_fd = os.dup(1)
@@ -194,9 +319,14 @@ def main():
                          "BASELINE configs[1] is the fp32 bit-exact mode); fp32 = CUDA-core exact; bf16 = tensor cores only")
     ap.add_argument("--measure", default="uncertainty")
     ap.add_argument("--pairs", type=int, default=None, help="pairs per GPU (default 1,000,000; config 3: 1,250,000)")
-    ap.add_argument("--config", type=int, default=2, choices=[2, 3],
+    ap.add_argument("--config", type=int, default=2, choices=[2, 3, 4, 5],
                     help="BASELINE.json configs ordinal: 2 = 1 M pairs x 512-d (default, the N=1 workload); "
-                         "3 = 10 M pairs x 2048-d bf16 over 8 GPUs (1.25 M pairs per GPU, bf16 table, BF16_TC)")
+                         "3 = 10 M pairs x 2048-d bf16 over 8 GPUs (1.25 M pairs per GPU, bf16 table, BF16_TC); "
+                         "4 = A2-LINK noise-augmented pool (1 M base pairs x 16 perturbed copies generated on the device, "
+                         "M1 K=5 + M2 K=1, disparity rule + top-1000 by min-disparity; base pairs sharded over the GPUs); "
+                         "5 = DFW-style 50k x 50k all-pairs, sharded by probe-row block over the GPUs")
+    ap.add_argument("--noise-types", type=int, default=16, help="config 4: T perturbed copies per base pair")
+    ap.add_argument("--probe-rows", type=int, default=50_000, help="config 5: P = G rows")
     ap.add_argument("--table-rows", type=int, default=None)
     ap.add_argument("--ref-sample", type=int, default=100_000)
     ap.add_argument("--cpu-sample", type=int, default=100_000)
@@ -227,6 +357,12 @@ def main():
         dist.init_process_group("nccl", device_id=dev)
     n_gpus = world
     peaks = load_peaks()
+    if args.config in (4, 5):
+        run_config45(args, rank, local_rank, world, dev, peaks, emit, torch, dist)
+        if world > 1:
+            dist.barrier()
+            dist.destroy_process_group()
+        return
 
     # ---- synthetic workload (identical table/heads on every rank; each rank draws its own shard of pairs)
     if args.pairs is None:
