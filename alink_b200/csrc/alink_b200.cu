@@ -76,7 +76,7 @@ int alink_destroy(alink_ctx *ctx) {
   DevBuf *bufs[] = {&ctx->idx_a, &ctx->idx_b, &ctx->h1ws, &ctx->probs, &ctx->cons, &ctx->util, &ctx->sel_state,
                     &ctx->sel_keys, &ctx->sel_idx, &ctx->sel_util, &ctx->sel_in, &ctx->misc0, &ctx->misc1,
                     &ctx->misc2, &ctx->misc3, &ctx->cand, &ctx->cia, &ctx->cib, &ctx->util_c, &ctx->rstat, &ctx->xscratch,
-                    &ctx->train_ws, &ctx->train_y, &ctx->train_out, &ctx->util2, &ctx->cia2, &ctx->cib2, &ctx->map2, &ctx->src2};
+                    &ctx->train_ws, &ctx->train_y, &ctx->train_out, &ctx->util2, &ctx->probs2, &ctx->cia2, &ctx->cib2, &ctx->map2, &ctx->src2};
   for (DevBuf *b : bufs) dev_release(*b);
   DevBuf *debufs[] = {&ctx->de.pop, &ctx->de.trial, &ctx->de.e_pop, &ctx->de.e_trial, &ctx->de.viol, &ctx->de.rows, &ctx->de.ia,
                       &ctx->de.ib, &ctx->de.consts, &ctx->de.aux};
@@ -810,8 +810,9 @@ static int refine_query_v2(alink_ctx *ctx, const HeadGroup &g, Table &A, Table &
   ctx->refine_version = 2;
   ctx->N = N; ctx->sK = g.K; ctx->sC = g.C; ctx->util_valid = false; ctx->probs_full = false;
   ctx->refine_f16 = 1;
-  const unsigned int wave = (unsigned int)(ctx->sm_count / 2) * 2u * tc::TILE_M;  // rows of one wave of the split kernel
-  const unsigned int ns_min = N < 4096 ? (unsigned int)N : 4096u, ns_max = ns_min > wave ? ns_min : wave, ns2_max = 256;
+  // rows one round of the split kernel covers: its CTA pairs each take one (tile pair, learner) unit per round
+  const unsigned int wave = ((unsigned int)(ctx->sm_count / 2) << 16) | (unsigned int)g.K;  // (clusters, K) for the sample's rounding
+  const unsigned int ns_min = N < 4096 ? (unsigned int)N : 4096u, ns_max = ns_min + (unsigned int)(ctx->sm_count / 2) * 256u, ns2_max = 256;
   // candidate capacities grow with the pool: at 2.5 G pairs (the 50k x 50k all-pairs matrix) the half filter's band alone
   // holds tens of millions of pairs, which is exactly what the split stage is for
   int64_t cap1 = N / 32 > (1 << 18) ? N / 32 : (1 << 18);
@@ -823,11 +824,12 @@ static int refine_query_v2(alink_ctx *ctx, const HeadGroup &g, Table &A, Table &
   const int64_t rows1 = cap1 + ns_max, rows2 = (int64_t)cap2 + ns2_max;
   ALINK_TRY(dev_reserve(ctx, ctx->util, sizeof(float) * (size_t)N));
   ALINK_TRY(dev_reserve(ctx, ctx->sel_state, 2 * sizeof(SelectState)));
-  ALINK_TRY(dev_reserve(ctx, ctx->rstat, 256));
+  ALINK_TRY(dev_reserve(ctx, ctx->rstat, 32768));
   ALINK_TRY(dev_reserve(ctx, ctx->cand, sizeof(uint32_t) * (size_t)(N > rows1 ? N : rows1)));
   ALINK_TRY(dev_reserve(ctx, ctx->cia, sizeof(int32_t) * (size_t)rows1));
   ALINK_TRY(dev_reserve(ctx, ctx->cib, sizeof(int32_t) * (size_t)rows1));
   ALINK_TRY(dev_reserve(ctx, ctx->util2, sizeof(float) * (size_t)rows1));
+  ALINK_TRY(dev_reserve(ctx, ctx->probs2, sizeof(float) * (size_t)rows1 * g.K * g.C));
   ALINK_TRY(dev_reserve(ctx, ctx->cia2, sizeof(int32_t) * (size_t)rows2));
   ALINK_TRY(dev_reserve(ctx, ctx->cib2, sizeof(int32_t) * (size_t)rows2));
   ALINK_TRY(dev_reserve(ctx, ctx->map2, sizeof(uint32_t) * (size_t)rows2));
@@ -840,7 +842,19 @@ static int refine_query_v2(alink_ctx *ctx, const HeadGroup &g, Table &A, Table &
   if (!ctx->rs_host) ALINK_CUDA(ctx, cudaMallocHost((void **)&ctx->rs_host, RS_WORDS * sizeof(unsigned int)));
   float *util_a = (float *)ctx->util.p;
   SelectState *st = (SelectState *)ctx->sel_state.p + 1;
-  unsigned int *rs = (unsigned int *)ctx->rstat.p + 40;
+  unsigned int *rs = (unsigned int *)ctx->rstat.p + 240;    // 16 statistics words, then 3 x 2048 histogram counters
+  unsigned int *hist = (unsigned int *)ctx->rstat.p + 256;
+  static const int coop_env = [] { const char *e = getenv("ALINK_REFINE_COOP"); return e ? atoi(e) : 1; }();
+  static int coop_blocks_per_sm = -1;
+  if (coop_blocks_per_sm < 0) {
+    int occ = 0, coop = 0;
+    cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, ctx->device);
+    if (coop && cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, refine_stage1_coop_kernel, 256, 0) == cudaSuccess && occ > 0)
+      coop_blocks_per_sm = occ < 4 ? occ : 4;
+    else
+      coop_blocks_per_sm = 0;
+  }
+  const bool coop = coop_env != 0 && coop_blocks_per_sm > 0;
   // the bounds: caller's value, else the larger of the per-format default and the a-priori statistical model
   const double apriori = refine_model_eps(g, A, Bt, true);
   ctx->refine_eps_apriori = apriori;
@@ -853,31 +867,49 @@ static int refine_query_v2(alink_ctx *ctx, const HeadGroup &g, Table &A, Table &
   // (1) approximate utilities of every pair (fused K-learner reduction in the kernel's epilogue)
   ALINK_TRY(tc_score(ctx, g, A, Bt, ia, ib, N, nullptr, util_a, measure, true));
   if (ev) ALINK_CUDA(ctx, cudaEventRecord(ev[2], ctx->stream));
-  // (2) B-th largest approximate utility tau1
+  // (2) B-th largest approximate utility tau1 (inside the cooperative stage-1 kernel when available)
   KeySrc asrc{util_a, nullptr, 0, nullptr};
-  ALINK_TRY(select_threshold(ctx, asrc, N, B, st, 3));
+  if (!coop) ALINK_TRY(select_threshold(ctx, asrc, N, B, st, 3));
   int64_t blocks = (N + 2047) / 2048;
   const int64_t capb = (int64_t)ctx->sm_count * 8;
   if (blocks > capb) blocks = capb;
   for (int round = 1;; ++round) {
     if (eps2 * 4.0 > eps1) eps2 = eps1 / 4.0;
-    ALINK_CUDA(ctx, cudaMemsetAsync(rs, 0, RS_WORDS * sizeof(unsigned int), ctx->stream));
     // (3) C1 = {u~ >= tau1 - 2 eps1}; + the stratified sample; table rows of both
-    refine_mark_kernel<<<(unsigned)blocks, 256, 0, ctx->stream>>>(util_a, N, st, nullptr, (float)(2.0 * eps1 * sc),
-                                                                  (uint32_t *)ctx->cand.p, rs + RS_COUNT1, (unsigned int)cap1);
-    ALINK_LAUNCHED(ctx);
-    refine_stage1_finish_kernel<<<(unsigned)(rows1 / 4096 > 64 ? (rows1 / 4096 > capb ? capb : rows1 / 4096) : 64), 256, 0, ctx->stream>>>(rs, (unsigned int)cap1, N, ns_min, ns_max, wave, (uint32_t *)ctx->cand.p,
-                                                             ia, ib, ia ? 0u : ctx->ap_G, ctx->ap_pair0, (int32_t *)ctx->cia.p,
-                                                             (int32_t *)ctx->cib.p);
-    ALINK_LAUNCHED(ctx);
+    if (coop) {
+      ALINK_CUDA(ctx, cudaMemsetAsync(rs, 0, (RS_WORDS + 3 * 2048) * sizeof(unsigned int), ctx->stream));
+      Stage1Args sa1;
+      sa1.util = util_a; sa1.N = N; sa1.B = (unsigned long long)B; sa1.margin = (float)(2.0 * eps1 * sc);
+      sa1.cap1 = (unsigned int)cap1; sa1.ns_min = ns_min; sa1.ns_max = ns_max; sa1.wave_rows = wave;
+      sa1.hist = hist; sa1.rs = rs; sa1.cand1 = (uint32_t *)ctx->cand.p; sa1.ia = ia; sa1.ib = ib;
+      sa1.G = ia ? 0u : ctx->ap_G; sa1.pair0 = ctx->ap_pair0; sa1.cia = (int32_t *)ctx->cia.p; sa1.cib = (int32_t *)ctx->cib.p;
+      void *kargs[] = {(void *)&sa1};
+      int64_t cb = (N + 2047) / 2048;
+      const int64_t cmax = (int64_t)ctx->sm_count * coop_blocks_per_sm;
+      if (cb > cmax) cb = cmax;
+      if (cb < 1) cb = 1;
+      ALINK_CUDA(ctx, cudaLaunchCooperativeKernel((const void *)refine_stage1_coop_kernel, dim3((unsigned)cb), dim3(256), kargs, 0, ctx->stream));
+      ALINK_LAUNCHED(ctx);
+    } else {
+      ALINK_CUDA(ctx, cudaMemsetAsync(rs, 0, RS_WORDS * sizeof(unsigned int), ctx->stream));
+      refine_mark_kernel<<<(unsigned)blocks, 256, 0, ctx->stream>>>(util_a, N, st, nullptr, (float)(2.0 * eps1 * sc),
+                                                                    (uint32_t *)ctx->cand.p, rs + RS_COUNT1, (unsigned int)cap1);
+      ALINK_LAUNCHED(ctx);
+      refine_stage1_finish_kernel<<<(unsigned)(rows1 / 4096 > 64 ? (rows1 / 4096 > capb ? capb : rows1 / 4096) : 64), 256, 0, ctx->stream>>>(
+          rs, (unsigned int)cap1, N, ns_min, ns_max, wave, (uint32_t *)ctx->cand.p, ia, ib, ia ? 0u : ctx->ap_G, ctx->ap_pair0,
+          (int32_t *)ctx->cia.p, (int32_t *)ctx->cib.p);
+      ALINK_LAUNCHED(ctx);
+    }
     // (4) split-operand tensor-core utilities u2 of C1 u S
     {
       const uint32_t apG = ctx->ap_G;
       ctx->ap_G = 0;  // the rows are explicit now
-      const int rc = tc_score_split(ctx, g, A, Bt, (const int32_t *)ctx->cia.p, (const int32_t *)ctx->cib.p, rows1, rs + RS_M1, nullptr,
-                                    (float *)ctx->util2.p, measure, xmax, h1max);
+      const int rc = tc_score_split(ctx, g, A, Bt, (const int32_t *)ctx->cia.p, (const int32_t *)ctx->cib.p, rows1, rs + RS_M1,
+                                    (float *)ctx->probs2.p, nullptr, measure, xmax, h1max);
       ctx->ap_G = apG;
       ALINK_TRY(rc);
+      // the kernel's unit of work is (tile pair, learner): the K-learner utility is this streaming pass
+      ALINK_TRY(launch_utility(ctx, (const float *)ctx->probs2.p, rows1, g.K, g.C, measure, (float *)ctx->util2.p, nullptr, rs + RS_M1));
     }
     // (5) tau2, C2 = {u2 >= tau2 - 2 eps2} + every 16th sample row; their table rows
     refine_stage2_kernel<<<1, 1024, 0, ctx->stream>>>(rs, (const float *)ctx->util2.p, (unsigned long long)B, (float)(2.0 * eps2 * sc), cap2,

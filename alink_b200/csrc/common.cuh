@@ -115,7 +115,7 @@ struct alink_ctx {
   int refine_f16 = 0;             // the last query's filter ran on half (1) or bf16 (0) operands
   bool probs_full = true;         // ctx->probs holds all N pairs (false after a refine query)
   DevBuf cand, cia, cib, util_c, rstat;
-  DevBuf util2, cia2, cib2, map2, src2;     // stage 2 / 3 of refine_query_v2
+  DevBuf util2, probs2, cia2, cib2, map2, src2;     // stage 2 / 3 of refine_query_v2
   unsigned int *rs_host = nullptr;          // pinned copy of the statistics words (read with the result)
   double refine_eps2 = 0.0, refine_eps2_used = 0.0;  // stage-2 (split operand) bound: caller's / used
   double refine_eps_apriori = 0.0;          // a-priori statistical MODEL of the stage-1 filter error (8 sigma) for the last query

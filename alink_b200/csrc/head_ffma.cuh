@@ -46,10 +46,15 @@ struct FfmaArgs {
   float *probs;                // [(row0 + row) * K + learner] * C + c
 };
 
-template <int BN, int AMODE, int EPI, int BK = (EPI == 0 ? 16 : 8)>
-__global__ void __launch_bounds__(256, 2) ffma_layer_kernel(const FfmaArgs a) {
-  constexpr int BM = 128, TM = 8, TN = BN / 16;
-  constexpr int NA = BK / 8;                                   // float4 of A per thread and chunk
+// BM = 128 (8 rows per thread) for bulk scoring; BM = 64 (4 rows per thread, 3 CTAs per SM) for the short candidate lists of
+// FP32_REFINE, where twice as many CTAs fill the 148 SMs better than one wave of large tiles.
+template <int BN, int AMODE, int EPI, int BK = (EPI == 0 ? 16 : 8), int BM = 128>
+__global__ void __launch_bounds__(256, (BM == 64 ? 3 : 2)) ffma_layer_kernel(const FfmaArgs a) {
+  constexpr int TM = BM / 16, TN = BN / 16;
+  constexpr int TPR = 256 / BM;                                // threads sharing one A row
+  constexpr int NA = BK / (4 * TPR);                           // float4 of A per thread and chunk
+  static_assert(BM == 128 || BM == 64, "row tile");
+  static_assert(NA >= 1, "BK too small for this row tile");
   constexpr int NB = (BK * BN / 4 + 255) / 256;                // float4 of B per thread and chunk
   __shared__ __align__(16) float As[2][BK][BM];
   __shared__ __align__(16) float Bs[2][BK][BN];
@@ -68,7 +73,7 @@ __global__ void __launch_bounds__(256, 2) ffma_layer_kernel(const FfmaArgs a) {
   }
 
   // ---- A loader state: this thread owns row (tid>>1), k-quads (tid&1)*4*NA + 4*i of every chunk
-  const int lrow = tid >> 1, kq = (tid & 1) * 4 * NA;
+  const int lrow = tid / TPR, kq = (tid % TPR) * 4 * NA;
   int grow = mtile * BM + lrow;
   if (grow >= Mrows) grow = Mrows - 1;
   const float *pa, *pb = nullptr;
@@ -164,9 +169,11 @@ __global__ void __launch_bounds__(256, 2) ffma_layer_kernel(const FfmaArgs a) {
     for (int k = 0; k < BK; ++k) {
       float av[TM], bv[TN];
       const float4 a0 = *reinterpret_cast<const float4 *>(&As[buf][k][ty * 4]);
-      const float4 a1 = *reinterpret_cast<const float4 *>(&As[buf][k][64 + ty * 4]);
       av[0] = a0.x; av[1] = a0.y; av[2] = a0.z; av[3] = a0.w;
-      av[4] = a1.x; av[5] = a1.y; av[6] = a1.z; av[7] = a1.w;
+      if constexpr (TM == 8) {
+        const float4 a1 = *reinterpret_cast<const float4 *>(&As[buf][k][64 + ty * 4]);
+        av[4] = a1.x; av[5] = a1.y; av[6] = a1.z; av[7] = a1.w;
+      }
       if constexpr (TN == 8) {
         const float4 b0 = *reinterpret_cast<const float4 *>(&Bs[buf][k][tx * 4]);
         const float4 b1 = *reinterpret_cast<const float4 *>(&Bs[buf][k][BN / 2 + tx * 4]);
@@ -275,11 +282,23 @@ static int ffma_head_chunk(alink_ctx *ctx, const HeadGroup &g, const float *ta, 
   a.W = g.pW1; a.bias = g.pb1;
   a.H = h1ws; a.h_learner_stride = h1_learner_stride;
   a.K = g.K; a.C = g.C; a.act = g.act;
-  dim3 grid1(a.ntiles * g.K, (Mc + 127) / 128);
-  if (g.feat_mode == ALINK_FEAT_ABSDIFF)
-    ffma_layer_kernel<128, 1, 0><<<grid1, 256, 0, ctx->stream>>>(a);
-  else
-    ffma_layer_kernel<128, 2, 0><<<grid1, 256, 0, ctx->stream>>>(a);
+  // (measured: the 64-row tile is SLOWER for FP32_REFINE's ~1.5 k exact rows — 151 + 50 us against 125 + 46 us: half the
+  // register reuse per shared-memory load outweighs the better fill; kept selectable for other shapes)
+  static const int small_env = [] { const char *e = getenv("ALINK_FFMA_SMALL"); return e ? atoi(e) : 0; }();
+  const bool small = m_dev != nullptr && small_env == 1;
+  if (small) {
+    dim3 grid1(a.ntiles * g.K, (Mc + 63) / 64);
+    if (g.feat_mode == ALINK_FEAT_ABSDIFF)
+      ffma_layer_kernel<128, 1, 0, 16, 64><<<grid1, 256, 0, ctx->stream>>>(a);
+    else
+      ffma_layer_kernel<128, 2, 0, 16, 64><<<grid1, 256, 0, ctx->stream>>>(a);
+  } else {
+    dim3 grid1(a.ntiles * g.K, (Mc + 127) / 128);
+    if (g.feat_mode == ALINK_FEAT_ABSDIFF)
+      ffma_layer_kernel<128, 1, 0><<<grid1, 256, 0, ctx->stream>>>(a);
+    else
+      ffma_layer_kernel<128, 2, 0><<<grid1, 256, 0, ctx->stream>>>(a);
+  }
   ALINK_LAUNCHED(ctx);
 
   FfmaArgs b;
@@ -288,8 +307,12 @@ static int ffma_head_chunk(alink_ctx *ctx, const HeadGroup &g, const float *ta, 
   b.row0 = row0; b.M = Mc; b.m_dev = m_dev; b.Kdim = g.H1; b.Ncols = g.H2; b.ntiles = 1;
   b.W = g.pW2; b.bias = g.pb2;
   b.W3 = g.pW3; b.b3 = g.pb3; b.C = g.C; b.act = g.act; b.K = g.K; b.probs = probs;
-  dim3 grid2(g.K, (Mc + 127) / 128);
-  if (g.H2 == 64)
+  dim3 grid2(g.K, small ? (Mc + 63) / 64 : (Mc + 127) / 128);
+  if (g.H2 == 64 && small)
+    ffma_layer_kernel<64, 0, 1, 16, 64><<<grid2, 256, 0, ctx->stream>>>(b);
+  else if (g.H2 == 32 && small)
+    ffma_layer_kernel<32, 0, 1, 16, 64><<<grid2, 256, 0, ctx->stream>>>(b);
+  else if (g.H2 == 64)
     ffma_layer_kernel<64, 0, 1><<<grid2, 256, 0, ctx->stream>>>(b);
   else if (g.H2 == 32)
     ffma_layer_kernel<32, 0, 1><<<grid2, 256, 0, ctx->stream>>>(b);

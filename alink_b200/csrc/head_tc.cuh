@@ -70,6 +70,7 @@ constexpr uint32_t P_ONES = P_B1;  // the constant A tile replaces the staged bi
 
 constexpr uint32_t TMEM_COLS = 512;
 constexpr uint32_t ACC2_COL = 256;  // two layer-2 accumulators of 64 columns (consecutive learners alternate)
+constexpr uint32_t HTM_COL = 384;   // ATM: the hidden chunk as layer 2's A operand IN TENSOR MEMORY: 128 halves = 64 columns
 
 struct Args {
   const void *ta, *tb;       // embedding tables (fp32 or bf16), D columns
@@ -163,7 +164,11 @@ __device__ __forceinline__ float4 ldg_bf4(const __nv_bfloat16 *p) {  // 4 bf16 -
 //           the last MMA of the previous tile has read that block. Without it the refill at a tile boundary is
 //           four dependent rounds of table loads (only two k-blocks of fp32 rows fit in the producers' registers)
 //           during which the tensor pipe idles — 22 % of the kernel in the profile of the unstaged version.
-template <bool TAB_BF16, int NCTA, bool F16, bool STAGED = false>
+// ATM:    the epilogue writes the relu'd hidden chunk straight into tensor memory (tcgen05.st) and layer 2 reads its A
+//           operand from there (tcgen05.mma with a TMEM A address) instead of a swizzled shared-memory tile: the
+//           shared-memory data pipe — 85 % busy feeding operands in the profile of round 1 — loses the 32 KB store
+//           and the 32 KB re-read per work item.
+template <bool TAB_BF16, int NCTA, bool F16, bool STAGED = false, bool ATM = false>
 __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
   constexpr uint32_t KPS = NCTA;                // k-blocks per ring slot (a pair CTA holds half of each block)
   constexpr uint32_t HB = STAGE_BYTES / NCTA;   // bytes of this CTA's part of one [128 n x 64 k] weight block
@@ -388,8 +393,15 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
           for (uint32_t kb2 = 0; kb2 < 2; ++kb2) {
             const uint64_t ad = hdesc0 + kb2 * STAGE_STEP;
 #pragma unroll
-            for (uint32_t k = 0; k < 4; ++k)
-              mma(acc2, ad + 2 * k, bd + kb2 * kb2_step + 2 * k, idesc2, (c | kb2 | k) != 0u);
+            for (uint32_t k = 0; k < 4; ++k) {
+              if (ATM) {
+                const uint32_t at = tmem + HTM_COL + (kb2 * 4u + k) * 8u;  // 16 halves of K = 8 columns per MMA
+                if (NCTA == 2) ptx::umma2_f16_ts(acc2, at, bd + kb2 * kb2_step + 2 * k, idesc2, (c | kb2 | k) != 0u);
+                else ptx::umma_f16_ts(acc2, at, bd + kb2 * kb2_step + 2 * k, idesc2, (c | kb2 | k) != 0u);
+              } else {
+                mma(acc2, ad + 2 * k, bd + kb2 * kb2_step + 2 * k, idesc2, (c | kb2 | k) != 0u);
+              }
+            }
           }
           commit(W_EMPTY + s);
           commit(H1_EMPTY);
@@ -563,9 +575,14 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
         const uint32_t w6 = pack16_relu<F16>(addb(v[12], bd.x), addb(v[13], bd.y));
         const uint32_t w7 = pack16_relu<F16>(addb(v[14], bd.z), addb(v[15], bd.w));
         if (k == 0) ptx::mbar_wait(bar(H1_EMPTY), (q & 1u) ^ 1u);  // layer 2 of the previous item has read the h1 buffer
-        const uint32_t hb = hrow + (k >> 2) * STAGE_BYTES, ch = (k & 3u) * 2u;
-        sts128(hb + ((ch ^ hx) << 4), w0, w1, w2, w3);
-        sts128(hb + (((ch + 1u) ^ hx) << 4), w4, w5, w6, w7);
+        if (ATM) {
+          if (k == 0) ptx::tc_fence_after();
+          ptx::tmem_st8(trow + HTM_COL + k * 8u, w0, w1, w2, w3, w4, w5, w6, w7);
+        } else {
+          const uint32_t hb = hrow + (k >> 2) * STAGE_BYTES, ch = (k & 3u) * 2u;
+          sts128(hb + ((ch ^ hx) << 4), w0, w1, w2, w3);
+          sts128(hb + (((ch + 1u) ^ hx) << 4), w4, w5, w6, w7);
+        }
       };
       uint32_t va[16], vb[16];
       float4 ba4[4] = {}, bb4[4] = {};
@@ -587,7 +604,8 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
         convert(vb, 2 * kk + 1, bb4);
         if (kk < 3) ptx::tc_wait_ld();
       }
-      ptx::fence_proxy_async_smem();
+      if (ATM) ptx::tc_wait_st();
+      else ptx::fence_proxy_async_smem();
       ptx::tc_fence_before();
       ptx::mbar_arrive(bar(A1_EMPTY + b));
       ptx::mbar_arrive(bar(H1_FULL));
@@ -974,7 +992,12 @@ static int tc_score(alink_ctx *ctx, const HeadGroup &g, const Table &A, const Ta
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    if (staged)
+    // layer 2's A operand from tensor memory (ATM) for the staged CTA-pair kernels; ALINK_TC_ATM=0 keeps it in shared memory
+    static const int atm_env = [] { const char *e = getenv("ALINK_TC_ATM"); return e ? atoi(e) : 1; }();
+    if (staged && atm_env)
+      kern = f16 ? tc::head_kernel<false, 2, true, true, true>
+                 : tb16 ? tc::head_kernel<true, 2, false, true, true> : tc::head_kernel<false, 2, false, true, true>;
+    else if (staged)
       kern = f16 ? tc::head_kernel<false, 2, true, true>
                  : tb16 ? tc::head_kernel<true, 2, false, true> : tc::head_kernel<false, 2, false, true>;
     else

@@ -16,6 +16,9 @@
 // into all chunk accumulators (4 x 128 TMEM columns at H1 = 512). The k loop runs over 3 x nkb "virtual" blocks:
 // (x_hi, W_hi), (x_hi, W_lo), (x_lo, W_hi). Layer 2 per chunk: 24 MMAs on (h_hi, W2_hi), (h_hi, W2_lo), (h_lo, W2_hi).
 // The number of pairs is read from DEVICE memory (n_dev) so that the host never waits for the candidate count.
+// Work unit = (pair of tiles, learner), units dealt round-robin to the CTA pairs: the candidate lists are a wave or two
+// of tiles, and at tile granularity 1.16 waves of work would cost two full waves; at learner granularity they cost 1.2.
+// The kernel therefore writes per-learner probabilities; the K-learner utility is a separate streaming pass.
 #pragma once
 #include "head_tc_ko.cuh"
 
@@ -111,9 +114,11 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel_split(const SplitArgs
   ptx::tc_fence_after();
   const uint32_t tmem = __shfl_sync(0xffffffffu, *reinterpret_cast<volatile uint32_t *>(smem + TOFF), 0);
 
-  const uint32_t nunits = (ntiles + 1) / 2;
-  const uint32_t T = nunits > unit0 ? (nunits - unit0 + nunit - 1) / nunit : 0u;  // tiles of this CTA
-  auto tile_of = [&](uint32_t i) -> int64_t { return ((int64_t)unit0 + (int64_t)i * nunit) * 2 + rank; };
+  const uint32_t nunits = ((ntiles + 1) / 2) * K;  // (tile pair, learner) units, learner fastest
+  const uint32_t T = nunits > unit0 ? (nunits - unit0 + nunit - 1) / nunit : 0u;  // units of this CTA pair
+  auto unit_of = [&](uint32_t i) -> uint32_t { return unit0 + i * nunit; };
+  auto tile_of = [&](uint32_t i) -> int64_t { return (int64_t)(unit_of(i) / K) * 2 + rank; };
+  auto learner_of = [&](uint32_t i) -> uint32_t { return unit_of(i) % K; };
   const uint32_t l2bytes = 2u * (uint32_t)a.H2 * 128u;  // one layer-2 slice of the pair; this CTA loads half
   const uint32_t stage_tx = XBLK + nc * WPART;
 
@@ -141,7 +146,8 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel_split(const SplitArgs
     for (uint32_t i = 0; i < T; ++i) {
       ptx::mbar_wait(bar(XS_FULL + (i & 1u)), (i >> 1) & 1u);  // this tile's operand images are in the scratch
       const uint8_t *xsrc = xs_mine + (size_t)(i & 1u) * (2 * nkb) * XBLK;
-      for (uint32_t l = 0; l < K; ++l) {
+      {
+        const uint32_t l = learner_of(i);
         for (uint32_t part = 0; part < 3; ++part) {
           const uint8_t *xp = xsrc + (part == 2 ? (size_t)nkb * XBLK : 0);
           const uint8_t *wp = part == 1 ? sa.w1lo : a.w1img;
@@ -177,8 +183,8 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel_split(const SplitArgs
     const uint32_t nkb3 = 3 * nkb;
     uint32_t s = 0, ph = 0, hq = 0, v = 0;
     for (uint32_t i = 0; i < T; ++i) {
-      for (uint32_t l = 0; l < K; ++l, ++v) {
-        ptx::mbar_wait(bar(A1_EMPTY), (v & 1u) ^ 1u);  // the previous learner's accumulators are drained
+      for (uint32_t l = K - 1; l < K; ++l, ++v) {  // one learner per unit (the loop body is kept for its structure)
+        ptx::mbar_wait(bar(A1_EMPTY), (v & 1u) ^ 1u);  // the previous unit's accumulators are drained
         ptx::tc_fence_after();
         for (uint32_t kb = 0; kb < nkb3; ++kb) {
           ptx::mbar_wait(bar(W_FULL + s), ph);
@@ -236,7 +242,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel_split(const SplitArgs
     const uint32_t nkb3 = 3 * nkb;
     uint32_t s = 0, ph = 0, hq = 0, v = 0;
     for (uint32_t i = 0; i < T; ++i) {
-      for (uint32_t l = 0; l < K; ++l, ++v) {
+      for (uint32_t l = K - 1; l < K; ++l, ++v) {
         if (v > 0) relay(A1_EMPTY, (v & 1u) ^ 1u);
         for (uint32_t kb = 0; kb < nkb3; ++kb) {
           relay(W_FULL + s, ph);
@@ -262,12 +268,12 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel_split(const SplitArgs
     float *b2s = reinterpret_cast<float *>(smem + P_B2);
     float *w3s = reinterpret_cast<float *>(smem + P_W3);
     float *b3s = reinterpret_cast<float *>(smem + P_B3);
-    float rows[2 * ALINK_MAX_K];
     const float inv1 = sa.inv1, sh = sa.sh, inv2 = sa.inv2;
     uint32_t hq = 0, v = 0;
     for (uint32_t i = 0; i < T; ++i) {
-      for (uint32_t l = 0; l < K; ++l, ++v) {
-        const uint32_t lb = l & 1u;
+      {
+        const uint32_t l = learner_of(i);
+        const uint32_t lb = v & 1u;
         if (et < a.H2) b2s[lb * 64 + et] = __ldg(a.b2 + (size_t)l * a.H2 + et);
         if (et < a.H2 * a.C) w3s[lb * 128 + et] = __ldg(a.W3 + (size_t)l * a.H2 * a.C + et);
         if (et < a.C) b3s[lb * 2 + et] = __ldg(a.b3 + (size_t)l * a.C + et);
@@ -344,13 +350,8 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel_split(const SplitArgs
           p0 = __fsub_rn(1.0f, p1);  // code/keras_wrapper.py:268
           if (a.probs && n < N) a.probs[(size_t)n * a.K + l] = p1;
         }
-        rows[2 * l] = p0;
-        rows[2 * l + 1] = p1;
-        if (l == K - 1 && a.util && n < N) {
-          float c0, c1;
-          alink_consensus2(rows, a.K, &c0, &c1);
-          a.util[n] = alink_utility2(a.measure, rows, a.K, c0, c1);
-        }
+        (void)p0;
+        ++v;
       }
     }
   } else if (warp >= 8) {
@@ -512,12 +513,15 @@ static int split_prepare_heads(alink_ctx *ctx, HeadGroup &g) {
   return ALINK_OK;
 }
 
-// Split-operand scoring of the pairs (ia[n], ib[n]), n < *n_dev (<= cap): util[n] = the K-learner utility, probs optional.
+// Split-operand scoring of the pairs (ia[n], ib[n]), n < *n_dev (<= cap): probs[n][K][C] per-learner probabilities
+// (`util` is unused: the unit of work is one learner, see the kernel).
 // xmax / h1max: a-priori bounds of |x| and |h1| (they set the power-of-two scales).
 static int tc_score_split(alink_ctx *ctx, const HeadGroup &g, const Table &A, const Table &B, const int32_t *ia,
                           const int32_t *ib, int64_t cap, const unsigned int *n_dev, float *probs, float *util, int measure,
                           double xmax, double h1max) {
   if (!g.S1hi) return alink_fail(ctx, ALINK_E_STATE, "split operand images were not prepared");
+  if (!probs) return alink_fail(ctx, ALINK_E_INVALID, "the split kernel writes per-learner probabilities");
+  (void)util;
   tcsp::SplitArgs sa;
   memset(&sa, 0, sizeof(sa));
   tc::Args &a = sa.a;
@@ -535,7 +539,7 @@ static int tc_score_split(alink_ctx *ctx, const HeadGroup &g, const Table &A, co
   sa.sh = split_scale_for(h1max);
   sa.inv1 = 1.0f / (sa.sx * g.sw1);
   sa.inv2 = 1.0f / (sa.sh * g.sw2);
-  const int units = (a.ntiles + 1) / 2, max_units = ctx->sm_count / 2;
+  const int64_t units = (int64_t)((a.ntiles + 1) / 2) * g.K, max_units = ctx->sm_count / 2;
   const unsigned grid = 2u * (unsigned)(units < max_units ? units : max_units);
   ALINK_TRY(dev_reserve(ctx, ctx->xscratch, (size_t)grid * 2 * (2 * a.nkb) * tcsp::XBLK));
   sa.xscratch = (uint8_t *)ctx->xscratch.p;

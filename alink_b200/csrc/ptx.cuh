@@ -234,6 +234,34 @@ __device__ __forceinline__ void umma2_commit_mc(uint32_t bar) {
       : "memory");
 }
 
+// A operand from TENSOR MEMORY (the ".ts" form): A[M x 16] of 16-bit elements lives in 8 consecutive 32-bit TMEM columns of
+// the CTA's 128 lanes (lane = row, column c holds k = 2c in its low half and k = 2c + 1 in its high half), B from shared
+// memory as usual. Saves the shared-memory round trip of an operand the epilogue has just produced.
+__device__ __forceinline__ void umma_f16_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}" ::"r"(d_tmem),
+      "r"(a_tmem), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void umma2_f16_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], [%1], %2, %3, p;\n\t}" ::"r"(d_tmem),
+      "r"(a_tmem), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// 8 consecutive 32-bit columns of this thread's TMEM lane <- 8 registers
+__device__ __forceinline__ void tmem_st8(uint32_t taddr, uint32_t r0, uint32_t r1, uint32_t r2, uint32_t r3, uint32_t r4, uint32_t r5,
+                                         uint32_t r6, uint32_t r7) {
+  asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"r"(taddr), "r"(r0), "r"(r1), "r"(r2),
+               "r"(r3), "r"(r4), "r"(r5), "r"(r6), "r"(r7)
+               : "memory");
+}
+__device__ __forceinline__ void tc_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+
 // UMMA shared-memory descriptor, K-major operand in the canonical SWIZZLE_128B layout:
 // rows of 128 bytes (64 bf16), 8-row groups 1024 bytes apart (SBO), 16-byte chunk c of row r stored
 // at chunk (c ^ (r & 7)); tile base 1024-byte aligned. start address / LBO / SBO in 16-byte units.

@@ -22,6 +22,7 @@
 #pragma once
 #include "common.cuh"
 #include "topk.cuh"
+#include <cooperative_groups.h>
 
 // candidates = pairs whose approximate utility is within `margin` of a reference value: the B-th largest
 // approximate utility (st->prefix = the high 32 bits of its key: select_threshold(..., passes = 3)) or, when `pilot_min` is given, the smallest EXACT utility of the
@@ -138,8 +139,12 @@ __global__ void __launch_bounds__(256) refine_stage1_finish_kernel(unsigned int 
                                                                    int32_t *__restrict__ cia, int32_t *__restrict__ cib) {
   const unsigned int count1 = rs[RS_COUNT1];
   const unsigned int n1 = count1 < cap1 ? count1 : cap1;
-  // the sample fills the last wave of the split kernel (at least ns_min pairs, at most ns_max)
-  unsigned int ns = ((n1 + ns_min + wave_rows - 1) / wave_rows) * wave_rows - n1;
+  // the sample fills the split kernel's last round of (tile pair, learner) units (at least ns_min pairs, at most ns_max):
+  // wave_rows = clusters << 16 | K; a round is `clusters` units = clusters / K tile pairs of 256 rows
+  const unsigned int ncl = wave_rows >> 16, Kl = wave_rows & 0xFFFFu;
+  const unsigned int pairs_min = (n1 + ns_min + 255u) / 256u;
+  const unsigned int rounds = (pairs_min * Kl + ncl - 1u) / ncl;
+  unsigned int ns = (rounds * ncl / Kl) * 256u - n1;
   if (ns > ns_max) ns = ns_max;
   if ((int64_t)ns > N) ns = (unsigned int)N;
   const unsigned int M1 = n1 + ns;
@@ -168,6 +173,152 @@ __global__ void __launch_bounds__(256) refine_stage1_finish_kernel(unsigned int 
     rs[RS_M1] = M1;
     rs[RS_N1] = n1;
     if (count1 > cap1) atomicOr(rs + RS_FLAGS, 1u);
+  }
+}
+
+// Stage 1's bookkeeping in ONE cooperative launch (was: select_init + 3 radix passes + mark + finish = 6 launches, each
+// ~10 us of launch + tail latency for 4 MB of L2-resident data): three histogram passes over the utility bits with a
+// grid-wide barrier after each (every CTA then scans the 2048-bin global histogram redundantly, so nothing has to be
+// broadcast), the candidate compaction, a barrier, and the clamp / sample / table-row translation.
+// hist: 3 x 2048 zeroed counters. tau_out: the B-th largest approximate utility's orderable bits (for the record).
+struct Stage1Args {
+  const float *util;
+  int64_t N;
+  unsigned long long B;
+  float margin;
+  unsigned int cap1, ns_min, ns_max, wave_rows;
+  unsigned int *hist, *rs;
+  uint32_t *cand1;
+  const int32_t *ia, *ib;
+  uint32_t G;
+  int64_t pair0;
+  int32_t *cia, *cib;
+};
+
+__device__ __forceinline__ void stage1_pick(const unsigned int *__restrict__ ghist, int nb, unsigned long long &remaining,
+                                            unsigned int &bin_out, unsigned int *sh, unsigned int *part) {
+  // descending scan of a global histogram by the whole CTA (256 threads); same walk as radix_pass_kernel's last CTA
+  const int tid = threadIdx.x;
+  for (int i = tid; i < nb; i += 256) sh[i] = __ldcg(ghist + i);
+  __syncthreads();
+  const int per = nb / 256;
+  unsigned int mine = 0;
+  for (int j = 0; j < per; ++j) mine += sh[nb - 1 - per * tid - j];
+  part[tid] = mine;
+  __syncthreads();
+  for (int off = 1; off < 256; off <<= 1) {
+    const unsigned int v = tid >= off ? part[tid - off] : 0u;
+    __syncthreads();
+    part[tid] += v;
+    __syncthreads();
+  }
+  __shared__ unsigned int s_bin;
+  __shared__ unsigned long long s_rem;
+  const unsigned long long incl = part[tid], before = incl - mine;
+  if (before < remaining && remaining <= incl) {
+    unsigned long long cum = before;
+    for (int j = 0; j < per; ++j) {
+      const int bin = nb - 1 - per * tid - j;
+      const unsigned int c = sh[bin];
+      if (cum + c >= remaining) {
+        s_bin = (unsigned int)bin;
+        s_rem = remaining - cum;
+        break;
+      }
+      cum += c;
+    }
+  }
+  __syncthreads();
+  bin_out = s_bin;
+  remaining = s_rem;
+  __syncthreads();
+}
+
+__global__ void __launch_bounds__(256) refine_stage1_coop_kernel(const Stage1Args a) {
+  namespace cg = cooperative_groups;
+  cg::grid_group grid = cg::this_grid();
+  __shared__ unsigned int sh[2048];
+  __shared__ unsigned int part[256];
+  const int tid = threadIdx.x, lane = tid & 31;
+  const int64_t stride = (int64_t)gridDim.x * 256;
+  unsigned long long remaining = a.B;
+  unsigned int prefix = 0;  // decided high bits of the orderable utility
+  const int shifts[3] = {21, 10, 0}, nbits[3] = {11, 11, 10};
+#pragma unroll 1
+  for (int p = 0; p < 3; ++p) {
+    const int nb = 1 << nbits[p];
+    for (int i = tid; i < nb; i += 256) sh[i] = 0;
+    __syncthreads();
+    const int hi = shifts[p] + nbits[p];
+    for (int64_t i = (int64_t)blockIdx.x * 256 + tid; i < a.N; i += stride) {
+      const unsigned int o = alink_orderable(__ldg(a.util + i));
+      if (p == 0 || (o >> hi) == prefix) atomicAdd(&sh[(o >> shifts[p]) & (unsigned)(nb - 1)], 1u);
+    }
+    __syncthreads();
+    unsigned int *gh = a.hist + p * 2048;
+    for (int i = tid; i < nb; i += 256)
+      if (sh[i]) atomicAdd(gh + i, sh[i]);
+    __threadfence();
+    grid.sync();
+    unsigned int bin;
+    stage1_pick(gh, nb, remaining, bin, sh, part);
+    prefix = p == 0 ? bin : ((prefix << nbits[p]) | bin);
+  }
+  // candidates: u~ >= tau - margin (ballot compaction, one atomic per warp)
+  const float tau = alink_unorderable(prefix);
+  const float thr = __fsub_rn(tau, a.margin);
+  unsigned int *count = a.rs + RS_COUNT1;
+  for (int64_t n0 = (int64_t)blockIdx.x * 256 + (tid & ~31); n0 < a.N; n0 += stride) {
+    const int64_t n = n0 + lane;
+    const bool keep = n < a.N && __ldg(a.util + n) >= thr;
+    const unsigned int m = __ballot_sync(0xffffffffu, keep);
+    if (m) {
+      const int first = __ffs(m) - 1;
+      unsigned int basepos = 0;
+      if (lane == first) basepos = atomicAdd(count, (unsigned int)__popc(m));
+      basepos = __shfl_sync(0xffffffffu, basepos, first);
+      const unsigned int pos = basepos + __popc(m & ((1u << lane) - 1u));
+      if (keep && pos < a.cap1) a.cand1[pos] = (uint32_t)n;
+    }
+  }
+  __threadfence();
+  grid.sync();
+  // clamp, sample, table rows (refine_stage1_finish_kernel's body)
+  const unsigned int count1 = __ldcg(count);
+  const unsigned int n1 = count1 < a.cap1 ? count1 : a.cap1;
+  const unsigned int ncl = a.wave_rows >> 16, Kl = a.wave_rows & 0xFFFFu;
+  const unsigned int pairs_min = (n1 + a.ns_min + 255u) / 256u;
+  const unsigned int rounds = (pairs_min * Kl + ncl - 1u) / ncl;
+  unsigned int ns = (rounds * ncl / Kl) * 256u - n1;
+  if (ns > a.ns_max) ns = a.ns_max;
+  if ((int64_t)ns > a.N) ns = (unsigned int)a.N;
+  const unsigned int M1 = n1 + ns;
+  for (unsigned int r = blockIdx.x * 256 + tid; r < M1; r += gridDim.x * 256) {
+    uint32_t n;
+    if (r < n1) {
+      n = __ldcg(a.cand1 + r);
+    } else {
+      const unsigned long long j = r - n1;
+      n = (uint32_t)(((2ull * j + 1ull) * (unsigned long long)a.N) / (2ull * ns));
+      a.cand1[r] = n;
+    }
+    if (a.ia) {
+      a.cia[r] = __ldg(a.ia + n);
+      a.cib[r] = __ldg(a.ib + n);
+    } else if (a.G) {
+      const int64_t pp = a.pair0 + n;
+      const int64_t ra = pp / a.G;
+      a.cia[r] = (int32_t)ra;
+      a.cib[r] = (int32_t)(pp - ra * a.G);
+    } else {
+      a.cia[r] = a.cib[r] = (int32_t)n;
+    }
+  }
+  if (blockIdx.x == 0 && tid == 0) {
+    a.rs[RS_M1] = M1;
+    a.rs[RS_N1] = n1;
+    a.rs[14] = prefix;
+    if (count1 > a.cap1) atomicOr(a.rs + RS_FLAGS, 1u);
   }
 }
 

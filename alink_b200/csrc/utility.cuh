@@ -12,8 +12,12 @@
 template <int KT>  // KT > 0: compile-time K (registers); KT == 0: runtime K (local array)
 __global__ void __launch_bounds__(256) utility_kernel(const float *__restrict__ probs, int64_t N, int K,
                                                       int C, int measure, float *__restrict__ util,
-                                                      float *__restrict__ cons) {
+                                                      float *__restrict__ cons, const unsigned int *__restrict__ n_dev = nullptr) {
   const int KK = KT > 0 ? KT : K;
+  if (n_dev) {  // the row count lives on the device (FP32_REFINE's candidate lists); N is then its capacity
+    const int64_t nd = (int64_t)__ldg(n_dev);
+    if (nd < N) N = nd;
+  }
   for (int64_t n = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; n < N;
        n += (int64_t)gridDim.x * blockDim.x) {
     float rows[2 * (KT > 0 ? KT : ALINK_MAX_K)];
@@ -46,20 +50,20 @@ __global__ void __launch_bounds__(256) utility_kernel(const float *__restrict__ 
 }
 
 static int launch_utility(alink_ctx *ctx, const float *probs, int64_t N, int K, int C, int measure,
-                          float *util, float *cons) {
+                          float *util, float *cons, const unsigned int *n_dev = nullptr) {
   if (N == 0) return ALINK_OK;
   int64_t blocks = (N + 255) / 256;
   const int64_t cap = (int64_t)ctx->sm_count * 8;
   if (blocks > cap) blocks = cap;
   dim3 grid((unsigned)blocks);
   switch (K) {
-    case 1: utility_kernel<1><<<grid, 256, 0, ctx->stream>>>(probs, N, K, C, measure, util, cons); break;
-    case 2: utility_kernel<2><<<grid, 256, 0, ctx->stream>>>(probs, N, K, C, measure, util, cons); break;
-    case 3: utility_kernel<3><<<grid, 256, 0, ctx->stream>>>(probs, N, K, C, measure, util, cons); break;
-    case 4: utility_kernel<4><<<grid, 256, 0, ctx->stream>>>(probs, N, K, C, measure, util, cons); break;
-    case 5: utility_kernel<5><<<grid, 256, 0, ctx->stream>>>(probs, N, K, C, measure, util, cons); break;
-    case 8: utility_kernel<8><<<grid, 256, 0, ctx->stream>>>(probs, N, K, C, measure, util, cons); break;
-    default: utility_kernel<0><<<grid, 256, 0, ctx->stream>>>(probs, N, K, C, measure, util, cons); break;
+    case 1: utility_kernel<1><<<grid, 256, 0, ctx->stream>>>(probs, N, K, C, measure, util, cons, n_dev); break;
+    case 2: utility_kernel<2><<<grid, 256, 0, ctx->stream>>>(probs, N, K, C, measure, util, cons, n_dev); break;
+    case 3: utility_kernel<3><<<grid, 256, 0, ctx->stream>>>(probs, N, K, C, measure, util, cons, n_dev); break;
+    case 4: utility_kernel<4><<<grid, 256, 0, ctx->stream>>>(probs, N, K, C, measure, util, cons, n_dev); break;
+    case 5: utility_kernel<5><<<grid, 256, 0, ctx->stream>>>(probs, N, K, C, measure, util, cons, n_dev); break;
+    case 8: utility_kernel<8><<<grid, 256, 0, ctx->stream>>>(probs, N, K, C, measure, util, cons, n_dev); break;
+    default: utility_kernel<0><<<grid, 256, 0, ctx->stream>>>(probs, N, K, C, measure, util, cons, n_dev); break;
   }
   ALINK_LAUNCHED(ctx);
   return ALINK_OK;
