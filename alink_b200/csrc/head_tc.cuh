@@ -53,8 +53,8 @@ constexpr uint32_t P_B2 = P_B1 + 2 * 128 * 4;                 // float [2][64]
 constexpr uint32_t P_W3 = P_B2 + 2 * 64 * 4;                  // float [2][128]
 constexpr uint32_t P_B3 = P_W3 + 2 * 128 * 4;                 // float [2][2]
 constexpr uint32_t BOFF = P_B3 + 16;                          // mbarriers
-enum { W_FULL = 0, W_EMPTY = 4, X_FULL = 8, X_EMPTY = 16, A1_FULL = 24, A1_EMPTY = 26, H1_FULL = 28, H1_EMPTY = 29,
-       A2_FULL = 30, A2_EMPTY = 32, S_FULL = 34, S_EMPTY = 36, NBARS = 38 };  // A2_*: one per layer-2 accumulator; S_*: staged feature tiles (2 buffers)
+enum { W_FULL = 0, W_EMPTY = 4, X_FULL = 8, X_EMPTY = 16, A1_FULL = 24, A1_EMPTY = 26, H1_FULL = 28, H1_EMPTY = 30,
+       A2_FULL = 32, A2_EMPTY = 34, S_FULL = 36, S_EMPTY = 38, NBARS = 40 };  // H1_*: two in ATM mode (the hidden chunk is double-buffered in TMEM), the first one otherwise  // A2_*: one per layer-2 accumulator; S_*: staged feature tiles (2 buffers)
 constexpr uint32_t TOFF = BOFF + NBARS * 8;                   // TMEM base address
 constexpr uint32_t SMEM_BYTES = TOFF + 16;
 static_assert(SMEM_BYTES <= 232448, "exceeds the 227 KB per-CTA shared memory limit");
@@ -70,7 +70,7 @@ constexpr uint32_t P_ONES = P_B1;  // the constant A tile replaces the staged bi
 
 constexpr uint32_t TMEM_COLS = 512;
 constexpr uint32_t ACC2_COL = 256;  // two layer-2 accumulators of 64 columns (consecutive learners alternate)
-constexpr uint32_t HTM_COL = 384;   // ATM: the hidden chunk as layer 2's A operand IN TENSOR MEMORY: 128 halves = 64 columns
+constexpr uint32_t HTM_COL = 384;   // ATM: the hidden chunk as layer 2's A operand IN TENSOR MEMORY: 128 halves = 64 columns, x 2 buffers
 
 struct Args {
   const void *ta, *tb;       // embedding tables (fp32 or bf16), D columns
@@ -213,8 +213,10 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
       ptx::mbar_init(bar(A1_FULL + b), 1);
       ptx::mbar_init(bar(A1_EMPTY + b), 128 + fwd);
     }
-    ptx::mbar_init(bar(H1_FULL), 128 + fwd);
-    ptx::mbar_init(bar(H1_EMPTY), 1);
+    for (int b = 0; b < 2; ++b) {
+      ptx::mbar_init(bar(H1_FULL + b), 128 + fwd);
+      ptx::mbar_init(bar(H1_EMPTY + b), 1);
+    }
     ptx::mbar_init(bar(A2_FULL), 1);
     ptx::mbar_init(bar(A2_FULL + 1), 1);
     ptx::mbar_init(bar(A2_EMPTY), 128 + fwd);
@@ -381,7 +383,8 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
       }
       if (q >= 1) {
         const uint32_t p = q - 1, c = c2;
-        ptx::mbar_wait(bar(H1_FULL), p & 1u);
+        const uint32_t hbuf = ATM ? (p & 1u) : 0u, hpar = ATM ? ((p >> 1) & 1u) : (p & 1u);  // hidden-chunk buffer of item p and its phase
+        ptx::mbar_wait(bar(H1_FULL + hbuf), hpar);
         const uint32_t acc2 = acc2_0 + (v2 & 1u) * 64u;
         // the epilogue has read what the learner before last left in this accumulator
         if (c == 0) ptx::mbar_wait(bar(A2_EMPTY + (v2 & 1u)), ((v2 >> 1) & 1u) ^ 1u);
@@ -395,7 +398,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
 #pragma unroll
             for (uint32_t k = 0; k < 4; ++k) {
               if (ATM) {
-                const uint32_t at = tmem + HTM_COL + (kb2 * 4u + k) * 8u;  // 16 halves of K = 8 columns per MMA
+                const uint32_t at = tmem + HTM_COL + hbuf * 64u + (kb2 * 4u + k) * 8u;  // 16 halves of K = 8 columns per MMA
                 if (NCTA == 2) ptx::umma2_f16_ts(acc2, at, bd + kb2 * kb2_step + 2 * k, idesc2, (c | kb2 | k) != 0u);
                 else ptx::umma_f16_ts(acc2, at, bd + kb2 * kb2_step + 2 * k, idesc2, (c | kb2 | k) != 0u);
               } else {
@@ -404,7 +407,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
             }
           }
           commit(W_EMPTY + s);
-          commit(H1_EMPTY);
+          commit(H1_EMPTY + hbuf);
           if (c == (uint32_t)a.nc - 1) commit(A2_FULL + (v2 & 1u));
         }
         __syncwarp();
@@ -447,7 +450,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
       if (++s == NS) { s = 0; ph ^= 1u; }
       if (q >= 1) {
         const uint32_t p = q - 1;
-        relay(H1_FULL, p & 1u);
+        relay(H1_FULL + (ATM ? (p & 1u) : 0u), ATM ? ((p >> 1) & 1u) : (p & 1u));
         if (c2 == 0 && v2 > 1) relay(A2_EMPTY + (v2 & 1u), ((v2 >> 1) & 1u) ^ 1u);
         if (++c2 == (uint32_t)a.nc) { c2 = 0; ++v2; }
       }
@@ -574,10 +577,11 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
         const uint32_t w5 = pack16_relu<F16>(addb(v[10], bc.z), addb(v[11], bc.w));
         const uint32_t w6 = pack16_relu<F16>(addb(v[12], bd.x), addb(v[13], bd.y));
         const uint32_t w7 = pack16_relu<F16>(addb(v[14], bd.z), addb(v[15], bd.w));
-        if (k == 0) ptx::mbar_wait(bar(H1_EMPTY), (q & 1u) ^ 1u);  // layer 2 of the previous item has read the h1 buffer
+        // layer 2 of the item that used this hidden buffer last (q - 1; q - 2 in ATM mode) has read it
+        if (k == 0) ptx::mbar_wait(bar(H1_EMPTY + (ATM ? b : 0u)), ((ATM ? u : q) & 1u) ^ 1u);
         if (ATM) {
           if (k == 0) ptx::tc_fence_after();
-          ptx::tmem_st8(trow + HTM_COL + k * 8u, w0, w1, w2, w3, w4, w5, w6, w7);
+          ptx::tmem_st8(trow + HTM_COL + b * 64u + k * 8u, w0, w1, w2, w3, w4, w5, w6, w7);
         } else {
           const uint32_t hb = hrow + (k >> 2) * STAGE_BYTES, ch = (k & 3u) * 2u;
           sts128(hb + ((ch ^ hx) << 4), w0, w1, w2, w3);
@@ -608,7 +612,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
       else ptx::fence_proxy_async_smem();
       ptx::tc_fence_before();
       ptx::mbar_arrive(bar(A1_EMPTY + b));
-      ptx::mbar_arrive(bar(H1_FULL));
+      ptx::mbar_arrive(bar(H1_FULL + (ATM ? b : 0u)));
       }  // q < Q
       if (pend) {
         // ---- learner pl is complete for tile pi: layer-2 accumulator -> Dense(H2, C) -> activation

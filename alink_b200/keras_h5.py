@@ -426,10 +426,20 @@ def load_head_weights(path, D_in, H1, H2, C):
     (code/siamese.py:29-32, code/siamese3.py:23-25) from a Keras `.h5` weight file. The head is the last
     three (kernel, bias) pairs of the file (encoder layers, when the file has them, come first); their
     shapes must chain D_in -> H1 -> H2 -> C, as Keras' own shape check in `load_weights` would demand."""
-    flat = [v for _, ws in read_keras_weights(path) for _, v in ws]
+    layers = read_keras_weights(path)
+    flat = [v for _, ws in layers for _, v in ws]
     if len(flat) < 6:
         raise H5FormatError(f"{len(flat)} weight arrays in the file, the head needs 6")
     arrs = [np.ascontiguousarray(a, dtype=np.float32) for a in flat[-6:]]
+    # prefer the LAST three layers whose weights are a (kernel, bias) pair chaining D_in -> H1 -> H2 -> C, wherever
+    # they sit in layer_names (a positional "last six arrays" would be wrong if a weighted layer followed the head)
+    pairs = [[np.ascontiguousarray(v, dtype=np.float32) for _, v in ws] for _, ws in layers
+             if len(ws) == 2 and np.ndim(ws[0][1]) == 2 and np.ndim(ws[1][1]) == 1]
+    for i in range(len(pairs) - 3, -1, -1):
+        cand = pairs[i] + pairs[i + 1] + pairs[i + 2]
+        if [a.shape for a in cand] == [(D_in, H1), (H1,), (H1, H2), (H2,), (H2, C), (C,)]:
+            arrs = cand
+            break
     want = [(D_in, H1), (H1,), (H1, H2), (H2,), (H2, C), (C,)]
     got = [a.shape for a in arrs]
     if got != want:
@@ -690,4 +700,6 @@ def save_head_weights(path, arrs, out_act="softmax"):
     layers = [("input_1", []), ("input_2", []), ("lambda_1", [])]
     for i, (W, b) in enumerate(((W1, b1), (W2, b2), (W3, b3)), 1):
         layers.append((f"dense_{i}", [(f"dense_{i}/kernel:0", W), (f"dense_{i}/bias:0", b)]))
+    if out_act == "softmax":
+        layers.append(("activation_1", []))  # code/siamese.py:32: Activation('softmax') is a (weightless) layer of its own
     return write_keras_weights(path, layers)

@@ -21,6 +21,11 @@ import os
 from . import engine, keras_h5
 
 
+# Keras 2.1.2 (the reference's pin, requirements.txt:18): Adadelta(lr=1.0, rho=0.95, epsilon=1e-8) — the switch to
+# K.epsilon() = 1e-7 came with 2.1.3 [external: keras/optimizers.py at tag 2.1.2, not checkable in this image]
+ADADELTA_EPS = 1e-8
+
+
 def _glorot_uniform(rng, fan_in, fan_out):
     lim = np.sqrt(6.0 / (fan_in + fan_out))  # Keras 2.1.2 Dense default kernel_initializer
     return rng.uniform(-lim, lim, size=(fan_in, fan_out)).astype(np.float32)
@@ -66,7 +71,7 @@ class SiameseNetwork:
 
     def save(self, customName=None):
         s = self._spec  # code/siamese.py:121-125: save_weights(<name> + ".h5")
-        keras_h5.save_head_weights((customName or self.modelName) + ".h5", [s.W1, s.b1, s.W2, s.b2, s.W3, s.b3])
+        keras_h5.save_head_weights((customName or self.modelName) + ".h5", [s.W1, s.b1, s.W2, s.b2, s.W3, s.b3], out_act=self._ACT)
 
     # ---- inference (the path)
     def preprocess(self, X):
@@ -93,7 +98,7 @@ class SiameseNetwork:
     def finetune(self, X, Y, epochs, batch_size, verbose=1, validation_split=0.2, _callbacks=True):
         """code/siamese.py:52-58: Keras `fit(X, to_categorical(Y), batch_size, epochs, validation_split=0.2,
         callbacks=[EarlyStopping('val_loss', min_delta=0.1, patience=5), ReduceLROnPlateau('val_loss', factor=0.2,
-        patience=5, min_lr=0.01)])` with Adadelta(self.learningRate) and binary cross-entropy. [external: Keras 2.1.2
+        patience=5, min_lr=0.01)])` with Adadelta(self.learningRate, rho 0.95, epsilon 1e-8) and binary cross-entropy. [external: Keras 2.1.2
         fit semantics] the LAST `validation_split` of the samples is held out, the rest is reshuffled every epoch
         with np.random.shuffle (seeded by the driver, code/ALINK.py:19) and cut into batches of `batch_size`.
         Every batch is one `alink_train_step` on device-resident weights; returns a Keras-History-like dict."""
@@ -124,13 +129,13 @@ class SiameseNetwork:
             tot_l = tot_a = 0.0
             for lo in range(0, len(idx), batch_size):
                 b = np.ascontiguousarray(idx[lo:lo + batch_size])
-                l, a = ctx.train_step(g, 0, sa, sb, b, b, y[b], lr=lr, apply=apply)
+                l, a = ctx.train_step(g, 0, sa, sb, b, b, y[b], lr=lr, eps=ADADELTA_EPS, apply=apply)
                 tot_l += l * len(b)
                 tot_a += a * len(b)
             return (tot_l / len(idx), tot_a / len(idx)) if len(idx) else (float("nan"), float("nan"))
 
+        order = tr_idx.copy()  # Keras' _fit_loop shuffles ONE index_array in place, epoch after epoch [external: Keras 2.1.2]
         for epoch in range(int(epochs)):
-            order = tr_idx.copy()
             np.random.shuffle(order)
             tl, ta = run(order, True)
             vl, va = run(va_idx, False)

@@ -237,7 +237,7 @@ int alink_disparity_select_sharded(alink_ctx *ctx, const float *p2, const float 
 /* One finetune ("teach") minibatch step of learner `learner` of a head group on the pairs (ia[n], ib[n]), labels
  * y[n] in {0, 1}. Replaces what Keras runs per batch in code/siamese.py:52-58 (finetune ->
  * fit(batch_size=16), called from code/ALINK.py:250) and :86-112 (train_on_batch / test_on_batch): forward,
- * binary cross-entropy + binary accuracy, backward, Adadelta(lr, rho = 0.95, eps = 1e-7) on the group's fp32
+ * binary cross-entropy + binary accuracy, backward, Adadelta(lr, rho, eps; Keras 2.1.2 defaults rho = 0.95, eps = 1e-8) on the group's fp32
  * master weights, which stay on the device (apply = 0: evaluate only, like test_on_batch). loss_out / acc_out:
  * host scalars (batch means, before the update); probs_out: host [nb][C] or NULL. ia, ib, y follow in_space.
  * alink_get_train_state / alink_set_train_state move one learner's six tensors (Keras order W1,b1,W2,b2,W3,b3;

@@ -36,7 +36,7 @@ def test_head_roundtrip_reference_layer_names(tmp_path):
     p = str(tmp_path / "m.h5")
     kh.save_head_weights(p, arrs)
     tree = kh.read_keras_weights(p)
-    assert [l for l, _ in tree] == ["input_1", "input_2", "lambda_1", "dense_1", "dense_2", "dense_3"]
+    assert [l for l, _ in tree] == ["input_1", "input_2", "lambda_1", "dense_1", "dense_2", "dense_3", "activation_1"]  # code/siamese.py:24-33
     assert [n for n, _ in tree[3][1]] == ["dense_1/kernel:0", "dense_1/bias:0"]
     f = kh.H5File(p)
     assert f.root.attrs["backend"] == b"tensorflow" and f.root.attrs["keras_version"] == b"2.1.2"

@@ -110,13 +110,13 @@ def test_finetune_like_alink_driver(ctx, oracle):
     ag, ad = _zeros_like(params), _zeros_like(params)
     np.random.seed(42)
     split = int(n * 0.8)
+    order = np.arange(split, dtype=np.int32)  # one index array shuffled in place every epoch (Keras _fit_loop)
     for epoch in range(3):
-        order = np.arange(split, dtype=np.int32)
         np.random.shuffle(order)
         tot = 0.0
         for lo in range(0, split, 16):
             b = order[lo:lo + 16]
-            l, _ = oracle.train_step(XL, XR, b, b, y[b], params, ag, ad, 512, 512, 64, 2, lr=0.1)
+            l, _ = oracle.train_step(XL, XR, b, b, y[b], params, ag, ad, 512, 512, 64, 2, lr=0.1, eps=siamese.ADADELTA_EPS)
             tot += l * len(b)
         assert hist["loss"][epoch] == pytest.approx(tot / split, rel=1e-6)
     for got, want in zip(model.get_weights(), params):

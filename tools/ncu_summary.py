@@ -4,6 +4,7 @@ Writes the metrics DESIGN.md quotes (duration, DRAM bytes = roofline.traffic, te
 optionally, the warp-stall samples per role (the source page split at each setmaxnreg) as text."""
 import collections
 import csv
+import os
 import io
 import json
 import subprocess
@@ -49,8 +50,8 @@ def main():
     m = {h: {"unit": u, "value": v} for h, u, v in zip(hdr, unit, val) if h in KEEP}
     traffic = sum(float(m[k]["value"]) * UNIT[m[k]["unit"]] for k in ("dram__bytes_read.sum", "dram__bytes_write.sum"))
     doc = {
-        "command": "ncu --set full --clock-control none --import-source on -k regex:head_kernel -c 1 python bench.py --steps 1 "
-                   "--warmup 0 --no-cpu-baseline --no-mode-compare --no-clock-sampling",
+        "command": os.environ.get("NCU_SUMMARY_COMMAND", "ncu --set full --clock-control none --import-source on -k regex:head_kernel "
+                                                         "-s 2 -c 2 python tools/refine_step.py (first of the two captured launches)"),
         "workload": "configs[1]: 1,000,000 pairs, 512-d fp32 table (M=200,000), K=5, one launch of the FP32_REFINE filter "
                     "(tc::head_kernel, pair mode, IEEE-half operands, staged feature tiles)",
         "report": rep,
@@ -65,7 +66,11 @@ def main():
     print("traffic", traffic, "duration", m.get("gpu__time_duration.sum"))
     if len(sys.argv) > 3:
         rows = page(rep, "source")
-        hdr, data = rows[1], rows[2:]
+        hdr = rows[1]
+        data = [r for r in rows[2:] if len(r) >= len(hdr)]  # a report with several kernels repeats the header block: first kernel only
+        cut = next((i for i, r in enumerate(rows[2:]) if len(r) < len(hdr)), None)
+        if cut is not None:
+            data = [r for r in rows[2:2 + cut]]
         isrc, isamp = hdr.index("Source"), hdr.index("# Samples")
         stall = [i for i, h in enumerate(hdr) if h.startswith("stall_") and "Not Issued" not in h]
         marks = [i for i, r in enumerate(data) if "USETMAXREG" in r[isrc]] + [len(data)]
