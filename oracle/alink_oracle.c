@@ -4,11 +4,16 @@
  * load this library, and only as the checker or the timed CPU baseline. The product
  * (alink_b200/) never links, imports or executes anything under oracle/.
  *
- * PARITY STATUS: "parity unpinned" by the reference — /root/reference ships no tests, golden
- * vectors or weights for this path and its Keras-2.1.2/TF-1.15 runtime is not
- * installable here. This restatement is pinned instead against an independent float64 numpy/scipy
- * transcription of the same reference lines (oracle/ref_numpy.py; tests/test_oracle.py) and against
- * committed golden vectors generated by that transcription (tests/golden/).
+ * PARITY STATUS: pinned to the reference's OWN code, executed in the build container, for every row except the Keras
+ * graph. tests/golden/make_ref_fixtures.py imports the unmodified /root/reference modules (uncertainty.py, committee.py,
+ * learners.py + base.py, keras_wrapper.py, readDFW.py, readMTP.py) under a stub of the three packages that cannot be
+ * installed here (modAL, keras, noise), exec's the text of ALINK.py:171-201, and writes tests/golden/ref_*.npz;
+ * tests/golden/make_ref_de_fixture.py does the same with differential_evolution.py. tests/test_ref_pinned.py checks this
+ * oracle against those fixtures (bit-exact; scipy's entropy to 2e-7), tests/test_gpu_ref_pinned.py the CUDA path.
+ * STILL "parity unpinned": the Dense / relu / softmax / sigmoid graph itself (siamese.py:24-33, siamese3.py:18-26), which
+ * exists only inside Keras 2.1.2 / TensorFlow 1.15 (not installable: no network). For it this restatement is pinned
+ * against an independent float64 numpy/scipy transcription (oracle/ref_numpy.py; tests/test_oracle.py) and the golden
+ * vectors generated from it (tests/golden/{softmax,sigmoid}_*.npz).
  *
  * Reference lines restated (paths relative to /root/reference):
  *   pair feature   x = |l - r| ............................ code/siamese.py:27-28, code/siamese3.py:21-22
