@@ -42,6 +42,7 @@ SYMBOLS = (
     "alink_train_step", "alink_get_train_state", "alink_set_train_state",
     "alink_set_refine_eps2", "alink_refine_report_get",
     "alink_perturb_rows", "alink_score_column", "alink_min_disparity",
+    "alink_comm_unique_id", "alink_comm_init", "alink_comm_destroy", "alink_query_sharded",
     "alink_de_init", "alink_de_mutate", "alink_de_repair", "alink_de_evaluate", "alink_de_select", "alink_de_get",
 )
 
@@ -157,6 +158,14 @@ def load():
     L.alink_set_refine_eps2.argtypes = [vp, dbl]
     L.alink_refine_report_get.restype = i32
     L.alink_refine_report_get.argtypes = [vp, C.POINTER(RefineReport)]
+    L.alink_comm_unique_id.restype = i32
+    L.alink_comm_unique_id.argtypes = [vp]
+    L.alink_comm_init.restype = i32
+    L.alink_comm_init.argtypes = [vp, vp, i32, i32]
+    L.alink_comm_destroy.restype = i32
+    L.alink_comm_destroy.argtypes = [vp]
+    L.alink_query_sharded.restype = i32
+    L.alink_query_sharded.argtypes = [vp, i32, i32, i32, vp, vp, i64, i32, i32, i64, i64, vp, vp, vp, i32, vp]
     L.alink_perturb_rows.restype = i32
     L.alink_perturb_rows.argtypes = [vp, i32, vp, i64, i32, i32, i32, u64, i64, i32, dbl, i32, i32]
     L.alink_score_column.restype = i32
@@ -506,6 +515,35 @@ class Context:
 
     def set_refine_eps(self, eps):
         self._check(self._L.alink_set_refine_eps(self._h, float(eps)))
+
+    # ---- multi-GPU exchange behind the C ABI (csrc/comm.cuh)
+    @staticmethod
+    def comm_unique_id():
+        """128 bytes from ncclGetUniqueId (rank 0), to be shipped to every rank."""
+        buf = C.create_string_buffer(128)
+        rc = load().alink_comm_unique_id(buf)
+        if rc != 0:
+            raise AlinkError(f"[{rc}] NCCL is not available (libnccl.so.2 could not be loaded)")
+        return buf.raw
+
+    def comm_init(self, uid, rank, world):
+        self._check(self._L.alink_comm_init(self._h, C.c_char_p(uid), int(rank), int(world)))
+
+    def comm_destroy(self):
+        self._check(self._L.alink_comm_destroy(self._h))
+
+    def query_sharded(self, group, slot_a, slot_b, ia, ib, N, measure, B, base=0, timing=False):
+        """alink_query on this rank's shard + NCCL all-gather of the keys + merge, all inside the library: every rank
+        returns the same GLOBAL (idx, util, keys)."""
+        pia, sp = _ptr_space(ia)
+        pib, _ = _ptr_space(ib)
+        _space_of(ia, ib)
+        idx, util, keys = np.empty((B,), np.int64), np.empty((B,), np.float32), np.empty((B,), np.uint64)
+        t = Timing() if timing else None
+        self._check(self._L.alink_query_sharded(self._h, group, slot_a, slot_b, pia, pib, N, sp, MEASURE_ID[measure], B, base,
+                                                idx.ctypes.data, util.ctypes.data, keys.ctypes.data, HOST,
+                                                C.byref(t) if timing else None))
+        return (idx, util, keys, t) if timing else (idx, util, keys)
 
     # ---- the A2-LINK noise-augmented pool on the device (csrc/perturb.cuh)
     def perturb_rows(self, slot_src, idx, N, side, t, seed, slot_dst, pair_base=0, ncoord=40, vmax=0.25, normalize=True):

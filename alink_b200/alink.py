@@ -34,14 +34,15 @@ def alink_select(bag, disguised_model, clean_X, noisy_Xs, col=1, disparity_ratio
 
 
 def a2link_pool_select(ctx, group_m1, group_m2, slot, ia, ib, N, K1, C=2, T=16, seed=46, col=1, disparity_ratio=0.25, eps=0.05,
-                       blind_strategy=False, y=None, ncoord=40, vmax=0.25, B=1000, scratch_slots=(3, 4), rule=True):
+                       blind_strategy=False, y=None, ncoord=40, vmax=0.25, B=1000, scratch_slots=(3, 4), rule=True, pair_base=0):
     """The A2-LINK noise-augmented pool (BASELINE configs[3]), everything on the device:
     p1 = column `col` of the M1 committee's Bagging mean on the N base pairs (code/ALINK.py:160); for each of the T noise
     types the perturbed copies of both sides are GENERATED on the GPU (alink_perturb_rows: counter-based stream keyed on
     (seed, pair, side, t), the embedding-space analogue of the re-featurised noisy images of :163-168), scored by the
     one-learner model M2 (:170) and reduced to p2[t]; then (i) the reference's disparity rule (:171-201) and (ii) the
     top-B pairs by min_t |p2_t - p1|. Scores never visit the host. `ia` / `ib`: torch cuda int32 (or numpy) row indices
-    into table slot `slot`. Returns (queryIndices, ACTIVE_COUNT, top_idx, top_util, (p1, p2) device tensors)."""
+    into table slot `slot`; `pair_base` = global index of this shard's first pair (it keys the perturbation stream, so a sharded
+    pool generates the same rows as the whole one). Returns (queryIndices, ACTIVE_COUNT, top_idx, top_util, (p1, p2) device tensors)."""
     import torch
     dev = torch.device("cuda", ctx.device)
     p1 = torch.empty((N,), dtype=torch.float32, device=dev)
@@ -50,8 +51,8 @@ def a2link_pool_select(ctx, group_m1, group_m2, slot, ia, ib, N, K1, C=2, T=16, 
     ctx.score_column(-1, col, out=p1)
     sl, sr = scratch_slots
     for t in range(T):
-        ctx.perturb_rows(slot, ia, N, 0, t, seed, sl, ncoord=ncoord, vmax=vmax)
-        ctx.perturb_rows(slot, ib, N, 1, t, seed, sr, ncoord=ncoord, vmax=vmax)
+        ctx.perturb_rows(slot, ia, N, 0, t, seed, sl, pair_base=pair_base, ncoord=ncoord, vmax=vmax)
+        ctx.perturb_rows(slot, ib, N, 1, t, seed, sr, pair_base=pair_base, ncoord=ncoord, vmax=vmax)
         ctx.score_indexed(group_m2, sl, sr, None, None, N, 1, C, want_per=False, want_cons=False)
         ctx.score_column(0, col, out=p2[t])
     idx, active = (ctx.disparity_select(p2, p1, disparity_ratio, eps, blind_strategy, y) if rule else (None, None))

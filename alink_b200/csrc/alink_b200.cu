@@ -14,6 +14,7 @@
 #include "train.cuh"
 #include "de.cuh"
 #include "perturb.cuh"
+#include "comm.cuh"
 
 #include <math.h>
 #include <new>
@@ -82,6 +83,8 @@ int alink_destroy(alink_ctx *ctx) {
                       &ctx->de.ib, &ctx->de.consts, &ctx->de.aux};
   for (DevBuf *b : debufs) dev_release(*b);
   if (ctx->rs_host) cudaFreeHost(ctx->rs_host);
+  if (ctx->comm && nccl_api()) nccl_api()->CommDestroy((alink_nccl_comm)ctx->comm);
+  dev_release(ctx->comm_keys);
   for (int i = 0; i < 8; ++i)
     if (ctx->ev[i]) cudaEventDestroy(ctx->ev[i]);
   if (ctx->copy_stream) {
@@ -1327,6 +1330,74 @@ int alink_set_train_state(alink_ctx *ctx, int group, int learner, int which, con
   return train_state_xfer(ctx, group, learner, which, (float *const *)host_in, false);
 }
 
+
+// ------------------------------------------------------------------------------------------ multi-GPU exchange
+int alink_comm_unique_id(void *id128) {
+  NcclApi *api = nccl_api();
+  if (!api || !id128) return ALINK_E_UNSUPPORTED;
+  alink_nccl_uid u;
+  if (api->GetUniqueId(&u) != 0) return ALINK_E_CUDA;
+  memcpy(id128, &u, sizeof(u));
+  return ALINK_OK;
+}
+
+int alink_comm_init(alink_ctx *ctx, const void *id128, int rank, int world) {
+  if (!ctx) return ALINK_E_INVALID;
+  if (!id128 || world < 1 || rank < 0 || rank >= world) return alink_fail(ctx, ALINK_E_INVALID, "bad rank %d of %d", rank, world);
+  NcclApi *api = nccl_api();
+  if (!api) return alink_fail(ctx, ALINK_E_UNSUPPORTED, "libnccl.so.2 could not be loaded: %s", dlerror() ? dlerror() : "missing symbols");
+  ALINK_CUDA(ctx, cudaSetDevice(ctx->device));
+  if (ctx->comm) {
+    api->CommDestroy((alink_nccl_comm)ctx->comm);
+    ctx->comm = nullptr;
+  }
+  alink_nccl_uid u;
+  memcpy(&u, id128, sizeof(u));
+  alink_nccl_comm c = nullptr;
+  ALINK_NCCL(ctx, api, api->CommInitRank(&c, world, u, rank));
+  ctx->comm = c;
+  ctx->comm_rank = rank;
+  ctx->comm_world = world;
+  return ALINK_OK;
+}
+
+int alink_comm_destroy(alink_ctx *ctx) {
+  if (!ctx) return ALINK_E_INVALID;
+  if (ctx->comm && nccl_api()) {
+    cudaStreamSynchronize(ctx->stream);
+    nccl_api()->CommDestroy((alink_nccl_comm)ctx->comm);
+  }
+  ctx->comm = nullptr;
+  ctx->comm_world = 1;
+  ctx->comm_rank = 0;
+  return ALINK_OK;
+}
+
+// The whole sharded step behind one call: alink_query on this rank's shard (keys stay on the device, indices carry `base`),
+// ncclAllGather of B keys per rank on the context's stream, the same deterministic merge on every rank, results out.
+int alink_query_sharded(alink_ctx *ctx, int group, int slot_a, int slot_b, const int32_t *ia, const int32_t *ib, int64_t N,
+                        int in_space, int measure, int64_t B, int64_t base, int64_t *idx_out, float *util_out, uint64_t *keys_out,
+                        int out_space, alink_timing *timing) {
+  if (!ctx) return ALINK_E_INVALID;
+  if (!ctx->comm || ctx->comm_world == 1)
+    return alink_query(ctx, group, slot_a, slot_b, ia, ib, N, in_space, measure, B < N ? B : N, base, idx_out, util_out, keys_out,
+                       out_space, timing);
+  if (B < 1) return alink_fail(ctx, ALINK_E_INVALID, "B must be >= 1");
+  NcclApi *api = nccl_api();
+  ALINK_CUDA(ctx, cudaSetDevice(ctx->device));
+  const int W = ctx->comm_world;
+  const int64_t bl = B < N ? B : N;  // a shard smaller than B contributes all its pairs; the rest of its slot stays 0
+  ALINK_TRY(dev_reserve(ctx, ctx->comm_keys, sizeof(uint64_t) * (size_t)B * (W + 1)));
+  uint64_t *mine = (uint64_t *)ctx->comm_keys.p, *all = mine + B;
+  ALINK_CUDA(ctx, cudaMemsetAsync(mine, 0, sizeof(uint64_t) * (size_t)B, ctx->stream));  // key 0 sorts below every real key
+  if (bl > 0)
+    ALINK_TRY(alink_query(ctx, group, slot_a, slot_b, ia, ib, N, in_space, measure, bl, base, nullptr, nullptr, mine, ALINK_DEVICE, timing));
+  ALINK_NCCL(ctx, api, api->AllGather(mine, all, (size_t)B, ALINK_NCCL_UINT64, (alink_nccl_comm)ctx->comm, ctx->stream));
+  ctx->launches++;  // the collective's kernel
+  KeySrc src{nullptr, all, 0, nullptr};
+  ALINK_TRY(topk_device(ctx, src, (int64_t)B * W, B));
+  return emit_selection(ctx, B, idx_out, util_out, keys_out, out_space);
+}
 
 // ------------------------------------------------------------------------------------------ A2-LINK pool
 int alink_perturb_rows(alink_ctx *ctx, int slot_src, const int32_t *idx, int64_t N, int in_space, int side, int t, uint64_t seed,

@@ -132,6 +132,10 @@ struct alink_ctx {
   DevBuf train_ws, train_y, train_out;  // train.cuh: activations / gradients of one minibatch
   unsigned long long *wd_host = nullptr;  // host-mapped watchdog record (ptx.cuh: mbar_timeout)
   DeState de;
+  // cross-shard exchange (comm.cuh): an NCCL communicator owned by the context
+  void *comm = nullptr;
+  int comm_rank = 0, comm_world = 1;
+  DevBuf comm_keys;
 };
 
 static inline int alink_fail(alink_ctx *ctx, int code, const char *fmt, ...) {

@@ -140,7 +140,7 @@ def workload_desc(pool, n_gpus, mode, cfg=2, table_rows=None):
                         f"(M={rows:,}), K={h.K} committee {h.D_in}->{h.H1}->{h.H2}->{h.C} {h.act}, "
                         f"measure={pool.measure}, top-{pool.B}",
             "pairs_per_gpu": pool.N, "D": pool.D, "K": h.K, "B": pool.B, "compute": mode,
-            "sharding": f"dp{n_gpus} by pair index, all-gather of top-B keys" if n_gpus > 1 else "single GPU",
+            "sharding": f"dp{n_gpus} by pair index; alink_query_sharded: ncclAllGather of the top-B keys + merge inside the library" if n_gpus > 1 else "single GPU",
             "l2": f"inputs larger than L2 (table {tbytes / 1e6:.0f} MB + {pool.N * 8 / 1e6:.0f} MB indices, random row "
                   "gather; no explicit flush)"}
 
@@ -233,7 +233,7 @@ def run_config45(args, rank, local_rank, world, dev, peaks, emit, torch, dist):
 
         def step():
             idx, active, top_idx, top_util, (p1, p2) = alink.a2link_pool_select(
-                ctx, 0, 1, 0, ia, ib, n, K1, T=T, seed=seed, y=y if world == 1 else None, B=min(B, n), rule=(world == 1))
+                ctx, 0, 1, 0, ia, ib, n, K1, T=T, seed=seed, y=y if world == 1 else None, B=min(B, n), rule=(world == 1), pair_base=lo)
             if world > 1:  # the per-noise prefix is a GLOBAL order statistic: distributed radix select, then local marks
                 idx, active = sharded_disparity_select(ctx, p2, p1, lo, n_total, 0.25, 0.05, False, y, dist=dist, device=dev)
                 keys = torch.zeros((B,), dtype=torch.int64, device=dev)
@@ -402,6 +402,11 @@ def main():
     ctx = _ffi.Context(local_rank)
     ctx.set_stream(torch.cuda.current_stream().cuda_stream)
     ctx.set_heads(0, pool.heads, compute=mode)
+    if world > 1:
+        # the library's own communicator (alink_comm_init): the id travels through the process group that torchrun set up
+        uid = [_ffi.Context.comm_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(uid, src=0)
+        ctx.comm_init(uid[0], rank, world)
     if table_dev is None:
         table_dev = torch.from_numpy(pool.table).to(dev)
     ia_dev = torch.from_numpy(pool.ia).to(dev)
@@ -420,8 +425,8 @@ def main():
         if world == 1:
             _, _, keys, t = ctx.query(0, 0, 0, ia_dev, ib_dev, N, args.measure, B, base=base, timing=True, out=out)
             return keys, t
-        _, _, keys, t = ctx.query(0, 0, 0, ia_dev, ib_dev, N, args.measure, B, base=base, timing=True, out=out_dev)
-        return merge_shards(keys, B, ctx.topk_keys, dist=dist, device=dev), t
+        _, _, keys, t = ctx.query_sharded(0, 0, 0, ia_dev, ib_dev, N, args.measure, B, base=base, timing=True)
+        return keys, t  # shard top-B -> ncclAllGather -> merge, all inside the library (alink_query_sharded)
 
     e2e_slot = {"cur": 1, "primed": False}
     feed = None
@@ -455,8 +460,8 @@ def main():
             _, _, keys, t = ctx.query(0, cur, cur, ia_pin.numpy(), ib_pin.numpy(), N, args.measure, B, base=base,
                                       timing=True, out=out)
             return keys, t
-        _, _, keys, t = ctx.query(0, cur, cur, ia_e, ib_e, N, args.measure, B, base=base, timing=True, out=out_dev)
-        return merge_shards(keys, B, ctx.topk_keys, dist=dist, device=dev), t
+        _, _, keys, t = ctx.query_sharded(0, cur, cur, ia_e, ib_e, N, args.measure, B, base=base, timing=True)
+        return keys, t
 
     def barrier():
         if world > 1:
@@ -581,8 +586,8 @@ def main():
         tbase = rank * NT
 
         def step_target():
-            _, _, keys, t = ctx.query(0, 0, 0, ta_dev, tb_dev, NT, args.measure, B, base=tbase, timing=True, out=out_dev)
-            return merge_shards(keys, B, ctx.topk_keys, dist=dist, device=dev), t
+            _, _, keys, t = ctx.query_sharded(0, 0, 0, ta_dev, tb_dev, NT, args.measure, B, base=tbase, timing=True)
+            return keys, t
 
         ms_t, stage_t, _, _, merged_t, dev_t = timed(step_target, max(3, args.steps), 3)
         tflops = FLOPS_PER_PAIR(K, h.D_in, h.H1, h.H2, h.C) * NT

@@ -259,6 +259,21 @@ int alink_roc_counts(alink_ctx *ctx, const float *scores, const int32_t *mask, i
                      int roc_case, const double *thresholds, int nthr, int in_space, uint64_t *tp, uint64_t *fp,
                      uint64_t *n_genuine, uint64_t *n_impostor);
 
+/* Multi-GPU: the cross-shard exchange behind the C ABI. One process per GPU; pairs shard by index;
+ * the only message of the query path is B packed keys per rank. NCCL is bound at run time (dlopen of libnccl.so.2 by
+ * soname: a process that already loaded NCCL, e.g. through PyTorch, shares that copy), so a host needs nothing but this
+ * header: rank 0 calls alink_comm_unique_id and ships the 128 bytes to the other ranks by any means (file, socket, MPI),
+ * every rank calls alink_comm_init on its context, then alink_query_sharded replaces alink_query: the shard's top-B
+ * (indices carry `base`), ncclAllGather over NVLink on the context's stream, the same deterministic merge on every rank —
+ * the result equals the single-GPU selection bit for bit, ties included. A zero-padded key sorts below every real key, so
+ * shards smaller than B are fine. Without alink_comm_init (or world = 1) alink_query_sharded is alink_query. */
+int alink_comm_unique_id(void *id128);
+int alink_comm_init(alink_ctx *ctx, const void *id128, int rank, int world);
+int alink_comm_destroy(alink_ctx *ctx);
+int alink_query_sharded(alink_ctx *ctx, int group, int slot_a, int slot_b, const int32_t *ia, const int32_t *ib, int64_t N,
+                        int in_space, int measure, int64_t B, int64_t base, int64_t *idx_out, float *util_out, uint64_t *keys_out,
+                        int out_space, alink_timing *timing);
+
 /* The A2-LINK noise-augmented pool generated on the device (BASELINE configs[3]). Replaces the
  * per-noise re-featurisation of code/ALINK.py:163-170 (bag.attackModel -> conversionModel.process) with its embedding-space
  * analogue: row n of slot_dst = normalize(e + delta), e = row idx[n] (or n) of slot_src, delta = `ncoord` coordinates set to

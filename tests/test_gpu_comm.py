@@ -1,0 +1,60 @@
+"""The cross-shard exchange behind the C ABI (alink_comm_init / alink_query_sharded, csrc/comm.cuh) on REAL GPUs, with no
+torch.distributed anywhere: two processes, one GPU each, the NCCL unique id shipped through the spawn arguments. Every rank
+must return the single-GPU selection bit for bit (keys carry global indices). Needs >= 2 GPUs (skipped on the
+one-GPU box; run with `gpurun --gpus 2`)."""
+import multiprocessing as mp
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def _worker(rank, world, uid, q):
+    try:
+        from alink_b200 import _ffi, synth
+        from alink_b200.dist import shard_range
+        pool = synth.make_pool(2, N=300_001)  # ragged: the shards differ in size
+        ctx = _ffi.Context(rank)
+        ctx.set_table(0, pool.table)
+        ctx.set_heads(0, pool.heads, compute=_ffi.FP32_REFINE)
+        whole = ctx.query(0, 0, 0, pool.ia, pool.ib, pool.N, "uncertainty", 1000)
+        ctx.comm_init(uid, rank, world)
+        lo, hi = shard_range(pool.N, rank, world)
+        out = {}
+        for measure in ("uncertainty", "neg_margin"):
+            ref = ctx.query(0, 0, 0, pool.ia, pool.ib, pool.N, measure, 1000)
+            got = ctx.query_sharded(0, 0, 0, np.ascontiguousarray(pool.ia[lo:hi]), np.ascontiguousarray(pool.ib[lo:hi]), hi - lo,
+                                    measure, 1000, base=lo)
+            out[measure] = all(np.array_equal(a, b) for a, b in zip(ref, got))
+        # a shard smaller than B: 600 pairs on rank 1, the rest on rank 0
+        cut = pool.N - 600
+        lo2, hi2 = (0, cut) if rank == 0 else (cut, pool.N)
+        got = ctx.query_sharded(0, 0, 0, np.ascontiguousarray(pool.ia[lo2:hi2]), np.ascontiguousarray(pool.ib[lo2:hi2]), hi2 - lo2,
+                                "uncertainty", 1000, base=lo2)
+        out["small_shard"] = all(np.array_equal(a, b) for a, b in zip(whole, got))
+        ctx.comm_destroy()
+        ctx.close()
+        q.put((rank, out, None))
+    except Exception as e:  # noqa: BLE001
+        import traceback
+        q.put((rank, None, traceback.format_exc() + str(e)))
+
+
+def test_two_ranks_merge_to_the_single_gpu_selection_without_torch_distributed():
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    from alink_b200 import _ffi
+    uid = _ffi.Context.comm_unique_id()
+    mpc = mp.get_context("spawn")
+    q = mpc.Queue()
+    procs = [mpc.Process(target=_worker, args=(r, 2, uid, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=600) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+    for rank, out, err in res:
+        assert err is None, f"rank {rank}: {err}"
+        assert out == {"uncertainty": True, "neg_margin": True, "small_shard": True}, (rank, out)
