@@ -42,7 +42,7 @@ SYMBOLS = (
     "alink_train_step", "alink_get_train_state", "alink_set_train_state",
     "alink_set_refine_eps2", "alink_refine_report_get",
     "alink_perturb_rows", "alink_score_column", "alink_min_disparity",
-    "alink_comm_unique_id", "alink_comm_init", "alink_comm_destroy", "alink_query_sharded",
+    "alink_comm_unique_id", "alink_comm_init", "alink_comm_destroy", "alink_query_sharded", "alink_disparity_select_comm",
     "alink_de_init", "alink_de_mutate", "alink_de_repair", "alink_de_evaluate", "alink_de_select", "alink_de_get",
 )
 
@@ -166,6 +166,9 @@ def load():
     L.alink_comm_destroy.argtypes = [vp]
     L.alink_query_sharded.restype = i32
     L.alink_query_sharded.argtypes = [vp, i32, i32, i32, vp, vp, i64, i32, i32, i64, i64, vp, vp, vp, i32, vp]
+    L.alink_disparity_select_comm.restype = i32
+    L.alink_disparity_select_comm.argtypes = [vp, vp, vp, i64, i32, i64, i64, dbl, dbl, i32, vp, i32, vp, i32,
+                                              C.POINTER(i64), C.POINTER(i64)]
     L.alink_perturb_rows.restype = i32
     L.alink_perturb_rows.argtypes = [vp, i32, vp, i64, i32, i32, i32, u64, i64, i32, dbl, i32, i32]
     L.alink_score_column.restype = i32
@@ -544,6 +547,25 @@ class Context:
                                                 idx.ctypes.data, util.ctypes.data, keys.ctypes.data, HOST,
                                                 C.byref(t) if timing else None))
         return (idx, util, keys, t) if timing else (idx, util, keys)
+
+    def disparity_select_comm(self, p2, p1, base, n_total, ratio=0.25, eps=0.05, blind=False, y=None):
+        """The A-LINK rule on this rank's shard of a pool of n_total pairs, thresholds selected on the device across the
+        communicator (collective call). Returns (this shard's selected GLOBAL indices ascending, global ACTIVE_COUNT)."""
+        dev_in = _is_torch(p2) and p2.is_cuda
+        if not dev_in:
+            p2, p1 = _f32(p2), _f32(p1)
+        T, N = int(p2.shape[0]), int(p2.shape[1])
+        yy = None if y is None else (y if _is_torch(y) else _f32(y).reshape(-1))
+        if dev_in and yy is not None and not _is_torch(yy):
+            import torch
+            yy = torch.from_numpy(yy).to(p2.device)
+        sp = _space_of(p2, p1) if yy is None else _space_of(p2, p1, yy)
+        idx = np.empty((max(N, 1),), np.int64)
+        n_out, active = C.c_int64(0), C.c_int64(0)
+        self._check(self._L.alink_disparity_select_comm(self._h, _ptr_space(p2)[0], _ptr_space(p1)[0], N, T, int(base), int(n_total),
+                                                        float(ratio), float(eps), int(bool(blind)), _ptr_space(yy)[0], sp,
+                                                        idx.ctypes.data, HOST, C.byref(n_out), C.byref(active)))
+        return idx[:n_out.value].copy(), int(active.value)
 
     # ---- the A2-LINK noise-augmented pool on the device (csrc/perturb.cuh)
     def perturb_rows(self, slot_src, idx, N, side, t, seed, slot_dst, pair_base=0, ncoord=40, vmax=0.25, normalize=True):

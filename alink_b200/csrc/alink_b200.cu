@@ -1726,7 +1726,8 @@ int alink_roc_counts(alink_ctx *ctx, const float *scores, const int32_t *mask, i
 // the returned indices carry base + j; thr == null: single shard, the threshold is selected here.
 static int disparity_impl(alink_ctx *ctx, const float *p2, const float *p1, int64_t N, int T, double ratio,
                           double eps, int blind, const float *y, int in_space, int64_t *idx_out, int out_space,
-                          int64_t *n_out, int64_t *active_count, int64_t base, const uint64_t *thr) {
+                          int64_t *n_out, int64_t *active_count, int64_t base, const uint64_t *thr,
+                          int64_t n_total_comm = -1) {
   if (!ctx) return ALINK_E_INVALID;
   if (N < 0 || T < 1 || !n_out) return alink_fail(ctx, ALINK_E_INVALID, "bad arguments (N=%lld, T=%d)", (long long)N, T);
   if (N > 0xFFFFFFFEll || base < 0 || base + N > 0xFFFFFFFFll) return alink_fail(ctx, ALINK_E_INVALID, "N / base out of range");
@@ -1758,12 +1759,33 @@ static int disparity_impl(alink_ctx *ctx, const float *p2, const float *p1, int6
   int64_t sb = (N + 2047) / 2048;
   const int64_t cap = (int64_t)ctx->sm_count * 8;
   if (sb > cap) sb = cap;
-  const int64_t m = (int64_t)((double)N * ratio);  // int(len * ratio), code/ALINK.py:183
+  const int64_t m = (int64_t)((double)(n_total_comm >= 0 ? n_total_comm : N) * ratio);  // int(len * ratio), code/ALINK.py:183
+  NcclApi *napi = n_total_comm >= 0 ? nccl_api() : nullptr;
+  static const int shifts6[6] = {53, 42, 32, 21, 10, 0};
+  static const int nbits6[6] = {11, 11, 10, 11, 11, 10};
   for (int t = 0; t < T; ++t) {
     const float *q = (const float *)dp2 + (size_t)t * N;
     if (blind) {
       disparity_blind_kernel<<<(unsigned)sb, 256, 0, ctx->stream>>>(q, (const float *)dp1, N, cnt);
       ALINK_LAUNCHED(ctx);
+    } else if (napi) {
+      // sharded pool, everything on the device: six histogram passes over this shard's keys, each summed across the
+      // ranks by ncclAllReduce on the context's stream, the bin picked by one CTA; then the marks against that key
+      if (m > 0) {
+        select_init_kernel<<<1, 256, 0, ctx->stream>>>(st, (unsigned long long)m);
+        ALINK_LAUNCHED(ctx);
+        for (int p = 0; p < 6; ++p) {
+          disparity_hist_kernel<<<(unsigned)sb, 256, 0, ctx->stream>>>(q, (const float *)dp1, N, (uint64_t)base, 0ull, shifts6[p], nbits6[p],
+                                                                        p == 0, st->hist, st);
+          ALINK_LAUNCHED(ctx);
+          ALINK_NCCL(ctx, napi, napi->AllReduce(st->hist, st->hist, 2048, ALINK_NCCL_UINT32, ALINK_NCCL_SUM, (alink_nccl_comm)ctx->comm, ctx->stream));
+          ctx->launches++;
+          select_pick_kernel<<<1, 256, 0, ctx->stream>>>(st->hist, nbits6[p], p == 0, st);
+          ALINK_LAUNCHED(ctx);
+        }
+        disparity_mark_thr_kernel<<<(unsigned)sb, 256, 0, ctx->stream>>>(q, (const float *)dp1, N, (uint64_t)base, 1ull, cnt, &st->prefix);
+        ALINK_LAUNCHED(ctx);
+      }
     } else if (thr) {
       if (thr[t]) {
         disparity_mark_thr_kernel<<<(unsigned)sb, 256, 0, ctx->stream>>>(q, (const float *)dp1, N, (uint64_t)base,
@@ -1804,7 +1826,10 @@ static int disparity_impl(alink_ctx *ctx, const float *p2, const float *p1, int6
     }
   }
   unsigned long long hc[2];
-  ALINK_CUDA(ctx, cudaMemcpyAsync(hc, counters, 16, cudaMemcpyDeviceToHost, ctx->stream));
+  ALINK_CUDA(ctx, cudaMemcpyAsync(hc + 1, counters + 1, 8, cudaMemcpyDeviceToHost, ctx->stream));
+  if (napi)  // ACTIVE_COUNT is a count over the whole pool
+    ALINK_NCCL(ctx, napi, napi->AllReduce(counters, counters, 1, ALINK_NCCL_UINT64, ALINK_NCCL_SUM, (alink_nccl_comm)ctx->comm, ctx->stream));
+  ALINK_CUDA(ctx, cudaMemcpyAsync(hc, counters, 8, cudaMemcpyDeviceToHost, ctx->stream));
   ALINK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
   *n_out = (int64_t)hc[1];
   if (active_count) *active_count = (int64_t)hc[0];
@@ -1830,6 +1855,16 @@ int alink_disparity_select_sharded(alink_ctx *ctx, const float *p2, const float 
   static const uint64_t none[1] = {0};
   return disparity_impl(ctx, p2, p1, N, T, 1.0, eps, blind, y, in_space, idx_out, out_space, n_out, active_count, base,
                         blind ? none : thr_keys);
+}
+
+int alink_disparity_select_comm(alink_ctx *ctx, const float *p2, const float *p1, int64_t N, int T, int64_t base, int64_t n_total,
+                                double ratio, double eps, int blind, const float *y, int in_space, int64_t *idx_out, int out_space,
+                                int64_t *n_out, int64_t *active_count) {
+  if (!ctx) return ALINK_E_INVALID;
+  if (!ctx->comm || !nccl_api()) return alink_fail(ctx, ALINK_E_STATE, "alink_comm_init first");
+  if (n_total < N) return alink_fail(ctx, ALINK_E_INVALID, "n_total (the whole pool) is smaller than this shard");
+  return disparity_impl(ctx, p2, p1, N, T, ratio, eps, blind, y, in_space, idx_out, out_space, n_out, active_count, base, nullptr,
+                        n_total);
 }
 
 int alink_disparity_hist(alink_ctx *ctx, const float *q, const float *p1, int64_t N, int64_t base, uint64_t prefix,

@@ -31,7 +31,9 @@ __global__ void __launch_bounds__(256) disparity_mark_kernel(const float *__rest
 // sharded pools (alink_b200/dist.py): membership against an explicit GLOBAL threshold key, keys carry base + j
 __global__ void __launch_bounds__(256) disparity_mark_thr_kernel(const float *__restrict__ q, const float *__restrict__ p1,
                                                                  int64_t N, uint64_t base, unsigned long long thr,
-                                                                 int *__restrict__ cnt) {
+                                                                 int *__restrict__ cnt, const unsigned long long *thr_dev = nullptr) {
+  if (thr_dev) thr = *thr_dev;  // the threshold was selected on the device (alink_disparity_select_comm)
+  if (thr == 0ull) return;      // 0 = nothing passes
   for (int64_t j = (int64_t)blockIdx.x * 256 + threadIdx.x; j < N; j += (int64_t)gridDim.x * 256)
     if (alink_pack_key(fabsf(__fsub_rn(__ldg(q + j), __ldg(p1 + j))), base + (uint64_t)j) >= thr) cnt[j] += 1;
 }
@@ -40,8 +42,10 @@ __global__ void __launch_bounds__(256) disparity_mark_thr_kernel(const float *__
 // histograms (all-reduce) and pick the bin on the host, so the threshold is the global order statistic
 __global__ void __launch_bounds__(256) disparity_hist_kernel(const float *__restrict__ q, const float *__restrict__ p1,
                                                              int64_t N, uint64_t base, unsigned long long prefix, int shift,
-                                                             int bits, int first, unsigned int *__restrict__ hist) {
+                                                             int bits, int first, unsigned int *__restrict__ hist,
+                                                             const SelectState *st = nullptr) {
   __shared__ unsigned int sh[2048];
+  if (st) prefix = st->prefix;  // device-resident select state (the bins are picked on the device after the all-reduce)
   const int nb = 1 << bits;
   const unsigned mask = (unsigned)nb - 1u;
   for (int i = threadIdx.x; i < nb; i += 256) sh[i] = 0;

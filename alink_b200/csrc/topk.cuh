@@ -104,6 +104,43 @@ __global__ void __launch_bounds__(256) radix_pass_kernel(KeySrc src, int64_t n, 
   if (threadIdx.x == 0) st->ticket = 0;
 }
 
+// The bin-picking tail of radix_pass_kernel on its own: for histograms that were summed ACROSS RANKS first (ncclAllReduce;
+// the sharded A-LINK rule, disparity.cuh). One CTA; narrows (prefix, remaining) in `st` and clears the histogram.
+__global__ void __launch_bounds__(256) select_pick_kernel(unsigned int *__restrict__ hist, int bits, int first, SelectState *st) {
+  __shared__ unsigned int sh[2048];
+  __shared__ unsigned int part[256];
+  const int nb = 1 << bits;
+  for (int i = threadIdx.x; i < nb; i += 256) sh[i] = hist[i];
+  __syncthreads();
+  const int per = nb / 256;
+  unsigned int mine = 0;
+  for (int j = 0; j < per; ++j) mine += sh[nb - 1 - per * threadIdx.x - j];
+  part[threadIdx.x] = mine;
+  const unsigned long long remaining = st->remaining, prefix = st->prefix;
+  __syncthreads();
+  for (int off = 1; off < 256; off <<= 1) {
+    unsigned int v = threadIdx.x >= off ? part[threadIdx.x - off] : 0u;
+    __syncthreads();
+    part[threadIdx.x] += v;
+    __syncthreads();
+  }
+  const unsigned long long incl = part[threadIdx.x], before = incl - mine;
+  if (before < remaining && remaining <= incl) {
+    unsigned long long cum = before;
+    for (int j = 0; j < per; ++j) {
+      const int bin = nb - 1 - per * threadIdx.x - j;
+      const unsigned int c = sh[bin];
+      if (cum + c >= remaining) {
+        st->prefix = first ? (unsigned long long)bin : ((prefix << bits) | (unsigned long long)bin);
+        st->remaining = remaining - cum;
+        break;
+      }
+      cum += c;
+    }
+  }
+  for (int i = threadIdx.x; i < 2048; i += 256) hist[i] = 0;
+}
+
 // Small sources (the exact re-score's candidates, the cross-shard merge of B keys per rank): the same passes
 // inside ONE CTA — no global histogram, no ticket, one launch instead of seven. Each multi-CTA pass costs
 // ~10 us of launch + tail-scan latency whatever n is, which is all a 10 k-key select consists of.

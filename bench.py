@@ -185,6 +185,10 @@ def run_config45(args, rank, local_rank, world, dev, peaks, emit, torch, dist):
     torch.cuda.set_stream(torch.cuda.Stream(device=dev))
     ctx = _ffi.Context(local_rank)
     ctx.set_stream(torch.cuda.current_stream().cuda_stream)
+    if world > 1:
+        uid = [_ffi.Context.comm_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(uid, src=0)
+        ctx.comm_init(uid[0], rank, world)
     mode = "bf16" if args.mode == "refine" and args.config == 4 else args.mode  # config 4 needs scores, not a selection
     cid = _ffi.COMPUTE_ID[mode]
     B = 1000
@@ -234,8 +238,11 @@ def run_config45(args, rank, local_rank, world, dev, peaks, emit, torch, dist):
         def step():
             idx, active, top_idx, top_util, (p1, p2) = alink.a2link_pool_select(
                 ctx, 0, 1, 0, ia, ib, n, K1, T=T, seed=seed, y=y if world == 1 else None, B=min(B, n), rule=(world == 1), pair_base=lo)
-            if world > 1:  # the per-noise prefix is a GLOBAL order statistic: distributed radix select, then local marks
-                idx, active = sharded_disparity_select(ctx, p2, p1, lo, n_total, 0.25, 0.05, False, y, dist=dist, device=dev)
+            if world > 1:  # the per-noise prefix is a GLOBAL order statistic: radix select across the ranks on the device
+                idx, active = ctx.disparity_select_comm(p2, p1, lo, n_total, 0.25, 0.05, False, y)
+                cnt = torch.tensor([len(idx)], dtype=torch.int64, device=dev)
+                dist.all_reduce(cnt)
+                idx = np.empty((int(cnt.item()),), np.int64)  # (only the count is reported; the indices stay sharded)
                 keys = torch.zeros((B,), dtype=torch.int64, device=dev)
                 _, _, k = ctx.select_topk(min(B, n), base=lo)
                 keys[:len(k)] = torch.from_numpy(k.view(np.int64)).to(dev)

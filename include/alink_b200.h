@@ -274,6 +274,16 @@ int alink_query_sharded(alink_ctx *ctx, int group, int slot_a, int slot_b, const
                         int in_space, int measure, int64_t B, int64_t base, int64_t *idx_out, float *util_out, uint64_t *keys_out,
                         int out_space, alink_timing *timing);
 
+/* The A-LINK rule on a pool sharded over the communicator's ranks, thresholds selected ON THE DEVICE: per noise type six
+ * histogram passes over this shard's keys, each summed across the ranks by ncclAllReduce on the context's stream, the bin
+ * picked by one CTA (no host round trip per pass: round 1 did 6 x T of them from Python), then marks, intersection, grey zone
+ * and oracle agreement locally. p2 (T x N), p1, y: this rank's pairs [base, base + N) of a pool of n_total pairs. idx_out:
+ * this rank's selected pairs as GLOBAL indices, ascending (capacity N); n_out: their count; active_count: ACTIVE_COUNT of the
+ * WHOLE pool (all-reduced). Every rank must call it (collective). */
+int alink_disparity_select_comm(alink_ctx *ctx, const float *p2, const float *p1, int64_t N, int T, int64_t base, int64_t n_total,
+                                double ratio, double eps, int blind, const float *y, int in_space, int64_t *idx_out, int out_space,
+                                int64_t *n_out, int64_t *active_count);
+
 /* The A2-LINK noise-augmented pool generated on the device (BASELINE configs[3]). Replaces the
  * per-noise re-featurisation of code/ALINK.py:163-170 (bag.attackModel -> conversionModel.process) with its embedding-space
  * analogue: row n of slot_dst = normalize(e + delta), e = row idx[n] (or n) of slot_src, delta = `ncoord` coordinates set to

@@ -33,6 +33,20 @@ def _worker(rank, world, uid, q):
         got = ctx.query_sharded(0, 0, 0, np.ascontiguousarray(pool.ia[lo2:hi2]), np.ascontiguousarray(pool.ib[lo2:hi2]), hi2 - lo2,
                                 "uncertainty", 1000, base=lo2)
         out["small_shard"] = all(np.array_equal(a, b) for a, b in zip(whole, got))
+        # the A-LINK rule with thresholds selected on the device across the ranks == the single-shot rule on the whole pool
+        rng = np.random.default_rng(5)
+        n, T = 40_001, 5
+        p1 = rng.random(n).astype(np.float32)
+        p2 = np.clip(p1[None, :] + rng.normal(0, 0.2, (T, n)), 0, 1).astype(np.float32)
+        p2[:, 100:140] = p2[:, 60:100]          # ties across ...
+        p1[100:140] = p1[60:100]
+        y = (rng.random(n) < 0.5).astype(np.float32)
+        for blind in (False, True):
+            ridx, ract = ctx.disparity_select(p2, p1, 0.25, 0.05, blind, y)
+            lo3, hi3 = shard_range(n, rank, world)
+            gidx, gact = ctx.disparity_select_comm(np.ascontiguousarray(p2[:, lo3:hi3]), np.ascontiguousarray(p1[lo3:hi3]), lo3, n, 0.25,
+                                                   0.05, blind, np.ascontiguousarray(y[lo3:hi3]))
+            out[f"rule_blind{int(blind)}"] = bool(np.array_equal(gidx, ridx[(ridx >= lo3) & (ridx < hi3)]) and gact == ract)
         ctx.comm_destroy()
         ctx.close()
         q.put((rank, out, None))
@@ -57,4 +71,4 @@ def test_two_ranks_merge_to_the_single_gpu_selection_without_torch_distributed()
         p.join(timeout=60)
     for rank, out, err in res:
         assert err is None, f"rank {rank}: {err}"
-        assert out == {"uncertainty": True, "neg_margin": True, "small_shard": True}, (rank, out)
+        assert out == {"uncertainty": True, "neg_margin": True, "small_shard": True, "rule_blind0": True, "rule_blind1": True}, (rank, out)
