@@ -867,6 +867,16 @@ static int refine_query_v2(alink_ctx *ctx, const HeadGroup &g, Table &A, Table &
   if (ctx->refine_eps <= 0.0 && ctx->refine_eps_hint[gi] > eps1) eps1 = ctx->refine_eps_hint[gi];
   double eps2 = ctx->refine_eps2 > 0.0 ? ctx->refine_eps2 : REFINE_EPS2;
   const double sc = REFINE_SCALE[measure];
+  // the band of the consensus measures lives in u = min(pbar, 1 - pbar) (refine_threshold): eps bounds the probability, and
+  // every learner's LOGIT is then off by at most ez = 4 sqrt(K) eps (eps is the 8-sigma bound of a mean of K learners at
+  // slope 1/4). ALINK_REFINE_BAND=0 keeps the additive band in utility space for every measure.
+  static const int band_env = [] { const char *e = getenv("ALINK_REFINE_BAND"); return e ? atoi(e) : 1; }();
+  const int band_measure = band_env ? measure : -1;
+  const bool band_on = band_measure == ALINK_UTIL_UNCERTAINTY || band_measure == ALINK_UTIL_NEG_MARGIN ||
+                       band_measure == ALINK_UTIL_ENTROPY || band_measure == ALINK_UTIL_CONSENSUS_ENTROPY;
+  const int band_stat = band_on ? band_measure : -1;  // error statistics in probability space (refine_finish_kernel)
+  const double scv = band_on ? 1.0 : sc;              // ... where the bounds apply without a per-measure factor
+  const double ezk = 4.0 * sqrt((double)g.K);
   // (1) approximate utilities of every pair (fused K-learner reduction in the kernel's epilogue)
   ALINK_TRY(tc_score(ctx, g, A, Bt, ia, ib, N, nullptr, util_a, measure, true));
   if (ev) ALINK_CUDA(ctx, cudaEventRecord(ev[2], ctx->stream));
@@ -883,6 +893,7 @@ static int refine_query_v2(alink_ctx *ctx, const HeadGroup &g, Table &A, Table &
       ALINK_CUDA(ctx, cudaMemsetAsync(rs, 0, (RS_WORDS + 3 * 2048) * sizeof(unsigned int), ctx->stream));
       Stage1Args sa1;
       sa1.util = util_a; sa1.N = N; sa1.B = (unsigned long long)B; sa1.margin = (float)(2.0 * eps1 * sc);
+      sa1.measure = band_measure; sa1.eps = eps1; sa1.ez = ezk * eps1;
       sa1.cap1 = (unsigned int)cap1; sa1.ns_min = ns_min; sa1.ns_max = ns_max; sa1.wave_rows = wave;
       sa1.hist = hist; sa1.rs = rs; sa1.cand1 = (uint32_t *)ctx->cand.p; sa1.ia = ia; sa1.ib = ib;
       sa1.G = ia ? 0u : ctx->ap_G; sa1.pair0 = ctx->ap_pair0; sa1.cia = (int32_t *)ctx->cia.p; sa1.cib = (int32_t *)ctx->cib.p;
@@ -896,7 +907,8 @@ static int refine_query_v2(alink_ctx *ctx, const HeadGroup &g, Table &A, Table &
     } else {
       ALINK_CUDA(ctx, cudaMemsetAsync(rs, 0, RS_WORDS * sizeof(unsigned int), ctx->stream));
       refine_mark_kernel<<<(unsigned)blocks, 256, 0, ctx->stream>>>(util_a, N, st, nullptr, (float)(2.0 * eps1 * sc),
-                                                                    (uint32_t *)ctx->cand.p, rs + RS_COUNT1, (unsigned int)cap1);
+                                                                    (uint32_t *)ctx->cand.p, rs + RS_COUNT1, (unsigned int)cap1,
+                                                                    band_measure, eps1, ezk * eps1);
       ALINK_LAUNCHED(ctx);
       refine_stage1_finish_kernel<<<(unsigned)(rows1 / 4096 > 64 ? (rows1 / 4096 > capb ? capb : rows1 / 4096) : 64), 256, 0, ctx->stream>>>(
           rs, (unsigned int)cap1, N, ns_min, ns_max, wave, (uint32_t *)ctx->cand.p, ia, ib, ia ? 0u : ctx->ap_G, ctx->ap_pair0,
@@ -915,7 +927,8 @@ static int refine_query_v2(alink_ctx *ctx, const HeadGroup &g, Table &A, Table &
       ALINK_TRY(launch_utility(ctx, (const float *)ctx->probs2.p, rows1, g.K, g.C, measure, (float *)ctx->util2.p, nullptr, rs + RS_M1));
     }
     // (5) tau2, C2 = {u2 >= tau2 - 2 eps2} + every 16th sample row; their table rows
-    refine_stage2_kernel<<<1, 1024, 0, ctx->stream>>>(rs, (const float *)ctx->util2.p, (unsigned long long)B, (float)(2.0 * eps2 * sc), cap2,
+    refine_stage2_kernel<<<1, 1024, 0, ctx->stream>>>(rs, (const float *)ctx->util2.p, (unsigned long long)B, (float)(2.0 * eps2 * sc),
+                                                      band_measure, eps2, ezk * eps2, cap2,
                                                       ns2_max, (const uint32_t *)ctx->cand.p, (const int32_t *)ctx->cia.p,
                                                       (const int32_t *)ctx->cib.p, (int32_t *)ctx->cia2.p, (int32_t *)ctx->cib2.p,
                                                       (uint32_t *)ctx->map2.p, (uint32_t *)ctx->src2.p);
@@ -939,7 +952,7 @@ static int refine_query_v2(alink_ctx *ctx, const HeadGroup &g, Table &A, Table &
   refine_finish_kernel<KT><<<fb, 256, 0, ctx->stream>>>(rs, (const float *)ctx->probs.p, g.K, g.C, measure, util_a,        \
                                                         (const float *)ctx->util2.p, (const uint32_t *)ctx->cand.p,        \
                                                         (const uint32_t *)ctx->map2.p, (const uint32_t *)ctx->src2.p,      \
-                                                        (float *)ctx->util_c.p)
+                                                        (float *)ctx->util_c.p, (const float *)ctx->probs2.p, band_stat)
       switch (g.K) {
         case 1: ALINK_FINISH(1); break;
         case 3: ALINK_FINISH(3); break;
@@ -988,11 +1001,16 @@ static int refine_query_v2(alink_ctx *ctx, const HeadGroup &g, Table &A, Table &
     }
     // Both bounds must hold on everything we can check: stage 2 against the exact values (C2 u S2), stage 1 against
     // stage 2 (C1 u S, to within eps2) and against the exact values. Otherwise widen past what was seen and redo.
-    const double seen2 = (double)e2 / sc;
-    const double s1a = (double)e1 / sc + eps2, s1b = (double)ea / sc;  // |u~ - u| <= |u~ - u2| + eps2
+    float rel1;
+    memcpy(&rel1, h + RS_REL1, 4);
+    const double seen2 = (double)e2 / scv;
+    const double s1a = (double)e1 / scv + eps2, s1b = (double)ea / scv;  // |u~ - u| <= |u~ - u2| + eps2
     double seen1 = s1a > s1b ? s1a : s1b;
-    const double tail1 = 8.0 * (double)ctx->refine_rms_err / sc;  // 8 sigma of the candidates' error must fit as well
-    const bool bad2 = seen2 > eps2, bad1 = seen1 > eps1 || tail1 > eps1;
+    const double tail1 = 8.0 * (double)ctx->refine_rms_err / scv;  // 8 sigma of the candidates' error must fit as well
+    // the multiplicative band's premise: relative error of u below e^ez - 1 (checked where u >= 1e-3)
+    const bool badrel = band_on && (double)rel1 > expm1(ezk * eps1);
+    if (badrel && (double)rel1 / ezk * 1.05 > seen1) seen1 = log1p((double)rel1) / ezk * 1.05;
+    const bool bad2 = seen2 > eps2, bad1 = seen1 > eps1 || tail1 > eps1 || badrel;
     if (tail1 > 2.0 * seen1) seen1 = 0.5 * tail1;
     if ((!bad1 && !bad2) || round >= 5) {
       if (bad1 || bad2) {  // could not be verified in 5 rounds: run it exactly

@@ -24,16 +24,72 @@
 #include "topk.cuh"
 #include <cooperative_groups.h>
 
+// ---- where the candidate band ends, in the space the error bound lives in -------------------------------------------------
+// For the measures that are monotone functions of u = min(pbar, 1 - pbar) of the two-column consensus — uncertainty U = u,
+// neg-margin U = 2u - 1, entropy / consensus entropy U = H(u) — the filter's error is bounded in u, not in U:
+//   additive        |u~ - u| <= eps                        (probability error; eps = the stage's bound)
+//   multiplicative  u e^-ez <= u~ <= u e^ez                 (each learner's LOGIT is off by at most ez, and sigma(d + e) lies
+//                                                            between sigma(d) e^-|e| and sigma(d) e^|e|; so does the mean)
+// Let a0 = g^-1(tau - nu) be the u of the B-th largest approximate utility (nu = evaluation noise of the fp32 measure).
+// The approximate top-B members have true u >= a1 = max(a0 - eps, a0 e^-ez), so the exact B-th utility is >= g(a1) - nu; a
+// pair at or above it has u >= a2 = g^-1(g(a1) - 2 nu) and therefore u~ >= a3 = max(a2 - eps, a2 e^-ez):
+//   threshold = g(a3) - nu.
+// For uncertainty this is tau - 2 eps (the additive band) unless the head is so confident that the B-th utility is small,
+// where the multiplicative band takes over (the additive one would swallow the pool); for the entropy measures, whose
+// utility is flat at the top (H ~ ln 2 - 2 (u - 1/2)^2), it is a band of 2 eps in u instead of 2.5 eps in H — 10-30 % of a
+// pool. Other measures (KL-max) keep the additive band in utility space. Double precision, once per CTA.
+__device__ __forceinline__ double refine_H(double u) {
+  if (u <= 0.0) return 0.0;
+  if (u >= 0.5) return 0.6931471805599453;
+  return -(u * log(u) + (1.0 - u) * log(1.0 - u));
+}
+__device__ __forceinline__ double refine_Hinv(double h) {  // u in [0, 1/2] with H(u) = h
+  if (h <= 0.0) return 0.0;
+  if (h >= 0.6931471805599453) return 0.5;
+  double lo = 0.0, hi = 0.5;
+  for (int i = 0; i < 60; ++i) {
+    const double mid = 0.5 * (lo + hi);
+    if (refine_H(mid) < h) lo = mid; else hi = mid;
+  }
+  return lo;  // the lower end: a smaller u only widens the band
+}
+__device__ __forceinline__ double refine_g(int measure, double u) {
+  return measure == ALINK_UTIL_UNCERTAINTY ? u : (measure == ALINK_UTIL_NEG_MARGIN ? 2.0 * u - 1.0 : refine_H(u));
+}
+__device__ __forceinline__ double refine_ginv(int measure, double U) {
+  const double u = measure == ALINK_UTIL_UNCERTAINTY ? U : (measure == ALINK_UTIL_NEG_MARGIN ? 0.5 * (U + 1.0) : refine_Hinv(U));
+  return u < 0.0 ? 0.0 : (u > 0.5 ? 0.5 : u);
+}
+__device__ __forceinline__ float refine_threshold(int measure, float tau, float margin, double eps, double ez) {
+  const bool ent = measure == ALINK_UTIL_ENTROPY || measure == ALINK_UTIL_CONSENSUS_ENTROPY;
+  if (!(measure == ALINK_UTIL_UNCERTAINTY || measure == ALINK_UTIL_NEG_MARGIN || ent) || !(eps > 0.0)) return __fsub_rn(tau, margin);
+  const double nu = ent ? 4.0e-7 : 1.2e-7;
+  const double shrink = exp(-ez);
+  const double a0 = refine_ginv(measure, (double)tau - nu);
+  const double a1 = fmax(a0 - eps, a0 * shrink);
+  const double a2 = refine_ginv(measure, refine_g(measure, a1) - 2.0 * nu);
+  const double a3 = fmax(a2 - eps, a2 * shrink);
+  double thr = refine_g(measure, a3) - nu;
+  if (!ent) {  // never wider than the plain additive band in utility space (the entropy band is the point of all this)
+    const double add = (double)tau - (double)margin;
+    if (add > thr) thr = add;
+  }
+  float t = (float)thr;
+  if ((double)t > thr) t = nextafterf(t, -INFINITY);
+  return t;
+}
+
 // candidates = pairs whose approximate utility is within `margin` of a reference value: the B-th largest
 // approximate utility (st->prefix = the high 32 bits of its key: select_threshold(..., passes = 3)) or, when `pilot_min` is given, the smallest EXACT utility of the
 // pilot set (an order-preserving uint, refine_min_kernel)
 __global__ void __launch_bounds__(256) refine_mark_kernel(const float *__restrict__ util, int64_t N, const SelectState *st,
                                                           const unsigned int *__restrict__ pilot_min, float margin,
                                                           uint32_t *__restrict__ cand, unsigned int *__restrict__ count,
-                                                          unsigned int cap) {
+                                                          unsigned int cap, int measure = -1, double eps = 0.0, double ez = 0.0) {
   const float tau = alink_key_utility(st->prefix << 32);
   // never above tau: the pilot set itself always stays in (it matters when the caller's bound is too tight)
-  const float thr = pilot_min ? fminf(__fsub_rn(alink_unorderable(*pilot_min), margin), tau) : __fsub_rn(tau, margin);
+  const float thr = pilot_min ? fminf(__fsub_rn(alink_unorderable(*pilot_min), margin), tau)
+                              : (measure >= 0 ? refine_threshold(measure, tau, margin, eps, ez) : __fsub_rn(tau, margin));
   const int lane = threadIdx.x & 31;
   // warp-uniform loop bound: every lane takes part in the ballot
   for (int64_t n0 = (int64_t)blockIdx.x * 256 + (threadIdx.x & ~31); n0 < N; n0 += (int64_t)gridDim.x * 256) {
@@ -129,7 +185,7 @@ __global__ void __launch_bounds__(256) absmax_kernel(const float4 *__restrict__ 
 //             5 max |u~ - u2| over C1 u S | 6 max |u2 - u| over C2 u S2 | 7 max |u~ - u| over C2 u S2 | 8-9 sum sq of |u~ - u2| over C1 (double)
 //             10-11 sum sq of 6 (double) | 12 n1 = min(count1, cap1) | 13 n2 = min(count2, cap2)
 enum { RS_COUNT1 = 0, RS_M1 = 1, RS_COUNT2 = 2, RS_M2 = 3, RS_FLAGS = 4, RS_ERR1 = 5, RS_ERR2 = 6, RS_ERRA = 7, RS_SS1 = 8,
-       RS_SS2 = 10, RS_N1 = 12, RS_N2 = 13, RS_WORDS = 16 };
+       RS_SS2 = 10, RS_N1 = 12, RS_N2 = 13, RS_TAU = 14, RS_REL1 = 15, RS_WORDS = 16 };
 
 // after refine_mark_kernel: clamp the count, append the stratified sample, translate rows to table rows
 __global__ void __launch_bounds__(256) refine_stage1_finish_kernel(unsigned int *__restrict__ rs, unsigned int cap1, int64_t N,
@@ -186,6 +242,8 @@ struct Stage1Args {
   int64_t N;
   unsigned long long B;
   float margin;
+  int measure;          // refine_threshold: the band lives in u-space for the consensus measures (-1: additive)
+  double eps, ez;
   unsigned int cap1, ns_min, ns_max, wave_rows;
   unsigned int *hist, *rs;
   uint32_t *cand1;
@@ -266,7 +324,10 @@ __global__ void __launch_bounds__(256) refine_stage1_coop_kernel(const Stage1Arg
   }
   // candidates: u~ >= tau - margin (ballot compaction, one atomic per warp)
   const float tau = alink_unorderable(prefix);
-  const float thr = __fsub_rn(tau, a.margin);
+  __shared__ float s_thr;
+  if (tid == 0) s_thr = a.measure >= 0 ? refine_threshold(a.measure, tau, a.margin, a.eps, a.ez) : __fsub_rn(tau, a.margin);
+  __syncthreads();
+  const float thr = s_thr;
   unsigned int *count = a.rs + RS_COUNT1;
   for (int64_t n0 = (int64_t)blockIdx.x * 256 + (tid & ~31); n0 < a.N; n0 += stride) {
     const int64_t n = n0 + lane;
@@ -317,7 +378,7 @@ __global__ void __launch_bounds__(256) refine_stage1_coop_kernel(const Stage1Arg
   if (blockIdx.x == 0 && tid == 0) {
     a.rs[RS_M1] = M1;
     a.rs[RS_N1] = n1;
-    a.rs[14] = prefix;
+    a.rs[RS_TAU] = prefix;
     if (count1 > a.cap1) atomicOr(a.rs + RS_FLAGS, 1u);
   }
 }
@@ -326,7 +387,8 @@ __global__ void __launch_bounds__(256) refine_stage1_coop_kernel(const Stage1Arg
 // the utility bits), C2 = rows within `margin` of it, plus every (|S| / ns2)-th sample row; emits the table rows, the
 // original pair index and the stage-2 row of every selected row.
 __global__ void __launch_bounds__(1024) refine_stage2_kernel(unsigned int *__restrict__ rs, const float *__restrict__ util2,
-                                                             unsigned long long B, float margin, unsigned int cap2,
+                                                             unsigned long long B, float margin, int measure, double eps,
+                                                             double ez, unsigned int cap2,
                                                              unsigned int ns2_max, const uint32_t *__restrict__ cand1,
                                                              const int32_t *__restrict__ cia1, const int32_t *__restrict__ cib1,
                                                              int32_t *__restrict__ cia2, int32_t *__restrict__ cib2,
@@ -340,7 +402,13 @@ __global__ void __launch_bounds__(1024) refine_stage2_kernel(unsigned int *__res
   if (tid == 0) s_count = 0;
   KeySrc src{util2, nullptr, 0, nullptr};
   radix_select_cta(src, (int)n1, B < n1 ? B : (unsigned long long)(n1 ? n1 : 1), 3, sh, part, s_prefix, s_remaining);
-  const float thr = __fsub_rn(alink_key_utility(s_prefix << 32), margin);
+  __shared__ float s_thr;
+  if (tid == 0) {
+    const float tau2 = alink_key_utility(s_prefix << 32);
+    s_thr = measure >= 0 ? refine_threshold(measure, tau2, margin, eps, ez) : __fsub_rn(tau2, margin);
+  }
+  __syncthreads();
+  const float thr = s_thr;
   for (unsigned int r = tid; r < n1; r += 1024) {
     if (util2[r] >= thr) {
       const unsigned int pos = atomicAdd(&s_count, 1u);
@@ -372,45 +440,74 @@ __global__ void __launch_bounds__(1024) refine_stage2_kernel(unsigned int *__res
 }
 
 // exact utilities of the stage-3 rows from their per-learner probabilities, and the error statistics of both filters
+// u = min(pbar, 1 - pbar) of the two-column consensus of one row of per-learner probabilities
+template <int KT>
+__device__ __forceinline__ float consensus_u(const float *__restrict__ probs, size_t row, int K, int C, float *rows) {
+  const int KK = KT > 0 ? KT : K;
+  if (C == 2) {
+    const float2 *src = reinterpret_cast<const float2 *>(probs) + row * KK;
+#pragma unroll
+    for (int k = 0; k < KK; ++k) {
+      const float2 v = src[k];
+      rows[2 * k] = v.x;
+      rows[2 * k + 1] = v.y;
+    }
+  } else {
+#pragma unroll
+    for (int k = 0; k < KK; ++k) {
+      const float p = probs[row * KK + k];
+      rows[2 * k] = __fsub_rn(1.0f, p);  // keras_wrapper.py:268
+      rows[2 * k + 1] = p;
+    }
+  }
+  float c0, c1;
+  alink_consensus2(rows, KK, &c0, &c1);
+  return fminf(c0, c1);
+}
+
+// Exact utilities of the stage-3 rows, and the error statistics of both filters. band >= 0 (a consensus measure): the errors
+// are taken in PROBABILITY space, u = min(pbar, 1 - pbar) — from the per-learner probabilities of stages 2 and 3, and from
+// the inverse of the measure for the filter's fused utility — because that is where the bounds live; in utility space the
+// entropy measures, flat at the top, would hide a probability error exactly where the candidates sit. band < 0: utility space.
+// rs[RS_REL1]: max relative error |u~ - u2| / u2 over rows with u2 >= 1e-3 (the multiplicative band's premise).
 template <int KT>
 __global__ void __launch_bounds__(256) refine_finish_kernel(unsigned int *__restrict__ rs, const float *__restrict__ probs, int K,
                                                             int C, int measure, const float *__restrict__ util_a,
                                                             const float *__restrict__ util2, const uint32_t *__restrict__ cand1,
                                                             const uint32_t *__restrict__ map2, const uint32_t *__restrict__ src2,
-                                                            float *__restrict__ util_c) {
+                                                            float *__restrict__ util_c, const float *__restrict__ probs2, int band) {
   const int KK = KT > 0 ? KT : K;
   const unsigned int M1 = rs[RS_M1], M2 = rs[RS_M2], n1 = rs[RS_N1];
-  float m1 = 0.0f, m2 = 0.0f, ma = 0.0f, ss1 = 0.0f, ss2 = 0.0f;
+  float m1 = 0.0f, m2 = 0.0f, ma = 0.0f, ss1 = 0.0f, ss2 = 0.0f, rel = 0.0f;
+  float rows[2 * (KT > 0 ? KT : ALINK_MAX_K)];
   for (unsigned int j = blockIdx.x * 256 + threadIdx.x; j < M2; j += gridDim.x * 256) {
-    float rows[2 * (KT > 0 ? KT : ALINK_MAX_K)];
-    if (C == 2) {
-      const float2 *src = reinterpret_cast<const float2 *>(probs) + (size_t)j * KK;
-#pragma unroll
-      for (int k = 0; k < KK; ++k) {
-        const float2 v = src[k];
-        rows[2 * k] = v.x;
-        rows[2 * k + 1] = v.y;
-      }
-    } else {
-#pragma unroll
-      for (int k = 0; k < KK; ++k) {
-        const float p = probs[(size_t)j * KK + k];
-        rows[2 * k] = __fsub_rn(1.0f, p);  // keras_wrapper.py:268
-        rows[2 * k + 1] = p;
-      }
-    }
+    const float ux = consensus_u<KT>(probs, j, K, C, rows);
     float c0, c1;
     alink_consensus2(rows, KK, &c0, &c1);
     const float u = alink_utility2(measure, rows, KK, c0, c1);
     util_c[j] = u;
-    const float e2 = fabsf(__fsub_rn(util2[src2[j]], u));
-    const float ea = fabsf(__fsub_rn(__ldg(util_a + map2[j]), u));
+    float e2, ea;
+    if (band >= 0) {
+      float r2[2 * (KT > 0 ? KT : ALINK_MAX_K)];
+      e2 = fabsf(__fsub_rn(consensus_u<KT>(probs2, src2[j], K, C, r2), ux));
+      ea = fabsf((float)refine_ginv(band, (double)__ldg(util_a + map2[j])) - ux);
+    } else {
+      e2 = fabsf(__fsub_rn(util2[src2[j]], u));
+      ea = fabsf(__fsub_rn(__ldg(util_a + map2[j]), u));
+    }
     m2 = fmaxf(m2, e2);
     ma = fmaxf(ma, ea);
     ss2 = __fmaf_rn(e2, e2, ss2);
   }
   for (unsigned int r = blockIdx.x * 256 + threadIdx.x; r < M1; r += gridDim.x * 256) {
-    const float e1 = fabsf(__fsub_rn(__ldg(util_a + cand1[r]), util2[r]));
+    float e1;
+    if (band >= 0) {
+      const float u2p = consensus_u<KT>(probs2, r, K, C, rows);
+      e1 = fabsf((float)refine_ginv(band, (double)__ldg(util_a + cand1[r])) - u2p);
+      if (u2p >= 1.0e-3f) rel = fmaxf(rel, __fdiv_rn(e1, u2p));
+    } else {
+      e1 = fabsf(__fsub_rn(__ldg(util_a + cand1[r]), util2[r]));
+    }
     m1 = fmaxf(m1, e1);
     if (r < n1) ss1 = __fmaf_rn(e1, e1, ss1);  // rms over the candidates (the pairs at risk: p near 1/2, largest slope)
   }
@@ -418,6 +515,7 @@ __global__ void __launch_bounds__(256) refine_finish_kernel(unsigned int *__rest
     m1 = fmaxf(m1, __shfl_xor_sync(0xffffffffu, m1, o));
     m2 = fmaxf(m2, __shfl_xor_sync(0xffffffffu, m2, o));
     ma = fmaxf(ma, __shfl_xor_sync(0xffffffffu, ma, o));
+    rel = fmaxf(rel, __shfl_xor_sync(0xffffffffu, rel, o));
     ss1 += __shfl_xor_sync(0xffffffffu, ss1, o);
     ss2 += __shfl_xor_sync(0xffffffffu, ss2, o);
   }
@@ -425,6 +523,7 @@ __global__ void __launch_bounds__(256) refine_finish_kernel(unsigned int *__rest
     if (m1 > 0.0f) atomicMax(rs + RS_ERR1, __float_as_uint(m1));
     if (m2 > 0.0f) atomicMax(rs + RS_ERR2, __float_as_uint(m2));
     if (ma > 0.0f) atomicMax(rs + RS_ERRA, __float_as_uint(ma));
+    if (rel > 0.0f) atomicMax(rs + RS_REL1, __float_as_uint(rel));
     if (ss1 > 0.0f) atomicAdd(reinterpret_cast<double *>(rs + RS_SS1), (double)ss1);
     if (ss2 > 0.0f) atomicAdd(reinterpret_cast<double *>(rs + RS_SS2), (double)ss2);
   }

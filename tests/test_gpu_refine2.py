@@ -61,6 +61,20 @@ def test_three_stage_report_on_configs1_shape(ctx):
     assert rep["eps1_worst"] > 10 * rep["eps1_apriori"]  # why the worst-case propagation is not used as the width
 
 
+@pytest.mark.parametrize("measure", ["entropy", "consensus_entropy", "neg_margin"])
+def test_entropy_measures_stay_in_three_stages(ctx, measure):
+    """The entropy utilities are flat at the top (H ~ ln 2 - 2 (p - 1/2)^2): an additive band in utility space holds
+    10-30 % of the pool (round 1: 148 k exact re-scores, 18 ms at 1 M pairs). The band lives in probability space
+    (refine_threshold), and so do the error statistics, or a probability error would hide exactly where the candidates sit."""
+    pool = synth.make_pool(2, N=400_000)
+    exact, refined, rep = _both(ctx, pool, measure, 1000)
+    _check(exact, refined)
+    print(measure, rep)
+    assert rep["version"] == 2 and rep["fallback"] == 0 and rep["rounds"] == 1
+    assert rep["n_stage2"] < 0.06 * pool.N and rep["n_exact"] < 6000
+    assert 2e-5 < rep["err1_max"] < rep["eps1_used"] and rep["err2_max"] < rep["eps2_used"]
+
+
 def test_resnet_shaped_2048d_pool_at_one_million_pairs(ctx):
     pool = synth.make_pool(3, N=1_000_000, M=60_000)
     assert pool.D == 2048
