@@ -548,12 +548,15 @@ def main():
     if args.config == 2 and args.mode != "fp32" and N == 1_000_000:
         # DRAM bytes of one launch of this kernel on this workload, from the committed ncu --set full capture
         try:
-            with open(os.path.join(ROOT, "profiles", "r2_ncu_hbm_stages.json")) as f:
-                hk = [l for l in json.load(f)["launches"] if "head_kernel<0, 2, 1, 1>" in l["kernel"] or "head_kernel<0, 2, 0, 1>" in l["kernel"]]
-            want = "<0, 2, 0, 1>" if args.mode == "bf16" else "<0, 2, 1, 1>"
-            hk = [l for l in hk if want in l["kernel"] and l["us"] > 1500]
-            roofline["traffic"] = hk[0]["dram_read_B"] + hk[0]["dram_write_B"]
-            roofline["traffic_source"] = "profiles/r2_ncu_hbm_stages.json (dram__bytes_read.sum + dram__bytes_write.sum of this kernel, K = 5 launch)"
+            if args.mode == "refine":  # ncu --set full of this build's filter launch (tools/r2_ncu.sh)
+                with open(os.path.join(ROOT, "profiles", "r2_ncu_head_full_summary.json")) as f:
+                    roofline["traffic"] = json.load(f)["traffic_bytes_per_launch"]
+                roofline["traffic_source"] = "profiles/r2_ncu_head_full_summary.json (dram__bytes_read.sum + dram__bytes_write.sum, one launch)"
+            else:  # the bf16 K = 5 launch of the HBM-stage capture
+                with open(os.path.join(ROOT, "profiles", "r2_ncu_hbm_stages.json")) as f:
+                    hk = [l for l in json.load(f)["launches"] if "head_kernel<0, 2, 0, 1>" in l["kernel"] and l["us"] > 1500]
+                roofline["traffic"] = hk[0]["dram_read_B"] + hk[0]["dram_write_B"]
+                roofline["traffic_source"] = "profiles/r2_ncu_hbm_stages.json (dram__bytes_read.sum + dram__bytes_write.sum of the K = 5 launch)"
         except Exception:
             pass
     if args.mode == "refine":
