@@ -75,7 +75,7 @@ int alink_destroy(alink_ctx *ctx) {
   for (auto &g : ctx->groups) free_group(g);
   for (auto &t : ctx->tables) dev_release(t.own);
   DevBuf *bufs[] = {&ctx->idx_a, &ctx->idx_b, &ctx->h1ws, &ctx->probs, &ctx->cons, &ctx->util, &ctx->sel_state,
-                    &ctx->sel_keys, &ctx->sel_idx, &ctx->sel_util, &ctx->sel_in, &ctx->misc0, &ctx->misc1,
+                    &ctx->sel_keys, &ctx->sel_idx, &ctx->sel_util, &ctx->sel_in, &ctx->sel_hist, &ctx->misc0, &ctx->misc1,
                     &ctx->misc2, &ctx->misc3, &ctx->cand, &ctx->cia, &ctx->cib, &ctx->util_c, &ctx->rstat, &ctx->xscratch,
                     &ctx->train_ws, &ctx->train_y, &ctx->train_out, &ctx->util2, &ctx->probs2, &ctx->cia2, &ctx->cib2, &ctx->map2, &ctx->src2};
   for (DevBuf *b : bufs) dev_release(*b);

@@ -103,7 +103,7 @@ struct alink_ctx {
   bool util_valid = false;
   int util_measure = -1;  // measure ctx->util holds
   // select scratch
-  DevBuf sel_state, sel_keys, sel_idx, sel_util, sel_in;
+  DevBuf sel_state, sel_keys, sel_idx, sel_util, sel_in, sel_hist;
   DevBuf misc0, misc1, misc2, misc3;
   // FP32_REFINE (refine.cuh)
   double refine_eps = 0.0;        // caller's bound on |filter probability - fp32 probability| (0 = per-format default)

@@ -22,7 +22,6 @@
 #pragma once
 #include "common.cuh"
 #include "topk.cuh"
-#include <cooperative_groups.h>
 
 // ---- where the candidate band ends, in the space the error bound lives in -------------------------------------------------
 // For the measures that are monotone functions of u = min(pbar, 1 - pbar) of the two-column consensus — uncertainty U = u,
@@ -252,45 +251,6 @@ struct Stage1Args {
   int64_t pair0;
   int32_t *cia, *cib;
 };
-
-__device__ __forceinline__ void stage1_pick(const unsigned int *__restrict__ ghist, int nb, unsigned long long &remaining,
-                                            unsigned int &bin_out, unsigned int *sh, unsigned int *part) {
-  // descending scan of a global histogram by the whole CTA (256 threads); same walk as radix_pass_kernel's last CTA
-  const int tid = threadIdx.x;
-  for (int i = tid; i < nb; i += 256) sh[i] = __ldcg(ghist + i);
-  __syncthreads();
-  const int per = nb / 256;
-  unsigned int mine = 0;
-  for (int j = 0; j < per; ++j) mine += sh[nb - 1 - per * tid - j];
-  part[tid] = mine;
-  __syncthreads();
-  for (int off = 1; off < 256; off <<= 1) {
-    const unsigned int v = tid >= off ? part[tid - off] : 0u;
-    __syncthreads();
-    part[tid] += v;
-    __syncthreads();
-  }
-  __shared__ unsigned int s_bin;
-  __shared__ unsigned long long s_rem;
-  const unsigned long long incl = part[tid], before = incl - mine;
-  if (before < remaining && remaining <= incl) {
-    unsigned long long cum = before;
-    for (int j = 0; j < per; ++j) {
-      const int bin = nb - 1 - per * tid - j;
-      const unsigned int c = sh[bin];
-      if (cum + c >= remaining) {
-        s_bin = (unsigned int)bin;
-        s_rem = remaining - cum;
-        break;
-      }
-      cum += c;
-    }
-  }
-  __syncthreads();
-  bin_out = s_bin;
-  remaining = s_rem;
-  __syncthreads();
-}
 
 __global__ void __launch_bounds__(256) refine_stage1_coop_kernel(const Stage1Args a) {
   namespace cg = cooperative_groups;

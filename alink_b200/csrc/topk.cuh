@@ -14,6 +14,7 @@
 // or raw keys (the cross-shard merge after the all-gather).
 #pragma once
 #include "common.cuh"
+#include <cooperative_groups.h>
 
 struct KeySrc {
   const float *util;
@@ -139,6 +140,89 @@ __global__ void __launch_bounds__(256) select_pick_kernel(unsigned int *__restri
     }
   }
   for (int i = threadIdx.x; i < 2048; i += 256) hist[i] = 0;
+}
+
+__device__ __forceinline__ void stage1_pick(const unsigned int *__restrict__ ghist, int nb, unsigned long long &remaining,
+                                            unsigned int &bin_out, unsigned int *sh, unsigned int *part) {
+  // descending scan of a global histogram by the whole CTA (256 threads); same walk as radix_pass_kernel's last CTA
+  const int tid = threadIdx.x;
+  for (int i = tid; i < nb; i += 256) sh[i] = __ldcg(ghist + i);
+  __syncthreads();
+  const int per = nb / 256;
+  unsigned int mine = 0;
+  for (int j = 0; j < per; ++j) mine += sh[nb - 1 - per * tid - j];
+  part[tid] = mine;
+  __syncthreads();
+  for (int off = 1; off < 256; off <<= 1) {
+    const unsigned int v = tid >= off ? part[tid - off] : 0u;
+    __syncthreads();
+    part[tid] += v;
+    __syncthreads();
+  }
+  __shared__ unsigned int s_bin;
+  __shared__ unsigned long long s_rem;
+  const unsigned long long incl = part[tid], before = incl - mine;
+  if (before < remaining && remaining <= incl) {
+    unsigned long long cum = before;
+    for (int j = 0; j < per; ++j) {
+      const int bin = nb - 1 - per * tid - j;
+      const unsigned int c = sh[bin];
+      if (cum + c >= remaining) {
+        s_bin = (unsigned int)bin;
+        s_rem = remaining - cum;
+        break;
+      }
+      cum += c;
+    }
+  }
+  __syncthreads();
+  bin_out = s_bin;
+  remaining = s_rem;
+  __syncthreads();
+}
+
+
+// The whole select of a LARGE source in ONE cooperative launch: six histogram passes over the packed keys with a grid-wide
+// barrier after each (every CTA scans the global histogram redundantly: nothing to broadcast), then the compaction of the
+// keys >= the B-th largest. Replaces select_init + 6 radix passes + compact (8 launches, ~10 us of launch + tail latency
+// each for a 4 MB source). hist: 6 x 2048 zeroed counters; st->out_count zeroed.
+__global__ void __launch_bounds__(256) topk_select_coop_kernel(KeySrc src, int64_t n, unsigned long long B, unsigned int *__restrict__ hist,
+                                                               SelectState *st, uint64_t *__restrict__ out, unsigned int cap) {
+  namespace cg = cooperative_groups;
+  cg::grid_group grid = cg::this_grid();
+  __shared__ unsigned int sh[2048];
+  __shared__ unsigned int part[256];
+  const int tid = threadIdx.x;
+  const int64_t stride = (int64_t)gridDim.x * 256;
+  const int shifts[6] = {53, 42, 32, 21, 10, 0}, nbits[6] = {11, 11, 10, 11, 11, 10};
+  unsigned long long remaining = B, prefix = 0;
+#pragma unroll 1
+  for (int p = 0; p < 6; ++p) {
+    const int nb = 1 << nbits[p], hi = shifts[p] + nbits[p];
+    for (int i = tid; i < nb; i += 256) sh[i] = 0;
+    __syncthreads();
+    for (int64_t i = (int64_t)blockIdx.x * 256 + tid; i < n; i += stride) {
+      const uint64_t key = load_key(src, i);
+      if (p == 0 || (key >> hi) == prefix) atomicAdd(&sh[(unsigned)(key >> shifts[p]) & (unsigned)(nb - 1)], 1u);
+    }
+    __syncthreads();
+    unsigned int *gh = hist + p * 2048;
+    for (int i = tid; i < nb; i += 256)
+      if (sh[i]) atomicAdd(gh + i, sh[i]);
+    __threadfence();
+    grid.sync();
+    unsigned int bin;
+    stage1_pick(gh, nb, remaining, bin, sh, part);
+    prefix = p == 0 ? (unsigned long long)bin : ((prefix << nbits[p]) | (unsigned long long)bin);
+  }
+  for (int64_t i = (int64_t)blockIdx.x * 256 + tid; i < n; i += stride) {
+    const uint64_t key = load_key(src, i);
+    if (key >= prefix) {
+      const unsigned int pos = atomicAdd(&st->out_count, 1u);
+      if (pos < cap) out[pos] = key;
+    }
+  }
+  if (blockIdx.x == 0 && tid == 0) st->prefix = prefix;
 }
 
 // Small sources (the exact re-score's candidates, the cross-shard merge of B keys per rank): the same passes
@@ -370,13 +454,36 @@ static int topk_device(alink_ctx *ctx, const KeySrc &src, int64_t n, int64_t B) 
     ALINK_LAUNCHED(ctx);
     return ALINK_OK;
   }
-  ALINK_TRY(select_threshold(ctx, src, n, B, st));
   int64_t blocks = (n + 256 * 8 - 1) / (256 * 8);
   const int64_t cap = (int64_t)ctx->sm_count * 8;
   if (blocks > cap) blocks = cap;
   if (blocks < 1) blocks = 1;
-  compact_kernel<<<(unsigned)blocks, 256, 0, ctx->stream>>>(src, n, st, out, (unsigned int)B);
-  ALINK_LAUNCHED(ctx);
+  static const int coop_env = [] { const char *e = getenv("ALINK_TOPK_COOP"); return e ? atoi(e) : 1; }();
+  static int coop_per_sm = -1;
+  if (coop_per_sm < 0) {
+    int occ = 0, coop = 0;
+    cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, ctx->device);
+    coop_per_sm = (coop && cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, topk_select_coop_kernel, 256, 0) == cudaSuccess && occ > 0)
+                      ? (occ < 4 ? occ : 4) : 0;
+  }
+  if (coop_env && coop_per_sm > 0) {
+    ALINK_TRY(dev_reserve(ctx, ctx->sel_hist, sizeof(unsigned int) * 6 * 2048));
+    ALINK_CUDA(ctx, cudaMemsetAsync(ctx->sel_hist.p, 0, sizeof(unsigned int) * 6 * 2048, ctx->stream));
+    ALINK_CUDA(ctx, cudaMemsetAsync(&st->out_count, 0, sizeof(unsigned int), ctx->stream));
+    int64_t cb = blocks < (int64_t)ctx->sm_count * coop_per_sm ? blocks : (int64_t)ctx->sm_count * coop_per_sm;
+    unsigned long long Bu = (unsigned long long)B;
+    unsigned int *hist = (unsigned int *)ctx->sel_hist.p;
+    unsigned int capu = (unsigned int)B;
+    KeySrc srcv = src;
+    int64_t nv = n;
+    void *kargs[] = {(void *)&srcv, (void *)&nv, (void *)&Bu, (void *)&hist, (void *)&st, (void *)&out, (void *)&capu};
+    ALINK_CUDA(ctx, cudaLaunchCooperativeKernel((const void *)topk_select_coop_kernel, dim3((unsigned)cb), dim3(256), kargs, 0, ctx->stream));
+    ALINK_LAUNCHED(ctx);
+  } else {
+    ALINK_TRY(select_threshold(ctx, src, n, B, st));
+    compact_kernel<<<(unsigned)blocks, 256, 0, ctx->stream>>>(src, n, st, out, (unsigned int)B);
+    ALINK_LAUNCHED(ctx);
+  }
   if (npad <= 4096) {
     const int threads = npad >= 2048 ? 1024 : (npad >= 64 ? (int)(npad / 2) : 32);
     bitonic_smem_kernel<<<1, threads, sizeof(uint64_t) * (size_t)npad, ctx->stream>>>(out, (int)B, (int)npad);
