@@ -58,7 +58,15 @@ class ShardedTableFeed:
     compute stream wait on the device (no host synchronisation). world == 1 degenerates to the plain upload.
     M is padded to a multiple of the world size (pad rows are never referenced)."""
 
-    def __init__(self, ctx, M, D, dist=None, device=None, dtype=None, n_buffers=2):
+    def __init__(self, ctx, M, D, dist=None, device=None, dtype=None, n_buffers=2, gather="nccl"):
+        """gather: "nccl" = in-place ncclAllGather (a kernel: it needs SMs, which the persistent head kernel holds, so it
+        runs after the filter and delays the split kernel's CTA pairs); "copy" = the buffers live in symmetric memory
+        (torch.distributed._symmetric_memory: cuMem allocations mapped into every rank) and every rank PULLS the other
+        ranks' slices with peer-to-peer copies on the copy engines over NVLink — no SMs, two device-side barriers per feed;
+        "auto" = "copy" when symmetric memory can be set up, else "nccl". Measured on 8 B200s (bench.py e2e): 3.59 ms
+        ("copy") against 3.54 ms ("nccl") per step — the refine stage no longer waits for SMs (0.50 instead of 0.70 ms), but
+        the barrier kernels cannot start before the persistent filter kernel ends either, so the table is ready just as
+        late; hence "nccl", the plainer path, is the default."""
         import torch
         self.ctx, self.dist, self.torch = ctx, dist, torch
         self.world = dist.get_world_size() if dist is not None and dist.is_initialized() else 1
@@ -67,7 +75,22 @@ class ShardedTableFeed:
         self.rows = (self.M + self.world - 1) // self.world  # rows per rank
         self.device = device if device is not None else torch.device("cuda", ctx.device)
         dtype = dtype or torch.float32
-        self.bufs = [torch.empty((self.rows * self.world, self.D), dtype=dtype, device=self.device) for _ in range(n_buffers)]
+        self.mode, self.hdl = "nccl", [None] * n_buffers
+        self.bufs = None
+        if self.world > 1 and gather in ("auto", "copy"):
+            try:
+                import torch.distributed._symmetric_memory as symm
+                bufs = [symm.empty((self.rows * self.world, self.D), dtype=dtype, device=self.device) for _ in range(n_buffers)]
+                self.hdl = [symm.rendezvous(b, dist.group.WORLD) for b in bufs]
+                if any(h is None for h in self.hdl):
+                    raise RuntimeError("rendezvous returned no handle")
+                self.bufs, self.mode = bufs, "copy"
+            except Exception as e:  # noqa: BLE001 — any failure of the experimental API falls back to NCCL
+                if gather == "copy":
+                    raise
+                self.why_nccl = repr(e)[:200]
+        if self.bufs is None:
+            self.bufs = [torch.empty((self.rows * self.world, self.D), dtype=dtype, device=self.device) for _ in range(n_buffers)]
         self.side = torch.cuda.Stream(device=self.device)
         self.ready = [torch.cuda.Event() for _ in range(n_buffers)]
         self.free = [torch.cuda.Event() for _ in range(n_buffers)]
@@ -103,7 +126,15 @@ class ShardedTableFeed:
                 self.nidx[buf] = int(host_indices[0].numel())
             mine = full[lo:lo + self.rows]
             mine[:host_shard.shape[0]].copy_(host_shard, non_blocking=True)
-            if self.world > 1:
+            if self.world > 1 and self.mode == "copy":
+                h = self.hdl[buf]
+                h.barrier()                      # every rank's slice has landed in its own buffer
+                for step in range(1, self.world):
+                    r = (self.rank - step) % self.world
+                    peer = h.get_buffer(r, full.shape, full.dtype)
+                    full[r * self.rows:(r + 1) * self.rows].copy_(peer[r * self.rows:(r + 1) * self.rows], non_blocking=True)
+                h.barrier()                      # nobody still reads a slice that the feed after next will overwrite
+            elif self.world > 1:
                 self.dist.all_gather_into_tensor(full, mine)  # in place: rank r's slice is already where it belongs
             self.ready[buf].record(self.side)
 

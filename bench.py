@@ -442,7 +442,8 @@ def main():
         # NVLink completes the replica on every GPU (alink_b200.dist.ShardedTableFeed); round 1 uploaded the whole table
         # N times from one NUMA node (e2e efficiency 0.42 at N = 8)
         from alink_b200.dist import ShardedTableFeed
-        feed = ShardedTableFeed(ctx, table_pin.shape[0], table_pin.shape[1], dist=dist, device=dev, dtype=table_pin.dtype)
+        feed = ShardedTableFeed(ctx, table_pin.shape[0], table_pin.shape[1], dist=dist, device=dev, dtype=table_pin.dtype,
+                                gather=os.environ.get("ALINK_FEED_GATHER", "nccl"))
         shard_pin = feed.shard_of(table_pin)
 
     def step_e2e():
@@ -583,7 +584,8 @@ def main():
                     "call": ("alink_set_table_async(HOST table of the next step, second slot) + alink_query(HOST indices) -> host top-B; every step uploads one table, overlapped with the previous step's query"
                              if feed is None else
                              "ShardedTableFeed: each rank uploads the next step's pair indices and its 1/N of the next step's table from pinned host memory (h2d_bytes_per_step is PER RANK) + in-place NCCL all-gather of the table over NVLink, all on a side stream overlapped with the current step's alink_query -> device keys -> all-gather + merge -> host top-B"),
-                    **({"table_allgather": {"bytes_received_per_rank": feed.bytes_gather, "ranks": world, "ms_alone": gather_ms,
+                    **({"table_allgather": {"mode": ("peer-to-peer copies out of symmetric memory (copy engines, no SMs)" if feed.mode == "copy" else "ncclAllGather"),
+                                             "bytes_received_per_rank": feed.bytes_gather, "ranks": world, "ms_alone_nccl": gather_ms,
                                              "busbw_GBps": feed.bytes_gather / (gather_ms / 1e3) / 1e9}} if feed is not None else {})},
             "gpu_launches": launches, "clocks": clocks}
 
