@@ -34,7 +34,7 @@ MAX_SLOTS = 8
 # every symbol include/alink_b200.h declares (tests/test_abi.py checks the .so exports them all)
 SYMBOLS = (
     "alink_abi_version", "alink_create", "alink_destroy", "alink_last_error", "alink_sync",
-    "alink_set_stream", "alink_launch_count", "alink_watchdog_record", "alink_host_alloc", "alink_host_free", "alink_set_heads", "alink_set_table", "alink_set_table_async",
+    "alink_set_stream", "alink_set_reserved_sms", "alink_launch_count", "alink_watchdog_record", "alink_host_alloc", "alink_host_free", "alink_set_heads", "alink_set_table", "alink_set_table_async",
     "alink_score_indexed", "alink_score_dense", "alink_utility", "alink_utility_from_proba",
     "alink_select_topk", "alink_topk_values", "alink_topk_keys", "alink_query", "alink_disparity_select",
     "alink_set_refine_eps", "alink_refine_stats", "alink_refine_detail", "alink_score_allpairs", "alink_query_allpairs",
@@ -152,6 +152,8 @@ def load():
     L.alink_disparity_select_sharded.restype = i32
     L.alink_disparity_select_sharded.argtypes = [vp, vp, vp, i64, i32, i64, vp, dbl, i32, vp, i32, vp, i32,
                                                  C.POINTER(i64), C.POINTER(i64)]
+    L.alink_set_reserved_sms.restype = i32
+    L.alink_set_reserved_sms.argtypes = [vp, i32]
     L.alink_refine_detail.restype = i32
     L.alink_refine_detail.argtypes = [vp, C.POINTER(C.c_int), C.POINTER(dbl), C.POINTER(C.c_float), C.POINTER(C.c_int)]
     L.alink_set_refine_eps2.restype = i32
@@ -668,6 +670,10 @@ class Context:
     def set_stream(self, cuda_stream):
         """cuda_stream: integer cudaStream_t (torch.cuda.current_stream().cuda_stream) or None."""
         self._check(self._L.alink_set_stream(self._h, C.c_void_p(cuda_stream) if cuda_stream else None))
+
+    def set_reserved_sms(self, n):
+        """Leave n SMs free of the persistent head kernels (for kernels of other streams: feed barriers, collectives)."""
+        self._check(self._L.alink_set_reserved_sms(self._h, int(n)))
 
     def sync(self):
         self._check(self._L.alink_sync(self._h))

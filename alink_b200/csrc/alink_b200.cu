@@ -117,6 +117,13 @@ int alink_set_stream(alink_ctx *ctx, void *cuda_stream) {
 
 int64_t alink_launch_count(const alink_ctx *ctx) { return ctx ? ctx->launches : 0; }
 
+int alink_set_reserved_sms(alink_ctx *ctx, int n) {
+  if (!ctx) return ALINK_E_INVALID;
+  if (n < 0 || n > ctx->sm_count - 2) return alink_fail(ctx, ALINK_E_INVALID, "reserved SMs outside [0, %d]", ctx->sm_count - 2);
+  ctx->reserved_sms = n & ~1;  // the kernels run CTA pairs
+  return ALINK_OK;
+}
+
 int alink_watchdog_record(const alink_ctx *ctx, uint64_t out[256]) {
   if (!ctx || !out) return ALINK_E_INVALID;
   for (int i = 0; i < 256; ++i) out[i] = ctx->wd_host ? (uint64_t)((volatile unsigned long long *)ctx->wd_host)[i] : 0;
@@ -899,7 +906,7 @@ static int refine_query_v2(alink_ctx *ctx, const HeadGroup &g, Table &A, Table &
       sa1.G = ia ? 0u : ctx->ap_G; sa1.pair0 = ctx->ap_pair0; sa1.cia = (int32_t *)ctx->cia.p; sa1.cib = (int32_t *)ctx->cib.p;
       void *kargs[] = {(void *)&sa1};
       int64_t cb = (N + 2047) / 2048;
-      const int64_t cmax = (int64_t)ctx->sm_count * coop_blocks_per_sm;
+      const int64_t cmax = (int64_t)(ctx->sm_count - ctx->reserved_sms) * coop_blocks_per_sm;
       if (cb > cmax) cb = cmax;
       if (cb < 1) cb = 1;
       ALINK_CUDA(ctx, cudaLaunchCooperativeKernel((const void *)refine_stage1_coop_kernel, dim3((unsigned)cb), dim3(256), kargs, 0, ctx->stream));

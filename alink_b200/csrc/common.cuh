@@ -78,6 +78,7 @@ struct DeState {
 struct alink_ctx {
   int device = 0;
   int sm_count = 148;
+  int reserved_sms = 0;               // SMs the persistent kernels leave free (alink_set_reserved_sms)
   cudaStream_t stream = nullptr;      // stream in use
   cudaStream_t own_stream = nullptr;  // private stream created by alink_create
   cudaStream_t copy_stream = nullptr; // alink_set_table_async uploads (created on first use)

@@ -988,7 +988,7 @@ static int tc_score(alink_ctx *ctx, const HeadGroup &g, const Table &A, const Ta
   cudaLaunchAttribute attr[1];
   void (*kern)(const tc::Args);
   if (ncta == 2) {
-    const int units = (a.ntiles + 1) / 2, max_units = ctx->sm_count / 2;
+    const int units = (a.ntiles + 1) / 2, max_units = (ctx->sm_count - ctx->reserved_sms) / 2;
     cfg.gridDim = dim3(2u * (unsigned)(units < max_units ? units : max_units));
     attr[0].id = cudaLaunchAttributeClusterDimension;
     attr[0].val.clusterDim.x = 2;
@@ -1007,7 +1007,7 @@ static int tc_score(alink_ctx *ctx, const HeadGroup &g, const Table &A, const Ta
     else
       kern = f16 ? tc::head_kernel<false, 2, true> : tb16 ? tc::head_kernel<true, 2, false> : tc::head_kernel<false, 2, false>;
   } else {
-    cfg.gridDim = dim3((unsigned)(a.ntiles < ctx->sm_count ? a.ntiles : ctx->sm_count));
+    cfg.gridDim = dim3((unsigned)(a.ntiles < ctx->sm_count - ctx->reserved_sms ? a.ntiles : ctx->sm_count - ctx->reserved_sms));
     if (staged)
       kern = f16 ? tc::head_kernel<false, 1, true, true>
                  : tb16 ? tc::head_kernel<true, 1, false, true> : tc::head_kernel<false, 1, false, true>;

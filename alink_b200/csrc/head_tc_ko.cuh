@@ -411,7 +411,7 @@ static int tc_score_ko(alink_ctx *ctx, const HeadGroup &g, const tc::Args &a0, b
   if (ctx->sm_count < 2) return alink_fail(ctx, ALINK_E_UNSUPPORTED, "the wide-feature tensor-core head needs CTA pairs");
   tcko::KoArgs ka;
   ka.a = a0;
-  const int units = (a0.ntiles + 1) / 2, max_units = ctx->sm_count / 2;
+  const int units = (a0.ntiles + 1) / 2, max_units = (ctx->sm_count - ctx->reserved_sms) / 2;
   const unsigned grid = 2u * (unsigned)(units < max_units ? units : max_units);
   ALINK_TRY(dev_reserve(ctx, ctx->xscratch, (size_t)grid * 2 * a0.nkb * tcko::XBLK));
   ka.xscratch = (uint8_t *)ctx->xscratch.p;

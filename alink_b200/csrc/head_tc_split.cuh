@@ -539,7 +539,7 @@ static int tc_score_split(alink_ctx *ctx, const HeadGroup &g, const Table &A, co
   sa.sh = split_scale_for(h1max);
   sa.inv1 = 1.0f / (sa.sx * g.sw1);
   sa.inv2 = 1.0f / (sa.sh * g.sw2);
-  const int64_t units = (int64_t)((a.ntiles + 1) / 2) * g.K, max_units = ctx->sm_count / 2;
+  const int64_t units = (int64_t)((a.ntiles + 1) / 2) * g.K, max_units = (ctx->sm_count - ctx->reserved_sms) / 2;
   const unsigned grid = 2u * (unsigned)(units < max_units ? units : max_units);
   ALINK_TRY(dev_reserve(ctx, ctx->xscratch, (size_t)grid * 2 * (2 * a.nkb) * tcsp::XBLK));
   sa.xscratch = (uint8_t *)ctx->xscratch.p;

@@ -508,7 +508,12 @@ def main():
     refine_stats = ctx.refine_stats() if args.mode == "refine" else None
     refine_detail = ctx.refine_detail() if args.mode == "refine" else None
     refine_report = ctx.refine_report() if args.mode == "refine" else None
+    reserve = int(os.environ.get("ALINK_RESERVE_SMS", "0"))
+    if feed is not None and reserve:
+        ctx.set_reserved_sms(reserve)  # the feed's communication kernels run beside the persistent head kernel
     ms_e2e, stage_e2e, _, _, merged_e2e, _ = timed(step_e2e, max(4, min(args.steps, 8)), 2)
+    if feed is not None and reserve:
+        ctx.set_reserved_sms(0)
     gather_ms = None
     if feed is not None:  # the table all-gather alone (device time, max over ranks), for its bus bandwidth
         g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)

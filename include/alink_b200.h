@@ -85,6 +85,10 @@ int alink_sync(alink_ctx *ctx);
  * instead of the context's own; NULL restores the private stream. Lets the host framework order its
  * own work and CUDA events with the library's kernels. */
 int alink_set_stream(alink_ctx *ctx, void *cuda_stream);
+/* The persistent tensor-core kernels take every SM (one CTA per SM, all of its registers and shared memory), so kernels of
+ * OTHER streams — the barriers of a peer-to-peer table feed, a collective — cannot start until they end. n > 0 (rounded down
+ * to an even number) leaves n SMs free: the head kernels then run on sm_count - n SMs (1.4 % slower at n = 2 of 148). */
+int alink_set_reserved_sms(alink_ctx *ctx, int n);
 /* total kernels launched by this context so far (bench.py's gpu_launches) */
 int64_t alink_launch_count(const alink_ctx *ctx);
 /* Failure detection: a device-side wait that exceeds ~2 s (a protocol deadlock) records itself in host-mapped
