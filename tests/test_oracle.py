@@ -147,3 +147,22 @@ def test_golden_vectors(oracle, name):
         order = R.topk_lowest_index(g, len(g))
         if g[order[B - 1]] - g[order[B]] > 2e-5:
             assert set(oracle.topk(u, B)[0].tolist()) == set(order[:B].tolist()), m
+
+
+@pytest.mark.parametrize("act", ["softmax", "sigmoid"])
+def test_scores_match_a_torch_cpu_twin(oracle, act):
+    """BASELINE.md §4's torch-CPU twin: the Dense / relu / softmax (sigmoid) graph of code/siamese.py:24-33 (siamese3.py:18-26)
+    in torch's own fp32 CPU kernels (MKL GEMM, its softmax / sigmoid) — a third implementation, independent of both the C
+    oracle and the numpy transcription. Not the reference (Keras / TF is not installable here), but it bounds how far any
+    faithful fp32 execution of the graph can sit from the oracle: within north_star's 1e-5."""
+    import torch
+    pool = synth.make_pool(1, N=2000, act=act)
+    out = oracle.score(pool.table, pool.table, pool.ia, pool.ib, pool.heads)
+    xl, xr = torch.from_numpy(pool.table[pool.ia]), torch.from_numpy(pool.table[pool.ib])
+    for k in range(pool.heads.K):
+        W1, b1, W2, b2, W3, b3 = (torch.from_numpy(a) for a in pool.heads.learner(k))
+        x = torch.abs(xl - xr)
+        h = torch.relu(torch.relu(x @ W1 + b1) @ W2 + b2)
+        z = h @ W3 + b3
+        p = torch.softmax(z, dim=1) if act == "softmax" else torch.sigmoid(z)
+        assert float((p - torch.from_numpy(out["per_learner"][:, k, :])).abs().max()) < TOL_P
