@@ -36,7 +36,7 @@ SYMBOLS = (
     "alink_abi_version", "alink_create", "alink_destroy", "alink_last_error", "alink_sync",
     "alink_set_stream", "alink_set_reserved_sms", "alink_launch_count", "alink_watchdog_record", "alink_host_alloc", "alink_host_free", "alink_set_heads", "alink_set_table", "alink_set_table_async",
     "alink_score_indexed", "alink_score_dense", "alink_utility", "alink_utility_from_proba",
-    "alink_select_topk", "alink_topk_values", "alink_topk_keys", "alink_query", "alink_disparity_select",
+    "alink_select_topk", "alink_topk_values", "alink_topk_values_noalloc", "alink_topk_keys", "alink_query", "alink_disparity_select",
     "alink_set_refine_eps", "alink_refine_stats", "alink_refine_detail", "alink_score_allpairs", "alink_query_allpairs",
     "alink_disparity_hist", "alink_disparity_select_sharded", "alink_roc_counts",
     "alink_train_step", "alink_get_train_state", "alink_set_train_state",
@@ -120,6 +120,8 @@ def load():
     L.alink_select_topk.argtypes = [vp, i64, i64, vp, vp, vp, i32]
     L.alink_topk_values.restype = i32
     L.alink_topk_values.argtypes = [vp, vp, i64, i64, i64, i32, vp, vp, vp, i32]
+    L.alink_topk_values_noalloc.restype = i32
+    L.alink_topk_values_noalloc.argtypes = [vp, vp, i64, i64, i64, vp, vp, vp]
     L.alink_topk_keys.restype = i32
     L.alink_topk_keys.argtypes = [vp, vp, i64, i64, i32, vp, i32]
     L.alink_query.restype = i32
@@ -388,6 +390,16 @@ class Context:
         self._check(self._L.alink_topk_values(self._h, p, N, base, B, sp, _ptr_space(idx)[0],
                                               _ptr_space(util)[0], _ptr_space(keys)[0], HOST))
         return idx, util, keys
+
+    def topk_values_noalloc(self, values, B, idx_out=None, util_out=None, keys_out=None, base=0):
+        """Top-B through the static-scratch entry point (B <= 4096). values and the outputs are torch CUDA tensors the
+        caller allocated (int64 / float32 / uint64-as-int64 of B entries); nothing is allocated and nothing synchronises."""
+        for t in (values, idx_out, util_out, keys_out):
+            if t is not None and not (_is_torch(t) and t.is_cuda):
+                raise AlinkError("alink_topk_values_noalloc takes device tensors only")
+        self._check(self._L.alink_topk_values_noalloc(self._h, _ptr_space(values)[0], values.shape[0], base, B,
+                                                      _ptr_space(idx_out)[0], _ptr_space(util_out)[0],
+                                                      _ptr_space(keys_out)[0]))
 
     def topk_keys(self, keys, B):
         if not _is_torch(keys):

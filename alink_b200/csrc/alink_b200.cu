@@ -1,6 +1,7 @@
 // alink_b200.cu — C ABI (include/alink_b200.h) over the sm_100a kernels of the query-selection path.
 // Build: alink_b200/csrc/Makefile (nvcc -gencode arch=compute_100a,code=sm_100a -fmad=false -lineinfo).
 // -fmad=false: no implicit contraction anywhere; every fused multiply-add is an explicit __fmaf_rn.
+#include <mutex>
 #include "common.cuh"
 #include "head_ffma.cuh"
 #include "head_tc.cuh"
@@ -597,6 +598,76 @@ int alink_topk_keys(alink_ctx *ctx, const uint64_t *keys, int64_t n, int64_t B, 
   KeySrc src{nullptr, (const uint64_t *)dk, 0};
   ALINK_TRY(topk_device(ctx, src, n, B));
   return emit_selection(ctx, B, nullptr, nullptr, keys_out, out_space);
+}
+
+// ------------------------------------------------------------------------------- no-allocation top-B
+// alink_topk_values_noalloc: the multi-launch top-B (6 radix passes -> compaction -> one-CTA bitonic sort) with its
+// scratch — the SelectState (threshold, ticket, 2048-bin histogram) and the B unsorted keys — in a file-scope device
+// array instead of the context's growable buffers, for callers that may not allocate (graph capture, serving loops).
+// 48 KB per GPU that loads the library, held until exit. B <= ALINK_NOALLOC_MAX_B. The array is shared by every call
+// and keeps the last call's contents: select_init_kernel clears the state each time; calls that overlap on the GPU race.
+#define ALINK_NOALLOC_STATE_BYTES 16384
+#define ALINK_NOALLOC_SCRATCH_BYTES (ALINK_NOALLOC_STATE_BYTES + 8 * ALINK_NOALLOC_MAX_B)
+static_assert(sizeof(SelectState) <= ALINK_NOALLOC_STATE_BYTES, "SelectState outgrew its scratch share");
+static __device__ __align__(256) unsigned char g_noalloc_scratch[ALINK_NOALLOC_SCRATCH_BYTES];
+static void *g_noalloc_addr[64];  // per device: the array's DEVICE address (its name is only a host-side handle here)
+static std::mutex g_noalloc_mu;
+
+static int noalloc_scratch(alink_ctx *ctx, unsigned char **out) {
+  if (ctx->device < 0 || ctx->device >= 64) return alink_fail(ctx, ALINK_E_UNSUPPORTED, "device ordinal %d >= 64", ctx->device);
+  std::lock_guard<std::mutex> lk(g_noalloc_mu);
+  if (!g_noalloc_addr[ctx->device]) {  // once per device, with that device current (the caller set it)
+    void *p = nullptr;
+    ALINK_CUDA(ctx, cudaGetSymbolAddress(&p, g_noalloc_scratch));
+    if (!p) return alink_fail(ctx, ALINK_E_CUDA, "cudaGetSymbolAddress returned a null address");
+    g_noalloc_addr[ctx->device] = p;
+  }
+  *out = (unsigned char *)g_noalloc_addr[ctx->device];
+  return ALINK_OK;
+}
+
+int alink_topk_values_noalloc(alink_ctx *ctx, const float *util_dev, int64_t N, int64_t base, int64_t B, int64_t *idx_out_dev,
+                              float *util_out_dev, uint64_t *keys_out_dev) {
+  if (!ctx) return ALINK_E_INVALID;
+  if (B > ALINK_NOALLOC_MAX_B)
+    return alink_fail(ctx, ALINK_E_UNSUPPORTED, "alink_topk_values_noalloc: B=%lld exceeds the static scratch (max %d); use alink_topk_values",
+                      (long long)B, ALINK_NOALLOC_MAX_B);
+  if (N < 0 || B < 0 || B > N) return alink_fail(ctx, ALINK_E_INVALID, "B=%lld outside [0, N=%lld]", (long long)B, (long long)N);
+  if (base < 0 || base + N > 0xFFFFFFFFll) return alink_fail(ctx, ALINK_E_INVALID, "base + N exceeds 2^32 - 1");
+  if (B == 0) return ALINK_OK;
+  if (!util_dev) return alink_fail(ctx, ALINK_E_INVALID, "null util");
+  ALINK_CUDA(ctx, cudaSetDevice(ctx->device));
+  unsigned char *scr = nullptr;
+  ALINK_TRY(noalloc_scratch(ctx, &scr));
+  SelectState *st = (SelectState *)scr;
+  uint64_t *keys = (uint64_t *)(scr + ALINK_NOALLOC_STATE_BYTES);
+  KeySrc src{util_dev, nullptr, (uint64_t)base, nullptr};
+  select_init_kernel<<<1, 256, 0, ctx->stream>>>(st, (unsigned long long)B);
+  ALINK_LAUNCHED(ctx);
+  int64_t blocks = (N + 256 * 8 - 1) / (256 * 8);
+  const int64_t cap = (int64_t)ctx->sm_count * 8;
+  if (blocks > cap) blocks = cap;
+  if (blocks < 1) blocks = 1;
+  static const int shifts[6] = {53, 42, 32, 21, 10, 0};
+  static const int nbits[6] = {11, 11, 10, 11, 11, 10};
+  for (int p = 0; p < 6; ++p) {
+    radix_pass_kernel<<<(unsigned)blocks, 256, 0, ctx->stream>>>(src, N, shifts[p], nbits[p], p == 0, st);
+    ALINK_LAUNCHED(ctx);
+  }
+  compact_kernel<<<(unsigned)blocks, 256, 0, ctx->stream>>>(src, N, st, keys, (unsigned int)B);
+  ALINK_LAUNCHED(ctx);
+  const int64_t npad = next_pow2(B) < 2 ? 2 : next_pow2(B);
+  const int threads = npad >= 2048 ? 1024 : (npad >= 64 ? (int)(npad / 2) : 32);
+  bitonic_smem_kernel<<<1, threads, sizeof(uint64_t) * (size_t)npad, ctx->stream>>>(keys, (int)B, (int)npad);
+  ALINK_LAUNCHED(ctx);
+  if (idx_out_dev || util_out_dev) {
+    unpack_keys_kernel<<<(unsigned)((B + 255) / 256), 256, 0, ctx->stream>>>(keys, B, idx_out_dev, util_out_dev);
+    ALINK_LAUNCHED(ctx);
+  }
+  if (keys_out_dev)
+    ALINK_CUDA(ctx, cudaMemcpyAsync(keys_out_dev, keys, sizeof(uint64_t) * (size_t)B, cudaMemcpyDeviceToDevice, ctx->stream));
+  ALINK_CUDA(ctx, cudaGetLastError());
+  return ALINK_OK;
 }
 
 // ------------------------------------------------------------------------------------------ fused step

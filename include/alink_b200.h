@@ -193,6 +193,20 @@ int alink_select_topk(alink_ctx *ctx, int64_t B, int64_t base, int64_t *idx_out,
 int alink_topk_values(alink_ctx *ctx, const float *util, int64_t N, int64_t base, int64_t B, int in_space,
                       int64_t *idx_out, float *util_out, uint64_t *keys_out, int out_space);
 
+/* Top-B of a utility vector WITHOUT allocating anything. No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid it). Same result as alink_topk_values, through the multi-launch selection (6 radix passes ->
+ * compaction -> one-CTA sort) with its scratch (selection state + the B unsorted keys) in a static 48 KB device array
+ * that every GPU loading the library holds until exit. Limit: B <= ALINK_NOALLOC_MAX_B (larger B is refused with
+ * ALINK_E_UNSUPPORTED and a message naming the limit); N and base as alink_topk_values. util_dev and the three outputs
+ * (B entries each, any may be NULL) are DEVICE pointers; the call enqueues on the context's stream and does not
+ * synchronise. No cudaMalloc / cudaFree / allocating library call on this path. The scratch is shared by every call and
+ * every context of the process on that GPU and keeps the last call's contents (the state is cleared at the start of
+ * each call): calls that overlap on the GPU (two streams, two contexts) race - serialise them. */
+#define ALINK_NOALLOC_MAX_B 4096
+int alink_topk_values_noalloc(alink_ctx *ctx, const float *util_dev, int64_t N, int64_t base, int64_t B,
+                              int64_t *idx_out_dev, float *util_out_dev, uint64_t *keys_out_dev);
+
 /* Top-B of n packed keys (the merge after the per-shard all-gather). keys_out: B keys, descending. */
 int alink_topk_keys(alink_ctx *ctx, const uint64_t *keys, int64_t n, int64_t B, int in_space,
                     uint64_t *keys_out, int out_space);
