@@ -1108,6 +1108,206 @@ static int refine_query_v2(alink_ctx *ctx, const HeadGroup &g, Table &A, Table &
   return ALINK_OK;
 }
 
+// FP32_REFINE for vote entropy (refine.cuh, last section): the half filter's votes are certain wherever every learner's
+// |p1 - p0| clears the per-learner bound; the rest is re-scored with split operands, and what is still within that
+// stage's bound exactly. All N utilities are exact afterwards; the selection is the ordinary top-B over them.
+// *handled = false: shape not taken, or a list overflowed / a bound could not be verified (the caller runs the exact
+// pipeline; ctx->refine_fallback says why).
+static int refine_vote_query(alink_ctx *ctx, const HeadGroup &g, Table &A, Table &Bt, const int32_t *ia, const int32_t *ib,
+                             int64_t N, int64_t B, int64_t base, cudaEvent_t *ev, int64_t *idx_out, float *util_out,
+                             uint64_t *keys_out, int out_space, bool *handled) {
+  static const int ver_env = [] { const char *e = getenv("ALINK_REFINE_V"); return e ? atoi(e) : 2; }();
+  static const int vote_env = [] { const char *e = getenv("ALINK_REFINE_VOTE"); return e ? atoi(e) : 1; }();
+  static const int fmt_env = [] { const char *e = getenv("ALINK_REFINE_FMT"); return e ? atoi(e) : 0; }();
+  *handled = false;
+  ctx->refine_fallback = 1;
+  ctx->refine_version = 1;
+  double ma = 0, mb = 0, ra = 0, rb = 0;
+  if (ver_env == 1 || !vote_env || fmt_env == 1 || !g.split_ok || g.bounds_stale || !g.W1h || !g.W2h || !tc_takes_vmin(g))
+    return ALINK_OK;
+  ALINK_TRY(table_absmax(ctx, A, &ma, &ra));
+  ALINK_TRY(table_absmax(ctx, Bt, &mb, &rb));
+  double xmax = ma + mb, xnorm = ra + rb;
+  if (g.feat_mode == ALINK_FEAT_ABSDIFF_HADAMARD) {
+    if (ma * mb > xmax) xmax = ma * mb;
+    const double hn = ra * mb < rb * ma ? ra * mb : rb * ma;
+    xnorm = sqrt(xnorm * xnorm + hn * hn);
+  }
+  const double h1max = xmax * g.w1_col_l1 + g.b1_absmax;
+  if (!(xmax < 6.0e4 && h1max < 6.0e4 && g.w_absmax < 6.0e4 && xmax > 0.0)) return ALINK_OK;
+  const int measure = ALINK_UTIL_VOTE_ENTROPY;
+  ctx->refine_version = 2;
+  ctx->refine_fallback = 0;
+  ctx->N = N; ctx->sK = g.K; ctx->sC = g.C; ctx->util_valid = false; ctx->probs_full = false;
+  ctx->refine_f16 = 1;
+  const unsigned int wave = ((unsigned int)(ctx->sm_count / 2) << 16) | (unsigned int)g.K;
+  const unsigned int ns_min = N < 4096 ? (unsigned int)N : 4096u, ns_max = ns_min + (unsigned int)(ctx->sm_count / 2) * 256u, ns2_max = 256;
+  int64_t cap1 = N / 4 > (1 << 18) ? N / 4 : (1 << 18);  // a vote is uncertain far more often than a utility is near tau
+  if (cap1 > (1ll << 27)) cap1 = 1ll << 27;
+  if (cap1 > N) cap1 = N;
+  int64_t cap2l = N / 256 > 8192 ? N / 256 : 8192;
+  if (cap2l > (1 << 20)) cap2l = 1 << 20;
+  const unsigned int cap2 = (unsigned int)cap2l;
+  const int64_t rows1 = cap1 + ns_max, rows2 = (int64_t)cap2 + ns2_max;
+  ALINK_TRY(dev_reserve(ctx, ctx->util, sizeof(float) * (size_t)N));
+  ALINK_TRY(dev_reserve(ctx, ctx->util2, sizeof(float) * (size_t)N));  // vmin of the filter
+  ALINK_TRY(dev_reserve(ctx, ctx->rstat, 32768));
+  ALINK_TRY(dev_reserve(ctx, ctx->cand, sizeof(uint32_t) * (size_t)rows1));
+  ALINK_TRY(dev_reserve(ctx, ctx->cia, sizeof(int32_t) * (size_t)rows1));
+  ALINK_TRY(dev_reserve(ctx, ctx->cib, sizeof(int32_t) * (size_t)rows1));
+  ALINK_TRY(dev_reserve(ctx, ctx->probs2, sizeof(float) * (size_t)rows1 * g.K * g.C));
+  ALINK_TRY(dev_reserve(ctx, ctx->cia2, sizeof(int32_t) * (size_t)rows2));
+  ALINK_TRY(dev_reserve(ctx, ctx->cib2, sizeof(int32_t) * (size_t)rows2));
+  ALINK_TRY(dev_reserve(ctx, ctx->map2, sizeof(uint32_t) * (size_t)rows2));
+  ALINK_TRY(dev_reserve(ctx, ctx->src2, sizeof(uint32_t) * (size_t)rows2));
+  ALINK_TRY(dev_reserve(ctx, ctx->probs, sizeof(float) * (size_t)rows2 * g.K * g.C));
+  ALINK_TRY(dev_reserve(ctx, ctx->h1ws, sizeof(float) * (size_t)rows2 * g.H1 * g.K));
+  if (!ctx->rs_host) ALINK_CUDA(ctx, cudaMallocHost((void **)&ctx->rs_host, RS_WORDS * sizeof(unsigned int)));
+  float *util_a = (float *)ctx->util.p, *vmin = (float *)ctx->util2.p;
+  unsigned int *rs = (unsigned int *)ctx->rstat.p + 240;
+  const double apriori = refine_model_eps(g, A, Bt, true);
+  ctx->refine_eps_apriori = apriori;
+  ctx->refine_eps_worst = refine_worst_eps(g, xmax, xnorm, true);
+  const int gi = (int)(&g - ctx->groups);
+  // eps1 / eps2 bound the error of a MEAN of K learners; one learner's probability is allowed sqrt(K) times that
+  const double rk = sqrt((double)g.K);
+  double eps1 = ctx->refine_eps > 0.0 ? ctx->refine_eps : (REFINE_EPS_F16 > apriori ? REFINE_EPS_F16 : apriori);
+  if (ctx->refine_eps <= 0.0 && ctx->refine_eps_hint[gi] > eps1) eps1 = ctx->refine_eps_hint[gi];
+  double eps2 = ctx->refine_eps2 > 0.0 ? ctx->refine_eps2 : REFINE_EPS2;
+  // (1) half-precision votes and vote entropy of every pair + how far each pair is from a flipped vote
+  ALINK_TRY(tc_score(ctx, g, A, Bt, ia, ib, N, nullptr, util_a, measure, true, vmin));
+  if (ev) ALINK_CUDA(ctx, cudaEventRecord(ev[2], ctx->stream));
+  int64_t blocks = (N + 2047) / 2048;
+  const int64_t capb = (int64_t)ctx->sm_count * 8;
+  if (blocks > capb) blocks = capb;
+  for (int round = 1;; ++round) {
+    if (eps2 * 4.0 > eps1) eps2 = eps1 / 4.0;
+    // |p1 - p0| moves by twice a learner's probability error (<= sqrt(K) eps); x 1.5 for safety
+    const float thr1 = (float)(3.0 * eps1 * rk), thr2 = (float)(3.0 * eps2 * rk);
+    ALINK_CUDA(ctx, cudaMemsetAsync(rs, 0, RS_WORDS * sizeof(unsigned int), ctx->stream));
+    // (2) C1 = {some learner within thr1 of a flip} + the stratified sample; their table rows
+    vote_mark_kernel<<<(unsigned)blocks, 256, 0, ctx->stream>>>(vmin, N, thr1, (uint32_t *)ctx->cand.p, rs + RS_COUNT1, (unsigned int)cap1);
+    ALINK_LAUNCHED(ctx);
+    refine_stage1_finish_kernel<<<(unsigned)(rows1 / 4096 > 64 ? (rows1 / 4096 > capb ? capb : rows1 / 4096) : 64), 256, 0, ctx->stream>>>(
+        rs, (unsigned int)cap1, N, ns_min, ns_max, wave, (uint32_t *)ctx->cand.p, ia, ib, ia ? 0u : ctx->ap_G, ctx->ap_pair0,
+        (int32_t *)ctx->cia.p, (int32_t *)ctx->cib.p);
+    ALINK_LAUNCHED(ctx);
+    // (3) split-operand tensor-core probabilities of C1 u S
+    {
+      const uint32_t apG = ctx->ap_G;
+      ctx->ap_G = 0;
+      const int rc = tc_score_split(ctx, g, A, Bt, (const int32_t *)ctx->cia.p, (const int32_t *)ctx->cib.p, rows1, rs + RS_M1,
+                                    (float *)ctx->probs2.p, nullptr, measure, xmax, h1max);
+      ctx->ap_G = apG;
+      ALINK_TRY(rc);
+    }
+    // (4) their votes replace the filter's; C2 = {still within thr2 of a flip} + 256 sample rows
+    {
+      int64_t fbl = rows1 / 4096 > 48 ? rows1 / 4096 : 48;
+      if (fbl > capb) fbl = capb;
+      const unsigned fb = (unsigned)fbl;
+#define ALINK_VOTE2(KT)                                                                                                        \
+  vote_stage2_kernel<KT><<<fb, 256, 0, ctx->stream>>>(rs, (const float *)ctx->probs2.p, g.K, g.C, util_a, vmin,                 \
+                                                      (const uint32_t *)ctx->cand.p, thr1, thr2, cap2,                          \
+                                                      (const int32_t *)ctx->cia.p, (const int32_t *)ctx->cib.p,                 \
+                                                      (int32_t *)ctx->cia2.p, (int32_t *)ctx->cib2.p, (uint32_t *)ctx->map2.p,  \
+                                                      (uint32_t *)ctx->src2.p)
+      switch (g.K) {
+        case 1: ALINK_VOTE2(1); break;
+        case 3: ALINK_VOTE2(3); break;
+        case 5: ALINK_VOTE2(5); break;
+        default: ALINK_VOTE2(0); break;
+      }
+#undef ALINK_VOTE2
+      ALINK_LAUNCHED(ctx);
+      vote_stage2_finish_kernel<<<1, 256, 0, ctx->stream>>>(rs, cap2, ns2_max, (const uint32_t *)ctx->cand.p, (const int32_t *)ctx->cia.p,
+                                                            (const int32_t *)ctx->cib.p, (int32_t *)ctx->cia2.p, (int32_t *)ctx->cib2.p,
+                                                            (uint32_t *)ctx->map2.p, (uint32_t *)ctx->src2.p);
+      ALINK_LAUNCHED(ctx);
+    }
+    // (5) bit-exact re-score of C2 u S2, exact votes
+    {
+      const uint32_t apG = ctx->ap_G;
+      ctx->ap_G = 0;
+      const int rc = ffma_head_chunk(ctx, g, (const float *)A.p, (const float *)Bt.p, A.D, (const int32_t *)ctx->cia2.p,
+                                     (const int32_t *)ctx->cib2.p, 0, (int)rows2, (float *)ctx->h1ws.p, rows2 * g.H1,
+                                     (float *)ctx->probs.p, rs + RS_M2);
+      ctx->ap_G = apG;
+      ALINK_TRY(rc);
+      const unsigned fb = (unsigned)(rows2 / 2048 > 8 ? rows2 / 2048 : 8);
+#define ALINK_VOTEF(KT)                                                                                                        \
+  vote_finish_kernel<KT><<<fb, 256, 0, ctx->stream>>>(rs, (const float *)ctx->probs.p, (const float *)ctx->probs2.p, g.K, g.C,  \
+                                                      util_a, (const uint32_t *)ctx->map2.p, (const uint32_t *)ctx->src2.p, thr2)
+      switch (g.K) {
+        case 1: ALINK_VOTEF(1); break;
+        case 3: ALINK_VOTEF(3); break;
+        case 5: ALINK_VOTEF(5); break;
+        default: ALINK_VOTEF(0); break;
+      }
+#undef ALINK_VOTEF
+      ALINK_LAUNCHED(ctx);
+    }
+    if (ev && round == 1) ALINK_CUDA(ctx, cudaEventRecord(ev[3], ctx->stream));
+    // (6) top-B of the N exact utilities (ties by lowest pair index, as everywhere)
+    KeySrc src{util_a, nullptr, (uint64_t)base};
+    ALINK_TRY(topk_device(ctx, src, N, B));
+    ALINK_CUDA(ctx, cudaMemcpyAsync(ctx->rs_host, rs, RS_WORDS * sizeof(unsigned int), cudaMemcpyDeviceToHost, ctx->stream));
+    if (ev && round == 1) ALINK_CUDA(ctx, cudaEventRecord(ev[4], ctx->stream));
+    ALINK_TRY(emit_selection(ctx, B, idx_out, util_out, keys_out, out_space));
+    ALINK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    const unsigned int *h = ctx->rs_host;
+    float e1, e2;
+    double ss1, ss2;
+    memcpy(&e1, h + RS_ERR1, 4);
+    memcpy(&e2, h + RS_ERR2, 4);
+    memcpy(&ss1, h + RS_SS1, 8);
+    memcpy(&ss2, h + RS_SS2, 8);
+    // reported at the scale of eps (a mean of K learners): the per-learner figures over sqrt(K)
+    ctx->refine_survivors = h[RS_N2];
+    ctx->refine_n1 = h[RS_N1];
+    ctx->refine_nsample = (int64_t)h[RS_M1] - (int64_t)h[RS_N1];
+    ctx->refine_nsample2 = (int64_t)h[RS_M2] - (int64_t)h[RS_N2];
+    ctx->refine_err1 = (float)(e1 / rk);
+    ctx->refine_err2 = (float)(e2 / rk);
+    ctx->refine_max_err = ctx->refine_err1;
+    ctx->refine_rms_err = h[RS_N1] ? (float)(sqrt(ss1 / (double)h[RS_N1]) / rk) : 0.0f;
+    ctx->refine_rms2 = h[RS_M2] ? (float)(sqrt(ss2 / (double)h[RS_M2]) / rk) : 0.0f;
+    ctx->refine_eps_used = eps1;
+    ctx->refine_eps2_used = eps2;
+    ctx->refine_rounds = round;
+    if (h[RS_FLAGS] & 3u) {  // a candidate list overflowed: the exact pipeline takes any pool
+      ctx->refine_version = 1;
+      ctx->refine_fallback = 2 + (int)(h[RS_FLAGS] & 3u);
+      return ALINK_OK;  // *handled stays false
+    }
+    // stage 2 against the exact values (C2 u S2), stage 1 against stage 2 (C1 u S, to within eps2); a sampled pair the
+    // filter (flag 4) or the split stage (flag 8) called certain and whose votes changed is a violation whatever the errors
+    const bool wit1 = (h[RS_FLAGS] & 4u) != 0, wit2 = (h[RS_FLAGS] & 8u) != 0;
+    const double seen2 = (double)e2 / rk;
+    double seen1 = (double)e1 / rk + eps2;
+    const double tail1 = 8.0 * (double)ctx->refine_rms_err;
+    const bool bad2 = seen2 > eps2 || wit2, bad1 = seen1 > eps1 || tail1 > eps1 || wit1;
+    if (tail1 > 2.0 * seen1) seen1 = 0.5 * tail1;
+    if ((!bad1 && !bad2) || round >= 5) {
+      if (bad1 || bad2) {
+        ctx->refine_version = 1;
+        ctx->refine_fallback = 6;
+        return ALINK_OK;
+      }
+      break;
+    }
+    if (bad2) eps2 = 2.0 * (seen2 > eps2 ? seen2 : eps2);
+    if (bad1) {
+      eps1 = 2.0 * (seen1 > eps1 ? seen1 : eps1);
+      if (ctx->refine_eps <= 0.0) ctx->refine_eps_hint[gi] = eps1;
+    }
+  }
+  ctx->util_valid = true;
+  ctx->util_measure = measure;
+  *handled = true;
+  return ALINK_OK;
+}
+
 int alink_set_refine_eps(alink_ctx *ctx, double eps) {
   if (!ctx) return ALINK_E_INVALID;
   if (!(eps >= 0.0 && eps < 1.0)) return alink_fail(ctx, ALINK_E_INVALID, "eps outside [0, 1) (0 = per-format default)");
@@ -1188,8 +1388,7 @@ int alink_query(alink_ctx *ctx, int group, int slot_a, int slot_b, const int32_t
   ctx->refine_max_err = 0.0f;
   ctx->refine_version = 0;
   if (group >= 0 && group < ALINK_MAX_GROUPS && ctx->groups[group].set &&
-      ctx->groups[group].compute == ALINK_COMPUTE_FP32_REFINE && ctx->groups[group].tc_ok &&
-      measure != ALINK_UTIL_VOTE_ENTROPY && B > 0 && N >= 8192) {
+      ctx->groups[group].compute == ALINK_COMPUTE_FP32_REFINE && ctx->groups[group].tc_ok && B > 0 && N >= 8192) {
     const HeadGroup &g = ctx->groups[group];
     Table &TA = ctx->tables[slot_a], &TB = ctx->tables[slot_b];
     if (!TA.p || !TB.p) return alink_fail(ctx, ALINK_E_STATE, "embedding table slot not set (alink_set_table)");
@@ -1197,8 +1396,14 @@ int alink_query(alink_ctx *ctx, int group, int slot_a, int slot_b, const int32_t
       return alink_fail(ctx, ALINK_E_INVALID, "FP32_REFINE needs fp32 tables matching the heads' fan-in");
     if (!dia && !ctx->ap_G && (N > TA.M || N > TB.M))
       return alink_fail(ctx, ALINK_E_INVALID, "identity pairs exceed table rows");
-    ALINK_TRY(refine_query_v2(ctx, g, TA, TB, (const int32_t *)dia, (const int32_t *)dib, N, measure, B, base,
-                              timing ? e : nullptr, idx_out, util_out, keys_out, out_space));
+    bool handled = true;
+    if (measure == ALINK_UTIL_VOTE_ENTROPY)
+      ALINK_TRY(refine_vote_query(ctx, g, TA, TB, (const int32_t *)dia, (const int32_t *)dib, N, B, base, timing ? e : nullptr,
+                                  idx_out, util_out, keys_out, out_space, &handled));
+    else
+      ALINK_TRY(refine_query_v2(ctx, g, TA, TB, (const int32_t *)dia, (const int32_t *)dib, N, measure, B, base,
+                                timing ? e : nullptr, idx_out, util_out, keys_out, out_space));
+    if (handled) {
     if (timing) {
       ALINK_CUDA(ctx, cudaEventRecord(e[5], ctx->stream));
       ALINK_CUDA(ctx, cudaEventSynchronize(e[5]));
@@ -1211,6 +1416,7 @@ int alink_query(alink_ctx *ctx, int group, int slot_a, int slot_b, const int32_t
       timing->launches = ctx->launches - l0;
     }
     return ALINK_OK;
+    }  // (else: vote entropy on a shape / pool the refine path does not take — the exact pipeline below)
   }
   ALINK_TRY(score_impl(ctx, group, ctx->tables[slot_a], ctx->tables[slot_b], (const int32_t *)dia,
                        (const int32_t *)dib, N, measure));

@@ -88,6 +88,8 @@ struct Args {
   int ntiles;
   const uint8_t *bimg;       // pair mode: [K][nc][2 ranks] layer-1 bias tiles of 2 KB (BIAS_TILE below)
   uint8_t *xscratch;         // STAGED: [gridDim.x][2][MAX_KB] feature-tile images of 16 KB (L2-resident scratch)
+  float *vmin;               // [N] or nullptr: min over learners of |p1 - p0| — how far the pair is from a flipped vote
+                             // (the vote-entropy filter of FP32_REFINE, refine.cuh)
   // debug build only (-DALINK_TC_DEBUG): bits 0-5 slow down one role per loop iteration by (dbg >> 8) ns —
   // 1 weight producer, 2 MMA issuer, 8 epilogue, 16 gather producers, 32 peer relay, 128 L2 prefetcher;
   // bit 6 publishes per-role progress counters in the watchdog buffer (ptx.cuh)
@@ -532,6 +534,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
     // epilogue -> layer 2 -> epilogue chain; consecutive learners use alternate accumulators.
     bool pend = false;
     uint32_t pl = 0, pi = 0, pvp = 0;  // the pending learner, its tile, its running index mod 4
+    float vmn = 0.0f;                  // min over the learners so far of |p1 - p0|
     for (uint32_t q = 0; q <= Q; ++q) {
       ALINK_DBG_ROLE(8u, 4 + (warp & 3), q);
       const uint32_t b = q & 1u, u = q >> 1;
@@ -706,10 +709,13 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
         }
         rows[2 * pl] = p0;
         rows[2 * pl + 1] = p1;
+        const float dv = fabsf(__fsub_rn(p1, p0));
+        vmn = pl == 0 ? dv : fminf(vmn, dv);
         if (pl == (uint32_t)a.K - 1 && a.util && n < a.N) {
           float c0, c1u;
           alink_consensus2(rows, a.K, &c0, &c1u);
           a.util[n] = alink_utility2(a.measure, rows, a.K, c0, c1u);
+          if (a.vmin) a.vmin[n] = vmn;
         }
       }
       if (q == Q) break;
@@ -942,10 +948,17 @@ static int tc_prepare_heads(alink_ctx *ctx, HeadGroup &g, int formats = 1) {
 
 static int tc_score_ko(alink_ctx *ctx, const HeadGroup &g, const tc::Args &a0, bool tb16, bool f16);  // head_tc_ko.cuh
 
+// whether tc_score can also return vmin (the k-inner kernel only)
+static bool tc_takes_vmin(const HeadGroup &g) {
+  const char *e = getenv("ALINK_TC_KO");
+  return g.D_in / tc::KBLK <= tc::MAX_KB && !(e && atoi(e) == 1);
+}
+
 // Scores N pairs with every learner; probs [N][K][C] and/or util [N] (measure) are written by the
 // kernel's epilogue. ia/ib are device pointers or null.
 static int tc_score(alink_ctx *ctx, const HeadGroup &g, const Table &A, const Table &B, const int32_t *ia,
-                    const int32_t *ib, int64_t N, float *probs, float *util, int measure, bool f16 = false) {
+                    const int32_t *ib, int64_t N, float *probs, float *util, int measure, bool f16 = false,
+                    float *vmin = nullptr) {
   if (f16 ? (!g.W1h || !g.W2h || A.dtype != ALINK_F32) : (!g.W1t || !g.W2t))
     return alink_fail(ctx, ALINK_E_STATE, "tensor-core weight images were not prepared");
   tc::Args a;
@@ -958,7 +971,7 @@ static int tc_score(alink_ctx *ctx, const HeadGroup &g, const Table &A, const Ta
   a.w2img = (const uint8_t *)(f16 ? (void *)g.W2h : (void *)g.W2t);
   a.bimg = a.w2img + (size_t)g.K * g.H1 * g.H2 * 2;
   a.b1 = g.b1; a.b2 = g.b2; a.W3 = g.W3; a.b3 = g.b3;
-  a.probs = probs; a.util = util;
+  a.probs = probs; a.util = util; a.vmin = vmin;
   a.ntiles = (int)((N + tc::TILE_M - 1) / tc::TILE_M);
   {
     const char *e = getenv("ALINK_TC_DBG_DELAY");  // "<role bits>:<ns>", read per launch; acts in the debug build only
@@ -967,7 +980,10 @@ static int tc_score(alink_ctx *ctx, const HeadGroup &g, const Table &A, const Ta
   }
   // Wide features (the tile does not fit in shared memory) take the k-outer kernel; ALINK_TC_KO=1 forces it.
   static const int ko_env = [] { const char *e = getenv("ALINK_TC_KO"); return e ? atoi(e) : 0; }();
-  if (a.nkb > tc::MAX_KB || (ko_env == 1 && g.H1 <= 512)) return tc_score_ko(ctx, g, a, A.dtype == ALINK_BF16, f16);
+  if (a.nkb > tc::MAX_KB || (ko_env == 1 && g.H1 <= 512)) {
+    if (vmin) return alink_fail(ctx, ALINK_E_UNSUPPORTED, "the vote filter is not in the k-outer kernel");
+    return tc_score_ko(ctx, g, a, A.dtype == ALINK_BF16, f16);
+  }
   // CTA pairs (cta_group::2) by default; ALINK_TC_NCTA=1 selects the independent-CTA variant.
   static const int ncta_env = [] { const char *e = getenv("ALINK_TC_NCTA"); return e ? atoi(e) : 2; }();
   const int ncta = (ncta_env == 1 || ctx->sm_count < 2 || (a.nkb & 1)) ? 1 : 2;  // a pair slot holds 2 k-blocks

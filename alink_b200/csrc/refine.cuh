@@ -513,3 +513,157 @@ __global__ void __launch_bounds__(256) table_stats_kernel(const float *__restric
     atomicAdd(reinterpret_cast<double *>(out + 2), (double)nsum);
   }
 }
+
+// ======================================================================================================================
+// FP32_REFINE for VOTE ENTROPY (modAL's vote_entropy_sampling, the DEFAULT query strategy of the reference's Committee,
+// code/learners.py:287): the utility is a function of the K hard votes, so it is exact wherever every vote is certain.
+// The filter also returns vmin = min_k |p1 - p0| per pair; a vote can only flip where vmin is within twice the
+// per-learner probability bound. Those pairs are re-scored with split operands, their votes replace the filter's, and
+// the handful still within the split stage's bound is re-scored exactly. The utilities of ALL N pairs are then exact
+// and the ordinary top-B (ties by lowest index: the plateaus are huge) runs over them.
+__global__ void __launch_bounds__(256) vote_mark_kernel(const float *__restrict__ vmin, int64_t N, float thr, uint32_t *__restrict__ cand,
+                                                        unsigned int *__restrict__ count, unsigned int cap) {
+  const int lane = threadIdx.x & 31;
+  for (int64_t n0 = (int64_t)blockIdx.x * 256 + (threadIdx.x & ~31); n0 < N; n0 += (int64_t)gridDim.x * 256) {
+    const int64_t n = n0 + lane;
+    const bool keep = n < N && __ldg(vmin + n) < thr;
+    const unsigned int m = __ballot_sync(0xffffffffu, keep);
+    if (m) {
+      const int first = __ffs(m) - 1;
+      unsigned int basepos = 0;
+      if (lane == first) basepos = atomicAdd(count, (unsigned int)__popc(m));
+      basepos = __shfl_sync(0xffffffffu, basepos, first);
+      const unsigned int pos = basepos + __popc(m & ((1u << lane) - 1u));
+      if (keep && pos < cap) cand[pos] = (uint32_t)n;
+    }
+  }
+}
+
+// rows of per-learner probabilities -> widened rows[], returns min_k |p1 - p0|
+template <int KT>
+__device__ __forceinline__ float vote_rows(const float *__restrict__ probs, size_t row, int K, int C, float *rows) {
+  const int KK = KT > 0 ? KT : K;
+  float vm = 2.0f;
+#pragma unroll
+  for (int k = 0; k < KK; ++k) {
+    float p0, p1;
+    if (C == 2) {
+      const float2 v = reinterpret_cast<const float2 *>(probs)[row * KK + k];
+      p0 = v.x;
+      p1 = v.y;
+    } else {
+      p1 = probs[row * KK + k];
+      p0 = __fsub_rn(1.0f, p1);
+    }
+    rows[2 * k] = p0;
+    rows[2 * k + 1] = p1;
+    vm = fminf(vm, fabsf(__fsub_rn(p1, p0)));
+  }
+  return vm;
+}
+
+// after the split stage: the votes of C1 replace the filter's; pairs still within thr2 of a flip go to the exact stage;
+// statistics: |vmin(filter) - vmin(split)| / 2 estimates the filter's per-learner probability error on C1 u S; a SAMPLE
+// row (a pair the filter called certain) whose vote entropy differs from the split stage's is a violation (flag 4).
+template <int KT>
+__global__ void __launch_bounds__(256) vote_stage2_kernel(unsigned int *__restrict__ rs, const float *__restrict__ probs2, int K, int C,
+                                                          float *__restrict__ util_a, const float *__restrict__ vmin,
+                                                          const uint32_t *__restrict__ cand1, float thr1, float thr2,
+                                                          unsigned int cap2, const int32_t *__restrict__ cia1,
+                                                          const int32_t *__restrict__ cib1, int32_t *__restrict__ cia2,
+                                                          int32_t *__restrict__ cib2, uint32_t *__restrict__ map2,
+                                                          uint32_t *__restrict__ src2) {
+  const int KK = KT > 0 ? KT : K;
+  const unsigned int M1 = rs[RS_M1], n1 = rs[RS_N1];
+  float m1 = 0.0f, ss1 = 0.0f;
+  float rows[2 * (KT > 0 ? KT : ALINK_MAX_K)];
+  for (unsigned int r = blockIdx.x * 256 + threadIdx.x; r < M1; r += gridDim.x * 256) {
+    const float vm2 = vote_rows<KT>(probs2, r, K, C, rows);
+    const float u2 = alink_utility2(ALINK_UTIL_VOTE_ENTROPY, rows, KK, 0.0f, 0.0f);
+    const uint32_t n = cand1[r];
+    const float vm1 = __ldg(vmin + n);
+    const float e1 = 0.5f * fabsf(__fsub_rn(vm1, vm2));
+    m1 = fmaxf(m1, e1);
+    if (r < n1) {
+      ss1 = __fmaf_rn(e1, e1, ss1);
+      util_a[n] = u2;
+      if (vm2 < thr2) {
+        const unsigned int pos = atomicAdd(rs + RS_COUNT2, 1u);
+        if (pos < cap2) {
+          src2[pos] = r;
+          map2[pos] = n;
+          cia2[pos] = cia1[r];
+          cib2[pos] = cib1[r];
+        }
+      }
+    } else if (vm1 >= thr1 && util_a[n] != u2) {  // (a sample pair that is also in C1 is no witness: C1 rewrites it)
+      atomicOr(rs + RS_FLAGS, 4u);
+    }
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    m1 = fmaxf(m1, __shfl_xor_sync(0xffffffffu, m1, o));
+    ss1 += __shfl_xor_sync(0xffffffffu, ss1, o);
+  }
+  if ((threadIdx.x & 31) == 0) {
+    if (m1 > 0.0f) atomicMax(rs + RS_ERR1, __float_as_uint(m1));
+    if (ss1 > 0.0f) atomicAdd(reinterpret_cast<double *>(rs + RS_SS1), (double)ss1);
+  }
+}
+
+// clamp |C2|, append ns2 evenly spaced sample rows for the exact stage
+__global__ void __launch_bounds__(256) vote_stage2_finish_kernel(unsigned int *__restrict__ rs, unsigned int cap2, unsigned int ns2_max,
+                                                                 const uint32_t *__restrict__ cand1, const int32_t *__restrict__ cia1,
+                                                                 const int32_t *__restrict__ cib1, int32_t *__restrict__ cia2,
+                                                                 int32_t *__restrict__ cib2, uint32_t *__restrict__ map2,
+                                                                 uint32_t *__restrict__ src2) {
+  const unsigned int count2 = rs[RS_COUNT2], n2 = count2 < cap2 ? count2 : cap2;
+  const unsigned int n1 = rs[RS_N1], nsamp = rs[RS_M1] - n1;
+  const unsigned int ns2 = nsamp < ns2_max ? nsamp : ns2_max;
+  for (unsigned int j = threadIdx.x; j < ns2; j += 256) {
+    const unsigned int r = n1 + (unsigned int)(((unsigned long long)j * nsamp) / ns2);
+    src2[n2 + j] = r;
+    map2[n2 + j] = cand1[r];
+    cia2[n2 + j] = cia1[r];
+    cib2[n2 + j] = cib1[r];
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    rs[RS_N2] = n2;
+    rs[RS_M2] = n2 + ns2;
+    if (count2 > cap2) atomicOr(rs + RS_FLAGS, 2u);
+  }
+}
+
+// exact votes of C2 replace the split stage's; per-learner |p2 - p| is the split stage's error; an exact SAMPLE row whose
+// vote entropy differs from what the earlier stages left in util_a is a violation (flag 8)
+template <int KT>
+__global__ void __launch_bounds__(256) vote_finish_kernel(unsigned int *__restrict__ rs, const float *__restrict__ probs,
+                                                          const float *__restrict__ probs2, int K, int C, float *__restrict__ util_a,
+                                                          const uint32_t *__restrict__ map2, const uint32_t *__restrict__ src2,
+                                                          float thr2) {
+  const int KK = KT > 0 ? KT : K;
+  const unsigned int M2 = rs[RS_M2], n2 = rs[RS_N2];
+  float m2 = 0.0f, ss2 = 0.0f;
+  float rows[2 * (KT > 0 ? KT : ALINK_MAX_K)], r2[2 * (KT > 0 ? KT : ALINK_MAX_K)];
+  for (unsigned int j = blockIdx.x * 256 + threadIdx.x; j < M2; j += gridDim.x * 256) {
+    vote_rows<KT>(probs, j, K, C, rows);
+    const float vm2 = vote_rows<KT>(probs2, src2[j], K, C, r2);
+    const float u = alink_utility2(ALINK_UTIL_VOTE_ENTROPY, rows, KK, 0.0f, 0.0f);
+    float e2 = 0.0f;
+#pragma unroll
+    for (int k = 0; k < KK; ++k) e2 = fmaxf(e2, fabsf(__fsub_rn(rows[2 * k + 1], r2[2 * k + 1])));
+    m2 = fmaxf(m2, e2);
+    ss2 = __fmaf_rn(e2, e2, ss2);
+    const uint32_t n = map2[j];
+    if (j < n2) util_a[n] = u;
+    else if (vm2 >= thr2 && util_a[n] != u) atomicOr(rs + RS_FLAGS, 8u);  // (vm2 < thr2: the pair may sit in C2 itself)
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    m2 = fmaxf(m2, __shfl_xor_sync(0xffffffffu, m2, o));
+    ss2 += __shfl_xor_sync(0xffffffffu, ss2, o);
+  }
+  if ((threadIdx.x & 31) == 0) {
+    if (m2 > 0.0f) atomicMax(rs + RS_ERR2, __float_as_uint(m2));
+    if (ss2 > 0.0f) atomicAdd(reinterpret_cast<double *>(rs + RS_SS2), (double)ss2);
+  }
+}

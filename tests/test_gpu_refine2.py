@@ -137,3 +137,51 @@ def test_gain_and_table_scale_property(ctx, gain, tscale, measure, act):
         pool.heads.W1[k] = (pool.heads.W1[k] / np.float32(tscale)).astype(np.float32)
     exact, refined, rep = _both(ctx, pool, measure, 500, table=table)
     _check(exact, refined)
+
+
+# ---- vote entropy (the reference Committee's default strategy, learners.py:287) in FP32_REFINE --------------------------
+def _all_utilities(ctx, N):
+    """every pair's utility of the last query, through the top-N selection (keys = utility bits + index, sorted)"""
+    return ctx.select_topk(N)[2]
+
+
+@pytest.mark.parametrize("gain", [1.0, 8.0])
+@pytest.mark.parametrize("config", [1, 2])
+def test_vote_entropy_refines_every_vote_exactly(ctx, config, gain):
+    """Vote entropy is a function of the K hard votes: the refine path must leave the EXACT utility on every one of the
+    N pairs (not only on the selected ones) — the plateaus are huge and the selection is decided by the lowest index."""
+    pool = _scaled(synth.make_pool(config, N=300_000), gain)
+    ctx.set_table(0, pool.table)
+    ctx.set_heads(0, pool.heads, compute=_ffi.FP32_EXACT)
+    ctx.set_heads(1, pool.heads, compute=_ffi.FP32_REFINE)
+    exact = ctx.query(0, 0, 0, pool.ia, pool.ib, pool.N, "vote_entropy", 1000)
+    all_exact = _all_utilities(ctx, pool.N)
+    refined = ctx.query(1, 0, 0, pool.ia, pool.ib, pool.N, "vote_entropy", 1000)
+    rep = ctx.refine_report()
+    all_refined = _all_utilities(ctx, pool.N)
+    _check(exact, refined)
+    print(f"vote entropy cfg{config} gain {gain}: {rep}")
+    assert rep["version"] == 2 and rep["fallback"] == 0 and rep["filter_f16"] == 1
+    assert rep["n_sample"] >= 4096 and 0 < rep["n_stage2"] < 0.25 * pool.N
+    assert rep["err1_max"] <= rep["eps1_used"] and rep["err2_max"] <= rep["eps2_used"]
+    np.testing.assert_array_equal(all_refined, all_exact)
+
+
+def test_vote_entropy_tight_bound_is_widened(ctx):
+    pool = synth.make_pool(2, N=200_000)
+    ctx.set_refine_eps(2e-5)  # far below the half filter's error: flipped votes outside C1 must be seen in the sample
+    try:
+        exact, refined, rep = _both(ctx, pool, "vote_entropy", 500)
+    finally:
+        ctx.set_refine_eps(0.0)
+    print("tight vote:", rep)
+    _check(exact, refined)
+    assert rep["rounds"] > 1 or rep["version"] == 1
+
+
+def test_vote_entropy_sigmoid_heads(ctx):
+    pool = synth.make_pool(2, N=150_000, act="sigmoid")
+    exact, refined, rep = _both(ctx, pool, "vote_entropy", 300)
+    _check(exact, refined)
+    print("sigmoid vote:", rep)
+    assert rep["version"] == 2 and rep["fallback"] == 0
