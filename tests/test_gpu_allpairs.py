@@ -142,3 +142,25 @@ def test_sharded_disparity_equals_single_shot(ctx, oracle, blind, shards):
         active += a
     np.testing.assert_array_equal(np.concatenate(parts), ridx)
     assert active == ractive
+
+
+def test_allpairs_vote_entropy_refine_vs_exact_and_oracle(ctx, oracle):
+    """Vote entropy (Committee's default strategy) over a probe x gallery block with implicit pair indices, through the
+    tensor-core vote filter: identical to the exact mode and to the oracle."""
+    pool = synth.make_pool(1, N=64, M=1200)
+    P, G, B = 200, 800, 300
+    probe = np.ascontiguousarray(pool.table[:P])
+    gallery = np.ascontiguousarray(pool.table[250:250 + G])
+    ctx.set_table(3, probe)
+    ctx.set_table(4, gallery)
+    ctx.set_heads(2, pool.heads, compute=_ffi.FP32_EXACT)
+    ctx.set_heads(3, pool.heads, compute=_ffi.FP32_REFINE)
+    exact = ctx.query_allpairs(2, 3, 4, 0, P, "vote_entropy", B)
+    refined = ctx.query_allpairs(3, 3, 4, 0, P, "vote_entropy", B)
+    rep = ctx.refine_report()
+    assert rep["version"] == 2 and rep["fallback"] == 0, rep
+    for a, b in zip(refined, exact):
+        np.testing.assert_array_equal(a.view(np.uint64) if a.dtype == np.uint64 else a, b)
+    ia, ib = _allpairs_indices(P, G)
+    ref = oracle.score(probe, gallery, ia, ib, pool.heads, measure="vote_entropy")
+    np.testing.assert_array_equal(refined[2], oracle.topk(ref["util"], B)[2])

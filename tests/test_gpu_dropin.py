@@ -160,3 +160,23 @@ def test_all_pairs_rows_like_generate_matrix(oracle):
         ib = np.arange(len(feats), dtype=np.int32)
         ref = oracle.score(feats, feats, ia, ib, pool.heads)
         np.testing.assert_array_equal(row, ref["per_learner"][:, 0, 0])
+
+
+def test_committee_default_query_in_refine_mode_equals_fp32():
+    """Committee(learner_list).query — vote_entropy_sampling by default (code/learners.py:287) — over a 200 k-pair pool:
+    'refine' mode (tensor-core vote filter, csrc/refine.cuh) must return the very same rows as 'fp32'."""
+    from alink_b200 import _ffi
+    pool = synth.make_pool(2, N=200_000)
+    pp = engine.PairPool(pool.table, pool.ia, pool.ib)
+    got = {}
+    for mode in ("fp32", "refine"):
+        engine.set_compute_mode(mode)
+        learners = [ActiveLearner(estimator=KerasClassifier(lambda n=n: n), query_strategy=uncertainty.uncertainty_sampling)
+                    for n in _nets(pool)]
+        com = Committee(learners)
+        got[mode], _ = com.query(pp, n_instances=500)
+        if mode == "refine":
+            rep = pp.ctx.refine_report()
+            assert rep["version"] == 2 and rep["fallback"] == 0, rep
+    np.testing.assert_array_equal(got["refine"], got["fp32"])
+    pp.close()
