@@ -42,7 +42,7 @@ SYMBOLS = (
     "alink_train_step", "alink_get_train_state", "alink_set_train_state",
     "alink_set_refine_eps2", "alink_refine_report_get",
     "alink_perturb_rows", "alink_score_column", "alink_min_disparity",
-    "alink_comm_unique_id", "alink_comm_init", "alink_comm_destroy", "alink_query_sharded", "alink_disparity_select_comm",
+    "alink_comm_unique_id", "alink_comm_init", "alink_comm_destroy", "alink_query_sharded", "alink_comm_push_state", "alink_disparity_select_comm",
     "alink_de_init", "alink_de_mutate", "alink_de_repair", "alink_de_evaluate", "alink_de_select", "alink_de_get",
 )
 
@@ -168,6 +168,8 @@ def load():
     L.alink_comm_init.argtypes = [vp, vp, i32, i32]
     L.alink_comm_destroy.restype = i32
     L.alink_comm_destroy.argtypes = [vp]
+    L.alink_comm_push_state.restype = i32
+    L.alink_comm_push_state.argtypes = [vp, C.POINTER(C.c_int), C.POINTER(C.c_int)]
     L.alink_query_sharded.restype = i32
     L.alink_query_sharded.argtypes = [vp, i32, i32, i32, vp, vp, i64, i32, i32, i64, i64, vp, vp, vp, i32, vp]
     L.alink_disparity_select_comm.restype = i32
@@ -548,6 +550,12 @@ class Context:
 
     def comm_destroy(self):
         self._check(self._L.alink_comm_destroy(self._h))
+
+    def comm_push_state(self):
+        """(enabled, used by the last query_sharded): the peer-push exchange of csrc/comm.cuh."""
+        en, used = C.c_int(0), C.c_int(0)
+        self._check(self._L.alink_comm_push_state(self._h, C.byref(en), C.byref(used)))
+        return bool(en.value), bool(used.value)
 
     def query_sharded(self, group, slot_a, slot_b, ia, ib, N, measure, B, base=0, timing=False):
         """alink_query on this rank's shard + NCCL all-gather of the keys + merge, all inside the library: every rank

@@ -17,6 +17,10 @@
 #include "perturb.cuh"
 #include "comm.cuh"
 
+extern "C" {
+static void push_teardown(alink_ctx *ctx);  // peer windows of the push exchange (below, with alink_comm_init)
+}
+
 #include <math.h>
 #include <new>
 #include <vector>
@@ -85,6 +89,7 @@ int alink_destroy(alink_ctx *ctx) {
   for (DevBuf *b : debufs) dev_release(*b);
   if (ctx->rs_host) cudaFreeHost(ctx->rs_host);
   if (ctx->comm && nccl_api()) nccl_api()->CommDestroy((alink_nccl_comm)ctx->comm);
+  push_teardown(ctx);
   dev_release(ctx->comm_keys);
   for (int i = 0; i < 8; ++i)
     if (ctx->ev[i]) cudaEventDestroy(ctx->ev[i]);
@@ -1643,6 +1648,69 @@ int alink_comm_unique_id(void *id128) {
   return ALINK_OK;
 }
 
+// The peer windows of the push exchange (comm.cuh). Every rank allocates one, the IPC handles travel through one
+// ncclAllGather, every rank maps its peers' windows; the path is used only if EVERY rank mapped every window (one
+// ncclAllReduce of the success bits, which also orders the windows' zero-fill before any peer's first store).
+static void push_teardown(alink_ctx *ctx) {
+  for (int r = 0; r < PUSH_MAX_W; ++r) {
+    if (ctx->push_win[r] && ctx->push_win[r] != ctx->push_own) cudaIpcCloseMemHandle(ctx->push_win[r]);
+    ctx->push_win[r] = nullptr;
+  }
+  if (ctx->push_own) cudaFree(ctx->push_own);
+  if (ctx->push_status) cudaFree(ctx->push_status);
+  if (ctx->push_host) cudaFreeHost(ctx->push_host);
+  ctx->push_own = nullptr;
+  ctx->push_status = nullptr;
+  ctx->push_host = nullptr;
+  ctx->push_ok = false;
+  ctx->push_epoch = 0;
+  cudaGetLastError();
+}
+
+static int push_setup(alink_ctx *ctx, NcclApi *api) {
+  const int W = ctx->comm_world, rank = ctx->comm_rank;
+  ALINK_CUDA(ctx, cudaMalloc((void **)&ctx->push_own, PUSH_WIN_BYTES));
+  ALINK_CUDA(ctx, cudaMalloc((void **)&ctx->push_status, 64 + 64 * PUSH_MAX_W + 16));
+  ALINK_CUDA(ctx, cudaMallocHost((void **)&ctx->push_host, 64));
+  ALINK_CUDA(ctx, cudaMemsetAsync(ctx->push_own, 0, PUSH_WIN_BYTES, ctx->stream));
+  ALINK_CUDA(ctx, cudaMemsetAsync(ctx->push_status, 0, 64 + 64 * PUSH_MAX_W + 16, ctx->stream));
+  unsigned char *hbuf = (unsigned char *)ctx->push_status + 64;       // W handles of 64 B
+  unsigned int *okw = (unsigned int *)(hbuf + 64 * PUSH_MAX_W);       // this rank's success bit, then the sum
+  cudaIpcMemHandle_t mine;
+  bool ok = cudaIpcGetMemHandle(&mine, ctx->push_own) == cudaSuccess;
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+  ALINK_CUDA(ctx, cudaMemcpyAsync(hbuf + 64 * rank, &mine, 64, cudaMemcpyHostToDevice, ctx->stream));
+  ALINK_NCCL(ctx, api, api->AllGather(hbuf + 64 * rank, hbuf, 8, ALINK_NCCL_UINT64, (alink_nccl_comm)ctx->comm, ctx->stream));
+  cudaIpcMemHandle_t all[PUSH_MAX_W];
+  ALINK_CUDA(ctx, cudaMemcpyAsync(all, hbuf, 64 * (size_t)W, cudaMemcpyDeviceToHost, ctx->stream));
+  ALINK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  for (int r = 0; r < W && ok; ++r) {
+    if (r == rank) {
+      ctx->push_win[r] = ctx->push_own;
+      continue;
+    }
+    void *p = nullptr;
+    if (cudaIpcOpenMemHandle(&p, all[r], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess || !p) {
+      ok = false;
+      cudaGetLastError();
+    } else {
+      ctx->push_win[r] = (uint8_t *)p;
+    }
+  }
+  const unsigned int okbit = ok ? 1u : 0u;
+  ALINK_CUDA(ctx, cudaMemcpyAsync(okw, &okbit, 4, cudaMemcpyHostToDevice, ctx->stream));
+  ALINK_NCCL(ctx, api, api->AllReduce(okw, okw + 1, 1, ALINK_NCCL_UINT32, ALINK_NCCL_SUM, (alink_nccl_comm)ctx->comm, ctx->stream));
+  unsigned int sum = 0;
+  ALINK_CUDA(ctx, cudaMemcpyAsync(&sum, okw + 1, 4, cudaMemcpyDeviceToHost, ctx->stream));
+  ALINK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  if (sum != (unsigned int)W) {  // some rank could not map a peer (no P2P / IPC in this container): NCCL serves the exchange
+    push_teardown(ctx);
+    return ALINK_OK;
+  }
+  ctx->push_ok = true;
+  return ALINK_OK;
+}
+
 int alink_comm_init(alink_ctx *ctx, const void *id128, int rank, int world) {
   if (!ctx) return ALINK_E_INVALID;
   if (!id128 || world < 1 || rank < 0 || rank >= world) return alink_fail(ctx, ALINK_E_INVALID, "bad rank %d of %d", rank, world);
@@ -1660,6 +1728,11 @@ int alink_comm_init(alink_ctx *ctx, const void *id128, int rank, int world) {
   ctx->comm = c;
   ctx->comm_rank = rank;
   ctx->comm_world = world;
+  push_teardown(ctx);
+  // off by default: measured on 2 B200s the NCCL all-gather + merge adds 25-35 us to the slowest rank's local query, the
+  // push kernel 130-200 us (tools/sharded_probe.py); ALINK_COMM_PUSH=1 selects it
+  static const int push_env = [] { const char *e = getenv("ALINK_COMM_PUSH"); return e ? atoi(e) : 0; }();
+  if (world > 1 && world <= PUSH_MAX_W && push_env) ALINK_TRY(push_setup(ctx, api));
   return ALINK_OK;
 }
 
@@ -1669,6 +1742,7 @@ int alink_comm_destroy(alink_ctx *ctx) {
     cudaStreamSynchronize(ctx->stream);
     nccl_api()->CommDestroy((alink_nccl_comm)ctx->comm);
   }
+  push_teardown(ctx);
   ctx->comm = nullptr;
   ctx->comm_world = 1;
   ctx->comm_rank = 0;
@@ -1694,11 +1768,39 @@ int alink_query_sharded(alink_ctx *ctx, int group, int slot_a, int slot_b, const
   ALINK_CUDA(ctx, cudaMemsetAsync(mine, 0, sizeof(uint64_t) * (size_t)B, ctx->stream));  // key 0 sorts below every real key
   if (bl > 0)
     ALINK_TRY(alink_query(ctx, group, slot_a, slot_b, ia, ib, N, in_space, measure, bl, base, nullptr, nullptr, mine, ALINK_DEVICE, timing));
+  ctx->push_used = 0;
+  if (ctx->push_ok && B <= PUSH_MAX_B) {
+    // exchange + merge in ONE launch over the peers' mapped windows (comm.cuh)
+    const int64_t npad = next_pow2(B);
+    ALINK_TRY(dev_reserve(ctx, ctx->sel_keys, sizeof(uint64_t) * (size_t)npad));
+    PushArgs pa;
+    memset(&pa, 0, sizeof(pa));
+    for (int r = 0; r < W; ++r) pa.win[r] = ctx->push_win[r];
+    pa.rank = ctx->comm_rank; pa.W = W; pa.B = (int)B; pa.npad = (int)(npad < 2 ? 2 : npad);
+    pa.epoch = ++ctx->push_epoch;
+    pa.mine = mine; pa.gathered = all; pa.out = (uint64_t *)ctx->sel_keys.p;
+    pa.status = ctx->push_status; pa.ok_dev = nullptr;
+    push_merge_kernel<<<1, 1024, 0, ctx->stream>>>(pa);
+    ALINK_LAUNCHED(ctx);
+    ctx->push_used = 1;
+    ALINK_CUDA(ctx, cudaMemcpyAsync(ctx->push_host, ctx->push_status, 8, cudaMemcpyDeviceToHost, ctx->stream));
+    ALINK_TRY(emit_selection(ctx, B, idx_out, util_out, keys_out, out_space));
+    if (out_space == ALINK_HOST && ctx->push_host[0])  // (device outputs: the caller's next synchronising call reports it)
+      return alink_fail(ctx, ALINK_E_CUDA, "peer push: a rank did not arrive within 2 s (epoch %llu)", ctx->push_epoch);
+    return ALINK_OK;
+  }
   ALINK_NCCL(ctx, api, api->AllGather(mine, all, (size_t)B, ALINK_NCCL_UINT64, (alink_nccl_comm)ctx->comm, ctx->stream));
   ctx->launches++;  // the collective's kernel
   KeySrc src{nullptr, all, 0, nullptr};
   ALINK_TRY(topk_device(ctx, src, (int64_t)B * W, B));
   return emit_selection(ctx, B, idx_out, util_out, keys_out, out_space);
+}
+
+int alink_comm_push_state(const alink_ctx *ctx, int *enabled, int *used_last) {
+  if (!ctx) return ALINK_E_INVALID;
+  if (enabled) *enabled = ctx->push_ok ? 1 : 0;
+  if (used_last) *used_last = ctx->push_used;
+  return ALINK_OK;
 }
 
 // ------------------------------------------------------------------------------------------ A2-LINK pool

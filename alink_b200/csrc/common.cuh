@@ -137,6 +137,14 @@ struct alink_ctx {
   void *comm = nullptr;
   int comm_rank = 0, comm_world = 1;
   DevBuf comm_keys;
+  // peer push (comm.cuh): the windows of all ranks as mapped here (IPC), this rank's own allocation, the step counter
+  uint8_t *push_win[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+  uint8_t *push_own = nullptr;
+  bool push_ok = false;
+  unsigned long long push_epoch = 0;
+  unsigned int *push_status = nullptr;  // device: [0] timeout, [1] all ranks ok, [2] this rank's ok bit
+  unsigned int *push_host = nullptr;    // pinned mirror of push_status
+  int push_used = 0;                    // 1: the last alink_query_sharded exchanged through the push kernel
 };
 
 static inline int alink_fail(alink_ctx *ctx, int code, const char *fmt, ...) {

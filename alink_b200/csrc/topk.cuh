@@ -299,12 +299,8 @@ __global__ void __launch_bounds__(1024) radix_select_small_kernel(KeySrc src, in
 // Whole top-B of a small source in one launch: select the B-th key, gather the B keys >= it into shared
 // memory, bitonic-sort them descending, write them out (B <= npad <= 4096).
 // n_dev: the source length lives on the device (FP32_REFINE's candidate count); n is then its capacity
-__global__ void __launch_bounds__(1024) topk_small_kernel(KeySrc src, int n, int B, int npad, uint64_t *__restrict__ out,
-                                                          const unsigned int *__restrict__ n_dev = nullptr) {
-  if (n_dev) {
-    const unsigned int nd = *n_dev;
-    if (nd < (unsigned int)n) n = (int)nd;
-  }
+// (the body as a device function: the peer-push merge of comm.cuh runs it in the tail of its own kernel; 1024 threads)
+__device__ __forceinline__ void topk_small_body(const KeySrc &src, int n, int B, int npad, uint64_t *__restrict__ out) {
   __shared__ unsigned int sh[2048];
   __shared__ unsigned int part[256];
   __shared__ unsigned long long s_prefix, s_remaining;
@@ -341,6 +337,15 @@ __global__ void __launch_bounds__(1024) topk_small_kernel(KeySrc src, int n, int
     }
   }
   for (int i = tid; i < B; i += 1024) out[i] = sk[i];
+}
+
+__global__ void __launch_bounds__(1024) topk_small_kernel(KeySrc src, int n, int B, int npad, uint64_t *__restrict__ out,
+                                                          const unsigned int *__restrict__ n_dev = nullptr) {
+  if (n_dev) {
+    const unsigned int nd = *n_dev;
+    if (nd < (unsigned int)n) n = (int)nd;
+  }
+  topk_small_body(src, n, B, npad, out);
 }
 
 // keys >= threshold (st->prefix after the last pass) -> out (exactly B of them, unordered)

@@ -302,6 +302,11 @@ int alink_disparity_select_comm(alink_ctx *ctx, const float *p2, const float *p1
                                 double ratio, double eps, int blind, const float *y, int in_space, int64_t *idx_out, int out_space,
                                 int64_t *n_out, int64_t *active_count);
 
+/* Whether alink_query_sharded exchanges the keys through the peer-push kernel (every rank mapped every peer's window
+ * through CUDA IPC at alink_comm_init; only with ALINK_COMM_PUSH=1 - measured slower than the NCCL all-gather, which is the default) and whether
+ * the last call did. SURVEY.md 5 ("one-shot peer-mapped push"); the reference is single-process. */
+int alink_comm_push_state(const alink_ctx *ctx, int *enabled, int *used_last);
+
 /* The A2-LINK noise-augmented pool generated on the device (BASELINE configs[3]). Replaces the
  * per-noise re-featurisation of code/ALINK.py:163-170 (bag.attackModel -> conversionModel.process) with its embedding-space
  * analogue: row n of slot_dst = normalize(e + delta), e = row idx[n] (or n) of slot_src, delta = `ncoord` coordinates set to

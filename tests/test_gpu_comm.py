@@ -10,8 +10,10 @@ import pytest
 pytestmark = pytest.mark.gpu
 
 
-def _worker(rank, world, uid, q):
+def _worker(rank, world, uid, q, push):
     try:
+        import os
+        os.environ["ALINK_COMM_PUSH"] = str(push)  # read once, at the first alink_comm_init of the process
         from alink_b200 import _ffi, synth
         from alink_b200.dist import shard_range
         pool = synth.make_pool(2, N=300_001)  # ragged: the shards differ in size
@@ -27,6 +29,9 @@ def _worker(rank, world, uid, q):
             got = ctx.query_sharded(0, 0, 0, np.ascontiguousarray(pool.ia[lo:hi]), np.ascontiguousarray(pool.ib[lo:hi]), hi - lo,
                                     measure, 1000, base=lo)
             out[measure] = all(np.array_equal(a, b) for a, b in zip(ref, got))
+        st = ctx.comm_push_state()  # (enabled, used): the one-launch peer push + merge of csrc/comm.cuh
+        out["push_consistent"] = st == (bool(push), bool(push))
+        print(f"rank {rank}: peer push enabled/used = {st}", flush=True)
         # a shard smaller than B: 600 pairs on rank 1, the rest on rank 0
         cut = pool.N - 600
         lo2, hi2 = (0, cut) if rank == 0 else (cut, pool.N)
@@ -55,7 +60,8 @@ def _worker(rank, world, uid, q):
         q.put((rank, None, traceback.format_exc() + str(e)))
 
 
-def test_two_ranks_merge_to_the_single_gpu_selection_without_torch_distributed():
+@pytest.mark.parametrize("push", [0, 1])  # the key exchange: ncclAllGather + merge (default) | one-launch peer push + merge
+def test_two_ranks_merge_to_the_single_gpu_selection_without_torch_distributed(push):
     import torch
     if torch.cuda.device_count() < 2:
         pytest.skip("needs two GPUs")
@@ -63,7 +69,7 @@ def test_two_ranks_merge_to_the_single_gpu_selection_without_torch_distributed()
     uid = _ffi.Context.comm_unique_id()
     mpc = mp.get_context("spawn")
     q = mpc.Queue()
-    procs = [mpc.Process(target=_worker, args=(r, 2, uid, q)) for r in range(2)]
+    procs = [mpc.Process(target=_worker, args=(r, 2, uid, q, push)) for r in range(2)]
     for p in procs:
         p.start()
     res = [q.get(timeout=600) for _ in procs]
@@ -71,4 +77,5 @@ def test_two_ranks_merge_to_the_single_gpu_selection_without_torch_distributed()
         p.join(timeout=60)
     for rank, out, err in res:
         assert err is None, f"rank {rank}: {err}"
-        assert out == {"uncertainty": True, "neg_margin": True, "small_shard": True, "rule_blind0": True, "rule_blind1": True}, (rank, out)
+        assert out == {"uncertainty": True, "neg_margin": True, "push_consistent": True, "small_shard": True, "rule_blind0": True,
+                       "rule_blind1": True}, (rank, out)
