@@ -39,7 +39,7 @@ SYMBOLS = (
     "alink_select_topk", "alink_topk_values", "alink_topk_values_noalloc", "alink_topk_keys", "alink_query", "alink_disparity_select",
     "alink_set_refine_eps", "alink_refine_stats", "alink_refine_detail", "alink_score_allpairs", "alink_query_allpairs",
     "alink_disparity_hist", "alink_disparity_select_sharded", "alink_roc_counts",
-    "alink_train_step", "alink_get_train_state", "alink_set_train_state",
+    "alink_train_step", "alink_train_epoch", "alink_get_train_state", "alink_set_train_state",
     "alink_set_refine_eps2", "alink_refine_report_get",
     "alink_perturb_rows", "alink_score_column", "alink_min_disparity",
     "alink_comm_unique_id", "alink_comm_init", "alink_comm_destroy", "alink_query_sharded", "alink_comm_push_state", "alink_disparity_select_comm",
@@ -138,6 +138,8 @@ def load():
     L.alink_set_refine_eps.argtypes = [vp, dbl]
     L.alink_refine_stats.restype = i32
     L.alink_refine_stats.argtypes = [vp, C.POINTER(i64), C.POINTER(C.c_float)]
+    L.alink_train_epoch.restype = i32
+    L.alink_train_epoch.argtypes = [vp, i32, i32, i32, i32, vp, vp, vp, i64, i32, i32, dbl, dbl, dbl, i32, vp]
     L.alink_train_step.restype = i32
     L.alink_train_step.argtypes = [vp, i32, i32, i32, i32, vp, vp, vp, i32, i32, dbl, dbl, dbl, i32,
                                    C.POINTER(C.c_float), C.POINTER(C.c_float), vp]
@@ -485,6 +487,19 @@ class Context:
                                              _ptr_space(yy)[0], nb, sp, float(lr), float(rho), float(eps), int(bool(apply)),
                                              C.byref(loss), C.byref(acc), _ptr_space(probs)[0]))
         return (float(loss.value), float(acc.value), probs) if want_probs else (float(loss.value), float(acc.value))
+
+    def train_epoch(self, group, learner, slot_a, slot_b, ia, ib, y, batch, lr=1.0, rho=0.95, eps=1e-7, apply=True):
+        """ceil(n / batch) minibatch steps enqueued back to back, one host round trip -> (loss[nbatch], acc[nbatch]);
+        bit-identical to a loop of train_step over the same batches."""
+        n = int(len(y))
+        yy = y if _is_torch(y) else _f32(y).reshape(-1)
+        sp = _space_of(ia, ib, yy)
+        nbatch = (n + int(batch) - 1) // int(batch)
+        out = np.empty((nbatch, 2), np.float32)
+        self._check(self._L.alink_train_epoch(self._h, group, learner, slot_a, slot_b, _ptr_space(ia)[0], _ptr_space(ib)[0],
+                                              _ptr_space(yy)[0], n, int(batch), sp, float(lr), float(rho), float(eps),
+                                              int(bool(apply)), _ptr_space(out)[0]))
+        return out[:, 0].copy(), out[:, 1].copy()
 
     def get_train_state(self, group, learner, which, shapes):
         """Six arrays (Keras order) of learner `learner`: which = 0 parameters, 1 Adadelta E[g^2], 2 E[dx^2]."""

@@ -1515,16 +1515,15 @@ static int ensure_opt_state(alink_ctx *ctx, HeadGroup &g) {
   return ALINK_OK;
 }
 
-int alink_train_step(alink_ctx *ctx, int group, int learner, int slot_a, int slot_b, const int32_t *ia, const int32_t *ib,
-                     const float *y, int nb, int in_space, double lr, double rho, double eps, int apply, float *loss_out,
-                     float *acc_out, float *probs_out) {
-  if (!ctx) return ALINK_E_INVALID;
+// argument checks shared by the step and the epoch call
+static int train_check(alink_ctx *ctx, int group, int learner, int slot_a, int slot_b, const int32_t *ia, const int32_t *ib,
+                       const float *y, int64_t n) {
   if (group < 0 || group >= ALINK_MAX_GROUPS || !ctx->groups[group].set)
     return alink_fail(ctx, ALINK_E_STATE, "head group %d not set (alink_set_heads)", group);
   HeadGroup &g = ctx->groups[group];
   if (learner < 0 || learner >= g.K) return alink_fail(ctx, ALINK_E_INVALID, "learner %d outside [0, %d)", learner, g.K);
   if (slot_a < 0 || slot_a >= ALINK_MAX_SLOTS || slot_b < 0 || slot_b >= ALINK_MAX_SLOTS) return alink_fail(ctx, ALINK_E_INVALID, "bad slot");
-  if (nb < 1 || nb > 65536 || !y) return alink_fail(ctx, ALINK_E_INVALID, "bad batch (nb=%d)", nb);
+  if (n < 1 || !y) return alink_fail(ctx, ALINK_E_INVALID, "bad batch (n=%lld)", (long long)n);
   if ((ia == nullptr) != (ib == nullptr)) return alink_fail(ctx, ALINK_E_INVALID, "ia and ib must both be given or both NULL");
   ALINK_TRY(table_wait(ctx, slot_a));
   ALINK_TRY(table_wait(ctx, slot_b));
@@ -1532,36 +1531,44 @@ int alink_train_step(alink_ctx *ctx, int group, int learner, int slot_a, int slo
   if (!A.p || !Bt.p) return alink_fail(ctx, ALINK_E_STATE, "embedding table slot not set (alink_set_table)");
   if (A.dtype != ALINK_F32 || Bt.dtype != ALINK_F32 || A.D != Bt.D || (g.feat_mode ? 2 * A.D : A.D) != g.D_in)
     return alink_fail(ctx, ALINK_E_INVALID, "the finetune step needs fp32 tables matching the heads' fan-in");
-  if (!ia && (nb > A.M || nb > Bt.M)) return alink_fail(ctx, ALINK_E_INVALID, "identity pairs exceed table rows");
-  ALINK_CUDA(ctx, cudaSetDevice(ctx->device));
-  ALINK_TRY(ensure_opt_state(ctx, g));
-  const void *dia, *dib, *dy;
-  ALINK_TRY(stage_in(ctx, ia, sizeof(int32_t) * (size_t)nb, in_space, ctx->idx_a, &dia));
-  ALINK_TRY(stage_in(ctx, ib, sizeof(int32_t) * (size_t)nb, in_space, ctx->idx_b, &dib));
-  ALINK_TRY(stage_in(ctx, y, sizeof(float) * (size_t)nb, in_space, ctx->train_y, &dy));
-  // workspace: X | h1 | h2 | dz1 | dz2 | dz3 | loss | acc | probs
+  if (!ia && (n > A.M || n > Bt.M)) return alink_fail(ctx, ALINK_E_INVALID, "identity pairs exceed table rows");
+  return ALINK_OK;
+}
+
+// One minibatch on the stream: forward, loss / accuracy means -> out2[0..1], and (apply) backward + Adadelta on the fp32
+// masters. dia/dib (or null = identity rows from row0) and dy are DEVICE pointers to this batch's nb entries.
+// The workspace (ctx->train_ws) must hold nb_max rows; successive batches reuse it in stream order.
+static int train_enqueue(alink_ctx *ctx, HeadGroup &g, int learner, const Table &A, const Table &Bt, const int32_t *dia,
+                         const int32_t *dib, const float *dy, int nb, double lr, double rho, double eps, int apply, float *out2,
+                         float **probs_dev) {
   const size_t nX = (size_t)nb * g.D_in, n1 = (size_t)nb * g.H1, n2 = (size_t)nb * g.H2, n3 = (size_t)nb * 2;
-  ALINK_TRY(dev_reserve(ctx, ctx->train_ws, sizeof(float) * (nX + 2 * n1 + 2 * n2 + 2 * n3 + 2 * (size_t)nb)));
-  ALINK_TRY(dev_reserve(ctx, ctx->train_out, 16));
+  // workspace: X | h1 | h2 | dz1 | dz2 | dz3 | loss | acc | probs
   float *X = (float *)ctx->train_ws.p, *h1 = X + nX, *h2 = h1 + n1, *dz1 = h2 + n2, *dz2 = dz1 + n1, *dz3 = dz2 + n2;
   float *lossv = dz3 + n3, *accv = lossv + nb, *probs = accv + nb;
+  if (probs_dev) *probs_dev = probs;
   size_t each[6];
   group_tensor_sizes(g, each);
   float *W1 = g.W1 + each[0] * learner, *b1 = g.b1 + each[1] * learner, *W2 = g.W2 + each[2] * learner;
   float *b2 = g.b2 + each[3] * learner, *W3 = g.W3 + each[4] * learner, *b3 = g.b3 + each[5] * learner;
   auto grid = [&](size_t n) { size_t b = (n + 255) / 256; return (unsigned)(b < 1 ? 1 : (b > 4096 ? 4096 : b)); };
   cudaStream_t st = ctx->stream;
-  train_feat_kernel<<<grid(nX), 256, 0, st>>>((const float *)A.p, (const float *)Bt.p, (const int32_t *)dia, (const int32_t *)dib, A.D,
+  train_feat_kernel<<<grid(nX), 256, 0, st>>>((const float *)A.p, (const float *)Bt.p, dia, dib, A.D,
                                               g.feat_mode == ALINK_FEAT_ABSDIFF_HADAMARD, nb, X);
   ALINK_LAUNCHED(ctx);
-  train_dense_fwd_kernel<<<grid(n1), 256, 0, st>>>(X, g.D_in, W1, b1, g.H1, nb, h1);
+  auto tiles = [&](int J) {
+    const long long t = (long long)((J + TD_COLS - 1) / TD_COLS) * ((nb + TD_ROWS - 1) / TD_ROWS);
+    return (unsigned)(t > 4096 ? 4096 : t);
+  };
+  train_dense_fwd_kernel<<<tiles(g.H1), 256, 0, st>>>(X, g.D_in, W1, b1, g.H1, nb, h1);
   ALINK_LAUNCHED(ctx);
-  train_dense_fwd_kernel<<<grid(n2), 256, 0, st>>>(h1, g.H1, W2, b2, g.H2, nb, h2);
+  train_dense_fwd_kernel<<<tiles(g.H2), 256, 0, st>>>(h1, g.H1, W2, b2, g.H2, nb, h2);
   ALINK_LAUNCHED(ctx);
-  train_head_kernel<<<grid(nb), 256, 0, st>>>(h2, W3, b3, g.H2, g.C, (const float *)dy, nb, lossv, accv, dz3, probs);
+  train_head_kernel<<<grid(nb), 256, 0, st>>>(h2, W3, b3, g.H2, g.C, dy, nb, lossv, accv, dz3, probs, nb <= 256 ? out2 : nullptr);
   ALINK_LAUNCHED(ctx);
-  train_mean_kernel<<<1, 32, 0, st>>>(lossv, accv, nb, (float *)ctx->train_out.p);
-  ALINK_LAUNCHED(ctx);
+  if (nb > 256) {  // (one CTA computes the means in the head kernel's tail)
+    train_mean_kernel<<<1, 32, 0, st>>>(lossv, accv, nb, out2);
+    ALINK_LAUNCHED(ctx);
+  }
   if (apply) {
     const float flr = (float)lr, frho = (float)rho, feps = (float)eps;
     train_grad_in_kernel<<<grid(n2), 256, 0, st>>>(dz3, g.C, W3, g.H2, h2, nb, dz2);
@@ -1573,36 +1580,108 @@ int alink_train_step(alink_ctx *ctx, int group, int learner, int slot_a, int slo
       oa[t] = g.opt_a[t] + each[t] * learner;
       od[t] = g.opt_d[t] + each[t] * learner;
     }
-    train_update_w_kernel<<<grid(each[4]), 256, 0, st>>>(h2, g.H2, dz3, g.C, nb, W3, oa[4], od[4], flr, frho, feps);
-    ALINK_LAUNCHED(ctx);
-    train_update_b_kernel<<<grid(each[5]), 256, 0, st>>>(dz3, g.C, nb, b3, oa[5], od[5], flr, frho, feps);
-    ALINK_LAUNCHED(ctx);
-    train_update_w_kernel<<<grid(each[2]), 256, 0, st>>>(h1, g.H1, dz2, g.H2, nb, W2, oa[2], od[2], flr, frho, feps);
-    ALINK_LAUNCHED(ctx);
-    train_update_b_kernel<<<grid(each[3]), 256, 0, st>>>(dz2, g.H2, nb, b2, oa[3], od[3], flr, frho, feps);
-    ALINK_LAUNCHED(ctx);
-    train_update_w_kernel<<<grid(each[0]), 256, 0, st>>>(X, g.D_in, dz1, g.H1, nb, W1, oa[0], od[0], flr, frho, feps);
-    ALINK_LAUNCHED(ctx);
-    train_update_b_kernel<<<grid(each[1]), 256, 0, st>>>(dz1, g.H1, nb, b1, oa[1], od[1], flr, frho, feps);
-    ALINK_LAUNCHED(ctx);
-    // the tensor-core operand images follow the fp32 masters; the half-overflow bound is recomputed by the next
-    // alink_set_heads (until then FP32_REFINE filters with bf16)
-    if (g.W1t) {
-      tc::prep_w1_kernel<false><<<ctx->sm_count * 4, 256, 0, st>>>(g.W1, (uint8_t *)g.W1t, g.K, g.D_in, g.H1);
-      ALINK_LAUNCHED(ctx);
-      tc::prep_w2_kernel<false><<<ctx->sm_count, 256, 0, st>>>(g.W2, (uint8_t *)g.W2t, g.K, g.H1, g.H2);
-      ALINK_LAUNCHED(ctx);
-      tc::prep_b1_kernel<false><<<ctx->sm_count, 256, 0, st>>>(g.b1, (uint8_t *)g.W2t + (size_t)g.K * g.H1 * g.H2 * 2, g.K, g.H1);
-      ALINK_LAUNCHED(ctx);
+    // the six gradient + Adadelta updates in one launch (train_update_all_kernel: same arithmetic per element)
+    TrainUpdArgs ua;
+    memset(&ua, 0, sizeof(ua));
+    ua.A[0] = X; ua.dZ[0] = dz1; ua.Kd[0] = g.D_in; ua.J[0] = g.H1; ua.W[0] = W1; ua.b[0] = b1;
+    ua.A[1] = h1; ua.dZ[1] = dz2; ua.Kd[1] = g.H1; ua.J[1] = g.H2; ua.W[1] = W2; ua.b[1] = b2;
+    ua.A[2] = h2; ua.dZ[2] = dz3; ua.Kd[2] = g.H2; ua.J[2] = g.C; ua.W[2] = W3; ua.b[2] = b3;
+    for (int l = 0; l < 3; ++l) {
+      ua.ag_w[l] = oa[2 * l]; ua.ad_w[l] = od[2 * l];
+      ua.ag_b[l] = oa[2 * l + 1]; ua.ad_b[l] = od[2 * l + 1];
     }
-    g.bounds_stale = true;
+    ua.nb = nb; ua.lr = flr; ua.rho = frho; ua.eps = feps;
+    train_update_all_kernel<<<grid(each[0] + each[1] + each[2] + each[3] + each[4] + each[5]), 256, 0, st>>>(ua);
+    ALINK_LAUNCHED(ctx);
   }
+  return ALINK_OK;
+}
+
+// the tensor-core operand images follow the fp32 masters; the half-overflow bound is recomputed by the next
+// alink_set_heads (until then FP32_REFINE filters with bf16)
+static int train_refresh_images(alink_ctx *ctx, HeadGroup &g) {
+  cudaStream_t st = ctx->stream;
+  if (g.W1t) {
+    tc::prep_w1_kernel<false><<<ctx->sm_count * 4, 256, 0, st>>>(g.W1, (uint8_t *)g.W1t, g.K, g.D_in, g.H1);
+    ALINK_LAUNCHED(ctx);
+    tc::prep_w2_kernel<false><<<ctx->sm_count, 256, 0, st>>>(g.W2, (uint8_t *)g.W2t, g.K, g.H1, g.H2);
+    ALINK_LAUNCHED(ctx);
+    tc::prep_b1_kernel<false><<<ctx->sm_count, 256, 0, st>>>(g.b1, (uint8_t *)g.W2t + (size_t)g.K * g.H1 * g.H2 * 2, g.K, g.H1);
+    ALINK_LAUNCHED(ctx);
+  }
+  g.bounds_stale = true;
+  return ALINK_OK;
+}
+
+static size_t train_ws_floats(const HeadGroup &g, size_t nb) {
+  return nb * g.D_in + 2 * nb * g.H1 + 2 * nb * g.H2 + 2 * nb * 2 + 2 * nb;
+}
+
+int alink_train_step(alink_ctx *ctx, int group, int learner, int slot_a, int slot_b, const int32_t *ia, const int32_t *ib,
+                     const float *y, int nb, int in_space, double lr, double rho, double eps, int apply, float *loss_out,
+                     float *acc_out, float *probs_out) {
+  if (!ctx) return ALINK_E_INVALID;
+  if (nb > 65536) return alink_fail(ctx, ALINK_E_INVALID, "bad batch (nb=%d)", nb);
+  ALINK_TRY(train_check(ctx, group, learner, slot_a, slot_b, ia, ib, y, nb));
+  HeadGroup &g = ctx->groups[group];
+  const Table &A = ctx->tables[slot_a], &Bt = ctx->tables[slot_b];
+  ALINK_CUDA(ctx, cudaSetDevice(ctx->device));
+  ALINK_TRY(ensure_opt_state(ctx, g));
+  const void *dia, *dib, *dy;
+  ALINK_TRY(stage_in(ctx, ia, sizeof(int32_t) * (size_t)nb, in_space, ctx->idx_a, &dia));
+  ALINK_TRY(stage_in(ctx, ib, sizeof(int32_t) * (size_t)nb, in_space, ctx->idx_b, &dib));
+  ALINK_TRY(stage_in(ctx, y, sizeof(float) * (size_t)nb, in_space, ctx->train_y, &dy));
+  ALINK_TRY(dev_reserve(ctx, ctx->train_ws, sizeof(float) * train_ws_floats(g, (size_t)nb)));
+  ALINK_TRY(dev_reserve(ctx, ctx->train_out, 16));
+  float *probs = nullptr;
+  ALINK_TRY(train_enqueue(ctx, g, learner, A, Bt, (const int32_t *)dia, (const int32_t *)dib, (const float *)dy, nb, lr, rho, eps,
+                          apply, (float *)ctx->train_out.p, &probs));
+  if (apply) ALINK_TRY(train_refresh_images(ctx, g));
+  cudaStream_t st = ctx->stream;
   float hout[2] = {0, 0};
   ALINK_CUDA(ctx, cudaMemcpyAsync(hout, ctx->train_out.p, 8, cudaMemcpyDeviceToHost, st));
   if (probs_out) ALINK_CUDA(ctx, cudaMemcpyAsync(probs_out, probs, sizeof(float) * (size_t)nb * g.C, cudaMemcpyDeviceToHost, st));
   ALINK_CUDA(ctx, cudaStreamSynchronize(st));
   if (loss_out) *loss_out = hout[0];
   if (acc_out) *acc_out = hout[1];
+  return ALINK_OK;
+}
+
+// A whole pass over n pairs in minibatches of `batch` (the last one ragged), WITHOUT a host round trip per batch: the
+// indices and labels cross PCIe once, the ceil(n / batch) steps are enqueued back to back — the same kernels in the same
+// order as alink_train_step, so parameters, accumulators and every batch's loss are bit-identical to the step loop —
+// the tensor-core images are refreshed once, and the per-batch (loss, accuracy) pairs come back in one copy.
+int alink_train_epoch(alink_ctx *ctx, int group, int learner, int slot_a, int slot_b, const int32_t *ia, const int32_t *ib,
+                      const float *y, int64_t n, int batch, int in_space, double lr, double rho, double eps, int apply,
+                      float *loss_acc_out) {
+  if (!ctx) return ALINK_E_INVALID;
+  if (batch < 1 || batch > 65536) return alink_fail(ctx, ALINK_E_INVALID, "bad batch size %d", batch);
+  if (n > (1ll << 30)) return alink_fail(ctx, ALINK_E_INVALID, "n too large");
+  ALINK_TRY(train_check(ctx, group, learner, slot_a, slot_b, ia, ib, y, n));
+  HeadGroup &g = ctx->groups[group];
+  const Table &A = ctx->tables[slot_a], &Bt = ctx->tables[slot_b];
+  if (!ia) return alink_fail(ctx, ALINK_E_INVALID, "alink_train_epoch needs explicit pair indices");
+  ALINK_CUDA(ctx, cudaSetDevice(ctx->device));
+  ALINK_TRY(ensure_opt_state(ctx, g));
+  const void *dia, *dib, *dy;
+  ALINK_TRY(stage_in(ctx, ia, sizeof(int32_t) * (size_t)n, in_space, ctx->idx_a, &dia));
+  ALINK_TRY(stage_in(ctx, ib, sizeof(int32_t) * (size_t)n, in_space, ctx->idx_b, &dib));
+  ALINK_TRY(stage_in(ctx, y, sizeof(float) * (size_t)n, in_space, ctx->train_y, &dy));
+  const int64_t nbatch = (n + batch - 1) / batch;
+  ALINK_TRY(dev_reserve(ctx, ctx->train_ws, sizeof(float) * train_ws_floats(g, (size_t)(batch < n ? batch : n))));
+  ALINK_TRY(dev_reserve(ctx, ctx->train_out, sizeof(float) * 2 * (size_t)nbatch));
+  float *out = (float *)ctx->train_out.p;
+  for (int64_t b = 0; b < nbatch; ++b) {
+    const int64_t lo = b * batch;
+    const int nb = (int)(n - lo < batch ? n - lo : batch);
+    ALINK_TRY(train_enqueue(ctx, g, learner, A, Bt, (const int32_t *)dia + lo, (const int32_t *)dib + lo, (const float *)dy + lo, nb,
+                            lr, rho, eps, apply, out + 2 * b, nullptr));
+  }
+  if (apply) ALINK_TRY(train_refresh_images(ctx, g));
+  if (loss_acc_out) {
+    ALINK_CUDA(ctx, cudaMemcpyAsync(loss_acc_out, out, sizeof(float) * 2 * (size_t)nbatch, cudaMemcpyDeviceToHost, ctx->stream));
+  }
+  ALINK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
   return ALINK_OK;
 }
 

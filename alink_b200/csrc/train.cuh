@@ -27,16 +27,46 @@ __global__ void __launch_bounds__(256) train_feat_kernel(const float *__restrict
   }
 }
 
-// out[n][j] = act(sum_k X[n][k] W[k][j] + b[j]); one thread per output, k ascending (the oracle's chain)
+// out[n][j] = act(sum_k X[n][k] W[k][j] + b[j]); one thread per output, k ascending (the oracle's chain, bit-identical).
+// A CTA owns an 8-row x 32-column tile of the output and walks k in slabs of 64 staged in shared memory: the slab's loads
+// (8 coalesced weight loads + 2 input loads per thread) are all in flight together, so a slab costs ONE L2 latency instead
+// of one per FMA — with a load in front of every FMA of the chain the layer took ~45 us for a batch of 16 (round 2: 5 us).
+constexpr int TD_ROWS = 8, TD_COLS = 32, TD_K = 64;
 __global__ void __launch_bounds__(256) train_dense_fwd_kernel(const float *__restrict__ X, int Kd, const float *__restrict__ W,
                                                               const float *__restrict__ b, int J, int nb, float *__restrict__ out) {
-  for (int e = blockIdx.x * 256 + threadIdx.x; e < nb * J; e += gridDim.x * 256) {
-    const int n = e / J, j = e - n * J;
-    const float *x = X + (size_t)n * Kd;
+  __shared__ float sW[TD_K][TD_COLS];
+  __shared__ float sX[TD_ROWS][TD_K];
+  const int c = threadIdx.x & 31, r = threadIdx.x >> 5;
+  const int ntj = (J + TD_COLS - 1) / TD_COLS, ntn = (nb + TD_ROWS - 1) / TD_ROWS;
+  for (int tile = blockIdx.x; tile < ntj * ntn; tile += gridDim.x) {
+    const int j0 = (tile % ntj) * TD_COLS, n0 = (tile / ntj) * TD_ROWS;
+    const int j = j0 + c, n = n0 + r;
     float acc = 0.0f;
-    for (int k = 0; k < Kd; ++k) acc = __fmaf_rn(x[k], W[(size_t)k * J + j], acc);
-    acc = __fadd_rn(acc, b[j]);
-    out[e] = acc > 0.0f ? acc : 0.0f;
+    for (int k0 = 0; k0 < Kd; k0 += TD_K) {
+      const int kk = Kd - k0 < TD_K ? Kd - k0 : TD_K;
+#pragma unroll
+      for (int i = 0; i < TD_K / TD_ROWS; ++i) {
+        const int k = r + TD_ROWS * i;
+        sW[k][c] = (k < kk && j < J) ? __ldg(W + (size_t)(k0 + k) * J + j) : 0.0f;
+      }
+#pragma unroll
+      for (int i = 0; i < TD_ROWS * TD_K / 256; ++i) {
+        const int idx = threadIdx.x + 256 * i, rr = idx / TD_K, k = idx - rr * TD_K;
+        sX[rr][k] = (k < kk && n0 + rr < nb) ? X[(size_t)(n0 + rr) * Kd + k0 + k] : 0.0f;
+      }
+      __syncthreads();
+      if (kk == TD_K) {
+#pragma unroll 16
+        for (int k = 0; k < TD_K; ++k) acc = __fmaf_rn(sX[r][k], sW[k][c], acc);
+      } else {
+        for (int k = 0; k < kk; ++k) acc = __fmaf_rn(sX[r][k], sW[k][c], acc);
+      }
+      __syncthreads();
+    }
+    if (n < nb && j < J) {
+      acc = __fadd_rn(acc, b[j]);
+      out[(size_t)n * J + j] = acc > 0.0f ? acc : 0.0f;
+    }
   }
 }
 
@@ -44,7 +74,8 @@ __global__ void __launch_bounds__(256) train_dense_fwd_kernel(const float *__res
 __global__ void __launch_bounds__(256) train_head_kernel(const float *__restrict__ h2, const float *__restrict__ W3,
                                                          const float *__restrict__ b3, int H2, int C, const float *__restrict__ y,
                                                          int nb, float *__restrict__ loss, float *__restrict__ acc,
-                                                         float *__restrict__ dz3, float *__restrict__ probs) {
+                                                         float *__restrict__ dz3, float *__restrict__ probs,
+                                                         float *__restrict__ mean_out = nullptr) {
   const float inv_nb = __fdiv_rn(1.0f, (float)nb);
   for (int n = blockIdx.x * 256 + threadIdx.x; n < nb; n += gridDim.x * 256) {
     const float *h = h2 + (size_t)n * H2;
@@ -65,6 +96,18 @@ __global__ void __launch_bounds__(256) train_head_kernel(const float *__restrict
       else probs[n] = p1;
     }
   }
+  if (mean_out) {  // single-CTA launches (nb <= 256): the batch means in the same launch, same sequential sums as train_mean_kernel
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      float sl = 0.0f, sa = 0.0f;
+      for (int n = 0; n < nb; ++n) {
+        sl = __fadd_rn(sl, loss[n]);
+        sa = __fadd_rn(sa, acc[n]);
+      }
+      mean_out[0] = __fdiv_rn(sl, (float)nb);
+      mean_out[1] = __fdiv_rn(sa, (float)nb);
+    }
+  }
 }
 
 // gradient w.r.t. a relu layer's pre-activation: out[n][k] = act[n][k] > 0 ? sum_j dZ[n][j] W[k][j] : 0 (j ascending)
@@ -81,32 +124,45 @@ __global__ void __launch_bounds__(256) train_grad_in_kernel(const float *__restr
   }
 }
 
-// weight gradient + Adadelta in one pass: g[k][j] = sum_n A[n][k] dZ[n][j] (n ascending), then the update
-__global__ void __launch_bounds__(256) train_update_w_kernel(const float *__restrict__ A, int Kd, const float *__restrict__ dZ, int J,
-                                                             int nb, float *__restrict__ W, float *__restrict__ acc_g,
-                                                             float *__restrict__ acc_d, float lr, float rho, float eps) {
-  for (int e = blockIdx.x * 256 + threadIdx.x; e < Kd * J; e += gridDim.x * 256) {
-    const int k = e / J, j = e - k * J;
-    float g = 0.0f;
-    for (int n = 0; n < nb; ++n) g = __fmaf_rn(A[(size_t)n * Kd + k], dZ[(size_t)n * J + j], g);
-    float a = acc_g[e], d = acc_d[e];
-    W[e] = alink_adadelta(W[e], g, &a, &d, lr, rho, eps);
-    acc_g[e] = a;
-    acc_d[e] = d;
-  }
-}
+// All six tensors' gradients + Adadelta updates in ONE launch (they are independent of each other once dz1..dz3 exist):
+// a flat index over [W | b] of the three layers. Weights: g[k][j] = sum_n A[n][k] dZ[n][j] (n ascending, fma chain), biases:
+// g[j] = sum_n dZ[n][j] (n ascending), then alink_adadelta on the fp32 master and its two accumulators — per element exactly
+// what the six separate launches of round 1 computed (bit-identical; tests/test_train_step.py against the oracle).
+struct TrainUpdArgs {
+  const float *A[3];   // layer input  [nb][Kd]
+  const float *dZ[3];  // d loss / d pre-activation [nb][J]
+  int Kd[3], J[3];
+  float *W[3], *b[3], *ag_w[3], *ad_w[3], *ag_b[3], *ad_b[3];
+  int nb;
+  float lr, rho, eps;
+};
 
-// bias gradient (sum over the batch, n ascending) + Adadelta
-__global__ void __launch_bounds__(256) train_update_b_kernel(const float *__restrict__ dZ, int J, int nb, float *__restrict__ b,
-                                                             float *__restrict__ acc_g, float *__restrict__ acc_d, float lr,
-                                                             float rho, float eps) {
-  for (int j = blockIdx.x * 256 + threadIdx.x; j < J; j += gridDim.x * 256) {
-    float g = 0.0f;
-    for (int n = 0; n < nb; ++n) g = __fadd_rn(g, dZ[(size_t)n * J + j]);
-    float a = acc_g[j], d = acc_d[j];
-    b[j] = alink_adadelta(b[j], g, &a, &d, lr, rho, eps);
-    acc_g[j] = a;
-    acc_d[j] = d;
+__global__ void __launch_bounds__(256) train_update_all_kernel(const TrainUpdArgs a) {
+  const long long n0 = (long long)a.Kd[0] * a.J[0] + a.J[0], n1 = (long long)a.Kd[1] * a.J[1] + a.J[1],
+                  n2 = (long long)a.Kd[2] * a.J[2] + a.J[2];
+  for (long long f = (long long)blockIdx.x * 256 + threadIdx.x; f < n0 + n1 + n2; f += (long long)gridDim.x * 256) {
+    const int l = f < n0 ? 0 : (f < n0 + n1 ? 1 : 2);
+    const long long e = f - (l == 0 ? 0 : (l == 1 ? n0 : n0 + n1));
+    const int Kd = a.Kd[l], J = a.J[l];
+    const float *dZ = a.dZ[l];
+    if (e < (long long)Kd * J) {
+      const int k = (int)(e / J), j = (int)(e - (long long)k * J);
+      const float *A = a.A[l];
+      float g = 0.0f;
+      for (int n = 0; n < a.nb; ++n) g = __fmaf_rn(A[(size_t)n * Kd + k], dZ[(size_t)n * J + j], g);
+      float ga = a.ag_w[l][e], d = a.ad_w[l][e];
+      a.W[l][e] = alink_adadelta(a.W[l][e], g, &ga, &d, a.lr, a.rho, a.eps);
+      a.ag_w[l][e] = ga;
+      a.ad_w[l][e] = d;
+    } else {
+      const int j = (int)(e - (long long)Kd * J);
+      float g = 0.0f;
+      for (int n = 0; n < a.nb; ++n) g = __fadd_rn(g, dZ[(size_t)n * J + j]);
+      float ga = a.ag_b[l][j], d = a.ad_b[l][j];
+      a.b[l][j] = alink_adadelta(a.b[l][j], g, &ga, &d, a.lr, a.rho, a.eps);
+      a.ag_b[l][j] = ga;
+      a.ad_b[l][j] = d;
+    }
   }
 }
 

@@ -101,7 +101,8 @@ class SiameseNetwork:
         patience=5, min_lr=0.01)])` with Adadelta(self.learningRate, rho 0.95, epsilon 1e-8) and binary cross-entropy. [external: Keras 2.1.2
         fit semantics] the LAST `validation_split` of the samples is held out, the rest is reshuffled every epoch
         with np.random.shuffle (seeded by the driver, code/ALINK.py:19) and cut into batches of `batch_size`.
-        Every batch is one `alink_train_step` on device-resident weights; returns a Keras-History-like dict."""
+        Every pass is one `alink_train_epoch` (= the batches' `alink_train_step`s back to back) on device-resident weights;
+        returns a Keras-History-like dict."""
         from . import _ffi
         XL, XR = engine._as_pair(self.preprocess(X))
         y = np.asarray(Y, dtype=np.float32).reshape(-1)
@@ -126,13 +127,18 @@ class SiameseNetwork:
         rl_best, rl_wait = np.inf, 0
 
         def run(idx, apply):
+            if not len(idx):
+                return float("nan"), float("nan")
+            idx = np.ascontiguousarray(idx, dtype=np.int32)
+            # one call per pass: the batches are enqueued back to back on the device (alink_train_epoch), bit-identical
+            # to a loop of alink_train_step; the sample-weighted means are formed here as Keras' fit loop forms them
+            ls, accs = ctx.train_epoch(g, 0, sa, sb, idx, idx, y[idx], batch_size, lr=lr, eps=ADADELTA_EPS, apply=apply)
             tot_l = tot_a = 0.0
-            for lo in range(0, len(idx), batch_size):
-                b = np.ascontiguousarray(idx[lo:lo + batch_size])
-                l, a = ctx.train_step(g, 0, sa, sb, b, b, y[b], lr=lr, eps=ADADELTA_EPS, apply=apply)
-                tot_l += l * len(b)
-                tot_a += a * len(b)
-            return (tot_l / len(idx), tot_a / len(idx)) if len(idx) else (float("nan"), float("nan"))
+            for i, lo in enumerate(range(0, len(idx), batch_size)):
+                nb = min(batch_size, len(idx) - lo)
+                tot_l += float(ls[i]) * nb
+                tot_a += float(accs[i]) * nb
+            return tot_l / len(idx), tot_a / len(idx)
 
         order = tr_idx.copy()  # Keras' _fit_loop shuffles ONE index_array in place, epoch after epoch [external: Keras 2.1.2]
         for epoch in range(int(epochs)):

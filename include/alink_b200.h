@@ -264,6 +264,14 @@ int alink_disparity_select_sharded(alink_ctx *ctx, const float *p2, const float 
 int alink_train_step(alink_ctx *ctx, int group, int learner, int slot_a, int slot_b, const int32_t *ia,
                      const int32_t *ib, const float *y, int nb, int in_space, double lr, double rho, double eps,
                      int apply, float *loss_out, float *acc_out, float *probs_out);
+/* A whole pass over n pairs in minibatches of `batch` (the last one ragged) without a host round trip per batch: what
+ * Keras' fit loop does per epoch (code/siamese.py:52-58 -> fit(batch_size=16); apply = 0: the validation pass). Same
+ * kernels in the same order as alink_train_step, so parameters, accumulators and every batch's loss are bit-identical
+ * to the step loop. ia, ib, y: n entries in the epoch's (shuffled) order, in_space as usual; loss_acc_out: host
+ * [ceil(n / batch)][2] = each batch's (mean loss, mean accuracy), or NULL. */
+int alink_train_epoch(alink_ctx *ctx, int group, int learner, int slot_a, int slot_b, const int32_t *ia,
+                      const int32_t *ib, const float *y, int64_t n, int batch, int in_space, double lr, double rho,
+                      double eps, int apply, float *loss_acc_out);
 int alink_get_train_state(alink_ctx *ctx, int group, int learner, int which, float *const *host_out);
 int alink_set_train_state(alink_ctx *ctx, int group, int learner, int which, const float *const *host_in);
 

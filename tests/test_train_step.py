@@ -177,3 +177,46 @@ def test_teach_runs_the_finetune_step_like_existing_al():
     assert not np.array_equal(nets[0].get_weights()[0], nets[1].get_weights()[0])  # different bootstraps
     p = com.predict_proba([XL, XR])
     assert p.shape == (400, 2)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("act", ["softmax", "sigmoid"])
+def test_train_epoch_equals_the_step_loop_bit_for_bit(ctx, act):
+    """alink_train_epoch = the batches' alink_train_steps enqueued back to back (one host round trip per pass instead of
+    one per batch): per-batch losses / accuracies, parameters and both Adadelta accumulators must be bit-identical,
+    with a ragged last batch, for the training pass and the evaluation pass (apply = 0)."""
+    import time
+    from alink_b200 import _ffi
+    n, batch = 203, 16
+    pool, _, params = _setup(act, n)
+    y = np.asarray(pool.genuine[:n], dtype=np.float32)
+    ia, ib = pool.ia[:n].copy(), pool.ib[:n].copy()
+    shapes = [p.shape for p in params]
+    ctx.set_table(0, pool.table)
+    state = {}
+    for how in ("steps", "epoch"):
+        ctx.set_heads(3, pool.heads, compute=_ffi.FP32_EXACT)  # fresh weights, zero accumulators
+        t0 = time.perf_counter()
+        for _ in range(2):
+            if how == "steps":
+                la = [ctx.train_step(3, 0, 0, 0, ia[lo:lo + batch].copy(), ib[lo:lo + batch].copy(), y[lo:lo + batch], lr=0.1)
+                      for lo in range(0, n, batch)]
+                ls, accs = np.float32([v[0] for v in la]), np.float32([v[1] for v in la])
+            else:
+                ls, accs = ctx.train_epoch(3, 0, 0, 0, ia, ib, y, batch, lr=0.1)
+        dt = (time.perf_counter() - t0) / 2
+        if how == "steps":
+            ev = [ctx.train_step(3, 0, 0, 0, ia[lo:lo + batch].copy(), ib[lo:lo + batch].copy(), y[lo:lo + batch], apply=False)
+                  for lo in range(0, n, batch)]
+            evl = np.float32([v[0] for v in ev])
+        else:
+            evl, _ = ctx.train_epoch(3, 0, 0, 0, ia, ib, y, batch, apply=False)
+        state[how] = (ls, accs, evl, [ctx.get_train_state(3, 0, w, shapes) for w in (0, 1, 2)])
+        print(f"{how}: {dt * 1e3:.2f} ms per pass of {len(ls)} batches ({dt * 1e6 / len(ls):.0f} us per batch)")
+    a, b = state["steps"], state["epoch"]
+    assert len(b[0]) == (n + batch - 1) // batch
+    for i in range(3):
+        np.testing.assert_array_equal(a[i].view(np.uint32), b[i].view(np.uint32))
+    for wa, wb in zip(a[3], b[3]):
+        for x, z in zip(wa, wb):
+            np.testing.assert_array_equal(x.view(np.uint32), z.view(np.uint32))
