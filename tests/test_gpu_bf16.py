@@ -110,7 +110,11 @@ def test_refine_selection_is_bit_identical_to_fp32(ctx, oracle, measure):
     np.testing.assert_array_equal(idx, ridx)
     np.testing.assert_array_equal(util.view(np.uint32), rutil.view(np.uint32))
     if measure == "vote_entropy":
-        assert survivors == 0  # discrete plateaus: runs fully exact
+        # the vote filter (refine.cuh): only pairs whose votes stayed uncertain after the split stage are re-scored exactly
+        rep = ctx.refine_report()
+        assert rep["version"] == 2 and rep["fallback"] == 0 and rep["rounds"] == 1, rep
+        assert 0 <= survivors < 0.01 * pool.N and 0 < rep["n_stage2"] < 0.25 * pool.N
+        assert rep["err1_max"] <= rep["eps1_used"] and rep["err2_max"] <= rep["eps2_used"]
     else:
         assert pool.B <= survivors < pool.N
         scale = {"uncertainty": 1.0, "neg_margin": 2.0, "entropy": 1.25, "consensus_entropy": 1.25, "kl_max": 5.0}[measure]
