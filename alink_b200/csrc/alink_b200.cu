@@ -88,6 +88,8 @@ int alink_destroy(alink_ctx *ctx) {
                       &ctx->de.ib, &ctx->de.consts, &ctx->de.aux};
   for (DevBuf *b : debufs) dev_release(*b);
   if (ctx->rs_host) cudaFreeHost(ctx->rs_host);
+  if (ctx->comm_status) cudaFree(ctx->comm_status);
+  if (ctx->comm_host) cudaFreeHost(ctx->comm_host);
   if (ctx->comm && nccl_api()) nccl_api()->CommDestroy((alink_nccl_comm)ctx->comm);
   push_teardown(ctx);
   dev_release(ctx->comm_keys);
@@ -861,6 +863,29 @@ static double refine_worst_eps(const HeadGroup &g, double xmax, double xnorm, bo
   return z * s2 * g.w3_gain * 0.25;
 }
 
+// the report of a three-stage query from its statistics words (after the synchronisation that brought them)
+static void refine_fill_report(alink_ctx *ctx, const unsigned int *h, double eps1, double eps2, int round) {
+  float e1, e2, ea;
+  double ss1, ss2;
+  memcpy(&e1, h + RS_ERR1, 4);
+  memcpy(&e2, h + RS_ERR2, 4);
+  memcpy(&ea, h + RS_ERRA, 4);
+  memcpy(&ss2, h + RS_SS2, 8);
+  memcpy(&ss1, h + RS_SS1, 8);
+  ctx->refine_survivors = h[RS_N2];
+  ctx->refine_n1 = h[RS_N1];
+  ctx->refine_nsample = (int64_t)h[RS_M1] - (int64_t)h[RS_N1];
+  ctx->refine_nsample2 = (int64_t)h[RS_M2] - (int64_t)h[RS_N2];
+  ctx->refine_err1 = e1;
+  ctx->refine_err2 = e2;
+  ctx->refine_max_err = ea > e1 ? ea : e1;                       // the stage-1 filter's largest observed error
+  ctx->refine_rms_err = h[RS_N1] ? (float)sqrt(ss1 / (double)h[RS_N1]) : 0.0f;
+  ctx->refine_rms2 = h[RS_M2] ? (float)sqrt(ss2 / (double)h[RS_M2]) : 0.0f;
+  ctx->refine_eps_used = eps1;
+  ctx->refine_eps2_used = eps2;
+  ctx->refine_rounds = round;
+}
+
 // FP32_REFINE in three stages with device-resident counts (refine.cuh): ONE host synchronisation, at the end, which
 // brings the result and 64 bytes of statistics. Emits the selection itself; falls back to refine_query (filter +
 // FFMA, host-sized grids) for shapes the split kernel does not take, B > 4096, or when a candidate list overflows.
@@ -928,7 +953,7 @@ static int refine_query_v2(alink_ctx *ctx, const HeadGroup &g, Table &A, Table &
   if (!ctx->rs_host) ALINK_CUDA(ctx, cudaMallocHost((void **)&ctx->rs_host, RS_WORDS * sizeof(unsigned int)));
   float *util_a = (float *)ctx->util.p;
   SelectState *st = (SelectState *)ctx->sel_state.p + 1;
-  unsigned int *rs = (unsigned int *)ctx->rstat.p + 240;    // 16 statistics words, then 3 x 2048 histogram counters
+  unsigned int *rs = (unsigned int *)ctx->rstat.p + 224;    // 32 statistics words, then 3 x 2048 histogram counters
   unsigned int *hist = (unsigned int *)ctx->rstat.p + 256;
   static const int coop_env = [] { const char *e = getenv("ALINK_REFINE_COOP"); return e ? atoi(e) : 1; }();
   static int coop_blocks_per_sm = -1;
@@ -1051,31 +1076,29 @@ static int refine_query_v2(alink_ctx *ctx, const HeadGroup &g, Table &A, Table &
     topk_small_kernel<<<1, 1024, 0, ctx->stream>>>(csrc, (int)cap2, (int)B, (int)(npad < 2 ? 2 : npad), (uint64_t *)ctx->sel_keys.p,
                                                    rs + RS_N2);
     ALINK_LAUNCHED(ctx);
+    if (ctx->defer_req) {
+      // a sharded step does not stop here: the verdict is evaluated on the device and travels with the keys
+      // (alink_query_sharded reads the statistics with the merged result and calls refine_fill_report)
+      VerifyConsts vc{eps1, eps2, scv, band_on ? expm1(ezk * eps1) : -1.0};
+      refine_verify_kernel<<<1, 32, 0, ctx->stream>>>(rs, vc);
+      ALINK_LAUNCHED(ctx);
+      ALINK_CUDA(ctx, cudaMemcpyAsync(ctx->rs_host, rs, RS_WORDS * sizeof(unsigned int), cudaMemcpyDeviceToHost, ctx->stream));
+      if (ev) ALINK_CUDA(ctx, cudaEventRecord(ev[4], ctx->stream));
+      ALINK_TRY(emit_selection(ctx, B, idx_out, util_out, keys_out, out_space));  // (device outputs: no synchronisation)
+      ctx->deferred = true;
+      ctx->defer_eps1 = eps1; ctx->defer_eps2 = eps2; ctx->defer_scv = scv;
+      ctx->defer_ok_dev = rs + RS_OK;
+      return ALINK_OK;
+    }
     ALINK_CUDA(ctx, cudaMemcpyAsync(ctx->rs_host, rs, RS_WORDS * sizeof(unsigned int), cudaMemcpyDeviceToHost, ctx->stream));
     if (ev && round == 1) ALINK_CUDA(ctx, cudaEventRecord(ev[4], ctx->stream));
     ALINK_TRY(emit_selection(ctx, B, idx_out, util_out, keys_out, out_space));
     ALINK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));  // the one host synchronisation of the step
     const unsigned int *h = ctx->rs_host;
-    float e1, e2, ea;
-    double ss2;
-    memcpy(&e1, h + RS_ERR1, 4);
-    memcpy(&e2, h + RS_ERR2, 4);
+    refine_fill_report(ctx, h, eps1, eps2, round);
+    const float e1 = ctx->refine_err1, e2 = ctx->refine_err2;
+    float ea;
     memcpy(&ea, h + RS_ERRA, 4);
-    memcpy(&ss2, h + RS_SS2, 8);
-    double ss1;
-    memcpy(&ss1, h + RS_SS1, 8);
-    ctx->refine_survivors = h[RS_N2];
-    ctx->refine_n1 = h[RS_N1];
-    ctx->refine_nsample = (int64_t)h[RS_M1] - (int64_t)h[RS_N1];
-    ctx->refine_nsample2 = (int64_t)h[RS_M2] - (int64_t)h[RS_N2];
-    ctx->refine_err1 = e1;
-    ctx->refine_err2 = e2;
-    ctx->refine_max_err = ea > e1 ? ea : e1;                       // the stage-1 filter's largest observed error
-    ctx->refine_rms_err = h[RS_N1] ? (float)sqrt(ss1 / (double)h[RS_N1]) : 0.0f;
-    ctx->refine_rms2 = h[RS_M2] ? (float)sqrt(ss2 / (double)h[RS_M2]) : 0.0f;
-    ctx->refine_eps_used = eps1;
-    ctx->refine_eps2_used = eps2;
-    ctx->refine_rounds = round;
     if (h[RS_FLAGS]) {  // a candidate list overflowed (plateaus of tied utilities): the host-sized pipeline takes any size
       ctx->refine_version = 1;
       ctx->refine_fallback = 2 + (int)(h[RS_FLAGS] & 3u);  // 3: stage-1 list, 4: stage-2 list, 5: both
@@ -1169,7 +1192,7 @@ static int refine_vote_query(alink_ctx *ctx, const HeadGroup &g, Table &A, Table
   ALINK_TRY(dev_reserve(ctx, ctx->h1ws, sizeof(float) * (size_t)rows2 * g.H1 * g.K));
   if (!ctx->rs_host) ALINK_CUDA(ctx, cudaMallocHost((void **)&ctx->rs_host, RS_WORDS * sizeof(unsigned int)));
   float *util_a = (float *)ctx->util.p, *vmin = (float *)ctx->util2.p;
-  unsigned int *rs = (unsigned int *)ctx->rstat.p + 240;
+  unsigned int *rs = (unsigned int *)ctx->rstat.p + 224;
   const double apriori = refine_model_eps(g, A, Bt, true);
   ctx->refine_eps_apriori = apriori;
   ctx->refine_eps_worst = refine_worst_eps(g, xmax, xnorm, true);
@@ -1409,6 +1432,10 @@ int alink_query(alink_ctx *ctx, int group, int slot_a, int slot_b, const int32_t
       ALINK_TRY(refine_query_v2(ctx, g, TA, TB, (const int32_t *)dia, (const int32_t *)dib, N, measure, B, base,
                                 timing ? e : nullptr, idx_out, util_out, keys_out, out_space));
     if (handled) {
+    if (ctx->deferred) {  // alink_query_sharded: no synchronisation here, the times are read with the merged result
+      if (timing) ALINK_CUDA(ctx, cudaEventRecord(e[5], ctx->stream));
+      return ALINK_OK;
+    }
     if (timing) {
       ALINK_CUDA(ctx, cudaEventRecord(e[5], ctx->stream));
       ALINK_CUDA(ctx, cudaEventSynchronize(e[5]));
@@ -1842,11 +1869,27 @@ int alink_query_sharded(alink_ctx *ctx, int group, int slot_a, int slot_b, const
   ALINK_CUDA(ctx, cudaSetDevice(ctx->device));
   const int W = ctx->comm_world;
   const int64_t bl = B < N ? B : N;  // a shard smaller than B contributes all its pairs; the rest of its slot stays 0
-  ALINK_TRY(dev_reserve(ctx, ctx->comm_keys, sizeof(uint64_t) * (size_t)B * (W + 1)));
-  uint64_t *mine = (uint64_t *)ctx->comm_keys.p, *all = mine + B;
+  // payload per rank: B keys + the verdict word (comm.cuh); slot W holds this rank's own
+  const int64_t S = B + 1;
+  ALINK_TRY(dev_reserve(ctx, ctx->comm_keys, sizeof(uint64_t) * (size_t)S * (W + 1)));
+  uint64_t *mine = (uint64_t *)ctx->comm_keys.p, *all = mine + S;
+  if (!ctx->comm_status) {
+    ALINK_CUDA(ctx, cudaMalloc((void **)&ctx->comm_status, 64));
+    ALINK_CUDA(ctx, cudaMallocHost((void **)&ctx->comm_host, 64));
+  }
+  static const int defer_env = [] { const char *e = getenv("ALINK_COMM_DEFER"); return e ? atoi(e) : 1; }();
   ALINK_CUDA(ctx, cudaMemsetAsync(mine, 0, sizeof(uint64_t) * (size_t)B, ctx->stream));  // key 0 sorts below every real key
-  if (bl > 0)
-    ALINK_TRY(alink_query(ctx, group, slot_a, slot_b, ia, ib, N, in_space, measure, bl, base, nullptr, nullptr, mine, ALINK_DEVICE, timing));
+  const int64_t l0 = ctx->launches;
+  ctx->deferred = false;
+  if (bl > 0) {
+    // FP32_REFINE: enqueue the three stages WITHOUT their host synchronisation; the verdict is left on the device
+    ctx->defer_req = defer_env != 0 && !(ctx->push_ok && B <= PUSH_MAX_B);
+    const int rc = alink_query(ctx, group, slot_a, slot_b, ia, ib, N, in_space, measure, bl, base, nullptr, nullptr, mine, ALINK_DEVICE, timing);
+    ctx->defer_req = false;
+    ALINK_TRY(rc);
+  }
+  const bool deferred = ctx->deferred;
+  ctx->deferred = false;
   ctx->push_used = 0;
   if (ctx->push_ok && B <= PUSH_MAX_B) {
     // exchange + merge in ONE launch over the peers' mapped windows (comm.cuh)
@@ -1868,10 +1911,45 @@ int alink_query_sharded(alink_ctx *ctx, int group, int slot_a, int slot_b, const
       return alink_fail(ctx, ALINK_E_CUDA, "peer push: a rank did not arrive within 2 s (epoch %llu)", ctx->push_epoch);
     return ALINK_OK;
   }
-  ALINK_NCCL(ctx, api, api->AllGather(mine, all, (size_t)B, ALINK_NCCL_UINT64, (alink_nccl_comm)ctx->comm, ctx->stream));
-  ctx->launches++;  // the collective's kernel
-  KeySrc src{nullptr, all, 0, nullptr};
-  ALINK_TRY(topk_device(ctx, src, (int64_t)B * W, B));
+  // keys + verdict -> ncclAllGather -> every rank reduces the W verdicts to the same all_ok and merges
+  auto exchange = [&](const unsigned int *ok_dev) -> int {
+    comm_flag_kernel<<<1, 32, 0, ctx->stream>>>(mine + B, ok_dev);
+    ALINK_LAUNCHED(ctx);
+    ALINK_NCCL(ctx, api, api->AllGather(mine, all, (size_t)S, ALINK_NCCL_UINT64, (alink_nccl_comm)ctx->comm, ctx->stream));
+    ctx->launches++;  // the collective's kernel
+    comm_flags_reduce_kernel<<<1, 32, 0, ctx->stream>>>(all, W, (int)S, (int)B, ctx->comm_status);
+    ALINK_LAUNCHED(ctx);
+    KeySrc src{nullptr, all, 0, nullptr};
+    ALINK_TRY(topk_device(ctx, src, S * W, B));
+    ALINK_CUDA(ctx, cudaMemcpyAsync(ctx->comm_host, ctx->comm_status, 8, cudaMemcpyDeviceToHost, ctx->stream));
+    return ALINK_OK;
+  };
+  ALINK_TRY(exchange(deferred ? ctx->defer_ok_dev : nullptr));
+  // ONE synchronisation: results, statistics and every rank's verdict arrive together. Every rank reads all_ok, deferred or
+  // not (a short shard runs exact and always reports ok) — the ranks must agree on whether the exchange is repeated.
+  cudaEvent_t *e = ctx->ev;
+  if (timing && deferred) ALINK_CUDA(ctx, cudaEventRecord(e[6], ctx->stream));
+  ALINK_TRY(emit_selection(ctx, B, idx_out, util_out, keys_out, out_space));
+  ALINK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  if (deferred) refine_fill_report(ctx, ctx->rs_host, ctx->defer_eps1, ctx->defer_eps2, 1);
+  if (timing && deferred) {
+    cudaEventElapsedTime(&timing->ms_h2d, e[0], e[1]);
+    cudaEventElapsedTime(&timing->ms_score, e[1], e[2]);
+    cudaEventElapsedTime(&timing->ms_utility, e[2], e[3]);
+    cudaEventElapsedTime(&timing->ms_select, e[3], e[4]);
+    cudaEventElapsedTime(&timing->ms_d2h, e[4], e[6]);  // (here: verdict + exchange + merge)
+    cudaEventElapsedTime(&timing->ms_total, e[0], e[6]);
+    timing->launches = ctx->launches - l0;
+  }
+  if (ctx->comm_host[1]) return ALINK_OK;
+  // Some rank's verification failed (every rank sees the same W verdicts, so every rank is here): that rank repeats its
+  // query the ordinary way — widened bounds or the exact pipeline, synchronising as often as it needs — the others keep
+  // their keys, and the exchange is repeated.
+  if (deferred && !ctx->rs_host[RS_OK] && bl > 0) {
+    ALINK_CUDA(ctx, cudaMemsetAsync(mine, 0, sizeof(uint64_t) * (size_t)B, ctx->stream));
+    ALINK_TRY(alink_query(ctx, group, slot_a, slot_b, ia, ib, N, in_space, measure, bl, base, nullptr, nullptr, mine, ALINK_DEVICE, nullptr));
+  }
+  ALINK_TRY(exchange(nullptr));
   return emit_selection(ctx, B, idx_out, util_out, keys_out, out_space);
 }
 

@@ -53,6 +53,24 @@ static NcclApi *nccl_api() {
                         (api)->GetErrorString ? (api)->GetErrorString(r__) : "?");                          \
   } while (0)
 
+// ------------------------------------------------------------------------------- the verdict that rides with the keys
+// A sharded FP32_REFINE step does not stop for its verification (refine_verify_kernel leaves the verdict on the device):
+// word B of every rank's all-gather payload carries it (2 = ok, 1 = not ok), every rank reduces the W words to the same
+// all_ok after the gather, and zeroes them so that the merge sees key 0 ("nothing") there.
+__global__ void comm_flag_kernel(uint64_t *flag, const unsigned int *ok_dev) {
+  if (threadIdx.x == 0) *flag = ok_dev ? (uint64_t)(*ok_dev & 1u) + 1ull : 2ull;
+}
+__global__ void comm_flags_reduce_kernel(uint64_t *all, int W, int stride, int B, unsigned int *status) {
+  const int r = threadIdx.x;
+  bool ok = true;
+  if (r < W) {
+    ok = all[(size_t)r * stride + B] == 2ull;
+    all[(size_t)r * stride + B] = 0ull;
+  }
+  const bool all_ok = __all_sync(0xffffffffu, ok);
+  if (r == 0) status[1] = all_ok ? 1u : 0u;
+}
+
 // ---------------------------------------------------------------------------------------------------- peer push
 // The key exchange WITHOUT a collective call ("one-shot peer-mapped push"): every rank owns a small window
 // that its peers map through CUDA IPC at alink_comm_init; ONE single-CTA kernel per step stores this rank's B sorted keys

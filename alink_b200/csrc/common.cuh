@@ -118,6 +118,13 @@ struct alink_ctx {
   DevBuf cand, cia, cib, util_c, rstat;
   DevBuf util2, probs2, cia2, cib2, map2, src2;     // stage 2 / 3 of refine_query_v2
   unsigned int *rs_host = nullptr;          // pinned copy of the statistics words (read with the result)
+  // deferred verification (alink_query_sharded): the three-stage query is enqueued without its host synchronisation, its
+  // verdict is evaluated on the device (refine_verify_kernel) and travels with the keys; the report is filled afterwards
+  bool defer_req = false, deferred = false;
+  double defer_eps1 = 0.0, defer_eps2 = 0.0, defer_scv = 1.0;
+  unsigned int *defer_ok_dev = nullptr;     // device address of the verdict word of the deferred query
+  unsigned int *comm_status = nullptr;      // device: [1] = every rank's verdict ok (alink_query_sharded)
+  unsigned int *comm_host = nullptr;        // pinned mirror
   double refine_eps2 = 0.0, refine_eps2_used = 0.0;  // stage-2 (split operand) bound: caller's / used
   double refine_eps_apriori = 0.0;          // a-priori statistical MODEL of the stage-1 filter error (8 sigma) for the last query
   double refine_eps_worst = 0.0;            // the same propagated with worst-case norms (reported, too loose to filter with)

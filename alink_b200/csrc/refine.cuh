@@ -183,8 +183,32 @@ __global__ void __launch_bounds__(256) absmax_kernel(const float4 *__restrict__ 
 // rs[] words: 0 count1 | 1 M1 = n1 + |S| | 2 count2 | 3 M2 = n2 + |S2| | 4 flags (1: C1 overflow, 2: C2 overflow)
 //             5 max |u~ - u2| over C1 u S | 6 max |u2 - u| over C2 u S2 | 7 max |u~ - u| over C2 u S2 | 8-9 sum sq of |u~ - u2| over C1 (double)
 //             10-11 sum sq of 6 (double) | 12 n1 = min(count1, cap1) | 13 n2 = min(count2, cap2)
+//             14 tau1 bits | 15 max relative error | 16 ok: the verification's verdict, evaluated ON THE DEVICE (refine_verify_kernel)
 enum { RS_COUNT1 = 0, RS_M1 = 1, RS_COUNT2 = 2, RS_M2 = 3, RS_FLAGS = 4, RS_ERR1 = 5, RS_ERR2 = 6, RS_ERRA = 7, RS_SS1 = 8,
-       RS_SS2 = 10, RS_N1 = 12, RS_N2 = 13, RS_TAU = 14, RS_REL1 = 15, RS_WORDS = 16 };
+       RS_SS2 = 10, RS_N1 = 12, RS_N2 = 13, RS_TAU = 14, RS_REL1 = 15, RS_OK = 16, RS_WORDS = 32 };
+
+// The host's acceptance test of a three-stage query (refine_query_v2, after its synchronisation), restated on the device so
+// that a SHARDED step can ship the verdict with its keys instead of stopping for it: ok = no list overflowed, stage 2 within
+// eps2 of the exact values, stage 1 within eps1 of stage 2 (+ eps2) and of the exact values, 8 sigma of the candidates'
+// error inside eps1, the multiplicative band's premise intact. Double arithmetic, IEEE sqrt: the same verdict as the host's.
+struct VerifyConsts {
+  double eps1, eps2, scv, relmax;  // relmax = expm1(ez) for the banded measures, < 0: not banded
+};
+__global__ void refine_verify_kernel(unsigned int *__restrict__ rs, const VerifyConsts c) {
+  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  const double e1 = (double)__uint_as_float(rs[RS_ERR1]), e2 = (double)__uint_as_float(rs[RS_ERR2]);
+  const double ea = (double)__uint_as_float(rs[RS_ERRA]), rel1 = (double)__uint_as_float(rs[RS_REL1]);
+  const double ss1 = *reinterpret_cast<const double *>(rs + RS_SS1);
+  const unsigned int n1 = rs[RS_N1];
+  const double seen2 = e2 / c.scv;
+  const double s1a = e1 / c.scv + c.eps2, s1b = ea / c.scv;
+  const double seen1 = s1a > s1b ? s1a : s1b;
+  const double rms1 = n1 ? (double)(float)sqrt(ss1 / (double)n1) : 0.0;  // (the host rounds the rms to float first)
+  const double tail1 = 8.0 * rms1 / c.scv;
+  const bool badrel = c.relmax >= 0.0 && rel1 > c.relmax;
+  const bool bad = rs[RS_FLAGS] != 0u || seen2 > c.eps2 || seen1 > c.eps1 || tail1 > c.eps1 || badrel;
+  rs[RS_OK] = bad ? 0u : 1u;
+}
 
 // after refine_mark_kernel: clamp the count, append the stratified sample, translate rows to table rows
 __global__ void __launch_bounds__(256) refine_stage1_finish_kernel(unsigned int *__restrict__ rs, unsigned int cap1, int64_t N,

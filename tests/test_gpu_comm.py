@@ -32,6 +32,19 @@ def _worker(rank, world, uid, q, push):
         st = ctx.comm_push_state()  # (enabled, used): the one-launch peer push + merge of csrc/comm.cuh
         out["push_consistent"] = st == (bool(push), bool(push))
         print(f"rank {rank}: peer push enabled/used = {st}", flush=True)
+        rep = ctx.refine_report()  # filled after the step's single synchronisation (the verdict travelled with the keys)
+        out["report"] = bool(rep["version"] == 2 and rep["rounds"] == 1 and rep["n_sample"] >= 4096 and rep["n_exact"] >= 1000
+                             and 0 < rep["err1_max"] <= rep["eps1_used"])
+        # rank 0 verifies against a bound far too tight: its verdict is "not ok", EVERY rank must learn that from the gathered
+        # verdicts, rank 0 repeats its query with widened bounds, and the exchange is repeated — same selection, no deadlock
+        if rank == 0:
+            ctx.set_refine_eps(2e-5)
+        got = ctx.query_sharded(0, 0, 0, np.ascontiguousarray(pool.ia[lo:hi]), np.ascontiguousarray(pool.ib[lo:hi]), hi - lo,
+                                "uncertainty", 1000, base=lo)
+        rep = ctx.refine_report()
+        ctx.set_refine_eps(0.0)
+        out["one_rank_not_ok"] = bool(all(np.array_equal(a, b) for a, b in zip(whole, got))
+                                      and (rank != 0 or push or rep["rounds"] > 1 or rep["version"] == 1))
         # a shard smaller than B: 600 pairs on rank 1, the rest on rank 0
         cut = pool.N - 600
         lo2, hi2 = (0, cut) if rank == 0 else (cut, pool.N)
@@ -77,5 +90,5 @@ def test_two_ranks_merge_to_the_single_gpu_selection_without_torch_distributed(p
         p.join(timeout=60)
     for rank, out, err in res:
         assert err is None, f"rank {rank}: {err}"
-        assert out == {"uncertainty": True, "neg_margin": True, "push_consistent": True, "small_shard": True, "rule_blind0": True,
-                       "rule_blind1": True}, (rank, out)
+        assert out == {"uncertainty": True, "neg_margin": True, "push_consistent": True, "report": True, "one_rank_not_ok": True,
+                       "small_shard": True, "rule_blind0": True, "rule_blind1": True}, (rank, out)
