@@ -61,14 +61,13 @@ __global__ void comm_flag_kernel(uint64_t *flag, const unsigned int *ok_dev) {
   if (threadIdx.x == 0) *flag = ok_dev ? (uint64_t)(*ok_dev & 1u) + 1ull : 2ull;
 }
 __global__ void comm_flags_reduce_kernel(uint64_t *all, int W, int stride, int B, unsigned int *status) {
-  const int r = threadIdx.x;
   bool ok = true;
-  if (r < W) {
-    ok = all[(size_t)r * stride + B] == 2ull;
+  for (int r = threadIdx.x; r < W; r += 32) {  // (one warp)
+    ok = ok && all[(size_t)r * stride + B] == 2ull;
     all[(size_t)r * stride + B] = 0ull;
   }
   const bool all_ok = __all_sync(0xffffffffu, ok);
-  if (r == 0) status[1] = all_ok ? 1u : 0u;
+  if (threadIdx.x == 0) status[1] = all_ok ? 1u : 0u;
 }
 
 // ---------------------------------------------------------------------------------------------------- peer push
