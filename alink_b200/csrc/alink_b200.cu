@@ -19,6 +19,7 @@
 
 extern "C" {
 static void push_teardown(alink_ctx *ctx);  // peer windows of the push exchange (below, with alink_comm_init)
+static int noalloc_resolve(int device);     // device address of the static scratch of alink_topk_values_noalloc (set-up time)
 }
 
 #include <math.h>
@@ -46,6 +47,7 @@ int alink_create(alink_ctx **out, int device, unsigned flags) {
     return ALINK_E_CUDA;
   }
   ctx->own_stream = ctx->stream;
+  noalloc_resolve(device);  // once per device, with that device current; a failure is reported by the entry point that needs it
   cudaDeviceGetAttribute(&ctx->sm_count, cudaDevAttrMultiProcessorCount, device);
   for (int i = 0; i < 8; ++i) cudaEventCreate(&ctx->ev[i]);
   // watchdog record: written by a kernel whose mbarrier wait times out (a protocol deadlock), readable
@@ -620,16 +622,31 @@ static __device__ __align__(256) unsigned char g_noalloc_scratch[ALINK_NOALLOC_S
 static void *g_noalloc_addr[64];  // per device: the array's DEVICE address (its name is only a host-side handle here)
 static std::mutex g_noalloc_mu;
 
+// Called from alink_create — set-up time, once per device, with that device current — so that the entry point itself makes
+// no CUDA call that could allocate or initialise anything (it may run under stream capture).
+static int noalloc_resolve(int device) {
+  if (device < 0 || device >= 64) return ALINK_E_UNSUPPORTED;
+  std::lock_guard<std::mutex> lk(g_noalloc_mu);
+  if (g_noalloc_addr[device]) return ALINK_OK;
+  void *p = nullptr;
+  const cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+  if (e != cudaSuccess || !p) {
+    cudaGetLastError();
+    return ALINK_E_CUDA;
+  }
+  g_noalloc_addr[device] = p;
+  return ALINK_OK;
+}
+
 static int noalloc_scratch(alink_ctx *ctx, unsigned char **out) {
   if (ctx->device < 0 || ctx->device >= 64) return alink_fail(ctx, ALINK_E_UNSUPPORTED, "device ordinal %d >= 64", ctx->device);
-  std::lock_guard<std::mutex> lk(g_noalloc_mu);
-  if (!g_noalloc_addr[ctx->device]) {  // once per device, with that device current (the caller set it)
-    void *p = nullptr;
-    ALINK_CUDA(ctx, cudaGetSymbolAddress(&p, g_noalloc_scratch));
-    if (!p) return alink_fail(ctx, ALINK_E_CUDA, "cudaGetSymbolAddress returned a null address");
-    g_noalloc_addr[ctx->device] = p;
+  void *p;
+  {
+    std::lock_guard<std::mutex> lk(g_noalloc_mu);
+    p = g_noalloc_addr[ctx->device];
   }
-  *out = (unsigned char *)g_noalloc_addr[ctx->device];
+  if (!p) return alink_fail(ctx, ALINK_E_CUDA, "the static scratch's device address could not be resolved at alink_create (cudaGetSymbolAddress failed)");
+  *out = (unsigned char *)p;
   return ALINK_OK;
 }
 
