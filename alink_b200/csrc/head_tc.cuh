@@ -535,6 +535,16 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
     bool pend = false;
     uint32_t pl = 0, pi = 0, pvp = 0;  // the pending learner, its tile, its running index mod 4
     float vmn = 0.0f;                  // min over the learners so far of |p1 - p0|
+    // vote entropy takes K + 1 values: lane v of every epilogue warp holds H(v votes of K) — the very expression of
+    // alink_utility2, so the bits are the same — and the row's value is one shuffle instead of two logs in the tail
+    const bool vote_lut = a.measure == ALINK_UTIL_VOTE_ENTROPY && a.K < 32;
+    const int lane_e = threadIdx.x & 31;
+    float vlut = 0.0f;
+    if (vote_lut && lane_e <= a.K) {
+      const float fk = (float)a.K;
+      vlut = alink_entropy2(ALINK_DIV((float)(a.K - lane_e), fk), ALINK_DIV((float)lane_e, fk));
+    }
+    int nvote = 0;
     for (uint32_t q = 0; q <= Q; ++q) {
       ALINK_DBG_ROLE(8u, 4 + (warp & 3), q);
       const uint32_t b = q & 1u, u = q >> 1;
@@ -711,7 +721,16 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_kernel(const Args a) {
         rows[2 * pl + 1] = p1;
         const float dv = fabsf(__fsub_rn(p1, p0));
         vmn = pl == 0 ? dv : fminf(vmn, dv);
-        if (pl == (uint32_t)a.K - 1 && a.util && n < a.N) {
+        nvote = (pl == 0 ? 0 : nvote) + (p1 > p0 ? 1 : 0);
+        if (vote_lut) {
+          if (pl == (uint32_t)a.K - 1) {  // (uniform across the warp: every lane shuffles)
+            const float ve = __shfl_sync(0xffffffffu, vlut, nvote);
+            if (a.util && n < a.N) {
+              a.util[n] = ve;
+              if (a.vmin) a.vmin[n] = vmn;
+            }
+          }
+        } else if (pl == (uint32_t)a.K - 1 && a.util && n < a.N) {
           float c0, c1u;
           alink_consensus2(rows, a.K, &c0, &c1u);
           a.util[n] = alink_utility2(a.measure, rows, a.K, c0, c1u);
