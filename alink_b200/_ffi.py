@@ -41,7 +41,7 @@ SYMBOLS = (
     "alink_disparity_hist", "alink_disparity_select_sharded", "alink_roc_counts",
     "alink_train_step", "alink_train_epoch", "alink_get_train_state", "alink_set_train_state",
     "alink_set_refine_eps2", "alink_refine_report_get",
-    "alink_perturb_rows", "alink_score_column", "alink_min_disparity",
+    "alink_perturb_rows", "alink_get_table_rows", "alink_score_column", "alink_min_disparity",
     "alink_comm_unique_id", "alink_comm_init", "alink_comm_destroy", "alink_query_sharded", "alink_comm_push_state", "alink_disparity_select_comm",
     "alink_de_init", "alink_de_mutate", "alink_de_repair", "alink_de_evaluate", "alink_de_select", "alink_de_get",
 )
@@ -177,6 +177,8 @@ def load():
     L.alink_disparity_select_comm.restype = i32
     L.alink_disparity_select_comm.argtypes = [vp, vp, vp, i64, i32, i64, i64, dbl, dbl, i32, vp, i32, vp, i32,
                                               C.POINTER(i64), C.POINTER(i64)]
+    L.alink_get_table_rows.restype = i32
+    L.alink_get_table_rows.argtypes = [vp, i32, i64, i64, vp, i32]
     L.alink_perturb_rows.restype = i32
     L.alink_perturb_rows.argtypes = [vp, i32, vp, i64, i32, i32, i32, u64, i64, i32, dbl, i32, i32]
     L.alink_score_column.restype = i32
@@ -609,6 +611,14 @@ class Context:
         p, sp = _ptr_space(idx)
         self._check(self._L.alink_perturb_rows(self._h, slot_src, p, int(N), sp, int(side), int(t), int(seed), int(pair_base),
                                                int(ncoord), float(vmax), int(bool(normalize)), slot_dst))
+
+    def get_table(self, slot, nrows, D, row0=0, out=None):
+        """fp32 rows [row0, row0 + nrows) of a table slot -> host array (or a torch cuda tensor `out`)."""
+        if out is None:
+            out = np.empty((int(nrows), int(D)), np.float32)
+        p, sp = _ptr_space(out)
+        self._check(self._L.alink_get_table_rows(self._h, int(slot), int(row0), int(nrows), p, sp))
+        return out
 
     def score_column(self, learner, col, out=None, N=None):
         """Column of the last scores (learner -1 = Bagging mean) into a torch cuda float32 tensor `out`, or a new host array."""

@@ -3,7 +3,7 @@
 `predict` = mean over the K learners of `model.predict(X)`, computed by ONE call into the CUDA path
 (all K heads loop over a resident feature tile; the mean is the fused K-learner reduction) when every
 model is an alink_b200 SiameseNetwork. Foreign models fall back to nothing: they raise.
-`attackModel` / `resize` (image-space augmentation, :22-37) are out of scope.
+`attackModel` (:28-37) drives alink_b200.noise objects over embedding pairs; `resize` (:22-26) is image-space and absent.
 """
 from __future__ import annotations
 
@@ -32,5 +32,14 @@ class Bagging:
         per, _ = engine.score(self._alink_specs(), predict_on, want_per=True, want_cons=False)
         return per
 
-    def attackModel(self, *a, **k):
-        raise NotImplementedError("image-space noise/attack is upstream of the pool (SURVEY.md §2 rows 10-11)")
+    def attackModel(self, pairs, target_size=None, target_labels=None):
+        """code/committee.py:28-37: one noisy copy of the pairs per attack object -> [lefts, rights] (lists indexed by
+        attack, the layout code/ALINK.py:170,219-224 reads). The attacks are alink_b200.noise objects over EMBEDDING
+        pairs; the reference's `resize` to the feature model's input size is an image operation and has no counterpart
+        (`target_size` is accepted and ignored)."""
+        perturbed_l, perturbed_r = [], []
+        for attack in self.attacks:
+            left, right = attack.addPairNoise(pairs, target_labels)
+            perturbed_l.append(left)
+            perturbed_r.append(right)
+        return [perturbed_l, perturbed_r]

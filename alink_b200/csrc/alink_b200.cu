@@ -2008,6 +2008,23 @@ int alink_perturb_rows(alink_ctx *ctx, int slot_src, const int32_t *idx, int64_t
   return ALINK_OK;
 }
 
+// rows [row0, row0 + nrows) of an fp32 table slot -> caller's buffer (the perturbed rows of alink_perturb_rows for a host
+// driver that wants them, code/ALINK.py:219-224; everything else keeps tables on the device)
+int alink_get_table_rows(alink_ctx *ctx, int slot, int64_t row0, int64_t nrows, float *out, int out_space) {
+  if (!ctx) return ALINK_E_INVALID;
+  if (slot < 0 || slot >= ALINK_MAX_SLOTS) return alink_fail(ctx, ALINK_E_INVALID, "bad slot");
+  ALINK_CUDA(ctx, cudaSetDevice(ctx->device));
+  ALINK_TRY(table_wait(ctx, slot));
+  const Table &T = ctx->tables[slot];
+  if (!T.p || T.dtype != ALINK_F32) return alink_fail(ctx, ALINK_E_STATE, "slot %d holds no fp32 table", slot);
+  if (row0 < 0 || nrows < 0 || row0 + nrows > T.M || !out) return alink_fail(ctx, ALINK_E_INVALID, "rows outside the table");
+  if (nrows == 0) return ALINK_OK;
+  ALINK_CUDA(ctx, cudaMemcpyAsync(out, (const float *)T.p + (size_t)row0 * T.D, sizeof(float) * (size_t)nrows * T.D,
+                                  out_space == ALINK_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, ctx->stream));
+  if (out_space == ALINK_HOST) ALINK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return ALINK_OK;
+}
+
 int alink_score_column(alink_ctx *ctx, int learner, int col, float *out, int out_space) {
   if (!ctx) return ALINK_E_INVALID;
   if (!ctx->probs.p || !ctx->probs_full) return alink_fail(ctx, ALINK_E_STATE, "no scores: call alink_score_* first");

@@ -326,6 +326,7 @@ int alink_comm_push_state(const alink_ctx *ctx, int *enabled, int *used_last);
  *   alink_min_disparity  util[j] = min_t |p2[t][j] - p1[j]| (kept in the context: alink_select_topk then ranks it). */
 int alink_perturb_rows(alink_ctx *ctx, int slot_src, const int32_t *idx, int64_t N, int in_space, int side, int t, uint64_t seed,
                        int64_t pair_base, int ncoord, double vmax, int normalize, int slot_dst);
+int alink_get_table_rows(alink_ctx *ctx, int slot, int64_t row0, int64_t nrows, float *out, int out_space);  /* fp32 rows of a slot (e.g. the perturbed rows, for a host driver: code/ALINK.py:219-224) */
 int alink_score_column(alink_ctx *ctx, int learner, int col, float *out, int out_space);
 int alink_min_disparity(alink_ctx *ctx, const float *p2, const float *p1, int64_t N, int T, int in_space, float *util, int out_space);
 

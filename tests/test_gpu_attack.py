@@ -73,3 +73,30 @@ def test_attack_all_device_stream_reaches_the_target_class():
     assert not de.active.any() and de.nit <= 20
     rows2 = att.attack_all(X, onehot, coord_count=40, maxiter=20, popsize=250, seed=5, rng="device")
     np.testing.assert_array_equal(rows, rows2)  # the device stream is a pure function of (seed, problem, generation, member, gene)
+
+
+def test_noise_objects_through_bagging_attack_model_like_alink_py():
+    """code/ALINK.py:93,97,160,170: `ensembleNoise = [cls(model=M2, sess, feature_model)]`, `bag = Bagging(ensemble,
+    ensembleNoise)`, `noisy = bag.attackModel(batch_x, IMAGERES, m1_labels)`, then M2 scores [noisy[0][jj], noisy[1][jj]].
+    The device-backed noise types: 'coordinate' rows equal the numpy restatement of the counter-based stream bit for bit;
+    'adversarial' moves every pair to the class its label names."""
+    from alink_b200 import committee, noise
+    from oracle import ref_numpy as R
+    pool, targets = mk.problem_inputs()
+    net = _net(pool)
+    n = 24
+    X = [np.ascontiguousarray(pool.table[pool.ia[:n]]), np.ascontiguousarray(pool.table[pool.ib[:n]])]
+    onehot = np.eye(2, dtype=np.float32)[targets[:n]]
+    attacks = [noise.get_relevant_noise("coordinate")(model=net, sess=None, feature_model=None),
+               noise.AdversarialNoise(net, None, None, coord_count=40, maxiter=20, popsize=250, seed=5)]
+    attacks[0].seed, attacks[0].t = 46, 3
+    bag = committee.Bagging([net], attacks)
+    noisy = bag.attackModel(X, 224, onehot)
+    assert len(noisy[0]) == 2 and len(noisy[1]) == 2
+    for side in (0, 1):
+        want = R.perturb_rows(X[side], np.arange(n), side, 3, 46)
+        np.testing.assert_array_equal(noisy[side][0].view(np.uint32), want.view(np.uint32))
+    np.testing.assert_array_equal(noisy[1][1], X[1])  # the embedding attacker perturbs the left side only
+    assert np.all((noisy[0][1] != X[0]).sum(axis=1) <= 40)
+    pred = np.argmax(net.predict([noisy[0][1], noisy[1][1]]), axis=1)
+    np.testing.assert_array_equal(pred, targets[:n])
