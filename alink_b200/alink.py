@@ -59,3 +59,70 @@ def a2link_pool_select(ctx, group_m1, group_m2, slot, ia, ib, N, K1, C=2, T=16, 
     ctx.min_disparity(p2, p1)
     top_idx, top_util, _ = ctx.select_topk(min(B, N))
     return idx, active, top_idx, top_util, (p1, p2)
+
+
+class ALinkState:
+    """What the reference's loop carries from one iteration to the next (code/ALINK.py:135-141): the pairs selected so far
+    for the disguised-faces model, the oracle-query count and the pool size seen."""
+
+    def __init__(self):
+        self.train_left, self.train_right, self.train_y = [], [], []
+        self.ACTIVE_COUNT = 0
+        self.UN_SIZE = 0
+        self.finetunes = 0
+
+    def pending(self):
+        return int(sum(len(y) for y in self.train_y))
+
+
+def roundoff(v):
+    """code/helpers.py:39-46: (n, 1) hard labels of scores at 0.5."""
+    return (np.asarray(v, dtype=np.float32) >= 0.5).astype(np.int64).reshape(-1, 1)
+
+
+def alink_iteration(bag, disguised_model, batch_features, batch_y, state, target_size=None, col=1, disparity_ratio=0.25,
+                    eps=0.05, blind_strategy=False, batch_send=64, ft_epochs=3, old_data=None, verbose=0):
+    """The body of the A-LINK loop, code/ALINK.py:155-250, on a batch of EMBEDDING pairs (the reference's
+    `conversionModel.process` calls of :158,167 are upstream of this package): committee prediction (:160), one noisy
+    copy per noise object (`bag.attackModel`, :163-164), the disguised-faces model on each (:170), the disparity rule
+    with the grey zone and the pseudo-oracle (:171-201), the per-noise partition of the selected pairs (:216-225), and —
+    once `batch_send` pairs are waiting — the finetune on them plus the clean selected pairs and `old_data` (:227-250).
+    `batch_y`: (N,) or (N, k) pseudo-oracle labels (column 0 is read, :195). Returns (queryIndices, ensemblePredictions)."""
+    XL, XR = engine._as_pair(batch_features)
+    y = np.asarray(batch_y, dtype=np.float32)
+    y = y[:, 0] if y.ndim == 2 else y
+    state.UN_SIZE += len(XL)
+    ens = bag.predict([XL, XR])
+    m1_labels = np.eye(2, dtype=np.float32)[np.argmax(ens, axis=1)]
+    noisy = bag.attackModel([XL, XR], target_size, m1_labels)
+    T = len(bag.attacks)
+    cidx = col if ens.shape[1] > 1 else 0
+    p2 = []
+    for jj in range(T):
+        dp = disguised_model.predict([noisy[0][jj], noisy[1][jj]])
+        p2.append(dp[:, col if dp.shape[1] > 1 else 0])
+    idx, active = disparity_select(np.stack(p2), np.ascontiguousarray(ens[:, cidx]), disparity_ratio, eps, blind_strategy, y)
+    state.ACTIVE_COUNT += int(active)
+    if len(idx) == 0:
+        return idx, ens
+    intermediate = ens[idx, cidx]
+    mp = int(len(intermediate) / float(T))
+    hard = roundoff(intermediate)
+    for i in range(T):
+        part = idx[i * mp:(i + 1) * mp]
+        state.train_left.append(np.asarray(noisy[0][i])[part])
+        state.train_right.append(np.asarray(noisy[1][i])[part])
+        state.train_y.append(hard[i * mp:(i + 1) * mp])
+    if state.pending() >= batch_send:
+        left = state.train_left + [XL[idx]]
+        right = state.train_right + [XR[idx]]
+        labels = state.train_y + [hard]
+        if old_data is not None:  # unperturbed pairs against overfitting on noise (:229-234)
+            (ol, orr), oy = old_data
+            left.append(np.asarray(ol, np.float32))
+            right.append(np.asarray(orr, np.float32))
+            labels.append(np.asarray(oy).reshape(-1, 1))
+        disguised_model.finetune([np.concatenate(left), np.concatenate(right)], np.concatenate(labels), ft_epochs, 16, verbose)
+        state.train_left, state.train_right, state.train_y = [], [], []
+        state.finetunes += 1
+    return idx, ens
